@@ -1,0 +1,912 @@
+// bwk_api.cu -- the C ABI of include/bwk_b200.h on top of the sm_100a kernels.
+//
+// Mirrors the reference driver's data life cycle (atmosphere/biharmonic_wk_kernel.F90):
+//   allocate_data + enter data pcreate  F90:37-44,553  -> bwk_init
+//   update device                        F90:573        -> bwk_upload
+//   bws_gpu2(...)                        F90:574        -> bwk_run
+//   update host                          F90:575        -> bwk_download
+// There is no CPU fallback: every compute entry point needs a CUDA device.
+#include "../../include/bwk_b200.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "bwk_internal.h"
+#include "bwk_kernels.h"
+
+using namespace bwk;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CK(call)                                                                                            \
+    do {                                                                                                    \
+        cudaError_t e_ = (call);                                                                            \
+        if (e_ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// ---- NCCL through dlopen: single-GPU users need no NCCL at all
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool load()
+    {
+        if (lib) return true;
+        lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) return false;
+#define SYM(name) *(void **)(&name) = dlsym(lib, "nccl" #name)
+        SYM(GetUniqueId);
+        SYM(CommInitRank);
+        SYM(CommDestroy);
+        SYM(Send);
+        SYM(Recv);
+        SYM(GroupStart);
+        SYM(GroupEnd);
+        SYM(GetErrorString);
+#undef SYM
+        return GetUniqueId && CommInitRank && CommDestroy && Send && Recv && GroupStart && GroupEnd && GetErrorString;
+    }
+} g_nccl;
+
+#define NK(call)                                                                                              \
+    do {                                                                                                      \
+        ncclResult_t r_ = (call);                                                                             \
+        if (r_ != ncclSuccess) return fail("%s failed: %s (%s:%d)", #call, g_nccl.GetErrorString(r_), __FILE__, __LINE__); \
+    } while (0)
+
+constexpr int NPARTIAL_BLOCKS = 148 * 8;
+constexpr int NEVENTS = 64;
+
+struct Ctx {
+    bool inited = false;
+    int nelem = 0, nlev = 0, qsize = 0, kq = 0;
+    size_t q_doubles = 0;
+    cudaStream_t s_main = nullptr, s_comm = nullptr, s_h2d = nullptr, s_d2h = nullptr;
+    double *d_q = nullptr, *d_tmp = nullptr, *d_we = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
+    double *d_save = nullptr, *d_table = nullptr, *d_partials = nullptr, *d_halo = nullptr, *d_send = nullptr, *d_dummy = nullptr;
+    double *h_partials = nullptr;
+    ElemDss *d_dss = nullptr;
+    int32_t *d_boundary = nullptr, *d_interior = nullptr, *d_dependent = nullptr, *d_independent = nullptr;
+    int32_t *d_send_elem = nullptr, *d_send_row = nullptr;
+    std::vector<int64_t> send_offset; // per peer, rows
+    bool have_metric = false, have_topology = false, have_rsph = false, have_maps2 = false;
+    SweepParams sp{};
+    Plan plan;
+    std::vector<double> h_spheremp; // spheremp of the local elements (16 each), for rspheremp
+    int64_t gen_nelem_global = -1;  // >=0 when the data came from bwk_initialize_data_device (LCG closed form)
+    int gen_seed_mode = 0;
+    int variant = 0;
+    int64_t launches = 0;
+    // comm
+    ncclComm_t comm = nullptr;
+    int rank = 0, nranks = 1;
+    cudaEvent_t ev_b = nullptr, ev_halo = nullptr, ev_misc = nullptr;
+    cudaEvent_t events[NEVENTS] = {};
+    std::vector<cudaEvent_t> chunk_up, chunk_done;
+};
+Ctx g;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+
+int get_encode()
+{
+    if (g_encode) return 0;
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (qres != cudaDriverEntryPointSuccess || !fn) return fail("cuTensorMapEncodeTiled is not available from this driver");
+    g_encode = (EncodeTiledFn)fn;
+    return 0;
+}
+
+int make_map(CUtensorMap *m, void *base, int rank, const uint64_t *dims, const uint64_t *strides_bytes /*rank-1*/, const uint32_t *box,
+             CUtensorMapSwizzle swz)
+{
+    if (get_encode()) return 1;
+    cuuint64_t gd[5], gs[4];
+    cuuint32_t bx[5], es[5];
+    for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+    for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
+    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, (cuuint32_t)rank, base, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with CUresult %d (rank %d, dims %llu %llu %llu)", (int)r, rank,
+                                       (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)(rank > 2 ? dims[2] : 0));
+    return 0;
+}
+
+// {16, KQ, nelem} slabs, box {16,32,1}, SWIZZLE_128B
+int make_slab_map(CUtensorMap *m, double *base, int kq, int64_t nelem)
+{
+    const uint64_t dims[3] = {16, (uint64_t)kq, (uint64_t)std::max<int64_t>(nelem, 1)};
+    const uint64_t str[2] = {128, (uint64_t)kq * 128};
+    const uint32_t box[3] = {16, TILE_SLABS, 1};
+    return make_map(m, base, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int need_init()
+{
+    if (!g.inited) return fail("bwk_init has not been called");
+    return 0;
+}
+
+int check_range(int nets, int nete)
+{
+    if (nets < 1 || nete > g.nelem || nets > nete + 1) return fail("element range nets=%d nete=%d outside 1..%d", nets, nete, g.nelem);
+    return 0;
+}
+
+// launch one sweep over local elements [first, first+count) or over a device list
+int sweep(int mode, int first, int count, const int32_t *list, cudaStream_t st)
+{
+    if (count <= 0) return 0;
+    SweepParams p = g.sp;
+    const SweepGeometry geo = choose_geometry(g.kq, count, mode);
+    p.tiles_per_unit = geo.tiles_per_unit;
+    p.units = geo.units;
+    p.elem_list = list;
+    p.elem_first = first;
+    p.elem_count = count;
+    CK(launch_sweep(mode, p, st));
+    g.launches++;
+    return 0;
+}
+
+int laplace_range(int first0, int count, cudaStream_t st)
+{
+    if (!g.have_metric) return fail("no element metric on the device: call bwk_upload(elem, ..., deriv) first");
+    if (g.variant == 1) {
+        CK(launch_laplace_plain(g.d_q, g.d_metric, first0, count, g.kq, st));
+        g.launches += (count + 65534) / 65535;
+        return 0;
+    }
+    return sweep(MODE_LAPLACE, first0, count, nullptr, st);
+}
+
+int upload_metric(const bwk_element_t *elem, const bwk_derivative_t *deriv, cudaStream_t st)
+{
+    if (elem) {
+        CK(cudaMemcpyAsync(g.d_elem, elem, sizeof(double) * ELEM_DOUBLES * g.nelem, cudaMemcpyHostToDevice, st));
+        CK(launch_fold_metric(g.d_elem, g.d_metric, g.nelem, st));
+        g.launches++;
+        g.have_metric = true;
+        g.gen_nelem_global = -1;
+        g.h_spheremp.resize((size_t)16 * g.nelem);
+        const double *e = reinterpret_cast<const double *>(elem);
+        for (int64_t ie = 0; ie < g.nelem; ++ie) std::memcpy(&g.h_spheremp[(size_t)16 * ie], e + ie * ELEM_DOUBLES + 64, 16 * sizeof(double));
+        g.have_rsph = false;
+    }
+    if (deriv) CK(set_dvv(&deriv->Dvv[0][0], st));
+    return 0;
+}
+
+void free_dev(void *p)
+{
+    if (p) cudaFree(p);
+}
+
+std::vector<double> lcg_table()
+{
+    std::vector<double> t(131072);
+    int old = 11; // F90:83-89
+    for (int i = 0; i < 131072; ++i) {
+        old = (1301 * old + 97) % (1024 * 128);
+        t[(size_t)i] = old / (double)(1024 * 128);
+    }
+    return t;
+}
+
+// rspheremp = 1 / DSS(spheremp); needs spheremp of remote sharers when nranks > 1
+int compute_rspheremp()
+{
+    if (g.have_rsph) return 0;
+    if (!g.have_topology) return fail("no topology set");
+    if ((int64_t)g.h_spheremp.size() != (int64_t)16 * g.nelem) return fail("no element metric uploaded/generated before the topology was used");
+    const Plan &pl = g.plan;
+    std::vector<double> table;
+    if (g.gen_nelem_global >= 0 && g.gen_seed_mode == 0) table = lcg_table();
+    auto remote_sp = [&](int64_t gp, double *out) -> bool {
+        if (g.gen_nelem_global < 0) return false;
+        const int64_t d = 16 + (int64_t)ELEM_DOUBLES * (gp / 16) + 64 + (gp % 16);
+        if (g.gen_seed_mode == 0) { *out = table[(size_t)(d & 131071)]; return true; }
+        uint64_t x = (uint64_t)d + 0x9E3779B97F4A7C15ull;
+        x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+        x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+        x ^= x >> 31;
+        *out = (double)(x >> 11) * 0x1.0p-53;
+        return true;
+    };
+    std::vector<double> rs((size_t)16 * g.nelem);
+    for (int64_t lp = 0; lp < (int64_t)16 * g.nelem; ++lp) {
+        double s = 0.0;
+        bool first = true;
+        for (int64_t t = pl.pt_start[(size_t)lp]; t < pl.pt_start[(size_t)lp + 1]; ++t) {
+            const int64_t gp = pl.pt_member[(size_t)t];
+            const int64_t le = gp / 16 - pl.first;
+            double v;
+            if (le >= 0 && le < g.nelem) v = g.h_spheremp[(size_t)(16 * le + gp % 16)];
+            else if (!remote_sp(gp, &v))
+                return fail("rspheremp needs spheremp of elements owned by other ranks: call bwk_set_rspheremp (or generate the data with "
+                            "bwk_initialize_data_device)");
+            s = first ? v : s + v;
+            first = false;
+        }
+        rs[(size_t)lp] = 1.0 / s;
+    }
+    CK(cudaMemcpyAsync(g.d_rsph, rs.data(), sizeof(double) * rs.size(), cudaMemcpyHostToDevice, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    g.have_rsph = true;
+    return 0;
+}
+
+int upload_list(const std::vector<int32_t> &v, int32_t **d)
+{
+    free_dev(*d);
+    *d = nullptr;
+    if (v.empty()) return 0;
+    CK(cudaMalloc(d, sizeof(int32_t) * v.size()));
+    CK(cudaMemcpy(*d, v.data(), sizeof(int32_t) * v.size(), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int install_plan(Plan &&pl)
+{
+    if (!pl.error.empty()) return fail("unsupported mesh: %s", pl.error.c_str());
+    if (pl.count != g.nelem) return fail("topology gives %lld local elements but bwk_init was called with %d", (long long)pl.count, g.nelem);
+    g.plan = std::move(pl);
+    const Plan &P = g.plan;
+    const int64_t kq = g.kq;
+    if (!g.d_tmp) CK(cudaMalloc(&g.d_tmp, sizeof(double) * g.q_doubles));
+    if (!g.d_we) CK(cudaMalloc(&g.d_we, sizeof(double) * g.q_doubles / 2));
+    if (!g.d_rsph) CK(cudaMalloc(&g.d_rsph, sizeof(double) * 16 * g.nelem));
+    free_dev(g.d_dss);
+    CK(cudaMalloc(&g.d_dss, sizeof(ElemDss) * (size_t)g.nelem));
+    CK(cudaMemcpy(g.d_dss, P.dss.data(), sizeof(ElemDss) * (size_t)g.nelem, cudaMemcpyHostToDevice));
+    if (upload_list(P.boundary_list, &g.d_boundary) || upload_list(P.interior_list, &g.d_interior) || upload_list(P.dependent_list, &g.d_dependent) ||
+        upload_list(P.independent_list, &g.d_independent))
+        return 1;
+    // halo (receive) buffer and send buffer, rows of [KQ][4] doubles
+    const int64_t nrecv = P.recv_offset.back();
+    free_dev(g.d_halo);
+    g.d_halo = nullptr;
+    if (nrecv > 0) CK(cudaMalloc(&g.d_halo, sizeof(double) * 4 * kq * nrecv));
+    std::vector<int32_t> se, sr;
+    g.send_offset.assign((size_t)P.nranks + 1, 0);
+    for (int p = 0; p < P.nranks; ++p) {
+        for (const RowRef &r : P.send[(size_t)p]) { se.push_back((int32_t)(r.elem - P.first)); sr.push_back(r.row); }
+        g.send_offset[(size_t)p + 1] = (int64_t)se.size();
+    }
+    free_dev(g.d_send);
+    g.d_send = nullptr;
+    if (!se.empty()) CK(cudaMalloc(&g.d_send, sizeof(double) * 4 * kq * se.size()));
+    if (upload_list(se, &g.d_send_elem) || upload_list(sr, &g.d_send_row)) return 1;
+
+    // tensor maps of the second sweep
+    if (make_slab_map(&g.sp.map_tmp, g.d_tmp, g.kq, g.nelem)) return 1;
+    {
+        const uint64_t dims[3] = {8, (uint64_t)kq, (uint64_t)g.nelem};
+        const uint64_t str[2] = {64, (uint64_t)kq * 64};
+        const uint32_t box[3] = {8, TILE_SLABS, 1};
+        if (make_map(&g.sp.map_we, g.d_we, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B)) return 1;
+    }
+    {
+        const uint64_t dims[4] = {4, 4, (uint64_t)kq, (uint64_t)g.nelem};
+        const uint64_t str[3] = {32, 128, (uint64_t)kq * 128};
+        const uint32_t box[4] = {4, 1, TILE_SLABS, 1};
+        if (make_map(&g.sp.map_tmp_rows, g.d_tmp, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+    }
+    {
+        const uint64_t dims[4] = {4, 2, (uint64_t)kq, (uint64_t)g.nelem};
+        const uint64_t str[3] = {32, 64, (uint64_t)kq * 64};
+        const uint32_t box[4] = {4, 1, TILE_SLABS, 1};
+        if (make_map(&g.sp.map_we_rows, g.d_we, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+    }
+    {
+        double *base = g.d_halo;
+        uint64_t rows = (uint64_t)nrecv;
+        if (!base) {
+            if (!g.d_dummy) CK(cudaMalloc(&g.d_dummy, sizeof(double) * 4 * kq));
+            base = g.d_dummy;
+            rows = 1;
+        }
+        const uint64_t dims[4] = {4, 1, (uint64_t)kq, rows};
+        const uint64_t str[3] = {32, 32, (uint64_t)kq * 32};
+        const uint32_t box[4] = {4, 1, TILE_SLABS, 1};
+        if (make_map(&g.sp.map_halo_rows, base, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+    }
+    g.sp.dss = g.d_dss;
+    g.sp.rsph = g.d_rsph;
+    g.have_topology = true;
+    g.have_rsph = false;
+    return 0;
+}
+
+// halo exchange of the rows listed in the plan (HOMME bndry_exchangeV): pack on s_comm, then
+// grouped ncclSend/ncclRecv with every peer.  Caller orders s_comm after the producers.
+int exchange_halo()
+{
+    const Plan &P = g.plan;
+    const int64_t nsend = g.send_offset.empty() ? 0 : g.send_offset.back();
+    if (P.nranks == 1) return 0;
+    if (!g.comm) return fail("topology spans %d ranks but bwk_comm_init was not called", P.nranks);
+    if (nsend > 0) {
+        CK(launch_edge_pack(g.d_tmp, g.d_we, g.d_send_elem, g.d_send_row, nsend, g.kq, g.d_send, g.s_comm));
+        g.launches += (nsend + 65534) / 65535;
+    }
+    const size_t row_doubles = (size_t)4 * g.kq;
+    NK(g_nccl.GroupStart());
+    for (int p = 0; p < P.nranks; ++p) {
+        if (p == P.rank) continue;
+        const int64_t ns = g.send_offset[(size_t)p + 1] - g.send_offset[(size_t)p];
+        const int64_t nr = P.recv_offset[(size_t)p + 1] - P.recv_offset[(size_t)p];
+        if (ns > 0) NK(g_nccl.Send(g.d_send + g.send_offset[(size_t)p] * row_doubles, (size_t)ns * row_doubles, ncclDouble, p, g.comm, g.s_comm));
+        if (nr > 0) NK(g_nccl.Recv(g.d_halo + P.recv_offset[(size_t)p] * row_doubles, (size_t)nr * row_doubles, ncclDouble, p, g.comm, g.s_comm));
+    }
+    NK(g_nccl.GroupEnd());
+    return 0;
+}
+
+int biharmonic_device()
+{
+    if (!g.have_metric) return fail("no element metric on the device");
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (compute_rspheremp()) return 1;
+    const Plan &P = g.plan;
+    if (P.nranks == 1) {
+        if (sweep(MODE_SWEEP1, 0, g.nelem, nullptr, g.s_main)) return 1;
+        return sweep(MODE_SWEEP2, 0, g.nelem, nullptr, g.s_main);
+    }
+    // boundary elements first so that their edge rows can travel while the interior is computed
+    if (sweep(MODE_SWEEP1, 0, (int)P.boundary_list.size(), g.d_boundary, g.s_main)) return 1;
+    CK(cudaEventRecord(g.ev_b, g.s_main));
+    CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
+    if (exchange_halo()) return 1;
+    CK(cudaEventRecord(g.ev_halo, g.s_comm));
+    if (sweep(MODE_SWEEP1, 0, (int)P.interior_list.size(), g.d_interior, g.s_main)) return 1;
+    if (sweep(MODE_SWEEP2, 0, (int)P.independent_list.size(), g.d_independent, g.s_main)) return 1;
+    CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
+    return sweep(MODE_SWEEP2, 0, (int)P.dependent_list.size(), g.d_dependent, g.s_main);
+}
+
+// chunk boundaries (in elements) for the host<->device pipelines
+std::vector<int> make_chunks(int first0, int count)
+{
+    const double bytes_per_elem = 128.0 * g.kq;
+    const double total = bytes_per_elem * count;
+    double chunk_bytes = std::min(128.0 * 1048576.0, std::max(1048576.0, total / 8.0));
+    int per = (int)std::max(1.0, std::floor(chunk_bytes / bytes_per_elem));
+    std::vector<int> b;
+    for (int e = first0; e < first0 + count; e += per) b.push_back(e);
+    b.push_back(first0 + count);
+    return b;
+}
+
+int ensure_chunk_events(size_t n)
+{
+    while (g.chunk_up.size() < n) {
+        cudaEvent_t a, b;
+        CK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        g.chunk_up.push_back(a);
+        g.chunk_done.push_back(b);
+    }
+    return 0;
+}
+
+} // namespace
+
+// =========================================================================================
+extern "C" {
+
+const char *bwk_last_error(void) { return g_err.c_str(); }
+
+int bwk_init(int nelemd, int nlev, int qsize)
+{
+    if (g.inited) return fail("bwk_init called twice without bwk_finalize");
+    if (nelemd < 1 || nlev < 1 || qsize < 1) return fail("bad sizes nelemd=%d nlev=%d qsize=%d", nelemd, nlev, qsize);
+    if ((int64_t)nlev * qsize > 0x7fffffff / 64) return fail("nlev*qsize too large");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev < 1) return fail("no CUDA device available (%s); libbwk_b200 has no CPU fallback", cudaGetErrorString(e));
+    cudaDeviceProp prop;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10) return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", dev, prop.major, prop.minor);
+    g = Ctx();
+    g.nelem = nelemd;
+    g.nlev = nlev;
+    g.qsize = qsize;
+    g.kq = nlev * qsize;
+    g.q_doubles = (size_t)16 * g.kq * nelemd;
+    CK(cudaStreamCreateWithFlags(&g.s_main, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&g.s_comm, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&g.ev_b, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&g.ev_halo, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&g.ev_misc, cudaEventDisableTiming));
+    for (int i = 0; i < NEVENTS; ++i) CK(cudaEventCreate(&g.events[i]));
+    CK(cudaMalloc(&g.d_q, sizeof(double) * g.q_doubles));
+    CK(cudaMalloc(&g.d_elem, sizeof(double) * ELEM_DOUBLES * nelemd));
+    CK(cudaMalloc(&g.d_metric, sizeof(double) * METRIC_DOUBLES * nelemd));
+    CK(cudaMalloc(&g.d_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS));
+    CK(cudaMallocHost(&g.h_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS));
+    if (make_slab_map(&g.sp.map_q, g.d_q, g.kq, nelemd)) return 1;
+    // until a topology is installed the other maps alias map_q (never dereferenced by MODE_LAPLACE)
+    g.sp.map_tmp = g.sp.map_we = g.sp.map_tmp_rows = g.sp.map_we_rows = g.sp.map_halo_rows = g.sp.map_q;
+    g.sp.metric = g.d_metric;
+    g.sp.kq = g.kq;
+    g.inited = true;
+    return 0;
+}
+
+int bwk_finalize(void)
+{
+    if (!g.inited) return 0;
+    cudaDeviceSynchronize();
+    if (g.comm && g_nccl.CommDestroy) g_nccl.CommDestroy(g.comm);
+    free_dev(g.d_q); free_dev(g.d_tmp); free_dev(g.d_we); free_dev(g.d_elem); free_dev(g.d_metric); free_dev(g.d_rsph);
+    free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
+    free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);
+    free_dev(g.d_send_elem); free_dev(g.d_send_row);
+    if (g.h_partials) cudaFreeHost(g.h_partials);
+    for (cudaEvent_t e : g.chunk_up) cudaEventDestroy(e);
+    for (cudaEvent_t e : g.chunk_done) cudaEventDestroy(e);
+    for (int i = 0; i < NEVENTS; ++i) if (g.events[i]) cudaEventDestroy(g.events[i]);
+    if (g.ev_b) cudaEventDestroy(g.ev_b);
+    if (g.ev_halo) cudaEventDestroy(g.ev_halo);
+    if (g.ev_misc) cudaEventDestroy(g.ev_misc);
+    if (g.s_main) cudaStreamDestroy(g.s_main);
+    if (g.s_comm) cudaStreamDestroy(g.s_comm);
+    if (g.s_h2d) cudaStreamDestroy(g.s_h2d);
+    if (g.s_d2h) cudaStreamDestroy(g.s_d2h);
+    g = Ctx();
+    return 0;
+}
+
+int bwk_upload(const bwk_element_t *elem, const double *qtens, const bwk_derivative_t *deriv)
+{
+    if (need_init()) return 1;
+    if (upload_metric(elem, deriv, g.s_main)) return 1;
+    if (qtens) CK(cudaMemcpyAsync(g.d_q, qtens, sizeof(double) * g.q_doubles, cudaMemcpyHostToDevice, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    return 0;
+}
+
+int bwk_run(int nets, int nete)
+{
+    if (need_init() || check_range(nets, nete)) return 1;
+    return laplace_range(nets - 1, nete - nets + 1, g.s_main);
+}
+
+int bwk_download(double *qtens)
+{
+    if (need_init()) return 1;
+    CK(cudaMemcpyAsync(qtens, g.d_q, sizeof(double) * g.q_doubles, cudaMemcpyDeviceToHost, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    return 0;
+}
+
+int bwk_sync(void)
+{
+    if (need_init()) return 1;
+    CK(cudaStreamSynchronize(g.s_main));
+    CK(cudaStreamSynchronize(g.s_comm));
+    CK(cudaStreamSynchronize(g.s_h2d));
+    CK(cudaStreamSynchronize(g.s_d2h));
+    return 0;
+}
+
+static int e2e_laplace(const bwk_element_t *elem, double *q_host_elem0 /*host address of local element 0*/, const bwk_derivative_t *deriv, int nets,
+                       int nete)
+{
+    if (need_init() || check_range(nets, nete)) return 1;
+    if (upload_metric(elem, deriv, g.s_main)) return 1;
+    const int first0 = nets - 1, count = nete - nets + 1;
+    if (count <= 0) return 0;
+    const std::vector<int> b = make_chunks(first0, count);
+    const size_t nch = b.size() - 1;
+    if (ensure_chunk_events(nch)) return 1;
+    const size_t es = (size_t)16 * g.kq; // doubles per element
+    for (size_t c = 0; c < nch; ++c) {
+        const size_t off = es * (size_t)b[c], n = es * (size_t)(b[c + 1] - b[c]);
+        CK(cudaMemcpyAsync(g.d_q + off, q_host_elem0 + off, sizeof(double) * n, cudaMemcpyHostToDevice, g.s_h2d));
+        CK(cudaEventRecord(g.chunk_up[c], g.s_h2d));
+        CK(cudaStreamWaitEvent(g.s_main, g.chunk_up[c], 0));
+        if (laplace_range(b[c], b[c + 1] - b[c], g.s_main)) return 1;
+        CK(cudaEventRecord(g.chunk_done[c], g.s_main));
+        CK(cudaStreamWaitEvent(g.s_d2h, g.chunk_done[c], 0));
+        CK(cudaMemcpyAsync(q_host_elem0 + off, g.d_q + off, sizeof(double) * n, cudaMemcpyDeviceToHost, g.s_d2h));
+    }
+    CK(cudaStreamSynchronize(g.s_d2h));
+    CK(cudaStreamSynchronize(g.s_main));
+    return 0;
+}
+
+int bwk_biharmonic_wk_scalar(const bwk_element_t *elem, double *qtens, double *grads, const bwk_derivative_t *deriv, const int *nets, const int *nete)
+{
+    (void)grads; // GPU2's global scratch (F90:529) is not needed by the fused kernel
+    if (!elem || !qtens || !deriv || !nets || !nete) return fail("null argument");
+    return e2e_laplace(elem, qtens, deriv, *nets, *nete);
+}
+
+int bwk_biharmonic_wk_scalar_nets(const bwk_element_t *elem, double *qtens_nets, const bwk_derivative_t *deriv, const int *nets, const int *nete)
+{
+    if (!elem || !qtens_nets || !deriv || !nets || !nete) return fail("null argument");
+    if (need_init()) return 1;
+    // qtens(np,np,nlev,qsize,nets:nete): the dummy's first element is element nets (F90:188)
+    return e2e_laplace(elem, qtens_nets - (size_t)16 * g.kq * (size_t)(*nets - 1), deriv, *nets, *nete);
+}
+
+int bwk_biharmonic_wk_scalar_full(const bwk_element_t *elem, double *qtens, const bwk_derivative_t *deriv)
+{
+    if (need_init()) return 1;
+    if (!elem || !qtens || !deriv) return fail("null argument");
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (upload_metric(elem, deriv, g.s_main)) return 1;
+    if (compute_rspheremp()) return 1;
+    const std::vector<int> b = make_chunks(0, g.nelem);
+    const size_t nch = b.size() - 1;
+    if (ensure_chunk_events(nch)) return 1;
+    const size_t es = (size_t)16 * g.kq;
+    // phase A: upload chunk c  ||  sweep 1 of chunk c-1
+    for (size_t c = 0; c < nch; ++c) {
+        const size_t off = es * (size_t)b[c], n = es * (size_t)(b[c + 1] - b[c]);
+        CK(cudaMemcpyAsync(g.d_q + off, qtens + off, sizeof(double) * n, cudaMemcpyHostToDevice, g.s_h2d));
+        CK(cudaEventRecord(g.chunk_up[c], g.s_h2d));
+        CK(cudaStreamWaitEvent(g.s_main, g.chunk_up[c], 0));
+        if (sweep(MODE_SWEEP1, b[c], b[c + 1] - b[c], nullptr, g.s_main)) return 1;
+    }
+    if (g.plan.nranks > 1) {
+        CK(cudaEventRecord(g.ev_b, g.s_main));
+        CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
+        if (exchange_halo()) return 1;
+        CK(cudaEventRecord(g.ev_halo, g.s_comm));
+        CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
+    }
+    // phase B: sweep 2 of chunk c  ||  download chunk c-1
+    for (size_t c = 0; c < nch; ++c) {
+        const size_t off = es * (size_t)b[c], n = es * (size_t)(b[c + 1] - b[c]);
+        if (sweep(MODE_SWEEP2, b[c], b[c + 1] - b[c], nullptr, g.s_main)) return 1;
+        CK(cudaEventRecord(g.chunk_done[c], g.s_main));
+        CK(cudaStreamWaitEvent(g.s_d2h, g.chunk_done[c], 0));
+        CK(cudaMemcpyAsync(qtens + off, g.d_q + off, sizeof(double) * n, cudaMemcpyDeviceToHost, g.s_d2h));
+    }
+    CK(cudaStreamSynchronize(g.s_d2h));
+    CK(cudaStreamSynchronize(g.s_main));
+    return 0;
+}
+
+int bwk_host_alloc(void **ptr, uint64_t bytes)
+{
+    CK(cudaMallocHost(ptr, bytes));
+    return 0;
+}
+int bwk_host_free(void *ptr)
+{
+    CK(cudaFreeHost(ptr));
+    return 0;
+}
+int bwk_host_register(void *ptr, uint64_t bytes)
+{
+    CK(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+    return 0;
+}
+int bwk_host_unregister(void *ptr)
+{
+    CK(cudaHostUnregister(ptr));
+    return 0;
+}
+
+int bwk_set_variant(int variant)
+{
+    if (variant != 0 && variant != 1) return fail("unknown variant %d", variant);
+    g.variant = variant;
+    return 0;
+}
+int64_t bwk_launch_count(void) { return g.launches; }
+int bwk_get_stream(uint64_t *stream)
+{
+    if (need_init()) return 1;
+    *stream = (uint64_t)(uintptr_t)g.s_main;
+    return 0;
+}
+int bwk_get_device_qtens(uint64_t *ptr)
+{
+    if (need_init()) return 1;
+    *ptr = (uint64_t)(uintptr_t)g.d_q;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------ harness
+int bwk_initialize_data_device(int64_t nelemd_global, int64_t elem_first, int seed_mode)
+{
+    if (need_init()) return 1;
+    if (elem_first < 0 || elem_first + g.nelem > nelemd_global) return fail("elements [%lld,%lld) outside global 0..%lld", (long long)elem_first,
+                                                                            (long long)(elem_first + g.nelem), (long long)nelemd_global);
+    const std::vector<double> table = lcg_table();
+    if (!g.d_table) CK(cudaMalloc(&g.d_table, sizeof(double) * 131072));
+    CK(cudaMemcpyAsync(g.d_table, table.data(), sizeof(double) * 131072, cudaMemcpyHostToDevice, g.s_main));
+    double dvv[16];
+    for (int t = 0; t < 16; ++t) {
+        if (seed_mode == 0) dvv[t] = table[(size_t)t];
+        else {
+            uint64_t x = (uint64_t)t + 0x9E3779B97F4A7C15ull;
+            x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+            x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+            x ^= x >> 31;
+            dvv[t] = (double)(x >> 11) * 0x1.0p-53;
+        }
+    }
+    CK(set_dvv(dvv, g.s_main));
+    CK(launch_init_data(g.d_table, nelemd_global, elem_first, g.nelem, g.kq, seed_mode, g.d_elem, g.d_q, g.s_main));
+    CK(launch_fold_metric(g.d_elem, g.d_metric, g.nelem, g.s_main));
+    g.launches += 2;
+    // keep the local spheremp on the host for rspheremp
+    std::vector<double> he((size_t)ELEM_DOUBLES * g.nelem);
+    CK(cudaMemcpyAsync(he.data(), g.d_elem, sizeof(double) * he.size(), cudaMemcpyDeviceToHost, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    g.h_spheremp.resize((size_t)16 * g.nelem);
+    for (int64_t ie = 0; ie < g.nelem; ++ie) std::memcpy(&g.h_spheremp[(size_t)16 * ie], &he[(size_t)(ie * ELEM_DOUBLES + 64)], 16 * sizeof(double));
+    g.have_metric = true;
+    g.have_rsph = false;
+    g.gen_nelem_global = nelemd_global;
+    g.gen_seed_mode = seed_mode;
+    return 0;
+}
+
+int bwk_save_qtens(void)
+{
+    if (need_init()) return 1;
+    if (!g.d_save) CK(cudaMalloc(&g.d_save, sizeof(double) * g.q_doubles));
+    CK(cudaMemcpyAsync(g.d_save, g.d_q, sizeof(double) * g.q_doubles, cudaMemcpyDeviceToDevice, g.s_main));
+    return 0;
+}
+
+int bwk_compute_l2norm(double *l2)
+{
+    if (need_init()) return 1;
+    if (!g.d_save) return fail("bwk_save_qtens has not been called");
+    CK(launch_l2_partials(g.d_q, g.d_save, (int64_t)g.q_doubles, g.d_partials, NPARTIAL_BLOCKS, g.s_main));
+    g.launches++;
+    CK(cudaMemcpyAsync(g.h_partials, g.d_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS, cudaMemcpyDeviceToHost, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    double num = 0, den = 0;
+    for (int i = 0; i < NPARTIAL_BLOCKS; ++i) { num += g.h_partials[i]; den += g.h_partials[NPARTIAL_BLOCKS + i]; }
+    *l2 = std::sqrt(num / den);
+    return 0;
+}
+
+int bwk_checksum(double *sum, double *sumsq)
+{
+    if (need_init()) return 1;
+    CK(launch_sum_partials(g.d_q, (int64_t)g.q_doubles, g.d_partials, NPARTIAL_BLOCKS, g.s_main));
+    g.launches++;
+    CK(cudaMemcpyAsync(g.h_partials, g.d_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS, cudaMemcpyDeviceToHost, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    double a = 0, b = 0;
+    for (int i = 0; i < NPARTIAL_BLOCKS; ++i) { a += g.h_partials[i]; b += g.h_partials[NPARTIAL_BLOCKS + i]; }
+    *sum = a;
+    *sumsq = b;
+    return 0;
+}
+
+int bwk_periodicity_defect(int64_t period_elems, double *max_abs_diff)
+{
+    if (need_init()) return 1;
+    if (period_elems < 1) return fail("bad period");
+    CK(launch_period_defect(g.d_q, (int64_t)g.q_doubles, period_elems * 16 * g.kq, g.d_partials, NPARTIAL_BLOCKS, g.s_main));
+    g.launches++;
+    CK(cudaMemcpyAsync(g.h_partials, g.d_partials, sizeof(double) * NPARTIAL_BLOCKS, cudaMemcpyDeviceToHost, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    double m = 0;
+    for (int i = 0; i < NPARTIAL_BLOCKS; ++i) m = std::max(m, g.h_partials[i]);
+    *max_abs_diff = m;
+    return 0;
+}
+
+int bwk_download_elements(int64_t first, int64_t count, double *dst)
+{
+    if (need_init()) return 1;
+    if (first < 0 || count < 0 || first + count > g.nelem) return fail("bad element range");
+    const size_t es = (size_t)16 * g.kq;
+    CK(cudaMemcpyAsync(dst, g.d_q + es * (size_t)first, sizeof(double) * es * (size_t)count, cudaMemcpyDeviceToHost, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    return 0;
+}
+
+int bwk_upload_elements(int64_t first, int64_t count, const double *src)
+{
+    if (need_init()) return 1;
+    if (first < 0 || count < 0 || first + count > g.nelem) return fail("bad element range");
+    const size_t es = (size_t)16 * g.kq;
+    CK(cudaMemcpyAsync(g.d_q + es * (size_t)first, src, sizeof(double) * es * (size_t)count, cudaMemcpyHostToDevice, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------ full biharmonic
+int bwk_cubed_sphere_gdof(int ne, int64_t *gdof)
+{
+    if (ne < 1 || !gdof) return fail("bad arguments");
+    cubed_sphere_gdof(ne, gdof);
+    return 0;
+}
+
+int bwk_set_topology_gdof(int64_t nelem_global, const int64_t *gdof, int64_t elem_first)
+{
+    if (need_init()) return 1;
+    int64_t f, c;
+    partition(nelem_global, g.rank, g.nranks, &f, &c);
+    if (f != elem_first || c != g.nelem)
+        return fail("rank %d of %d owns elements [%lld,%lld) of %lld, but the context holds %d elements from %lld", g.rank, g.nranks, (long long)f,
+                    (long long)(f + c), (long long)nelem_global, g.nelem, (long long)elem_first);
+    return install_plan(build_plan(nelem_global, gdof, g.rank, g.nranks));
+}
+
+int bwk_set_topology_cubed_sphere(int ne, int64_t elem_first)
+{
+    if (ne < 1) return fail("bad ne");
+    const int64_t n = (int64_t)6 * ne * ne;
+    std::vector<int64_t> gdof((size_t)16 * n);
+    cubed_sphere_gdof(ne, gdof.data());
+    return bwk_set_topology_gdof(n, gdof.data(), elem_first);
+}
+
+int bwk_set_rspheremp(const double *rs)
+{
+    if (need_init()) return 1;
+    if (!g.d_rsph) CK(cudaMalloc(&g.d_rsph, sizeof(double) * 16 * g.nelem));
+    CK(cudaMemcpy(g.d_rsph, rs, sizeof(double) * 16 * g.nelem, cudaMemcpyHostToDevice));
+    g.sp.rsph = g.d_rsph;
+    g.have_rsph = true;
+    return 0;
+}
+
+int bwk_get_rspheremp(double *rs)
+{
+    if (need_init()) return 1;
+    if (compute_rspheremp()) return 1;
+    CK(cudaMemcpy(rs, g.d_rsph, sizeof(double) * 16 * g.nelem, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int bwk_run_biharmonic(void)
+{
+    if (need_init()) return 1;
+    return biharmonic_device();
+}
+
+// ------------------------------------------------------------------------------ several GPUs
+int bwk_comm_unique_id(void *id_bytes)
+{
+    if (!g_nccl.load()) return fail("cannot load libnccl.so.2: %s", dlerror());
+    static_assert(sizeof(ncclUniqueId) == BWK_UNIQUE_ID_BYTES, "ncclUniqueId size");
+    ncclUniqueId id;
+    NK(g_nccl.GetUniqueId(&id));
+    std::memcpy(id_bytes, &id, sizeof id);
+    return 0;
+}
+
+int bwk_comm_init(int rank, int nranks, const void *id_bytes)
+{
+    if (need_init()) return 1;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail("bad rank %d of %d", rank, nranks);
+    if (g.have_topology) return fail("bwk_comm_init must precede bwk_set_topology_*");
+    g.rank = rank;
+    g.nranks = nranks;
+    if (nranks == 1) return 0;
+    if (!g_nccl.load()) return fail("cannot load libnccl.so.2: %s", dlerror());
+    ncclUniqueId id;
+    std::memcpy(&id, id_bytes, sizeof id);
+    NK(g_nccl.CommInitRank(&g.comm, nranks, id, rank));
+    return 0;
+}
+
+int bwk_comm_finalize(void)
+{
+    if (g.comm) {
+        cudaDeviceSynchronize();
+        NK(g_nccl.CommDestroy(g.comm));
+        g.comm = nullptr;
+    }
+    g.rank = 0;
+    g.nranks = 1;
+    return 0;
+}
+
+int bwk_partition(int64_t nelem_global, int rank, int nranks, int64_t *first, int64_t *count)
+{
+    if (nranks < 1 || rank < 0 || rank >= nranks || nelem_global < 0) return fail("bad arguments");
+    partition(nelem_global, rank, nranks, first, count);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------ events (timing on the library stream)
+int bwk_event_record(int slot)
+{
+    if (need_init()) return 1;
+    if (slot < 0 || slot >= NEVENTS) return fail("event slot out of range");
+    CK(cudaEventRecord(g.events[slot], g.s_main));
+    return 0;
+}
+int bwk_event_elapsed_ms(int a, int b, float *ms)
+{
+    if (need_init()) return 1;
+    if (a < 0 || a >= NEVENTS || b < 0 || b >= NEVENTS) return fail("event slot out of range");
+    CK(cudaEventSynchronize(g.events[b]));
+    CK(cudaEventElapsedTime(ms, g.events[a], g.events[b]));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------ plan introspection (host only)
+struct bwk_plan {
+    Plan p;
+};
+
+bwk_plan_t *bwk_plan_create(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
+{
+    if (nelem_global < 1 || !gdof || nranks < 1 || rank < 0 || rank >= nranks) { fail("bad arguments"); return nullptr; }
+    bwk_plan *h = new bwk_plan;
+    h->p = build_plan(nelem_global, gdof, rank, nranks);
+    if (!h->p.error.empty()) {
+        fail("unsupported mesh: %s", h->p.error.c_str());
+        delete h;
+        return nullptr;
+    }
+    return h;
+}
+void bwk_plan_destroy(bwk_plan_t *h) { delete h; }
+int64_t bwk_plan_unique_nodes(const bwk_plan_t *h) { return h->p.unique_nodes; }
+int64_t bwk_plan_local_first(const bwk_plan_t *h) { return h->p.first; }
+int64_t bwk_plan_local_count(const bwk_plan_t *h) { return h->p.count; }
+int64_t bwk_plan_recv_rows(const bwk_plan_t *h, int peer) { return (int64_t)h->p.recv[(size_t)peer].size(); }
+int64_t bwk_plan_send_rows(const bwk_plan_t *h, int peer) { return (int64_t)h->p.send[(size_t)peer].size(); }
+static int copy_list(const std::vector<RowRef> &v, int64_t *elem, int32_t *row)
+{
+    for (size_t i = 0; i < v.size(); ++i) { elem[i] = v[i].elem; row[i] = v[i].row; }
+    return 0;
+}
+int bwk_plan_send_list(const bwk_plan_t *h, int peer, int64_t *elem, int32_t *row) { return copy_list(h->p.send[(size_t)peer], elem, row); }
+int bwk_plan_recv_list(const bwk_plan_t *h, int peer, int64_t *elem, int32_t *row) { return copy_list(h->p.recv[(size_t)peer], elem, row); }
+int64_t bwk_plan_boundary_elems(const bwk_plan_t *h) { return (int64_t)h->p.boundary_list.size(); }
+int64_t bwk_plan_dependent_elems(const bwk_plan_t *h) { return (int64_t)h->p.dependent_list.size(); }
+int bwk_plan_apply_host(const bwk_plan_t *h, const double *field, double *out)
+{
+    for (int64_t le = 0; le < h->p.count; ++le) gather_elem_host(h->p, le, field, out + 16 * le);
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,88 @@
+// bwk_internal.h -- shared declarations of libbwk_b200 (not part of the public ABI).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <utility>
+#include <vector>
+
+namespace bwk {
+
+// Row ids of the edge rows a neighbour can ask for.  Rows 0..3 are the natural j-rows of a
+// slab (4 contiguous doubles); 4/5 are the packed i=1 / i=4 columns ("W"/"E" edge pack).
+enum : int { ROW_S = 0, ROW_N = 3, ROW_W = 4, ROW_E = 5 };
+// Edge order used everywhere: S (j=1), N (j=4), W (i=1), E (i=4).
+enum : int { EDGE_S = 0, EDGE_N = 1, EDGE_W = 2, EDGE_E = 3 };
+// Where a source row lives on the device.
+enum : int { SRC_TMP = 0, SRC_WEPACK = 1, SRC_HALO = 2 };
+
+// Per-element DSS gather descriptor consumed by the sweep-2 kernel (64 bytes).
+// Replaces HOMME's edge putmap/getmap for this path (upstream edge_mod_base.F90; the
+// reference itself has no DSS, only the comment F90:518-519).
+struct ElemDss {
+    int32_t edge_src[4];    // S,N,W,E: local element index (SRC_TMP/SRC_WEPACK) or halo row slot; -1 = no neighbour
+    int32_t diag_src[4];    // corners (1,1),(4,1),(1,4),(4,4): same encoding; -1 = no diagonal contributor
+    uint8_t edge_kind[4];   // SRC_*
+    uint8_t edge_row[4];    // 2nd TMA coordinate: natural row 0/3 (SRC_TMP), 0/1 (SRC_WEPACK), 0 (SRC_HALO)
+    uint8_t edge_rev[4];    // 1 = neighbour's edge runs in the opposite direction
+    uint8_t diag_kind[4];   // SRC_TMP or SRC_HALO
+    uint8_t diag_row[4];    // natural row 0/3 (SRC_TMP) or 0 (SRC_HALO)
+    uint8_t diag_pos[4];    // position (0 or 3) of the corner value inside that row
+    uint8_t corner_n[4];    // number of contributors to the corner node (own included)
+    uint8_t corner_perm[4]; // summation order, 2 bits per slot: 0 own, 1 S/N-edge nbr, 2 W/E-edge nbr, 3 diagonal
+};
+static_assert(sizeof(ElemDss) == 64, "ElemDss must be 64 bytes");
+
+struct RowRef {
+    int64_t elem; // global element id
+    int32_t row;  // ROW_*
+    bool operator<(const RowRef &o) const { return elem != o.elem ? elem < o.elem : row < o.row; }
+    bool operator==(const RowRef &o) const { return elem == o.elem && row == o.row; }
+};
+
+struct Plan {
+    int64_t nelem_global = 0, first = 0, count = 0;
+    int rank = 0, nranks = 1;
+    int64_t unique_nodes = 0;
+    std::vector<ElemDss> dss;                // [count]
+    std::vector<std::vector<RowRef>> send;   // [nranks] rows this rank sends, wire order
+    std::vector<std::vector<RowRef>> recv;   // [nranks] rows this rank receives, wire order
+    std::vector<int64_t> recv_offset;        // [nranks+1] first halo slot of each peer
+    std::vector<int32_t> boundary_list, interior_list;     // sweep-1 split (feeds a peer / does not)
+    std::vector<int32_t> dependent_list, independent_list; // sweep-2 split (needs a halo / does not)
+    // node groups of the local points: members of point p are pt_member[pt_start[p] .. pt_start[p+1]),
+    // global point ids 16*e+pt in ascending order (own point included)
+    std::vector<int64_t> pt_start, pt_member;
+    std::string error; // non-empty if the mesh is not supported
+};
+
+// partition: rank r owns [first, first+count)
+void partition(int64_t nelem_global, int rank, int nranks, int64_t *first, int64_t *count);
+int owner_of(int64_t nelem_global, int nranks, int64_t e);
+void cubed_sphere_gdof(int ne, int64_t *gdof);
+// Builds the plan; on unsupported meshes plan.error is set.
+Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks);
+// Host restatement of the sweep-2 gather for one local element (test hook).
+void gather_elem_host(const Plan &pl, int64_t local_e, const double *field_global, double *out16);
+
+// point index of position t (0..3) along edge `edge`
+inline int edge_pt(int edge, int t)
+{
+    switch (edge) {
+    case EDGE_S: return t;
+    case EDGE_N: return 12 + t;
+    case EDGE_W: return 4 * t;
+    default: return 3 + 4 * t;
+    }
+}
+inline int edge_rowid(int edge)
+{
+    switch (edge) {
+    case EDGE_S: return ROW_S;
+    case EDGE_N: return ROW_N;
+    case EDGE_W: return ROW_W;
+    default: return ROW_E;
+    }
+}
+inline int rowid_edge(int row) { return row == ROW_S ? EDGE_S : row == ROW_N ? EDGE_N : row == ROW_W ? EDGE_W : EDGE_E; }
+
+} // namespace bwk

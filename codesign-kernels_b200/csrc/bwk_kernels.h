@@ -1,0 +1,63 @@
+// bwk_kernels.h -- launch interface between the C-ABI layer (bwk_api.cu) and the sm_100a kernels.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "bwk_internal.h"
+
+namespace bwk {
+
+constexpr int TILE_SLABS = 32;      // one warp, one slab per thread
+constexpr int METRIC_DOUBLES = 64;  // folded metric: 4 doubles per GLL point
+constexpr int ELEM_DOUBLES = 144;   // element_t, F90:23-27
+
+enum SweepMode : int {
+    MODE_LAPLACE = 0, // qtens -> qtens in place              (reference-pinned, F90:186-200)
+    MODE_SWEEP1 = 1,  // qtens -> tmp + W/E edge pack          (laplace + edgeVpack of local edges)
+    MODE_SWEEP2 = 2   // tmp + neighbour rows -> *rspheremp -> laplace -> qtens  (edgeVunpack + second laplace)
+};
+
+// Everything a sweep launch needs.  Tensor maps are passed by value (__grid_constant__).
+struct SweepParams {
+    CUtensorMap map_q;      // qtens   as {16, KQ, nelem}, box {16,32,1}, SWIZZLE_128B
+    CUtensorMap map_tmp;    // tmp     same shape
+    CUtensorMap map_we;     // wepack  as {8, KQ, nelem},  box {8,32,1},  SWIZZLE_64B
+    CUtensorMap map_tmp_rows;  // tmp    as {4, 4, KQ, nelem}, box {4,1,32,1}
+    CUtensorMap map_we_rows;   // wepack as {4, 2, KQ, nelem}, box {4,1,32,1}
+    CUtensorMap map_halo_rows; // halo   as {4, 1, KQ, nrows}, box {4,1,32,1}
+    const double *metric;   // [nelem][64] folded metric
+    const double *rsph;     // [nelem][16]
+    const ElemDss *dss;     // [nelem]
+    const int32_t *elem_list; // optional list of local element indices, else contiguous from elem_first
+    int elem_first;         // 0-based first local element (when elem_list == nullptr)
+    int elem_count;         // grid x
+    int kq;                 // nlev*qsize
+    int tiles_per_unit;     // tiles (of 32 slabs) per CTA work unit
+    int units;              // grid y
+};
+
+// geometry chosen by the host for a given KQ / element count
+struct SweepGeometry {
+    int tiles_per_unit, units;
+};
+SweepGeometry choose_geometry(int kq, int64_t nelem, int mode);
+
+cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st);
+// plain-load variant of MODE_LAPLACE (no TMA, no shared-memory staging); for ncu A/B only
+cudaError_t launch_laplace_plain(double *qtens, const double *metric, int elem_first, int elem_count, int kq, cudaStream_t st);
+
+cudaError_t set_dvv(const double *dvv16_host, cudaStream_t st);
+// folded metric M = -(rrearth^2) * spheremp * Dinv * tensorVisc * Dinv^T per GLL point
+cudaError_t launch_fold_metric(const double *elem, double *metric, int64_t nelem, cudaStream_t st);
+// edge pack: copy rows (local element, row id) x KQ into a contiguous send buffer (HOMME edgeVpack analogue)
+cudaError_t launch_edge_pack(const double *tmp, const double *wepack, const int32_t *row_elem, const int32_t *row_id,
+                             int64_t nrows, int kq, double *sendbuf, cudaStream_t st);
+// harness: initialize_data on the device (F90:48-58), table = the 131072 LCG draws
+cudaError_t launch_init_data(const double *table, int64_t nelemd_global, int64_t elem_first, int64_t nelem, int kq,
+                             int seed_mode, double *elem, double *qtens, cudaStream_t st);
+cudaError_t launch_l2_partials(const double *q, const double *qs, int64_t n, double *partials /*[2*nblocks]*/, int nblocks, cudaStream_t st);
+cudaError_t launch_sum_partials(const double *q, int64_t n, double *partials /*[2*nblocks]*/, int nblocks, cudaStream_t st);
+cudaError_t launch_period_defect(const double *q, int64_t n, int64_t period, double *partials /*[nblocks]*/, int nblocks, cudaStream_t st);
+
+} // namespace bwk

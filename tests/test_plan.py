@@ -1,0 +1,80 @@
+"""CPU: the DSS plan (host logic of libbwk_b200) against the oracle's node-wise DSS on the
+synthetic cubed sphere.  No GPU, no compute kernels."""
+import numpy as np
+import pytest
+
+
+@pytest.mark.parametrize("ne", [1, 2, 3, 4, 8])
+def test_cubed_sphere_node_counts(bwk, oracle, ne):
+    g = bwk.cubed_sphere_gdof(ne)
+    assert np.array_equal(g, oracle.cubed_sphere_gdof(ne))
+    n = 6 * ne * ne
+    d = oracle.Dss(n, g)
+    assert d.unique_nodes() == 54 * ne * ne + 2
+    m = d.multiplicity_hist()
+    assert m[3] == 8 and m[5:].sum() == 0  # exactly the 8 cube vertices have multiplicity 3
+    assert m[1] * 1 + m[2] * 2 + m[3] * 3 + m[4] * 4 == 16 * n
+    if ne == 4:
+        assert (m[1], m[2], m[4]) == (384, 384, 90)
+    assert bwk.Plan(n, g).unique_nodes == 54 * ne * ne + 2
+
+
+@pytest.mark.parametrize("ne,nranks", [(1, 1), (2, 1), (3, 1), (4, 1), (2, 2), (3, 4), (4, 8), (5, 3), (8, 8)])
+def test_plan_gather_equals_nodewise_dss_bit_for_bit(bwk, oracle, ne, nranks):
+    n = 6 * ne * ne
+    g = bwk.cubed_sphere_gdof(ne)
+    rng = np.random.default_rng(ne * 100 + nranks)
+    field = rng.standard_normal((4, 4, 1, 1, n))
+    field = np.asfortranarray(field)
+    ref = oracle.Dss(n, g).apply(field.copy(order="F")).reshape(-1, order="F")
+    got = np.empty(16 * n)
+    for r in range(nranks):
+        pl = bwk.Plan(n, g, r, nranks)
+        got[16 * pl.local_first : 16 * (pl.local_first + pl.local_count)] = pl.apply_host(field.reshape(-1, order="F"))
+    assert np.array_equal(got, ref)  # same values, same summation order
+
+
+@pytest.mark.parametrize("ne,nranks", [(2, 2), (3, 4), (4, 8), (6, 5)])
+def test_send_and_recv_lists_agree_between_ranks(bwk, ne, nranks):
+    n = 6 * ne * ne
+    g = bwk.cubed_sphere_gdof(ne)
+    plans = [bwk.Plan(n, g, r, nranks) for r in range(nranks)]
+    total = 0
+    for a in range(nranks):
+        assert plans[a].send_list(a)[0].size == 0 and plans[a].recv_list(a)[0].size == 0
+        for b in range(nranks):
+            se, sr = plans[a].send_list(b)
+            re_, rr = plans[b].recv_list(a)
+            assert np.array_equal(se, re_) and np.array_equal(sr, rr)
+            lo, cnt = plans[a].local_first, plans[a].local_count
+            assert np.all((se >= lo) & (se < lo + cnt))
+            assert set(np.unique(sr)) <= {0, 3, 4, 5}
+            total += se.size
+    assert total > 0
+    # every element that needs a halo is flagged dependent, every feeder boundary
+    assert all(p.dependent_elems > 0 and p.boundary_elems > 0 for p in plans)
+
+
+def test_single_rank_has_no_halo(bwk):
+    g = bwk.cubed_sphere_gdof(3)
+    pl = bwk.Plan(54, g)
+    assert pl.dependent_elems == 0 and pl.boundary_elems == 0
+
+
+def test_open_boundary_mesh_is_supported(bwk, oracle):
+    # a single face of the cube = planar patch with open edges (multiplicity-1 boundary points)
+    ne = 3
+    g = bwk.cubed_sphere_gdof(ne)[: 16 * ne * ne]
+    n = ne * ne
+    field = np.asfortranarray(np.random.default_rng(1).standard_normal((4, 4, 1, 1, n)))
+    ref = oracle.Dss(n, g).apply(field.copy(order="F")).reshape(-1, order="F")
+    got = bwk.Plan(n, g).apply_host(field.reshape(-1, order="F"))
+    assert np.array_equal(got, ref)
+
+
+def test_unsupported_mesh_is_rejected_loudly(bwk):
+    # five elements around one corner node: not a structured quad corner
+    g = np.arange(16 * 5, dtype=np.int64) + 1000
+    g[[0, 16, 32, 48, 64]] = 7
+    with pytest.raises(bwk.BwkError):
+        bwk.Plan(5, g)
