@@ -1,0 +1,380 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the biharmonic_wk hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--ne NE] [--nlev L] [--qsize Q]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Metric (BASELINE.json): biharmonic_wk GLL-point x level x tracer updates/s on ne120np4 L72 q40,
+one update = the FULL biharmonic (Laplace -> DSS -> *rspheremp -> Laplace) at one GLL point of one
+level of one tracer.  Strong scaling: the 86,400 elements are split into contiguous blocks over
+the N ranks, DSS edge rows travel with ncclSend/ncclRecv.
+
+A step = one pass of the operator over the whole (device-resident) field.  Inputs are
+re-generated on the device before every step (outside the timed region: repeated application
+would underflow), each step is timed with CUDA events on the library's stream, the K step
+durations are summed, and the maximum over ranks is reported.  The 32 GB working set is far
+larger than the 126 MB L2, so no explicit flush is needed between steps.
+
+The same JSON line also carries
+  laplace_only : the reference-pinned single Laplacian (what the reference's own
+                 biharmonic_wk_scalar computes, F90:186-200) on the same data,
+  roofline     : the slower of the two sweep kernels against the measured HBM copy rate,
+  cpu_baseline : the CPU oracle (C port of the reference, OpenMP over elements) on a bounded
+                 sample, timed on this box's host cores (N=1 only),
+  e2e          : the same metric through bwk_biharmonic_wk_scalar_full with pinned HOST buffers,
+                 H2D and D2H copies inside the timed region.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "biharmonic_wk GLL-pt*lev*tracer updates/s (ne120np4 L72 q40)"
+UNIT = "updates/s"
+
+
+def measured_hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def mark(self):
+        return time.time()
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        sm, mx, reasons = [], [], set()
+        for t, line in self.rows:
+            if t < t0 - 0.05 or t > t1 + 0.05:
+                continue
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0]))
+                mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(ne, nlev, qsize, reps, want_serial=False):
+    """The oracle (C port of F90:100-202 + DSS) with OpenMP over elements on all host cores."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as orc
+
+    orc.build()
+    n = 6 * ne * ne
+    dvv, elem, q0 = orc.initialize_data(n, nlev, qsize)
+    dss = orc.Dss(n, orc.cubed_sphere_gdof(ne))
+    rs = dss.rspheremp(elem)
+    cores = orc.lib(omp=True).bwko_omp_max_threads()
+    times, lap_times = [], []
+    for _ in range(reps):
+        q = q0.copy(order="F")
+        t = time.perf_counter()
+        dss.biharmonic_full(elem, rs, q, dvv, omp=True)
+        times.append(time.perf_counter() - t)
+        q = q0.copy(order="F")
+        t = time.perf_counter()
+        orc.biharmonic_wk_scalar_cpu(elem, q, dvv, omp=True)
+        lap_times.append(time.perf_counter() - t)
+    updates = 16.0 * nlev * qsize * n
+    out = {
+        "value": updates / min(times), "unit": UNIT, "cores": cores, "kind": "port",
+        "sample": f"ne{ne}np4 L{nlev} q{qsize} ({n} elements), full biharmonic, OpenMP over elements, best of {reps}",
+        "times_s": [round(t, 4) for t in times],
+        "laplace_only_value": updates / min(lap_times),
+    }
+    if want_serial:
+        q = q0.copy(order="F")
+        t = time.perf_counter()
+        orc.biharmonic_wk_scalar_cpu(elem, q, dvv)
+        out["laplace_only_serial_value"] = updates / (time.perf_counter() - t)
+        out["serial_note"] = "1 core, no OpenMP: the reference's own CPU path is serial (no !$omp in atmosphere/)"
+    return out
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (C oracle port; the
+    Fortran original cannot be compiled here) on a bounded sample, all host threads."""
+    if rank != 0:
+        return
+    ne_s = args.cpu_ne
+    times = []
+    res = None
+    for i in range(args.warmup + args.steps):
+        res = cpu_baseline(ne_s, args.nlev, args.qsize, 1)
+        if i >= args.warmup:
+            times.append(res["times_s"][0])
+    n = 6 * ne_s * ne_s
+    updates = 16.0 * args.nlev * args.qsize * n
+    tot = sum(times)
+    value = updates * len(times) / tot
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * tot / len(times), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic (reference LCG, F90:77-91)",
+        "config": {"workload": f"ne{args.ne}np4 L{args.nlev} q{args.qsize} full biharmonic", "sample": res["sample"]},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": res["cores"], "kind": "port", "sample": res["sample"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ne", type=int, default=120)
+    ap.add_argument("--nlev", type=int, default=72)
+    ap.add_argument("--qsize", type=int, default=40)
+    ap.add_argument("--cpu-ne", type=int, default=30, help="cubed-sphere size of the CPU sample")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--variant", type=int, default=0)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as ge
+
+    bwk = ge.build(oracle=(rank == 0))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("gloo", rank=rank, world_size=world)  # control plane only; data plane = NCCL inside libbwk_b200
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    ne, nlev, qsize = args.ne, args.nlev, args.qsize
+    nglob = 6 * ne * ne
+    first, count = bwk.partition(nglob, rank, world)
+    updates_global = 16.0 * nlev * qsize * nglob
+    kq = nlev * qsize
+
+    ku = bwk.KernelUtils(count, nlev, qsize).allocate_data(host_arrays=False)
+    ku.set_variant(args.variant)
+    if world > 1:
+        idb = [bwk.KernelUtils.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(idb, src=0)
+        bwk.KernelUtils.comm_init(rank, world, idb[0])
+    ku.initialize_data_device(nglob, first)
+    ku.set_topology_cubed_sphere(ne, first)
+    ku.get_rspheremp()  # force the (host) rspheremp setup out of the timed region
+
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+
+    def timed_steps(run, nwarm, nsteps):
+        for _ in range(nwarm):
+            ku.initialize_data_device(nglob, first)
+            run()
+        barrier()
+        t_wall0 = time.time()
+        l0 = ku.launch_count()
+        tot_ms = 0.0
+        launches = 0
+        for _ in range(nsteps):
+            ku.initialize_data_device(nglob, first)  # untimed re-init (also sweeps L2)
+            ku.sync()
+            if world > 1:
+                dist.barrier()
+            la = ku.launch_count()
+            ku.event_record(0)
+            run()
+            ku.event_record(1)
+            tot_ms += ku.event_elapsed_ms(0, 1)
+            launches += ku.launch_count() - la
+        barrier()
+        t_wall1 = time.time()
+        return max_over_ranks(tot_ms), launches, (t_wall0, t_wall1)
+
+    # ---- headline: full biharmonic, device resident
+    tot_ms, launches, wall = timed_steps(ku.run_biharmonic_device, args.warmup, args.steps)
+    ms_per_step = tot_ms / args.steps
+    value = updates_global / (ms_per_step * 1e-3)
+
+    # ---- reference-pinned single Laplacian on the same data
+    lap_ms, lap_launches, _ = timed_steps(lambda: ku.run_device(1, count), 1, args.steps)
+    lap_ms /= args.steps
+    peak, peak_src = measured_hbm_peak()
+    bytes_sweep_local = count * (256.0 * kq + 1152.0) + 128.0  # 16 B/pt + metric
+    lap = {"value": updates_global / (lap_ms * 1e-3), "unit": UNIT, "ms_per_step": lap_ms,
+           "note": "one laplace_sphere_wk per update (what the reference's biharmonic_wk_scalar computes, F90:186-200)"}
+    if world == 1:
+        lap["roofline_frac"] = bytes_sweep_local / (lap_ms * 1e-3) / 1e9 / peak
+
+    # ---- per-kernel timing for the roofline (single rank only: the phase hook has no halo)
+    roofline = None
+    kernels = {}
+    if world == 1:
+        for phase, name in ((1, "sweep1 (laplace + edge pack)"), (2, "sweep2 (unpack + rspheremp + laplace)")):
+            ms = []
+            for _ in range(max(3, min(args.steps, 10))):
+                ku.initialize_data_device(nglob, first)
+                if phase == 2:
+                    ku.run_biharmonic_phase(1)
+                ku.sync()
+                ku.event_record(2)
+                ku.run_biharmonic_phase(phase)
+                ku.event_record(3)
+                ms.append(ku.event_elapsed_ms(2, 3))
+            avg = sum(ms) / len(ms)
+            kernels[name] = {"avg_ms": avg, "algorithmic_GBps": bytes_sweep_local / (avg * 1e-3) / 1e9}
+        dom = max(kernels, key=lambda k: kernels[k]["avg_ms"])
+        ach = kernels[dom]["algorithmic_GBps"]
+        roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "kernel": dom, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_sweep_local,
+                    "step_frac_of_32B_per_update": (2 * bytes_sweep_local) / (ms_per_step * 1e-3) / 1e9 / peak,
+                    "frac_of_nominal_8TBs": ach / 8000.0, "kernels": kernels}
+        tr = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tr):
+            try:
+                roofline["traffic"] = json.load(open(tr)).get(dom.split()[0])
+            except Exception:
+                pass
+
+    clocks = sampler.summary(*wall) if sampler else None
+
+    # ---- e2e: host buffers through the drop-in call (H2D + D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        es = 16 * kq
+        try:
+            hq = ku._pinned_array((4, 4, nlev, qsize, count))
+            helem = np.zeros(count, dtype=bwk.ELEMENT_DTYPE)
+            hderiv = np.zeros((), dtype=bwk.DERIVATIVE_DTYPE)
+            # host inputs = the device-generated LCG data (reference generator), copied back once
+            import ctypes as C
+
+            def refill():
+                ku.initialize_data_device(nglob, first)
+                bwk.binding._ck(bwk.lib().bwk_download(hq.ctypes.data_as(C.c_void_p)))
+
+            # element metric on the host from the closed-form LCG (F90:52-56)
+            state, tab = 11, np.empty(131072)
+            for t in range(131072):
+                state = (1301 * state + 97) % 131072
+                tab[t] = state / 131072.0
+            d = 16 + 144 * (first + np.arange(count, dtype=np.int64))[:, None] + np.arange(144, dtype=np.int64)[None, :]
+            helem.view(np.float64).reshape(count, 144)[...] = tab[d % 131072]
+            hderiv["Dvv"] = tab[:16].reshape(4, 4)
+            tot = 0.0
+            nst = max(1, args.e2e_steps)
+            for i in range(1 + nst):
+                refill()
+                barrier()
+                t0 = time.perf_counter()
+                ku.biharmonic_wk_scalar_full(helem, hq, hderiv)
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+                if i >= 1:
+                    tot += max_over_ranks(dt)
+            bytes_q = 8.0 * es * count
+            e2e = {"value": updates_global * nst / tot, "unit": UNIT, "h2d_bytes_per_step": bytes_q + 1152.0 * count + 128,
+                   "d2h_bytes_per_step": bytes_q, "ms_per_step": 1e3 * tot / nst, "steps": nst,
+                   "api": "bwk_biharmonic_wk_scalar_full(elem, qtens, deriv) with pinned host arrays, host wall clock"}
+        except Exception as ex:  # e.g. not enough pinned host memory
+            e2e = {"value": None, "unit": UNIT, "error": str(ex)[:200]}
+
+    if sampler:
+        sampler.stop()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline(args.cpu_ne, nlev, qsize, 3, want_serial=True)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic (reference LCG F90:77-91, generated on the device; cubed-sphere connectivity SURVEY App. D)",
+            "config": {"workload": f"ne{ne}np4 L{nlev} q{qsize}, {nglob} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
+                       "partition": f"contiguous element blocks over {world} rank(s)", "l2": "working set >> L2 (no flush needed); inputs re-generated before every step",
+                       "variant": args.variant},
+            "laplace_only": lap, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    ku.finalize()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

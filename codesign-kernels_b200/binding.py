@@ -80,6 +80,7 @@ def lib():
         "bwk_set_rspheremp": [p],
         "bwk_get_rspheremp": [p],
         "bwk_run_biharmonic": [],
+        "bwk_run_biharmonic_phase": [i32],
         "bwk_comm_unique_id": [p],
         "bwk_comm_init": [i32, i32, p],
         "bwk_comm_finalize": [],
@@ -269,6 +270,9 @@ class KernelUtils:
 
     def run_biharmonic_device(self):
         _ck(lib().bwk_run_biharmonic())
+
+    def run_biharmonic_phase(self, phase):
+        _ck(lib().bwk_run_biharmonic_phase(phase))
 
     def sync(self):
         _ck(lib().bwk_sync())

@@ -105,6 +105,7 @@ struct Ctx {
     std::vector<double> h_spheremp; // spheremp of the local elements (16 each), for rspheremp
     int64_t gen_nelem_global = -1;  // >=0 when the data came from bwk_initialize_data_device (LCG closed form)
     int gen_seed_mode = 0;
+    int64_t gen_elem_first = -1;
     int variant = 0;
     int64_t launches = 0;
     // comm
@@ -674,16 +675,21 @@ int bwk_initialize_data_device(int64_t nelemd_global, int64_t elem_first, int se
     CK(launch_init_data(g.d_table, nelemd_global, elem_first, g.nelem, g.kq, seed_mode, g.d_elem, g.d_q, g.s_main));
     CK(launch_fold_metric(g.d_elem, g.d_metric, g.nelem, g.s_main));
     g.launches += 2;
-    // keep the local spheremp on the host for rspheremp
-    std::vector<double> he((size_t)ELEM_DOUBLES * g.nelem);
-    CK(cudaMemcpyAsync(he.data(), g.d_elem, sizeof(double) * he.size(), cudaMemcpyDeviceToHost, g.s_main));
-    CK(cudaStreamSynchronize(g.s_main));
-    g.h_spheremp.resize((size_t)16 * g.nelem);
-    for (int64_t ie = 0; ie < g.nelem; ++ie) std::memcpy(&g.h_spheremp[(size_t)16 * ie], &he[(size_t)(ie * ELEM_DOUBLES + 64)], 16 * sizeof(double));
     g.have_metric = true;
-    g.have_rsph = false;
-    g.gen_nelem_global = nelemd_global;
-    g.gen_seed_mode = seed_mode;
+    const bool same = g.gen_nelem_global == nelemd_global && g.gen_elem_first == elem_first && g.gen_seed_mode == seed_mode &&
+                      (int64_t)g.h_spheremp.size() == (int64_t)16 * g.nelem;
+    if (!same) {
+        // keep the local spheremp on the host for rspheremp
+        std::vector<double> he((size_t)ELEM_DOUBLES * g.nelem);
+        CK(cudaMemcpyAsync(he.data(), g.d_elem, sizeof(double) * he.size(), cudaMemcpyDeviceToHost, g.s_main));
+        CK(cudaStreamSynchronize(g.s_main));
+        g.h_spheremp.resize((size_t)16 * g.nelem);
+        for (int64_t ie = 0; ie < g.nelem; ++ie) std::memcpy(&g.h_spheremp[(size_t)16 * ie], &he[(size_t)(ie * ELEM_DOUBLES + 64)], 16 * sizeof(double));
+        g.have_rsph = false;
+        g.gen_nelem_global = nelemd_global;
+        g.gen_elem_first = elem_first;
+        g.gen_seed_mode = seed_mode;
+    }
     return 0;
 }
 
@@ -807,6 +813,18 @@ int bwk_run_biharmonic(void)
 {
     if (need_init()) return 1;
     return biharmonic_device();
+}
+
+int bwk_run_biharmonic_phase(int phase)
+{
+    if (need_init()) return 1;
+    if (!g.have_metric) return fail("no element metric on the device");
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (g.plan.nranks != 1) return fail("bwk_run_biharmonic_phase is a single-rank profiling hook");
+    if (compute_rspheremp()) return 1;
+    if (phase == 1) return sweep(MODE_SWEEP1, 0, g.nelem, nullptr, g.s_main);
+    if (phase == 2) return sweep(MODE_SWEEP2, 0, g.nelem, nullptr, g.s_main);
+    return fail("phase must be 1 or 2");
 }
 
 // ------------------------------------------------------------------------------ several GPUs

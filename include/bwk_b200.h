@@ -141,6 +141,9 @@ int bwk_get_rspheremp(double *rspheremp);
 
 /* Laplace -> DSS -> *rspheremp -> Laplace on all local elements; asynchronous. */
 int bwk_run_biharmonic(void);
+/* one phase of the above on a single rank, for per-kernel timing and profiling only:
+ * 1 = first sweep (laplace + local edge pack), 2 = second sweep (unpack, rspheremp, laplace) */
+int bwk_run_biharmonic_phase(int phase);
 /* same through host buffers (upload, both sweeps, download), GPU2-style signature */
 int bwk_biharmonic_wk_scalar_full(const bwk_element_t *elem, double *qtens,
                                   const bwk_derivative_t *deriv);

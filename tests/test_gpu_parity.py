@@ -210,6 +210,7 @@ def test_full_biharmonic_small_cubed_spheres(bwk, oracle, ne, nlev, qsize):
     with bwk.KernelUtils(n, nlev, qsize).allocate_data() as ku:
         ku.initialize_data()
         ku.set_topology_cubed_sphere(ne)
+        ku.update_device()
         assert np.array_equal(ku.get_rspheremp(), rs)
         ku.biharmonic_wk_scalar_full(ku.elem, ku.qtens, ku.deriv)
         mr = oracle.max_rel(ku.qtens, ref)
