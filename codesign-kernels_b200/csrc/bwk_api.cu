@@ -313,39 +313,11 @@ int install_plan(Plan &&pl)
     if (!se.empty()) CK(cudaMalloc(&g.d_send, sizeof(double) * 4 * kq * se.size()));
     if (upload_list(se, &g.d_send_elem) || upload_list(sr, &g.d_send_row)) return 1;
 
-    // tensor maps of the second sweep
+    // tensor map of the sweep-1 output; everything else sweep 2 reads goes through plain pointers
     if (make_slab_map(&g.sp.map_tmp, g.d_tmp, g.kq, g.nelem)) return 1;
-    {
-        const uint64_t dims[3] = {8, (uint64_t)kq, (uint64_t)g.nelem};
-        const uint64_t str[2] = {64, (uint64_t)kq * 64};
-        const uint32_t box[3] = {8, TILE_SLABS, 1};
-        if (make_map(&g.sp.map_we, g.d_we, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B)) return 1;
-    }
-    {
-        const uint64_t dims[4] = {4, 4, (uint64_t)kq, (uint64_t)g.nelem};
-        const uint64_t str[3] = {32, 128, (uint64_t)kq * 128};
-        const uint32_t box[4] = {4, 1, TILE_SLABS, 1};
-        if (make_map(&g.sp.map_tmp_rows, g.d_tmp, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
-    }
-    {
-        const uint64_t dims[4] = {4, 2, (uint64_t)kq, (uint64_t)g.nelem};
-        const uint64_t str[3] = {32, 64, (uint64_t)kq * 64};
-        const uint32_t box[4] = {4, 1, TILE_SLABS, 1};
-        if (make_map(&g.sp.map_we_rows, g.d_we, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
-    }
-    {
-        double *base = g.d_halo;
-        uint64_t rows = (uint64_t)nrecv;
-        if (!base) {
-            if (!g.d_dummy) CK(cudaMalloc(&g.d_dummy, sizeof(double) * 4 * kq));
-            base = g.d_dummy;
-            rows = 1;
-        }
-        const uint64_t dims[4] = {4, 1, (uint64_t)kq, rows};
-        const uint64_t str[3] = {32, 32, (uint64_t)kq * 32};
-        const uint32_t box[4] = {4, 1, TILE_SLABS, 1};
-        if (make_map(&g.sp.map_halo_rows, base, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
-    }
+    g.sp.tmp = g.d_tmp;
+    g.sp.wepack = g.d_we;
+    g.sp.halo = g.d_halo;
     g.sp.dss = g.d_dss;
     g.sp.rsph = g.d_rsph;
     g.have_topology = true;
@@ -465,8 +437,8 @@ int bwk_init(int nelemd, int nlev, int qsize)
     CK(cudaMalloc(&g.d_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS));
     CK(cudaMallocHost(&g.h_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS));
     if (make_slab_map(&g.sp.map_q, g.d_q, g.kq, nelemd)) return 1;
-    // until a topology is installed the other maps alias map_q (never dereferenced by MODE_LAPLACE)
-    g.sp.map_tmp = g.sp.map_we = g.sp.map_tmp_rows = g.sp.map_we_rows = g.sp.map_halo_rows = g.sp.map_q;
+    // until a topology is installed map_tmp aliases map_q (never dereferenced by MODE_LAPLACE)
+    g.sp.map_tmp = g.sp.map_q;
     g.sp.metric = g.d_metric;
     g.sp.kq = g.kq;
     g.inited = true;

@@ -22,10 +22,10 @@ struct ElemDss {
     int32_t edge_src[4];    // S,N,W,E: local element index (SRC_TMP/SRC_WEPACK) or halo row slot; -1 = no neighbour
     int32_t diag_src[4];    // corners (1,1),(4,1),(1,4),(4,4): same encoding; -1 = no diagonal contributor
     uint8_t edge_kind[4];   // SRC_*
-    uint8_t edge_row[4];    // 2nd TMA coordinate: natural row 0/3 (SRC_TMP), 0/1 (SRC_WEPACK), 0 (SRC_HALO)
+    uint8_t edge_row[4];    // natural row 0/3 (SRC_TMP), side 0=W/1=E (SRC_WEPACK), 0 (SRC_HALO)
     uint8_t edge_rev[4];    // 1 = neighbour's edge runs in the opposite direction
-    uint8_t diag_kind[4];   // SRC_TMP or SRC_HALO
-    uint8_t diag_row[4];    // natural row 0/3 (SRC_TMP) or 0 (SRC_HALO)
+    uint8_t diag_kind[4];   // SRC_WEPACK or SRC_HALO: corner values are the ends of the W/E edge rows
+    uint8_t diag_row[4];    // side 0=W/1=E (SRC_WEPACK) or 0 (SRC_HALO)
     uint8_t diag_pos[4];    // position (0 or 3) of the corner value inside that row
     uint8_t corner_n[4];    // number of contributors to the corner node (own included)
     uint8_t corner_perm[4]; // summation order, 2 bits per slot: 0 own, 1 S/N-edge nbr, 2 W/E-edge nbr, 3 diagonal

@@ -19,12 +19,13 @@
 //   * the per-element folded metric (64 doubles) is staged once per CTA in shared memory
 //     and read as warp-wide broadcasts; Dvv lives in __constant__ memory and is consumed
 //     directly as a constant-bank operand of DFMA;
-//   * sweep 2 of the full biharmonic fetches the neighbour edge rows it must add (DSS,
-//     HOMME edgeVunpack) with 4-D TMA boxes of 32-byte rows straight from the neighbours'
-//     sweep-1 output / halo buffer.
+//   * sweep 2 of the full biharmonic adds the neighbours' coincident edge values (DSS, HOMME
+//     edgeVunpack) read with one 256-bit load per edge straight from the neighbours' sweep-1
+//     output / W-E edge pack / halo buffer.
 #include "bwk_kernels.h"
 
 #include <cstdio>
+#include <cstdlib>
 
 namespace bwk {
 
@@ -77,12 +78,6 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map
 {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
-                 : "memory");
-}
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2, int c3, uint32_t bar)
-{
-    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
-                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
                  : "memory");
 }
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, int c0, int c1, int c2, uint32_t src)
@@ -163,11 +158,25 @@ struct GlobalMetric {
 };
 
 // ------------------------------------------------------------------------------------------
-// Sweep kernel
+// Sweep kernel (all three modes share the warp-private TMA pipeline)
+//
+//   MODE_LAPLACE : qtens tile -> laplace -> qtens tile (in place)
+//   MODE_SWEEP1  : qtens tile -> laplace -> tmp tile, plus the W/E edge pack (the i=1 / i=np
+//                  columns of every slab, stored kq-contiguous so that a neighbour reads them as
+//                  fully coalesced 32-byte rows) -- the on-device part of HOMME's edgeVpack
+//   MODE_SWEEP2  : tmp tile + the neighbours' coincident edge/corner values (edgeVunpack)
+//                  -> * rspheremp -> laplace -> qtens tile
+//
+// Sweep 2 reads each neighbour's facing edge row as ONE 256-bit load per thread (LDG.E.256),
+// straight from where sweep 1 left it: rows j=1/j=np of the neighbour's slab in tmp, the W/E
+// pack, or the halo buffer filled by ncclRecv.  The loads are issued before the wait on the
+// tile's mbarrier, so their latency overlaps the TMA wait; 12 resident warps per SM hide the rest.
+// (A first version staged these rows with 4-D TMA boxes of 32-byte rows; it was bound by the TMA
+// request rate -- see profiles/.)
 // ------------------------------------------------------------------------------------------
 template <int MODE>
 struct StageBytes {
-    static constexpr int value = MODE == MODE_LAPLACE ? 4096 : (MODE == MODE_SWEEP1 ? 4096 + 2048 : 4096 + 8 * 1024);
+    static constexpr int value = MODE == MODE_SWEEP1 ? 4096 + 2048 : 4096;
 };
 
 template <int MODE, int STAGES, int WARPS>
@@ -175,6 +184,21 @@ constexpr int sweep_smem_bytes()
 {
     // 1024 alignment slack + stages + mbarriers + metric + rsph + dss
     return 1024 + WARPS * STAGES * StageBytes<MODE>::value + ((WARPS * STAGES * 8 + 15) / 16) * 16 + METRIC_DOUBLES * 8 + 16 * 8 + 64 + 64;
+}
+
+__device__ __forceinline__ void ldg256(const void *ptr, double &a, double &b, double &c, double &d)
+{
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(ptr));
+}
+__device__ __forceinline__ double ldg64(const void *ptr)
+{
+    double a;
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(a) : "l"(ptr));
+    return a;
+}
+__device__ __forceinline__ void bulk_store_1d(void *gdst, uint32_t src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(src), "r"(bytes) : "memory");
 }
 
 template <int MODE, int STAGES, int WARPS, int MINB>
@@ -188,7 +212,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + WARPS * STAGES * SB);
     double *metric_s = reinterpret_cast<double *>(smem + WARPS * STAGES * SB + ((WARPS * STAGES * 8 + 15) / 16) * 16);
     double *rsph_s = metric_s + METRIC_DOUBLES;
-    ElemDss *dss_s = reinterpret_cast<ElemDss *>(rsph_s + 16);
+    uint32_t *dss_s = reinterpret_cast<uint32_t *>(rsph_s + 16);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int le = p.elem_list ? p.elem_list[blockIdx.x] : p.elem_first + (int)blockIdx.x;
@@ -197,7 +221,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
     for (int t = threadIdx.x; t < METRIC_DOUBLES; t += WARPS * 32) metric_s[t] = p.metric[(size_t)le * METRIC_DOUBLES + t];
     if (MODE == MODE_SWEEP2) {
         if (threadIdx.x < 16) rsph_s[threadIdx.x] = p.rsph[(size_t)le * 16 + threadIdx.x];
-        if (threadIdx.x < 16) reinterpret_cast<uint32_t *>(dss_s)[threadIdx.x] = reinterpret_cast<const uint32_t *>(p.dss + le)[threadIdx.x];
+        if (threadIdx.x >= 32 && threadIdx.x < 48) dss_s[threadIdx.x - 32] = reinterpret_cast<const uint32_t *>(p.dss + le)[threadIdx.x - 32];
     }
     if (lane == 0) {
 #pragma unroll
@@ -216,37 +240,40 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
     const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
     const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
 
-    // number of neighbour rows sweep 2 fetches per tile (CTA-uniform)
-    int nrows = 0;
+    // ---- sweep 2: the element's DSS descriptor decoded once into CTA-uniform values:
+    //      per source a base address and the byte stride between consecutive (k,q) slabs
+    const unsigned char *src_ptr[8]; // 0..3 edge rows S,N,W,E ; 4..7 diagonal corner values
+    int src_stride[8];
+    bool edge_rev[4];
+    int corner_perm[4], corner_n[4];
     if (MODE == MODE_SWEEP2) {
+        const uint32_t w_ekind = dss_s[8], w_erow = dss_s[9], w_erev = dss_s[10], w_dkind = dss_s[11], w_drow = dss_s[12], w_dpos = dss_s[13];
+        const size_t kq = (size_t)p.kq;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) nrows += (dss_s->edge_src[e] >= 0) + (dss_s->diag_src[e] >= 0);
+        for (int e = 0; e < 4; ++e) {
+            const int src = (int)dss_s[e];
+            const uint32_t kind = (w_ekind >> (8 * e)) & 0xffu, row = (w_erow >> (8 * e)) & 0xffu;
+            edge_rev[e] = ((w_erev >> (8 * e)) & 0xffu) != 0;
+            if (src < 0) { src_ptr[e] = nullptr; src_stride[e] = 0; }
+            else if (kind == SRC_TMP) { src_ptr[e] = reinterpret_cast<const unsigned char *>(p.tmp + ((size_t)src * kq * 16 + row * 4)); src_stride[e] = 128; }
+            else if (kind == SRC_WEPACK) { src_ptr[e] = reinterpret_cast<const unsigned char *>(p.wepack + ((size_t)src * 2 + row) * kq * 4); src_stride[e] = 32; }
+            else { src_ptr[e] = reinterpret_cast<const unsigned char *>(p.halo + (size_t)src * kq * 4); src_stride[e] = 32; }
+            const int dsrc = (int)dss_s[4 + e];
+            const uint32_t dkind = (w_dkind >> (8 * e)) & 0xffu, drow = (w_drow >> (8 * e)) & 0xffu, dpos = (w_dpos >> (8 * e)) & 0xffu;
+            src_stride[4 + e] = 32;
+            if (dsrc < 0) src_ptr[4 + e] = nullptr;
+            else if (dkind == SRC_WEPACK) src_ptr[4 + e] = reinterpret_cast<const unsigned char *>(p.wepack + ((size_t)dsrc * 2 + drow) * kq * 4 + dpos);
+            else src_ptr[4 + e] = reinterpret_cast<const unsigned char *>(p.halo + (size_t)dsrc * kq * 4 + dpos);
+            corner_perm[e] = (int)((dss_s[15] >> (8 * e)) & 0xffu);
+            corner_n[e] = (int)((dss_s[14] >> (8 * e)) & 0xffu);
+        }
     }
 
     auto issue_load = [&](int n, int s) {
         const int kq0 = (t0 + warp + n * WARPS) * TILE_SLABS;
         const uint32_t dst = stage0 + s * SB, bar = bar0 + s * 8;
-        mbar_expect_tx(bar, 4096u + 1024u * (uint32_t)nrows);
+        mbar_expect_tx(bar, 4096u);
         tma_load_3d(dst, MODE == MODE_SWEEP2 ? &p.map_tmp : &p.map_q, 0, kq0, le, bar);
-        if (MODE == MODE_SWEEP2) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int src = dss_s->edge_src[e];
-                if (src >= 0) {
-                    const int kind = dss_s->edge_kind[e];
-                    const CUtensorMap *m = kind == SRC_TMP ? &p.map_tmp_rows : (kind == SRC_WEPACK ? &p.map_we_rows : &p.map_halo_rows);
-                    tma_load_4d(dst + 4096 + e * 1024, m, 0, dss_s->edge_row[e], kq0, src, bar);
-                }
-            }
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const int src = dss_s->diag_src[c];
-                if (src >= 0) {
-                    const CUtensorMap *m = dss_s->diag_kind[c] == SRC_TMP ? &p.map_tmp_rows : &p.map_halo_rows;
-                    tma_load_4d(dst + 8192 + c * 1024, m, 0, dss_s->diag_row[c], kq0, src, bar);
-                }
-            }
-        }
     };
 
     if (lane == 0) {
@@ -259,7 +286,22 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
 
     for (int n = 0; n < my_n; ++n) {
         const int s = n % STAGES;
+        const int kq0 = (t0 + warp + n * WARPS) * TILE_SLABS;
         unsigned char *tile = stages + ((size_t)warp * STAGES + s) * SB;
+
+        // ---- sweep 2: fetch the neighbours' edge rows / corner values for my slab (registers)
+        double nb[4][4], dg[4];
+        if (MODE == MODE_SWEEP2) {
+            const bool live = kq0 + lane < p.kq;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                nb[e][0] = nb[e][1] = nb[e][2] = nb[e][3] = 0.0;
+                if (src_ptr[e] != nullptr && live) ldg256(src_ptr[e] + (size_t)(kq0 + lane) * src_stride[e], nb[e][0], nb[e][1], nb[e][2], nb[e][3]);
+                dg[e] = 0.0;
+                if (src_ptr[4 + e] != nullptr && live) dg[e] = ldg64(src_ptr[4 + e] + (size_t)(kq0 + lane) * 32);
+            }
+        }
+
         mbar_wait(bar0 + s * 8, (uint32_t)((n / STAGES) & 1));
 
         double v[16];
@@ -273,41 +315,30 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
 
         if (MODE == MODE_SWEEP2) {
             // ---- DSS: add the neighbours' coincident values (edgeVunpack), then * rspheremp
-            double nb[4][4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                if (dss_s->edge_src[e] >= 0) {
-                    const double2 a = *reinterpret_cast<const double2 *>(tile + 4096 + e * 1024 + lane * 32);
-                    const double2 b = *reinterpret_cast<const double2 *>(tile + 4096 + e * 1024 + lane * 32 + 16);
-                    const bool rev = dss_s->edge_rev[e] != 0;
-                    nb[e][0] = rev ? b.y : a.x;
-                    nb[e][1] = rev ? b.x : a.y;
-                    nb[e][2] = rev ? a.y : b.x;
-                    nb[e][3] = rev ? a.x : b.y;
-                } else {
-                    nb[e][0] = nb[e][1] = nb[e][2] = nb[e][3] = 0.0;
+                if (edge_rev[e]) { // neighbour's edge runs the other way
+                    double t = nb[e][0]; nb[e][0] = nb[e][3]; nb[e][3] = t;
+                    t = nb[e][1]; nb[e][1] = nb[e][2]; nb[e][2] = t;
                 }
             }
             // mid-edge points: exactly two contributors, a+b is order independent
-            if (dss_s->edge_src[EDGE_S] >= 0) { v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2]; }
-            if (dss_s->edge_src[EDGE_N] >= 0) { v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2]; }
-            if (dss_s->edge_src[EDGE_W] >= 0) { v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2]; }
-            if (dss_s->edge_src[EDGE_E] >= 0) { v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2]; }
+            if (src_ptr[EDGE_S] != nullptr) { v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2]; }
+            if (src_ptr[EDGE_N] != nullptr) { v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2]; }
+            if (src_ptr[EDGE_W] != nullptr) { v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2]; }
+            if (src_ptr[EDGE_E] != nullptr) { v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2]; }
             // corners: up to four contributors, summed in ascending global point order
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const int pt = c == 0 ? 0 : (c == 1 ? 3 : (c == 2 ? 12 : 15));
-                double cv[4];
-                cv[0] = v[pt];
-                cv[1] = nb[c < 2 ? EDGE_S : EDGE_N][(c & 1) ? 3 : 0];
-                cv[2] = nb[(c & 1) ? EDGE_E : EDGE_W][c < 2 ? 0 : 3];
-                cv[3] = 0.0;
-                if (dss_s->diag_src[c] >= 0)
-                    cv[3] = *reinterpret_cast<const double *>(tile + 8192 + c * 1024 + lane * 32 + dss_s->diag_pos[c] * 8);
-                const int perm = dss_s->corner_perm[c], cn = dss_s->corner_n[c];
+                const double cv0 = v[pt];
+                const double cv1 = nb[c < 2 ? EDGE_S : EDGE_N][(c & 1) ? 3 : 0];
+                const double cv2 = nb[(c & 1) ? EDGE_E : EDGE_W][c < 2 ? 0 : 3];
+                const double cv3 = dg[c];
+                const int perm = corner_perm[c], cn = corner_n[c];
                 auto pick = [&](int k) {
                     const int w = (perm >> (2 * k)) & 3;
-                    return w == 0 ? cv[0] : (w == 1 ? cv[1] : (w == 2 ? cv[2] : cv[3]));
+                    return w == 0 ? cv0 : (w == 1 ? cv1 : (w == 2 ? cv2 : cv3));
                 };
                 double sum = pick(0);
                 if (cn > 1) sum = sum + pick(1);
@@ -328,24 +359,25 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
         if (MODE == MODE_SWEEP1) {
-            // W/E edge pack (the strided edges a neighbour cannot fetch as one 32-byte row), SWIZZLE_64B staging:
-            // 16-byte chunk c of 64-byte row r sits at byte (64 r + 16 c) ^ (((64 r + 16 c) >> 7 & 3) << 4)
-            unsigned char *we = tile + 4096;
-            const uint32_t o = lane * 64;
-            const uint32_t x = ((o >> 7) & 3) << 4;
-            *reinterpret_cast<double2 *>(we + ((o + 0) ^ x)) = make_double2(v[0], v[4]);
-            *reinterpret_cast<double2 *>(we + ((o + 16) ^ x)) = make_double2(v[8], v[12]);
-            *reinterpret_cast<double2 *>(we + ((o + 32) ^ x)) = make_double2(v[3], v[7]);
-            *reinterpret_cast<double2 *>(we + ((o + 48) ^ x)) = make_double2(v[11], v[15]);
+            // W/E edge pack staging: [side][lane][4]
+            unsigned char *we = tile + 4096 + lane * 32;
+            *reinterpret_cast<double2 *>(we) = make_double2(v[0], v[4]);
+            *reinterpret_cast<double2 *>(we + 16) = make_double2(v[8], v[12]);
+            *reinterpret_cast<double2 *>(we + 1024) = make_double2(v[3], v[7]);
+            *reinterpret_cast<double2 *>(we + 1024 + 16) = make_double2(v[11], v[15]);
         }
         fence_proxy_async();
         __syncwarp();
 
         if (lane == 0) {
-            const int kq0 = (t0 + warp + n * WARPS) * TILE_SLABS;
             const uint32_t src = stage0 + s * SB;
             tma_store_3d(MODE == MODE_SWEEP1 ? &p.map_tmp : &p.map_q, 0, kq0, le, src);
-            if (MODE == MODE_SWEEP1) tma_store_3d(&p.map_we, 0, kq0, le, src + 4096);
+            if (MODE == MODE_SWEEP1) {
+                const uint32_t nvalid = (uint32_t)min(TILE_SLABS, p.kq - kq0);
+                double *w = p.wepack + (((size_t)le * 2) * p.kq + kq0) * 4;
+                bulk_store_1d(w, src + 4096, nvalid * 32u);
+                bulk_store_1d(w + (size_t)p.kq * 4, src + 4096 + 1024, nvalid * 32u);
+            }
             bulk_commit();
             // refill the stage tile n-1 used, once its store has finished reading shared memory
             if (n >= 1 && n - 1 + STAGES < my_n) {
@@ -360,20 +392,17 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
 // kernel configurations: (STAGES, WARPS, MINB)
 #define BWK_CFG_LAPLACE 3, 4, 3
 #define BWK_CFG_SWEEP1 3, 4, 3
-#define BWK_CFG_SWEEP2 2, 4, 2
+#define BWK_CFG_SWEEP2 3, 4, 3
 
 template <int MODE>
-struct ModeWarps;
-template <>
-struct ModeWarps<MODE_LAPLACE> { static constexpr int value = 4; };
-template <>
-struct ModeWarps<MODE_SWEEP1> { static constexpr int value = 4; };
-template <>
-struct ModeWarps<MODE_SWEEP2> { static constexpr int value = 4; };
+struct ModeWarps {
+    static constexpr int value = 4;
+};
 
 SweepGeometry choose_geometry(int kq, int64_t nelem, int mode)
 {
-    const int warps = mode == MODE_LAPLACE ? ModeWarps<MODE_LAPLACE>::value : (mode == MODE_SWEEP1 ? ModeWarps<MODE_SWEEP1>::value : ModeWarps<MODE_SWEEP2>::value);
+    (void)mode;
+    const int warps = 4;
     const int ntiles = (kq + TILE_SLABS - 1) / TILE_SLABS;
     // enough CTAs for ~8 per SM, but at most ~6 tiles per warp (short CTAs balance better, and in
     // sweep 2 a short unit keeps a neighbour's rows L2-resident until its own CTA reads them)
@@ -503,7 +532,7 @@ __global__ void edge_pack_kernel(const double *__restrict__ tmp, const double *_
     const int slab = x >> 1, half = x & 1;
     const int64_t e = row_elem[r];
     const int row = row_id[r];
-    const double *src = row < 4 ? tmp + ((e * kq + slab) * 16 + row * 4 + half * 2) : wepack + ((e * kq + slab) * 8 + (row - 4) * 4 + half * 2);
+    const double *src = row < 4 ? tmp + ((e * kq + slab) * 16 + row * 4 + half * 2) : wepack + (((e * 2 + (row - 4)) * kq + slab) * 4 + half * 2);
     *reinterpret_cast<double2 *>(sendbuf + (((int64_t)r * kq + slab) * 4 + half * 2)) = *reinterpret_cast<const double2 *>(src);
 }
 

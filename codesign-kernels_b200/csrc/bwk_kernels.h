@@ -21,14 +21,13 @@ enum SweepMode : int {
 // Everything a sweep launch needs.  Tensor maps are passed by value (__grid_constant__).
 struct SweepParams {
     CUtensorMap map_q;      // qtens   as {16, KQ, nelem}, box {16,32,1}, SWIZZLE_128B
-    CUtensorMap map_tmp;    // tmp     same shape
-    CUtensorMap map_we;     // wepack  as {8, KQ, nelem},  box {8,32,1},  SWIZZLE_64B
-    CUtensorMap map_tmp_rows;  // tmp    as {4, 4, KQ, nelem}, box {4,1,32,1}
-    CUtensorMap map_we_rows;   // wepack as {4, 2, KQ, nelem}, box {4,1,32,1}
-    CUtensorMap map_halo_rows; // halo   as {4, 1, KQ, nrows}, box {4,1,32,1}
+    CUtensorMap map_tmp;    // tmp     same shape (sweep-1 output)
     const double *metric;   // [nelem][64] folded metric
     const double *rsph;     // [nelem][16]
     const ElemDss *dss;     // [nelem]
+    const double *tmp;      // sweep-1 output, natural layout (neighbours' S/N edge rows are read from here)
+    double *wepack;         // W/E edge pack [nelem][2][KQ][4]: the i=1 / i=np columns, kq-contiguous
+    const double *halo;     // received edge rows [nrows][KQ][4]
     const int32_t *elem_list; // optional list of local element indices, else contiguous from elem_first
     int elem_first;         // 0-based first local element (when elem_list == nullptr)
     int elem_count;         // grid x

@@ -188,7 +188,7 @@ void sources_of(const ElemTopo &T, std::vector<RowRef> *out)
     for (int ed = 0; ed < 4; ++ed)
         if (T.edge[ed].elem >= 0) out->push_back({T.edge[ed].elem, edge_rowid(T.edge[ed].edge)});
     for (int c = 0; c < 4; ++c)
-        if (T.diag[c].elem >= 0) out->push_back({T.diag[c].elem, T.diag[c].pt / 4 == 0 ? ROW_S : ROW_N});
+        if (T.diag[c].elem >= 0) out->push_back({T.diag[c].elem, T.diag[c].pt % 4 == 0 ? ROW_W : ROW_E});
 }
 
 } // namespace
@@ -294,9 +294,9 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
             const DiagNbr &dg = T.diag[c];
             d.diag_src[c] = -1;
             if (dg.elem >= 0) {
-                d.diag_pos[c] = (uint8_t)(dg.pt % 4);
-                const int row = dg.pt / 4 == 0 ? ROW_S : ROW_N;
-                if (dg.elem >= lo && dg.elem < hi) { d.diag_kind[c] = SRC_TMP; d.diag_row[c] = (uint8_t)row; d.diag_src[c] = (int32_t)(dg.elem - lo); }
+                d.diag_pos[c] = (uint8_t)(dg.pt / 4); // position along the W/E column = j
+                const int row = dg.pt % 4 == 0 ? ROW_W : ROW_E;
+                if (dg.elem >= lo && dg.elem < hi) { d.diag_kind[c] = SRC_WEPACK; d.diag_row[c] = (uint8_t)(row == ROW_W ? 0 : 1); d.diag_src[c] = (int32_t)(dg.elem - lo); }
                 else { d.diag_kind[c] = SRC_HALO; d.diag_row[c] = 0; d.diag_src[c] = halo_slot({dg.elem, row}); is_dependent[(size_t)le] = 1; }
             }
             // summation order: ascending global point id (== the oracle's order)
