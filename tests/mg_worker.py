@@ -1,0 +1,91 @@
+"""Worker for the multi-rank tests (launched by torch.distributed.run).
+
+mode "gpu":  one rank per GPU; full biharmonic through libbwk_b200 with NCCL halo exchange;
+             every rank saves its block of the result.
+mode "cpu":  gloo only, no GPU: the ranks exchange exactly the rows the plan lists (the wire
+             format of bwk's halo) and evaluate the plan's gather on the host.
+"""
+import os
+import sys
+
+import numpy as np
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    mode, ne, nlev, qsize, outdir = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), sys.argv[5]
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import codesign_kernels_b200 as bwk
+
+    n = 6 * ne * ne
+    first, count = bwk.partition(n, rank, world)
+    if mode == "gpu":
+        import torch
+
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        ku = bwk.KernelUtils(count, nlev, qsize).allocate_data(host_arrays=False)
+        idb = [bwk.KernelUtils.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(idb, src=0)
+        bwk.KernelUtils.comm_init(rank, world, idb[0])
+        ku.initialize_data_device(n, first)
+        ku.set_topology_cubed_sphere(ne, first)
+        for rep in range(2):  # twice: the halo buffers are reused across steps
+            ku.initialize_data_device(n, first)
+            ku.run_biharmonic_device()
+            ku.sync()
+        np.save(os.path.join(outdir, f"dev_{rank}.npy"), ku.download_elements(0, count))
+        dist.barrier()
+        ku.finalize()
+    else:
+        g = bwk.cubed_sphere_gdof(ne)
+        pl = bwk.Plan(n, g, rank, world)
+        rng = np.random.default_rng(1234)
+        field = rng.standard_normal(16 * n)  # same on every rank
+        mine = np.full(16 * n, np.nan)
+        mine[16 * first : 16 * (first + count)] = field[16 * first : 16 * (first + count)]
+
+        def row_of(arr, e, row):
+            s = arr[16 * e : 16 * e + 16]
+            return s[4 * row : 4 * row + 4].copy() if row < 4 else s[(0 if row == 4 else 3) :: 4].copy()
+
+        import torch
+
+        reqs, recvbufs = [], {}
+        for p in range(world):
+            if p == rank:
+                continue
+            se, sr = pl.send_list(p)
+            if se.size:
+                buf = torch.from_numpy(np.concatenate([row_of(mine, int(e), int(r)) for e, r in zip(se, sr)]))
+                reqs.append(dist.isend(buf, p))
+            re_, rr = pl.recv_list(p)
+            if re_.size:
+                recvbufs[p] = torch.empty(4 * re_.size, dtype=torch.float64)
+                reqs.append(dist.irecv(recvbufs[p], p))
+        for r in reqs:
+            r.wait()
+        # scatter the received rows into the (otherwise NaN) global array: only those entries may be read
+        for p, buf in recvbufs.items():
+            re_, rr = pl.recv_list(p)
+            b = buf.numpy().reshape(-1, 4)
+            for k, (e, row) in enumerate(zip(re_, rr)):
+                s = mine[16 * int(e) : 16 * int(e) + 16]
+                if row < 4:
+                    s[4 * row : 4 * row + 4] = b[k]
+                else:
+                    s[(0 if row == 4 else 3) :: 4] = b[k]
+        out = pl.apply_host(mine)
+        assert not np.isnan(out).any(), "the plan read a value that was neither local nor received"
+        np.save(os.path.join(outdir, f"cpu_{rank}.npy"), out)
+        if rank == 0:
+            np.save(os.path.join(outdir, "field.npy"), field)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
