@@ -284,7 +284,7 @@ def main():
     roofline = None
     kernels = {}
     if world == 1:
-        for phase, name in ((1, "sweep1 (laplace + edge pack)"), (2, "sweep2 (unpack + rspheremp + laplace)")):
+        for phase, name in ((1, "sweep1 (laplace -> tmp)"), (2, "sweep2 (strip DSS unpack + rspheremp + laplace)")):
             ms = []
             for _ in range(max(3, min(args.steps, 10))):
                 ku.initialize_data_device(nglob, first)
@@ -335,6 +335,10 @@ def main():
             d = 16 + 144 * (first + np.arange(count, dtype=np.int64))[:, None] + np.arange(144, dtype=np.int64)[None, :]
             helem.view(np.float64).reshape(count, 144)[...] = tab[d % 131072]
             hderiv["Dvv"] = tab[:16].reshape(4, 4)
+            if world > 1:
+                # with host-supplied element records a rank cannot see its neighbours' spheremp:
+                # hand the library its rspheremp explicitly (HOMME keeps elem%rspheremp per element)
+                ku.set_rspheremp(ku.get_rspheremp())
             tot = 0.0
             nst = max(1, args.e2e_steps)
             for i in range(1 + nst):

@@ -88,6 +88,7 @@ def lib():
         "bwk_plan_apply_host": [p, p, p],
         "bwk_plan_send_list": [p, i32, p, p],
         "bwk_plan_recv_list": [p, i32, p, p],
+        "bwk_plan_strip_list": [p, i32, p, p, p],
     }
     for name, args in sig.items():
         f = getattr(L, name)
@@ -107,6 +108,8 @@ def lib():
     for name in ("bwk_plan_recv_rows", "bwk_plan_send_rows"):
         getattr(L, name).restype = i64
         getattr(L, name).argtypes = [p, i32]
+    L.bwk_plan_strip_count.restype = i64
+    L.bwk_plan_strip_count.argtypes = [p, i32]
     _lib = L
     return L
 
@@ -168,6 +171,17 @@ class Plan:
 
     def recv_list(self, peer):
         return self._list(peer, "recv")
+
+    def strips(self, which=0):
+        """(first local element, count) of every sweep-2 strip; which 0 all, 1 dependent, 2 independent."""
+        n = lib().bwk_plan_strip_count(self._h, which)
+        f = np.empty(n, dtype=np.int32)
+        c = np.empty(n, dtype=np.int32)
+        r = np.empty(n, dtype=np.int32)
+        if n:
+            _ck(lib().bwk_plan_strip_list(self._h, which, _ptr(f), _ptr(c), _ptr(r)))
+        self.strip_regular = r
+        return f, c
 
     def apply_host(self, field_global):
         f = np.ascontiguousarray(field_global, dtype=np.float64)

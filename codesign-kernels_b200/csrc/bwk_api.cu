@@ -17,6 +17,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -92,14 +93,16 @@ struct Ctx {
     int nelem = 0, nlev = 0, qsize = 0, kq = 0;
     size_t q_doubles = 0;
     cudaStream_t s_main = nullptr, s_comm = nullptr, s_h2d = nullptr, s_d2h = nullptr;
-    double *d_q = nullptr, *d_tmp = nullptr, *d_we = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
+    double *d_q = nullptr, *d_tmp = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
     double *d_save = nullptr, *d_table = nullptr, *d_partials = nullptr, *d_halo = nullptr, *d_send = nullptr, *d_dummy = nullptr;
     double *h_partials = nullptr;
     ElemDss *d_dss = nullptr;
     int32_t *d_boundary = nullptr, *d_interior = nullptr, *d_dependent = nullptr, *d_independent = nullptr;
     int32_t *d_send_elem = nullptr, *d_send_row = nullptr;
+    int32_t *d_strips_all = nullptr, *d_strips_dep = nullptr, *d_strips_indep = nullptr;
+    StripReg *d_reg_all = nullptr, *d_reg_dep = nullptr, *d_reg_indep = nullptr;
     std::vector<int64_t> send_offset; // per peer, rows
-    bool have_metric = false, have_topology = false, have_rsph = false, have_maps2 = false;
+    bool have_metric = false, have_topology = false, have_rsph = false, rsph_user = false;
     SweepParams sp{};
     Plan plan;
     std::vector<double> h_spheremp; // spheremp of the local elements (16 each), for rspheremp
@@ -168,7 +171,8 @@ int check_range(int nets, int nete)
     return 0;
 }
 
-// launch one sweep over local elements [first, first+count) or over a device list
+// launch one element-local sweep (MODE_LAPLACE / MODE_SWEEP1) over local elements
+// [first, first+count) or over a device list
 int sweep(int mode, int first, int count, const int32_t *list, cudaStream_t st)
 {
     if (count <= 0) return 0;
@@ -180,6 +184,22 @@ int sweep(int mode, int first, int count, const int32_t *list, cudaStream_t st)
     p.elem_first = first;
     p.elem_count = count;
     CK(launch_sweep(mode, p, st));
+    g.launches++;
+    return 0;
+}
+
+// launch sweep 2 over `count` strips of a device strip list
+int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaStream_t st)
+{
+    if (count <= 0) return 0;
+    SweepParams p = g.sp;
+    const SweepGeometry geo = choose_geometry(g.kq, count, MODE_SWEEP2);
+    p.tiles_per_unit = geo.tiles_per_unit;
+    p.units = geo.units;
+    p.strips = d_strips;
+    p.strip_reg = d_reg;
+    p.strip_count = (int)count;
+    CK(launch_sweep(MODE_SWEEP2, p, st));
     g.launches++;
     return 0;
 }
@@ -206,7 +226,7 @@ int upload_metric(const bwk_element_t *elem, const bwk_derivative_t *deriv, cuda
         g.h_spheremp.resize((size_t)16 * g.nelem);
         const double *e = reinterpret_cast<const double *>(elem);
         for (int64_t ie = 0; ie < g.nelem; ++ie) std::memcpy(&g.h_spheremp[(size_t)16 * ie], e + ie * ELEM_DOUBLES + 64, 16 * sizeof(double));
-        g.have_rsph = false;
+        if (!g.rsph_user) g.have_rsph = false; // a caller-supplied rspheremp (bwk_set_rspheremp) stays in force
     }
     if (deriv) CK(set_dvv(&deriv->Dvv[0][0], st));
     return 0;
@@ -281,6 +301,16 @@ int upload_list(const std::vector<int32_t> &v, int32_t **d)
     return 0;
 }
 
+int upload_regs(const std::vector<StripReg> &v, StripReg **d)
+{
+    free_dev(*d);
+    *d = nullptr;
+    if (v.empty()) return 0;
+    CK(cudaMalloc(d, sizeof(StripReg) * v.size()));
+    CK(cudaMemcpy(*d, v.data(), sizeof(StripReg) * v.size(), cudaMemcpyHostToDevice));
+    return 0;
+}
+
 int install_plan(Plan &&pl)
 {
     if (!pl.error.empty()) return fail("unsupported mesh: %s", pl.error.c_str());
@@ -289,13 +319,14 @@ int install_plan(Plan &&pl)
     const Plan &P = g.plan;
     const int64_t kq = g.kq;
     if (!g.d_tmp) CK(cudaMalloc(&g.d_tmp, sizeof(double) * g.q_doubles));
-    if (!g.d_we) CK(cudaMalloc(&g.d_we, sizeof(double) * g.q_doubles / 2));
     if (!g.d_rsph) CK(cudaMalloc(&g.d_rsph, sizeof(double) * 16 * g.nelem));
     free_dev(g.d_dss);
     CK(cudaMalloc(&g.d_dss, sizeof(ElemDss) * (size_t)g.nelem));
     CK(cudaMemcpy(g.d_dss, P.dss.data(), sizeof(ElemDss) * (size_t)g.nelem, cudaMemcpyHostToDevice));
     if (upload_list(P.boundary_list, &g.d_boundary) || upload_list(P.interior_list, &g.d_interior) || upload_list(P.dependent_list, &g.d_dependent) ||
-        upload_list(P.independent_list, &g.d_independent))
+        upload_list(P.independent_list, &g.d_independent) || upload_list(P.strips_all, &g.d_strips_all) ||
+        upload_list(P.strips_dependent, &g.d_strips_dep) || upload_list(P.strips_independent, &g.d_strips_indep) ||
+        upload_regs(P.reg_all, &g.d_reg_all) || upload_regs(P.reg_dependent, &g.d_reg_dep) || upload_regs(P.reg_independent, &g.d_reg_indep))
         return 1;
     // halo (receive) buffer and send buffer, rows of [KQ][4] doubles
     const int64_t nrecv = P.recv_offset.back();
@@ -315,13 +346,19 @@ int install_plan(Plan &&pl)
 
     // tensor map of the sweep-1 output; everything else sweep 2 reads goes through plain pointers
     if (make_slab_map(&g.sp.map_tmp, g.d_tmp, g.kq, g.nelem)) return 1;
+    {
+        const uint64_t dims[3] = {16, (uint64_t)g.kq, (uint64_t)g.nelem};
+        const uint64_t str[2] = {128, (uint64_t)g.kq * 128};
+        const uint32_t box[3] = {4, TILE_SLABS, 1};
+        if (make_map(&g.sp.map_rows, g.d_tmp, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+    }
     g.sp.tmp = g.d_tmp;
-    g.sp.wepack = g.d_we;
     g.sp.halo = g.d_halo;
     g.sp.dss = g.d_dss;
     g.sp.rsph = g.d_rsph;
     g.have_topology = true;
     g.have_rsph = false;
+    g.rsph_user = false;
     return 0;
 }
 
@@ -334,7 +371,7 @@ int exchange_halo()
     if (P.nranks == 1) return 0;
     if (!g.comm) return fail("topology spans %d ranks but bwk_comm_init was not called", P.nranks);
     if (nsend > 0) {
-        CK(launch_edge_pack(g.d_tmp, g.d_we, g.d_send_elem, g.d_send_row, nsend, g.kq, g.d_send, g.s_comm));
+        CK(launch_edge_pack(g.d_tmp, g.d_send_elem, g.d_send_row, nsend, g.kq, g.d_send, g.s_comm));
         g.launches += (nsend + 65534) / 65535;
     }
     const size_t row_doubles = (size_t)4 * g.kq;
@@ -358,7 +395,7 @@ int biharmonic_device()
     const Plan &P = g.plan;
     if (P.nranks == 1) {
         if (sweep(MODE_SWEEP1, 0, g.nelem, nullptr, g.s_main)) return 1;
-        return sweep(MODE_SWEEP2, 0, g.nelem, nullptr, g.s_main);
+        return sweep2(g.d_strips_all, g.d_reg_all, (int64_t)P.strips_all.size(), g.s_main);
     }
     // boundary elements first so that their edge rows can travel while the interior is computed
     if (sweep(MODE_SWEEP1, 0, (int)P.boundary_list.size(), g.d_boundary, g.s_main)) return 1;
@@ -367,9 +404,9 @@ int biharmonic_device()
     if (exchange_halo()) return 1;
     CK(cudaEventRecord(g.ev_halo, g.s_comm));
     if (sweep(MODE_SWEEP1, 0, (int)P.interior_list.size(), g.d_interior, g.s_main)) return 1;
-    if (sweep(MODE_SWEEP2, 0, (int)P.independent_list.size(), g.d_independent, g.s_main)) return 1;
+    if (sweep2(g.d_strips_indep, g.d_reg_indep, (int64_t)P.strips_independent.size(), g.s_main)) return 1;
     CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
-    return sweep(MODE_SWEEP2, 0, (int)P.dependent_list.size(), g.d_dependent, g.s_main);
+    return sweep2(g.d_strips_dep, g.d_reg_dep, (int64_t)P.strips_dependent.size(), g.s_main);
 }
 
 // chunk boundaries (in elements) for the host<->device pipelines
@@ -382,6 +419,21 @@ std::vector<int> make_chunks(int first0, int count)
     std::vector<int> b;
     for (int e = first0; e < first0 + count; e += per) b.push_back(e);
     b.push_back(first0 + count);
+    return b;
+}
+
+// the same for sweep 2: boundaries in STRIPS of strips_all (strips tile [0,nelem) in ascending order)
+std::vector<int> make_strip_chunks(const std::vector<int> &elem_bounds)
+{
+    const std::vector<int32_t> &S = g.plan.strips_all;
+    std::vector<int> b;
+    size_t si = 0;
+    for (size_t c = 0; c + 1 < elem_bounds.size(); ++c) {
+        while (si < S.size() && strip_first(S[si]) < elem_bounds[c]) ++si; // first strip starting at or after the boundary
+        if (b.empty() || (int)si > b.back()) b.push_back((int)si);
+    }
+    if (b.empty() || b.front() != 0) b.insert(b.begin(), 0);
+    b.push_back((int)S.size());
     return b;
 }
 
@@ -409,6 +461,7 @@ int bwk_init(int nelemd, int nlev, int qsize)
     if (g.inited) return fail("bwk_init called twice without bwk_finalize");
     if (nelemd < 1 || nlev < 1 || qsize < 1) return fail("bad sizes nelemd=%d nlev=%d qsize=%d", nelemd, nlev, qsize);
     if ((int64_t)nlev * qsize > 0x7fffffff / 64) return fail("nlev*qsize too large");
+    if (nelemd >= (1 << 28)) return fail("nelemd too large (strip ids are packed into 32 bits)");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev < 1) return fail("no CUDA device available (%s); libbwk_b200 has no CPU fallback", cudaGetErrorString(e));
@@ -418,6 +471,8 @@ int bwk_init(int nelemd, int nlev, int qsize)
     CK(cudaGetDeviceProperties(&prop, dev));
     if (prop.major != 10) return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", dev, prop.major, prop.minor);
     g = Ctx();
+    if (const char *e = std::getenv("BWK_SWEEP2_TPU")) set_sweep2_tiles_per_unit(std::atoi(e));
+    if (const char *e = std::getenv("BWK_DBG")) g.sp.dbg = std::atoi(e);
     g.nelem = nelemd;
     g.nlev = nlev;
     g.qsize = qsize;
@@ -450,10 +505,10 @@ int bwk_finalize(void)
     if (!g.inited) return 0;
     cudaDeviceSynchronize();
     if (g.comm && g_nccl.CommDestroy) g_nccl.CommDestroy(g.comm);
-    free_dev(g.d_q); free_dev(g.d_tmp); free_dev(g.d_we); free_dev(g.d_elem); free_dev(g.d_metric); free_dev(g.d_rsph);
+    free_dev(g.d_q); free_dev(g.d_tmp); free_dev(g.d_elem); free_dev(g.d_metric); free_dev(g.d_rsph);
     free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
     free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);
-    free_dev(g.d_send_elem); free_dev(g.d_send_row);
+    free_dev(g.d_send_elem); free_dev(g.d_send_row); free_dev(g.d_strips_all); free_dev(g.d_strips_dep); free_dev(g.d_strips_indep); free_dev(g.d_reg_all); free_dev(g.d_reg_dep); free_dev(g.d_reg_indep);
     if (g.h_partials) cudaFreeHost(g.h_partials);
     for (cudaEvent_t e : g.chunk_up) cudaEventDestroy(e);
     for (cudaEvent_t e : g.chunk_done) cudaEventDestroy(e);
@@ -569,10 +624,15 @@ int bwk_biharmonic_wk_scalar_full(const bwk_element_t *elem, double *qtens, cons
         CK(cudaEventRecord(g.ev_halo, g.s_comm));
         CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
     }
-    // phase B: sweep 2 of chunk c  ||  download chunk c-1
-    for (size_t c = 0; c < nch; ++c) {
-        const size_t off = es * (size_t)b[c], n = es * (size_t)(b[c + 1] - b[c]);
-        if (sweep(MODE_SWEEP2, b[c], b[c + 1] - b[c], nullptr, g.s_main)) return 1;
+    // phase B: sweep 2 of chunk c  ||  download chunk c-1   (chunks = runs of whole strips)
+    const std::vector<int> sb = make_strip_chunks(b);
+    const std::vector<int32_t> &S = g.plan.strips_all;
+    if (ensure_chunk_events(sb.size())) return 1;
+    for (size_t c = 0; c + 1 < sb.size(); ++c) {
+        const int e0 = strip_first(S[(size_t)sb[c]]);
+        const int e1 = sb[c + 1] < (int)S.size() ? strip_first(S[(size_t)sb[c + 1]]) : g.nelem;
+        const size_t off = es * (size_t)e0, n = es * (size_t)(e1 - e0);
+        if (sweep2(g.d_strips_all + sb[c], g.d_reg_all + sb[c], sb[c + 1] - sb[c], g.s_main)) return 1;
         CK(cudaEventRecord(g.chunk_done[c], g.s_main));
         CK(cudaStreamWaitEvent(g.s_d2h, g.chunk_done[c], 0));
         CK(cudaMemcpyAsync(qtens + off, g.d_q + off, sizeof(double) * n, cudaMemcpyDeviceToHost, g.s_d2h));
@@ -770,6 +830,7 @@ int bwk_set_rspheremp(const double *rs)
     CK(cudaMemcpy(g.d_rsph, rs, sizeof(double) * 16 * g.nelem, cudaMemcpyHostToDevice));
     g.sp.rsph = g.d_rsph;
     g.have_rsph = true;
+    g.rsph_user = true;
     return 0;
 }
 
@@ -795,7 +856,7 @@ int bwk_run_biharmonic_phase(int phase)
     if (g.plan.nranks != 1) return fail("bwk_run_biharmonic_phase is a single-rank profiling hook");
     if (compute_rspheremp()) return 1;
     if (phase == 1) return sweep(MODE_SWEEP1, 0, g.nelem, nullptr, g.s_main);
-    if (phase == 2) return sweep(MODE_SWEEP2, 0, g.nelem, nullptr, g.s_main);
+    if (phase == 2) return sweep2(g.d_strips_all, g.d_reg_all, (int64_t)g.plan.strips_all.size(), g.s_main);
     return fail("phase must be 1 or 2");
 }
 
@@ -893,6 +954,27 @@ int bwk_plan_send_list(const bwk_plan_t *h, int peer, int64_t *elem, int32_t *ro
 int bwk_plan_recv_list(const bwk_plan_t *h, int peer, int64_t *elem, int32_t *row) { return copy_list(h->p.recv[(size_t)peer], elem, row); }
 int64_t bwk_plan_boundary_elems(const bwk_plan_t *h) { return (int64_t)h->p.boundary_list.size(); }
 int64_t bwk_plan_dependent_elems(const bwk_plan_t *h) { return (int64_t)h->p.dependent_list.size(); }
+static const std::vector<int32_t> *strip_vec(const bwk_plan_t *h, int which)
+{
+    return which == 0 ? &h->p.strips_all : which == 1 ? &h->p.strips_dependent : which == 2 ? &h->p.strips_independent : nullptr;
+}
+int64_t bwk_plan_strip_count(const bwk_plan_t *h, int which)
+{
+    const std::vector<int32_t> *v = strip_vec(h, which);
+    return v ? (int64_t)v->size() : -1;
+}
+int bwk_plan_strip_list(const bwk_plan_t *h, int which, int32_t *first, int32_t *count, int32_t *regular)
+{
+    const std::vector<int32_t> *v = strip_vec(h, which);
+    if (!v) return fail("which must be 0, 1 or 2");
+    const std::vector<StripReg> &r = which == 0 ? h->p.reg_all : which == 1 ? h->p.reg_dependent : h->p.reg_independent;
+    for (size_t i = 0; i < v->size(); ++i) {
+        first[i] = strip_first((*v)[i]);
+        count[i] = strip_count((*v)[i]);
+        if (regular) regular[i] = r[i].regular;
+    }
+    return 0;
+}
 int bwk_plan_apply_host(const bwk_plan_t *h, const double *field, double *out)
 {
     for (int64_t le = 0; le < h->p.count; ++le) gather_elem_host(h->p, le, field, out + 16 * le);

@@ -12,25 +12,44 @@ namespace bwk {
 enum : int { ROW_S = 0, ROW_N = 3, ROW_W = 4, ROW_E = 5 };
 // Edge order used everywhere: S (j=1), N (j=4), W (i=1), E (i=4).
 enum : int { EDGE_S = 0, EDGE_N = 1, EDGE_W = 2, EDGE_E = 3 };
-// Where a source row lives on the device.
-enum : int { SRC_TMP = 0, SRC_WEPACK = 1, SRC_HALO = 2 };
+// Where a source row lives on the device: a natural j-row of a slab in the sweep-1 output (4
+// contiguous doubles), an i-column of such a slab (4 doubles, 32-byte stride), or a packed row of
+// the halo buffer received from another rank.
+enum : int { SRC_TMP = 0, SRC_TMPCOL = 1, SRC_HALO = 2 };
 
 // Per-element DSS gather descriptor consumed by the sweep-2 kernel (64 bytes).
 // Replaces HOMME's edge putmap/getmap for this path (upstream edge_mod_base.F90; the
 // reference itself has no DSS, only the comment F90:518-519).
 struct ElemDss {
-    int32_t edge_src[4];    // S,N,W,E: local element index (SRC_TMP/SRC_WEPACK) or halo row slot; -1 = no neighbour
+    int32_t edge_src[4];    // S,N,W,E: local element index (SRC_TMP/SRC_TMPCOL) or halo row slot; -1 = no neighbour
     int32_t diag_src[4];    // corners (1,1),(4,1),(1,4),(4,4): same encoding; -1 = no diagonal contributor
     uint8_t edge_kind[4];   // SRC_*
-    uint8_t edge_row[4];    // natural row 0/3 (SRC_TMP), side 0=W/1=E (SRC_WEPACK), 0 (SRC_HALO)
+    uint8_t edge_row[4];    // natural row 0/3 (SRC_TMP), side 0=W/1=E (SRC_TMPCOL), 0 (SRC_HALO)
     uint8_t edge_rev[4];    // 1 = neighbour's edge runs in the opposite direction
-    uint8_t diag_kind[4];   // SRC_WEPACK or SRC_HALO: corner values are the ends of the W/E edge rows
-    uint8_t diag_row[4];    // side 0=W/1=E (SRC_WEPACK) or 0 (SRC_HALO)
+    uint8_t diag_kind[4];   // SRC_TMPCOL or SRC_HALO: corner values are the ends of the W/E edge columns
+    uint8_t diag_row[4];    // side 0=W/1=E (SRC_TMPCOL) or 0 (SRC_HALO)
     uint8_t diag_pos[4];    // position (0 or 3) of the corner value inside that row
     uint8_t corner_n[4];    // number of contributors to the corner node (own included)
     uint8_t corner_perm[4]; // summation order, 2 bits per slot: 0 own, 1 S/N-edge nbr, 2 W/E-edge nbr, 3 diagonal
 };
 static_assert(sizeof(ElemDss) == 64, "ElemDss must be 64 bytes");
+
+// Gather sources of a REGULAR strip: every member is a face-interior element of a row-major
+// structured patch -- all neighbours local, none reversed, S/N neighbours face us with their N/S
+// rows, strip-end W/E neighbours with their E/W columns, four contributors per corner in the
+// standard order, and the diagonal contributors of interior corners are the S/N neighbours of the
+// strip mates.  Such a strip runs the fully asynchronous (cp.async-staged) sweep-2 path; any other
+// strip runs the generic descriptor-driven path.  Element indices are local.
+struct StripReg {
+    int32_t regular;          // 0: use the generic path (other fields unused)
+    int32_t s_src[4];         // S neighbour of member w (its N row is read)
+    int32_t n_src[4];         // N neighbour of member w (its S row is read)
+    int32_t w_src, e_src;     // W neighbour of the first member (E column), E neighbour of the last (W column)
+    int32_t dsw, dnw;         // SW / NW diagonal contributors of the first member (their points 15 / 3)
+    int32_t dse, dne;         // SE / NE diagonal contributors of the last member  (their points 12 / 0)
+    int32_t pad;
+};
+static_assert(sizeof(StripReg) == 64, "StripReg must be 64 bytes");
 
 struct RowRef {
     int64_t elem; // global element id
@@ -49,11 +68,22 @@ struct Plan {
     std::vector<int64_t> recv_offset;        // [nranks+1] first halo slot of each peer
     std::vector<int32_t> boundary_list, interior_list;     // sweep-1 split (feeds a peer / does not)
     std::vector<int32_t> dependent_list, independent_list; // sweep-2 split (needs a halo / does not)
+    // sweep-2 work units: W-E strips of up to STRIP_MAX consecutive local elements whose facing
+    // edges coincide (e's E edge == (e+1)'s W edge, same orientation), packed first*8 + (count-1),
+    // ascending.  A strip's interior W/E edges are exchanged through shared memory.  Strips are a
+    // performance grouping only: the kernel re-checks the link and falls back to global loads.
+    std::vector<int32_t> strips_all, strips_dependent, strips_independent;
+    // one StripReg per strip, same order: the gather sources of a "regular" strip (see StripReg)
+    std::vector<StripReg> reg_all, reg_dependent, reg_independent;
     // node groups of the local points: members of point p are pt_member[pt_start[p] .. pt_start[p+1]),
     // global point ids 16*e+pt in ascending order (own point included)
     std::vector<int64_t> pt_start, pt_member;
     std::string error; // non-empty if the mesh is not supported
 };
+
+constexpr int STRIP_MAX = 4;
+inline int strip_first(int32_t s) { return s >> 3; }
+inline int strip_count(int32_t s) { return (s & 7) + 1; }
 
 // partition: rank r owns [first, first+count)
 void partition(int64_t nelem_global, int rank, int nranks, int64_t *first, int64_t *count);

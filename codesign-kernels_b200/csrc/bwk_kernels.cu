@@ -24,6 +24,7 @@
 //     output / W-E edge pack / halo buffer.
 #include "bwk_kernels.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 
@@ -158,32 +159,17 @@ struct GlobalMetric {
 };
 
 // ------------------------------------------------------------------------------------------
-// Sweep kernel (all three modes share the warp-private TMA pipeline)
-//
-//   MODE_LAPLACE : qtens tile -> laplace -> qtens tile (in place)
-//   MODE_SWEEP1  : qtens tile -> laplace -> tmp tile, plus the W/E edge pack (the i=1 / i=np
-//                  columns of every slab, stored kq-contiguous so that a neighbour reads them as
-//                  fully coalesced 32-byte rows) -- the on-device part of HOMME's edgeVpack
-//   MODE_SWEEP2  : tmp tile + the neighbours' coincident edge/corner values (edgeVunpack)
-//                  -> * rspheremp -> laplace -> qtens tile
-//
-// Sweep 2 reads each neighbour's facing edge row as ONE 256-bit load per thread (LDG.E.256),
-// straight from where sweep 1 left it: rows j=1/j=np of the neighbour's slab in tmp, the W/E
-// pack, or the halo buffer filled by ncclRecv.  The loads are issued before the wait on the
-// tile's mbarrier, so their latency overlaps the TMA wait; 12 resident warps per SM hide the rest.
-// (A first version staged these rows with 4-D TMA boxes of 32-byte rows; it was bound by the TMA
-// request rate -- see profiles/.)
+// Element-local sweep (MODE_LAPLACE in place, MODE_SWEEP1 qtens -> tmp): warp-private TMA pipeline.
+// grid = (elements, units); the 4 warps of a CTA share one element (one staged metric) and
+// interleave its tiles.
 // ------------------------------------------------------------------------------------------
-template <int MODE>
-struct StageBytes {
-    static constexpr int value = MODE == MODE_SWEEP1 ? 4096 + 2048 : 4096;
-};
+constexpr int TILE_BYTES = TILE_SLABS * 128;
 
-template <int MODE, int STAGES, int WARPS>
+template <int STAGES, int WARPS>
 constexpr int sweep_smem_bytes()
 {
-    // 1024 alignment slack + stages + mbarriers + metric + rsph + dss
-    return 1024 + WARPS * STAGES * StageBytes<MODE>::value + ((WARPS * STAGES * 8 + 15) / 16) * 16 + METRIC_DOUBLES * 8 + 16 * 8 + 64 + 64;
+    // 1024 alignment slack + stages + mbarriers + metric
+    return 1024 + WARPS * STAGES * TILE_BYTES + ((WARPS * STAGES * 8 + 15) / 16) * 16 + METRIC_DOUBLES * 8 + 64;
 }
 
 __device__ __forceinline__ void ldg256(const void *ptr, double &a, double &b, double &c, double &d)
@@ -196,33 +182,23 @@ __device__ __forceinline__ double ldg64(const void *ptr)
     asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(a) : "l"(ptr));
     return a;
 }
-__device__ __forceinline__ void bulk_store_1d(void *gdst, uint32_t src, uint32_t bytes)
-{
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(src), "r"(bytes) : "memory");
-}
 
 template <int MODE, int STAGES, int WARPS, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_constant__ SweepParams p)
 {
-    constexpr int SB = StageBytes<MODE>::value;
+    constexpr int SB = TILE_BYTES;
     extern __shared__ unsigned char smem_raw[];
     // keep the pointer derived from smem_raw so that the compiler emits LDS/STS, not generic LD/ST
     unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     unsigned char *stages = smem;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + WARPS * STAGES * SB);
     double *metric_s = reinterpret_cast<double *>(smem + WARPS * STAGES * SB + ((WARPS * STAGES * 8 + 15) / 16) * 16);
-    double *rsph_s = metric_s + METRIC_DOUBLES;
-    uint32_t *dss_s = reinterpret_cast<uint32_t *>(rsph_s + 16);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int le = p.elem_list ? p.elem_list[blockIdx.x] : p.elem_first + (int)blockIdx.x;
 
-    // ---- per-CTA staging of the element's folded metric (and DSS descriptor, rspheremp)
+    // ---- per-CTA staging of the element's folded metric
     for (int t = threadIdx.x; t < METRIC_DOUBLES; t += WARPS * 32) metric_s[t] = p.metric[(size_t)le * METRIC_DOUBLES + t];
-    if (MODE == MODE_SWEEP2) {
-        if (threadIdx.x < 16) rsph_s[threadIdx.x] = p.rsph[(size_t)le * 16 + threadIdx.x];
-        if (threadIdx.x >= 32 && threadIdx.x < 48) dss_s[threadIdx.x - 32] = reinterpret_cast<const uint32_t *>(p.dss + le)[threadIdx.x - 32];
-    }
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
@@ -240,40 +216,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
     const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
     const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
 
-    // ---- sweep 2: the element's DSS descriptor decoded once into CTA-uniform values:
-    //      per source a base address and the byte stride between consecutive (k,q) slabs
-    const unsigned char *src_ptr[8]; // 0..3 edge rows S,N,W,E ; 4..7 diagonal corner values
-    int src_stride[8];
-    bool edge_rev[4];
-    int corner_perm[4], corner_n[4];
-    if (MODE == MODE_SWEEP2) {
-        const uint32_t w_ekind = dss_s[8], w_erow = dss_s[9], w_erev = dss_s[10], w_dkind = dss_s[11], w_drow = dss_s[12], w_dpos = dss_s[13];
-        const size_t kq = (size_t)p.kq;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int src = (int)dss_s[e];
-            const uint32_t kind = (w_ekind >> (8 * e)) & 0xffu, row = (w_erow >> (8 * e)) & 0xffu;
-            edge_rev[e] = ((w_erev >> (8 * e)) & 0xffu) != 0;
-            if (src < 0) { src_ptr[e] = nullptr; src_stride[e] = 0; }
-            else if (kind == SRC_TMP) { src_ptr[e] = reinterpret_cast<const unsigned char *>(p.tmp + ((size_t)src * kq * 16 + row * 4)); src_stride[e] = 128; }
-            else if (kind == SRC_WEPACK) { src_ptr[e] = reinterpret_cast<const unsigned char *>(p.wepack + ((size_t)src * 2 + row) * kq * 4); src_stride[e] = 32; }
-            else { src_ptr[e] = reinterpret_cast<const unsigned char *>(p.halo + (size_t)src * kq * 4); src_stride[e] = 32; }
-            const int dsrc = (int)dss_s[4 + e];
-            const uint32_t dkind = (w_dkind >> (8 * e)) & 0xffu, drow = (w_drow >> (8 * e)) & 0xffu, dpos = (w_dpos >> (8 * e)) & 0xffu;
-            src_stride[4 + e] = 32;
-            if (dsrc < 0) src_ptr[4 + e] = nullptr;
-            else if (dkind == SRC_WEPACK) src_ptr[4 + e] = reinterpret_cast<const unsigned char *>(p.wepack + ((size_t)dsrc * 2 + drow) * kq * 4 + dpos);
-            else src_ptr[4 + e] = reinterpret_cast<const unsigned char *>(p.halo + (size_t)dsrc * kq * 4 + dpos);
-            corner_perm[e] = (int)((dss_s[15] >> (8 * e)) & 0xffu);
-            corner_n[e] = (int)((dss_s[14] >> (8 * e)) & 0xffu);
-        }
-    }
-
     auto issue_load = [&](int n, int s) {
         const int kq0 = (t0 + warp + n * WARPS) * TILE_SLABS;
         const uint32_t dst = stage0 + s * SB, bar = bar0 + s * 8;
-        mbar_expect_tx(bar, 4096u);
-        tma_load_3d(dst, MODE == MODE_SWEEP2 ? &p.map_tmp : &p.map_q, 0, kq0, le, bar);
+        mbar_expect_tx(bar, (uint32_t)TILE_BYTES);
+        tma_load_3d(dst, &p.map_q, 0, kq0, le, bar);
     };
 
     if (lane == 0) {
@@ -289,19 +236,6 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
         const int kq0 = (t0 + warp + n * WARPS) * TILE_SLABS;
         unsigned char *tile = stages + ((size_t)warp * STAGES + s) * SB;
 
-        // ---- sweep 2: fetch the neighbours' edge rows / corner values for my slab (registers)
-        double nb[4][4], dg[4];
-        if (MODE == MODE_SWEEP2) {
-            const bool live = kq0 + lane < p.kq;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                nb[e][0] = nb[e][1] = nb[e][2] = nb[e][3] = 0.0;
-                if (src_ptr[e] != nullptr && live) ldg256(src_ptr[e] + (size_t)(kq0 + lane) * src_stride[e], nb[e][0], nb[e][1], nb[e][2], nb[e][3]);
-                dg[e] = 0.0;
-                if (src_ptr[4 + e] != nullptr && live) dg[e] = ldg64(src_ptr[4 + e] + (size_t)(kq0 + lane) * 32);
-            }
-        }
-
         mbar_wait(bar0 + s * 8, (uint32_t)((n / STAGES) & 1));
 
         double v[16];
@@ -313,71 +247,15 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
             v[2 * c + 1] = t.y;
         }
 
-        if (MODE == MODE_SWEEP2) {
-            // ---- DSS: add the neighbours' coincident values (edgeVunpack), then * rspheremp
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                if (edge_rev[e]) { // neighbour's edge runs the other way
-                    double t = nb[e][0]; nb[e][0] = nb[e][3]; nb[e][3] = t;
-                    t = nb[e][1]; nb[e][1] = nb[e][2]; nb[e][2] = t;
-                }
-            }
-            // mid-edge points: exactly two contributors, a+b is order independent
-            if (src_ptr[EDGE_S] != nullptr) { v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2]; }
-            if (src_ptr[EDGE_N] != nullptr) { v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2]; }
-            if (src_ptr[EDGE_W] != nullptr) { v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2]; }
-            if (src_ptr[EDGE_E] != nullptr) { v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2]; }
-            // corners: up to four contributors, summed in ascending global point order
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const int pt = c == 0 ? 0 : (c == 1 ? 3 : (c == 2 ? 12 : 15));
-                const double cv0 = v[pt];
-                const double cv1 = nb[c < 2 ? EDGE_S : EDGE_N][(c & 1) ? 3 : 0];
-                const double cv2 = nb[(c & 1) ? EDGE_E : EDGE_W][c < 2 ? 0 : 3];
-                const double cv3 = dg[c];
-                const int perm = corner_perm[c], cn = corner_n[c];
-                auto pick = [&](int k) {
-                    const int w = (perm >> (2 * k)) & 3;
-                    return w == 0 ? cv0 : (w == 1 ? cv1 : (w == 2 ? cv2 : cv3));
-                };
-                double sum = pick(0);
-                if (cn > 1) sum = sum + pick(1);
-                if (cn > 2) sum = sum + pick(2);
-                if (cn > 3) sum = sum + pick(3);
-                v[pt] = sum;
-            }
-#pragma unroll
-            for (int t = 0; t < 16; t += 2) {
-                const double2 r = *reinterpret_cast<const double2 *>(rsph_s + t);
-                v[t] *= r.x;
-                v[t + 1] *= r.y;
-            }
-        }
-
         laplace_slab(v, M);
 
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
-        if (MODE == MODE_SWEEP1) {
-            // W/E edge pack staging: [side][lane][4]
-            unsigned char *we = tile + 4096 + lane * 32;
-            *reinterpret_cast<double2 *>(we) = make_double2(v[0], v[4]);
-            *reinterpret_cast<double2 *>(we + 16) = make_double2(v[8], v[12]);
-            *reinterpret_cast<double2 *>(we + 1024) = make_double2(v[3], v[7]);
-            *reinterpret_cast<double2 *>(we + 1024 + 16) = make_double2(v[11], v[15]);
-        }
         fence_proxy_async();
         __syncwarp();
 
         if (lane == 0) {
-            const uint32_t src = stage0 + s * SB;
-            tma_store_3d(MODE == MODE_SWEEP1 ? &p.map_tmp : &p.map_q, 0, kq0, le, src);
-            if (MODE == MODE_SWEEP1) {
-                const uint32_t nvalid = (uint32_t)min(TILE_SLABS, p.kq - kq0);
-                double *w = p.wepack + (((size_t)le * 2) * p.kq + kq0) * 4;
-                bulk_store_1d(w, src + 4096, nvalid * 32u);
-                bulk_store_1d(w + (size_t)p.kq * 4, src + 4096 + 1024, nvalid * 32u);
-            }
+            tma_store_3d(MODE == MODE_SWEEP1 ? &p.map_tmp : &p.map_q, 0, kq0, le, stage0 + s * SB);
             bulk_commit();
             // refill the stage tile n-1 used, once its store has finished reading shared memory
             if (n >= 1 && n - 1 + STAGES < my_n) {
@@ -389,29 +267,568 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
     if (lane == 0) bulk_wait<0>();
 }
 
+// ------------------------------------------------------------------------------------------
+// Sweep 2 of the full biharmonic (HOMME edgeVunpack + rspheremp + second laplace_sphere_wk):
+//     tmp + the neighbours' coincident edge/corner values -> * rspheremp -> laplace -> qtens
+//
+// A CTA owns a W-E *strip* of up to WARPS consecutive elements (warp w <-> element first+w) and
+// walks the same (k,q) tiles for all of them in lock step.  Each warp TMA-loads its own element's
+// tile.  W/E edges between strip mates never leave the SM: a warp reads the facing column of its
+// mate's tile from shared memory.  Every other contributor (S/N neighbours' rows, the strip ends'
+// W/E columns, diagonal corner values, other ranks' halo rows) is read straight from the
+// neighbour's slab in tmp / from the halo buffer with 256-bit or 64-bit global loads issued
+// before the tile's mbarrier wait.  Those lines are the ones the neighbour's own CTA streams
+// at (nearly) the same time -- strips are launched in element order, S/N neighbours are ne/4
+// CTAs apart -- so they are served by the 126 MB L2 and DRAM sees each slab once.
+// Corners are summed in ascending global point order (bit-identical for any rank count).
+// ------------------------------------------------------------------------------------------
+struct WarpDss {                  // per warp in shared memory, built once per CTA (112 bytes)
+    const unsigned char *edge_ptr[4]; // S,N,W,E: address of value 0 for slab 0
+    const unsigned char *diag_ptr[4]; // corners (1,1),(4,1),(1,4),(4,4): address for slab 0, nullptr = none
+    int32_t edge_stride[4];       // bytes between consecutive (k,q) slabs
+    int32_t diag_stride[4];
+    uint8_t edge_mode[4];         // EM_*
+    uint8_t edge_rev[4];
+    uint8_t corner_n[4];
+    uint8_t corner_perm[4];
+    // 1 = "face interior" element: S/N rows and W/E columns (global or strip mate) all present and
+    // not reversed, four diagonal contributors, and the ascending-global-id summation order of a
+    // row-major structured patch -> straight-line code without mode branches and selects
+    int32_t fast;
+    int32_t pad;
+};
+// corner_perm of a face-interior element with element ids row-major (e = je*ne + ie), 2 bits per
+// summation slot (0 own, 1 S/N neighbour, 2 W/E neighbour, 3 diagonal):
+//   SW: diag, S, W, own   SE: S, diag, own, E   NW: W, own, diag, N   NE: own, E, N, diag
+constexpr int PERM_SW = 3 | (1 << 2) | (2 << 4) | (0 << 6), PERM_SE = 1 | (3 << 2) | (0 << 4) | (2 << 6);
+constexpr int PERM_NW = 2 | (0 << 2) | (3 << 4) | (1 << 6), PERM_NE = 0 | (2 << 2) | (1 << 4) | (3 << 6);
+enum : int { EM_NONE = 0, EM_ROW = 1, EM_COL = 2, EM_MATE_LEFT = 3, EM_MATE_RIGHT = 4 };
+
+// shared memory after the tile ring: tile mbarriers, neighbour-staging mbarriers, per-warp metric and
+// rspheremp, then EITHER the generic path's WarpDss records OR the regular path's staging buffers
+constexpr int ROWBUF_BYTES = 2 * STRIP_MAX * 2 * 32 * 32; // [set][warp][S,N][slab][4 doubles]
+constexpr int COLBUF_BYTES = 2 * 2 * 4 * 32 * 8;          // [set][W end, E end][value t][slab]
+constexpr int DIAGBUF_BYTES = 2 * 4 * 32 * 8;             // [set][SW,NW,SE,NE][slab]
+constexpr int STRIP_EXTRA_BYTES = ROWBUF_BYTES + COLBUF_BYTES + DIAGBUF_BYTES;
+static_assert(STRIP_EXTRA_BYTES >= STRIP_MAX * (int)sizeof(WarpDss) && STRIP_EXTRA_BYTES % 16 == 0, "the generic path's records share the staging area");
+template <int STAGES, int WARPS>
+constexpr int strip_smem_bytes()
+{
+    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 2) * 8 + WARPS * (METRIC_DOUBLES * 8 + 16 * 8) + 6 * 8 + 64;
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void *src, uint32_t src_bytes)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+// the mbarrier gets one arrival from this thread once all its earlier cp.async have landed
+__device__ __forceinline__ void cp_async_arrive(uint32_t bar)
+{
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// ---- regular path: a strip of face-interior elements (StripReg).  Everything a tile needs from
+// other elements is staged into shared memory with cp.async one tile ahead (double buffered) and
+// tracked by an mbarrier, so the compute phase never waits on a global load:
+//   rowbuf : the facing N row of each member's S neighbour and S row of its N neighbour (2 x 32 B per slab)
+//   colbuf : the facing column of the strip's W-end and E-end neighbours
+//   diagbuf: the four diagonal corner values of the strip ends; interior diagonals are the end
+//            values of the mates' rowbuf rows, interior W/E columns come from the mates' tiles.
+// rowbuf is written by TMA with SWIZZLE_32B: 16-byte chunk c of slab l sits at chunk c ^ ((l >> 2) & 1)
+// (bank-conflict-free 128-bit reads).
+template <int STAGES, int WARPS>
+__device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned char *stages, uint64_t *bars, uint64_t *nbars, double *metric_all,
+                                               double *rsph_all, unsigned char *extra, int first, int cnt, const StripReg &rg)
+{
+    constexpr int SB = TILE_BYTES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool active = warp < cnt;
+    const int le = first + warp;
+    double *metric_s = metric_all + warp * METRIC_DOUBLES;
+    double *rsph_s = rsph_all + warp * 16;
+    unsigned char *rowbuf = extra;                       // [set][warp][2][32][32 B]
+    unsigned char *colbuf = extra + ROWBUF_BYTES;        // [set][2][32][32 B]
+    unsigned char *diagbuf = colbuf + COLBUF_BYTES;      // [set][4][32][8 B]
+    const double **endsrc = reinterpret_cast<const double **>(rsph_all + STRIP_MAX * 16); // W col, SW, NW, E col, SE, NE sources (slab 0)
+
+    if (threadIdx.x == 0) {
+        const size_t ekq = (size_t)p.kq * 16;
+        endsrc[0] = p.tmp + (size_t)rg.w_src * ekq + 3;  // W neighbour's E column
+        endsrc[1] = p.tmp + (size_t)rg.dsw * ekq + 15;
+        endsrc[2] = p.tmp + (size_t)rg.dnw * ekq + 3;
+        endsrc[3] = p.tmp + (size_t)rg.e_src * ekq;      // E neighbour's W column
+        endsrc[4] = p.tmp + (size_t)rg.dse * ekq + 12;
+        endsrc[5] = p.tmp + (size_t)rg.dne * ekq;
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
+        mbar_init(smem_u32(&nbars[warp * 2]), 33); // 32 cp.async arrivals + lane 0's expect_tx for the two TMA row boxes
+        mbar_init(smem_u32(&nbars[warp * 2 + 1]), 33);
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    if (active) { // metric (512 B) and rspheremp (128 B) arrive asynchronously, behind the first tile loads
+        cp_async16(smem_u32(metric_s) + lane * 16, p.metric + (size_t)le * METRIC_DOUBLES + lane * 2, 16u);
+        if (lane < 8) cp_async16(smem_u32(rsph_s) + lane * 16, p.rsph + (size_t)le * 16 + lane * 2, 16u);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
+    const int t0 = blockIdx.y * p.tiles_per_unit;
+    const int my_n = min(t0 + p.tiles_per_unit, ntiles) - t0;
+    const size_t kq = (size_t)p.kq;
+
+    const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
+    const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
+    const uint32_t nbar0 = smem_u32(&nbars[warp * 2]);
+    const bool w_end = warp == 0, e_end = warp == cnt - 1;
+    const int swz = (lane >> 2) & 1;
+
+    // sources: S neighbour's N row / N neighbour's S row come as TMA boxes {4 doubles, 32 slabs};
+    // strip-end columns and diagonal corners as 8-byte cp.async (doubles from the start of tmp, slab 0)
+    const int elemS = rg.s_src[warp & 3], elemN = rg.n_src[warp & 3];
+    // (kept in shared memory, not registers: only the two end warps use them, once per tile)
+
+    auto issue_tile = [&](int n, int s) {
+        const uint32_t dst = stage0 + s * SB, bar = bar0 + s * 8;
+        mbar_expect_tx(bar, (uint32_t)TILE_BYTES);
+        tma_load_3d(dst, &p.map_tmp, 0, (t0 + n) * TILE_SLABS, le, bar);
+    };
+    // all lanes: stage the neighbours' values of tile n into buffer set n & 1
+    auto issue_nbr = [&](int n) {
+        const int q = n & 1;
+        const int kq0 = (t0 + n) * TILE_SLABS;
+        const uint32_t nbar = nbar0 + q * 8;
+        if (lane == 0) {
+            const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2 * 1024);
+            mbar_expect_tx(nbar, 2048u);
+            tma_load_3d(rb, &p.map_rows, 12, kq0, elemS, nbar);
+            tma_load_3d(rb + 1024, &p.map_rows, 0, kq0, elemN, nbar);
+        }
+        if (w_end || e_end) {
+            const uint32_t ok8 = kq0 + lane < p.kq ? 8u : 0u;
+            const size_t o = ((size_t)kq0 + lane) * 16;
+            const uint32_t db = smem_u32(diagbuf) + (uint32_t)(q * 1024 + lane * 8);
+            if (w_end) {
+                const uint32_t cb = smem_u32(colbuf) + (uint32_t)(q * 2048 + lane * 8);
+                const double *srcW = endsrc[0] + o;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) cp_async8(cb + t * 256, srcW + 4 * t, ok8);
+                cp_async8(db, endsrc[1] + o, ok8);
+                cp_async8(db + 256, endsrc[2] + o, ok8);
+            }
+            if (e_end) {
+                const uint32_t cb = smem_u32(colbuf) + (uint32_t)(q * 2048 + 1024 + lane * 8);
+                const double *srcE = endsrc[3] + o;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) cp_async8(cb + t * 256, srcE + 4 * t, ok8);
+                cp_async8(db + 512, endsrc[4] + o, ok8);
+                cp_async8(db + 768, endsrc[5] + o, ok8);
+            }
+        }
+        cp_async_arrive(nbar);
+    };
+
+    if (active) {
+        if (lane == 0) {
+            const int pre = my_n < STAGES ? my_n : STAGES;
+            for (int n = 0; n < pre; ++n) issue_tile(n, n);
+        }
+        if (my_n > 0 && !(p.dbg & 2)) issue_nbr(0);
+        if (my_n > 1 && !(p.dbg & 2)) issue_nbr(1);
+    }
+
+    const SmemMetric M{metric_s};
+    const int sw = lane & 7;
+
+    for (int n = 0; n < my_n; ++n) {
+        const int s = n % STAGES, q = n & 1;
+        const int kq0 = (t0 + n) * TILE_SLABS;
+        const uint32_t parity = (uint32_t)((n / STAGES) & 1), nparity = (uint32_t)((n >> 1) & 1);
+        unsigned char *row = stages + ((size_t)warp * STAGES + s) * SB + lane * 128;
+        double v[16], nb[4][4], dg[4];
+
+        if (active) {
+            mbar_wait(bar0 + s * 8, parity);
+            if (!(p.dbg & 2)) mbar_wait(nbar0 + q * 8, nparity);
+            if (n == 0) { // metric / rspheremp staged by this warp's own cp.async group
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                __syncwarp();
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+                v[2 * c] = t.x;
+                v[2 * c + 1] = t.y;
+            }
+            const unsigned char *rb = rowbuf + (size_t)((q * STRIP_MAX + warp) * 2 * 1024) + lane * 32;
+            {
+                const double2 a = *reinterpret_cast<const double2 *>(rb + (swz << 4)), b = *reinterpret_cast<const double2 *>(rb + ((1 ^ swz) << 4));
+                nb[EDGE_S][0] = a.x; nb[EDGE_S][1] = a.y; nb[EDGE_S][2] = b.x; nb[EDGE_S][3] = b.y;
+                const double2 c = *reinterpret_cast<const double2 *>(rb + 1024 + (swz << 4)), d = *reinterpret_cast<const double2 *>(rb + 1024 + ((1 ^ swz) << 4));
+                nb[EDGE_N][0] = c.x; nb[EDGE_N][1] = c.y; nb[EDGE_N][2] = d.x; nb[EDGE_N][3] = d.y;
+            }
+            const unsigned char *db = diagbuf + q * 1024 + lane * 8;
+            if (w_end) {
+                const unsigned char *cb = colbuf + q * 2048 + lane * 8;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(cb + t * 256);
+                dg[0] = *reinterpret_cast<const double *>(db);
+                dg[2] = *reinterpret_cast<const double *>(db + 256);
+            } else if (!(p.dbg & 4)) { // mate on the left: E column of its tile, and the east ends of its S/N neighbour rows
+                mbar_wait(bar0 - STAGES * 8 + s * 8, parity);
+                if (!(p.dbg & 2)) mbar_wait(nbar0 - 16 + q * 8, nparity);
+                const unsigned char *mrow = row - STAGES * SB;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(mrow + (((2 * t + 1) ^ sw) << 4) + 8);
+                dg[0] = *reinterpret_cast<const double *>(rb - 2048 + ((1 ^ swz) << 4) + 8);        // mate's S-row value 3
+                dg[2] = *reinterpret_cast<const double *>(rb - 2048 + 1024 + ((1 ^ swz) << 4) + 8); // mate's N-row value 3
+            }
+            if (e_end) {
+                const unsigned char *cb = colbuf + q * 2048 + 1024 + lane * 8;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(cb + t * 256);
+                dg[1] = *reinterpret_cast<const double *>(db + 512);
+                dg[3] = *reinterpret_cast<const double *>(db + 768);
+            } else if (!(p.dbg & 4)) { // mate on the right: W column of its tile, west ends of its S/N neighbour rows
+                mbar_wait(bar0 + STAGES * 8 + s * 8, parity);
+                if (!(p.dbg & 2)) mbar_wait(nbar0 + 16 + q * 8, nparity);
+                const unsigned char *mrow = row + STAGES * SB;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(mrow + (((2 * t) ^ sw) << 4));
+                dg[1] = *reinterpret_cast<const double *>(rb + 2048 + (swz << 4));        // mate's S-row value 0
+                dg[3] = *reinterpret_cast<const double *>(rb + 2048 + 1024 + (swz << 4)); // mate's N-row value 0
+            }
+        }
+        // every warp has read what it needs from the stage-s tiles and buffer set q
+        if (!(p.dbg & 1)) __syncthreads();
+        if (!active) continue;
+        // buffer set q is free again: stage the neighbours of tile n+2 into it, two tiles ahead
+        if (n + 2 < my_n && !(p.dbg & 2)) issue_nbr(n + 2);
+
+        // ---- DSS (edgeVunpack): mid-edge points, then corners in ascending global point order
+        v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2];
+        v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2];
+        v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2];
+        v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2];
+        v[0] = ((dg[0] + nb[EDGE_S][0]) + nb[EDGE_W][0]) + v[0];       // PERM_SW
+        v[3] = ((nb[EDGE_S][3] + dg[1]) + v[3]) + nb[EDGE_E][0];       // PERM_SE
+        v[12] = ((nb[EDGE_W][3] + v[12]) + dg[2]) + nb[EDGE_N][0];     // PERM_NW
+        v[15] = ((v[15] + nb[EDGE_E][3]) + nb[EDGE_N][3]) + dg[3];     // PERM_NE
+#pragma unroll
+        for (int t = 0; t < 16; t += 2) {
+            const double2 r = *reinterpret_cast<const double2 *>(rsph_s + t);
+            v[t] *= r.x;
+            v[t + 1] *= r.y;
+        }
+
+        laplace_slab(v, M);
+
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
+        fence_proxy_async();
+        __syncwarp();
+
+        if (lane == 0) {
+            tma_store_3d(&p.map_q, 0, kq0, le, stage0 + s * SB);
+            bulk_commit();
+            if (n >= 1 && n - 1 + STAGES < my_n) {
+                bulk_wait_read<1>();
+                issue_tile(n - 1 + STAGES, (n - 1) % STAGES);
+            }
+        }
+    }
+    if (active && lane == 0) bulk_wait<0>();
+}
+
+// ---- generic path: any connectivity the plan accepts (face edges, cube corners, halo rows, reversed edges)
+template <int STAGES, int WARPS>
+__device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, double *rsph_all,
+                                               unsigned char *extra, int first, int cnt)
+{
+    constexpr int SB = TILE_BYTES;
+    WarpDss *wd_all = reinterpret_cast<WarpDss *>(extra);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool active = warp < cnt;
+    const int le = first + warp;
+    double *metric_s = metric_all + warp * METRIC_DOUBLES;
+    double *rsph_s = rsph_all + warp * 16;
+    WarpDss &wd = wd_all[warp];
+
+    if (active) {
+        metric_s[lane] = p.metric[(size_t)le * METRIC_DOUBLES + lane];
+        metric_s[lane + 32] = p.metric[(size_t)le * METRIC_DOUBLES + lane + 32];
+        if (lane < 16) rsph_s[lane] = p.rsph[(size_t)le * 16 + lane];
+        if (lane < 4) {
+            // lane e decodes edge e and corner e of the element's DSS descriptor
+            const ElemDss &d = p.dss[le];
+            const int e = lane;
+            const size_t kq = (size_t)p.kq;
+            const int src = d.edge_src[e];
+            const int kind = d.edge_kind[e], row = d.edge_row[e], rev = d.edge_rev[e];
+            const unsigned char *ptr = nullptr;
+            int stride = 0, mode = EM_NONE;
+            if (src >= 0) {
+                if (kind == SRC_TMP) { ptr = reinterpret_cast<const unsigned char *>(p.tmp + ((size_t)src * kq * 16 + row * 4)); stride = 128; mode = EM_ROW; }
+                else if (kind == SRC_TMPCOL) {
+                    if (e == EDGE_W && !rev && row == 1 && warp > 0 && src == le - 1) mode = EM_MATE_LEFT;
+                    else if (e == EDGE_E && !rev && row == 0 && warp + 1 < cnt && src == le + 1) mode = EM_MATE_RIGHT;
+                    else { ptr = reinterpret_cast<const unsigned char *>(p.tmp + ((size_t)src * kq * 16 + (row ? 3 : 0))); stride = 128; mode = EM_COL; }
+                } else { ptr = reinterpret_cast<const unsigned char *>(p.halo + (size_t)src * kq * 4); stride = 32; mode = EM_ROW; }
+            }
+            wd.edge_ptr[e] = ptr;
+            wd.edge_stride[e] = stride;
+            wd.edge_mode[e] = (uint8_t)mode;
+            wd.edge_rev[e] = (uint8_t)rev;
+            const int dsrc = d.diag_src[e];
+            const unsigned char *dptr = nullptr;
+            int dstride = 0;
+            if (dsrc >= 0) {
+                if (d.diag_kind[e] == SRC_TMPCOL) { dptr = reinterpret_cast<const unsigned char *>(p.tmp + ((size_t)dsrc * kq * 16 + (d.diag_row[e] ? 3 : 0) + 4 * d.diag_pos[e])); dstride = 128; }
+                else { dptr = reinterpret_cast<const unsigned char *>(p.halo + (size_t)dsrc * kq * 4 + d.diag_pos[e]); dstride = 32; }
+            }
+            wd.diag_ptr[e] = dptr;
+            wd.diag_stride[e] = dstride;
+            wd.corner_n[e] = d.corner_n[e];
+            wd.corner_perm[e] = d.corner_perm[e];
+            const int std_perm = e == 0 ? PERM_SW : (e == 1 ? PERM_SE : (e == 2 ? PERM_NW : PERM_NE));
+            const bool edge_ok = !rev && (e < 2 ? mode == EM_ROW : (mode == EM_COL || mode == EM_MATE_LEFT || mode == EM_MATE_RIGHT));
+            const bool ok = edge_ok && dptr != nullptr && d.corner_n[e] == 4 && d.corner_perm[e] == std_perm;
+            const unsigned all_ok = __ballot_sync(0xfu, ok);
+            if (lane == 0) wd.fast = all_ok == 0xfu ? 1 : 0;
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    __syncthreads();
+
+    // ---- all warps walk the same tiles t0 .. t1-1, each for its own element
+    const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
+    const int t0 = blockIdx.y * p.tiles_per_unit;
+    const int my_n = min(t0 + p.tiles_per_unit, ntiles) - t0;
+
+    const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
+    const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
+
+    auto issue_load = [&](int n, int s) {
+        const uint32_t dst = stage0 + s * SB, bar = bar0 + s * 8;
+        mbar_expect_tx(bar, (uint32_t)TILE_BYTES);
+        tma_load_3d(dst, &p.map_tmp, 0, (t0 + n) * TILE_SLABS, le, bar);
+    };
+    if (active && lane == 0) {
+        const int pre = my_n < STAGES ? my_n : STAGES;
+        for (int n = 0; n < pre; ++n) issue_load(n, n);
+    }
+
+    const SmemMetric M{metric_s};
+    const int sw = lane & 7;
+
+    for (int n = 0; n < my_n; ++n) {
+        const int s = n % STAGES;
+        const int kq0 = (t0 + n) * TILE_SLABS;
+        const uint32_t parity = (uint32_t)((n / STAGES) & 1);
+        unsigned char *row = stages + ((size_t)warp * STAGES + s) * SB + lane * 128;
+        double v[16], nb[4][4], dg[4];
+
+        const bool fast = active && wd.fast != 0;
+        if (active) {
+            // ---- contributors that live in global memory: issue the loads before the tile wait
+            const bool live = kq0 + lane < p.kq;
+            const size_t slab = (size_t)(kq0 + lane);
+            if (fast) {
+                // out-of-range lanes of a ragged last tile re-read slab 0 (valid memory, results clipped by the TMA store)
+                const size_t sl = live ? slab : 0;
+                ldg256(wd.edge_ptr[EDGE_S] + sl * (size_t)wd.edge_stride[EDGE_S], nb[EDGE_S][0], nb[EDGE_S][1], nb[EDGE_S][2], nb[EDGE_S][3]);
+                ldg256(wd.edge_ptr[EDGE_N] + sl * (size_t)wd.edge_stride[EDGE_N], nb[EDGE_N][0], nb[EDGE_N][1], nb[EDGE_N][2], nb[EDGE_N][3]);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) dg[c] = ldg64(wd.diag_ptr[c] + sl * (size_t)wd.diag_stride[c]);
+                if (wd.edge_mode[EDGE_W] == EM_COL) {
+                    const unsigned char *q = wd.edge_ptr[EDGE_W] + sl * 128;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = ldg64(q + 32 * t);
+                }
+                if (wd.edge_mode[EDGE_E] == EM_COL) {
+                    const unsigned char *q = wd.edge_ptr[EDGE_E] + sl * 128;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = ldg64(q + 32 * t);
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    nb[e][0] = nb[e][1] = nb[e][2] = nb[e][3] = 0.0;
+                    const int mode = wd.edge_mode[e];
+                    if (live && mode == EM_ROW) ldg256(wd.edge_ptr[e] + slab * (size_t)wd.edge_stride[e], nb[e][0], nb[e][1], nb[e][2], nb[e][3]);
+                    else if (live && mode == EM_COL) {
+                        const unsigned char *q = wd.edge_ptr[e] + slab * 128;
+                        nb[e][0] = ldg64(q);
+                        nb[e][1] = ldg64(q + 32);
+                        nb[e][2] = ldg64(q + 64);
+                        nb[e][3] = ldg64(q + 96);
+                    }
+                    dg[e] = 0.0;
+                    const unsigned char *dp = wd.diag_ptr[e];
+                    if (live && dp != nullptr) dg[e] = ldg64(dp + slab * (size_t)wd.diag_stride[e]);
+                }
+            }
+
+            mbar_wait(bar0 + s * 8, parity);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+                v[2 * c] = t.x;
+                v[2 * c + 1] = t.y;
+            }
+            // ---- strip mates: the facing column of the mate's tile, straight from shared memory
+            if (wd.edge_mode[EDGE_W] == EM_MATE_LEFT) { // mate's E column: points 3,7,11,15 = upper half of chunks 1,3,5,7
+                mbar_wait(bar0 - STAGES * 8 + s * 8, parity);
+                const unsigned char *mrow = row - STAGES * SB;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(mrow + (((2 * t + 1) ^ sw) << 4) + 8);
+            }
+            if (wd.edge_mode[EDGE_E] == EM_MATE_RIGHT) { // mate's W column: points 0,4,8,12 = lower half of chunks 0,2,4,6
+                mbar_wait(bar0 + STAGES * 8 + s * 8, parity);
+                const unsigned char *mrow = row + STAGES * SB;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(mrow + (((2 * t) ^ sw) << 4));
+            }
+        }
+        // every warp has read what it needs from the stage-s tiles: they may now be overwritten in place
+        __syncthreads();
+        if (!active) continue;
+
+        // ---- DSS: add the neighbours' coincident values (edgeVunpack), then * rspheremp
+        if (fast) {
+            v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2];
+            v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2];
+            v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2];
+            v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2];
+            // corners in ascending global point order of a face-interior element (PERM_SW/SE/NW/NE)
+            v[0] = ((dg[0] + nb[EDGE_S][0]) + nb[EDGE_W][0]) + v[0];
+            v[3] = ((nb[EDGE_S][3] + dg[1]) + v[3]) + nb[EDGE_E][0];
+            v[12] = ((nb[EDGE_W][3] + v[12]) + dg[2]) + nb[EDGE_N][0];
+            v[15] = ((v[15] + nb[EDGE_E][3]) + nb[EDGE_N][3]) + dg[3];
+        } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (wd.edge_rev[e]) { // neighbour's edge runs the other way
+                    double t = nb[e][0]; nb[e][0] = nb[e][3]; nb[e][3] = t;
+                    t = nb[e][1]; nb[e][1] = nb[e][2]; nb[e][2] = t;
+                }
+            }
+            // mid-edge points: exactly two contributors
+            if (wd.edge_mode[EDGE_S] != EM_NONE) { v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2]; }
+            if (wd.edge_mode[EDGE_N] != EM_NONE) { v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2]; }
+            if (wd.edge_mode[EDGE_W] != EM_NONE) { v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2]; }
+            if (wd.edge_mode[EDGE_E] != EM_NONE) { v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2]; }
+            // corners: up to four contributors, summed in ascending global point order
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int pt = c == 0 ? 0 : (c == 1 ? 3 : (c == 2 ? 12 : 15));
+                const double cv0 = v[pt];
+                const double cv1 = nb[c < 2 ? EDGE_S : EDGE_N][(c & 1) ? 3 : 0];
+                const double cv2 = nb[(c & 1) ? EDGE_E : EDGE_W][c < 2 ? 0 : 3];
+                const double cv3 = dg[c];
+                const int perm = wd.corner_perm[c], cn = wd.corner_n[c];
+                auto pick = [&](int k) {
+                    const int w = (perm >> (2 * k)) & 3;
+                    return w == 0 ? cv0 : (w == 1 ? cv1 : (w == 2 ? cv2 : cv3));
+                };
+                double sum = pick(0);
+                if (cn > 1) sum = sum + pick(1);
+                if (cn > 2) sum = sum + pick(2);
+                if (cn > 3) sum = sum + pick(3);
+                v[pt] = sum;
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < 16; t += 2) {
+            const double2 r = *reinterpret_cast<const double2 *>(rsph_s + t);
+            v[t] *= r.x;
+            v[t + 1] *= r.y;
+        }
+
+        laplace_slab(v, M);
+
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
+        fence_proxy_async();
+        __syncwarp();
+
+        if (lane == 0) {
+            tma_store_3d(&p.map_q, 0, kq0, le, stage0 + s * SB);
+            bulk_commit();
+            // refill the stage tile n-1 used: its store has read shared memory, and the mates
+            // finished reading it before the __syncthreads of iteration n-1
+            if (n >= 1 && n - 1 + STAGES < my_n) {
+                bulk_wait_read<1>();
+                issue_load(n - 1 + STAGES, (n - 1) % STAGES);
+            }
+        }
+    }
+    if (active && lane == 0) bulk_wait<0>();
+}
+
+template <int STAGES, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __grid_constant__ SweepParams p)
+{
+    static_assert(WARPS == STRIP_MAX, "one warp per strip element");
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    unsigned char *stages = smem;                                  // tile ring, 1024-byte aligned (SWIZZLE_128B)
+    unsigned char *extra = smem + WARPS * STAGES * TILE_BYTES;     // staging buffers (1024-aligned, SWIZZLE_32B rows) or WarpDss records
+    uint64_t *bars = reinterpret_cast<uint64_t *>(extra + STRIP_EXTRA_BYTES);
+    uint64_t *nbars = bars + WARPS * STAGES;
+    double *metric_all = reinterpret_cast<double *>(nbars + WARPS * 2);
+    double *rsph_all = metric_all + WARPS * METRIC_DOUBLES;
+
+    const int32_t strip = p.strips[blockIdx.x];
+    const int first = strip >> 3, cnt = (strip & 7) + 1;
+    const StripReg &rg = p.strip_reg[blockIdx.x];
+    if (rg.regular) sweep2_regular<STAGES, WARPS>(p, stages, bars, nbars, metric_all, rsph_all, extra, first, cnt, rg);
+    else sweep2_generic<STAGES, WARPS>(p, stages, bars, metric_all, rsph_all, extra, first, cnt);
+}
+
 // kernel configurations: (STAGES, WARPS, MINB)
 #define BWK_CFG_LAPLACE 3, 4, 3
 #define BWK_CFG_SWEEP1 3, 4, 3
 #define BWK_CFG_SWEEP2 3, 4, 3
 
-template <int MODE>
-struct ModeWarps {
-    static constexpr int value = 4;
-};
+static int g_sweep2_tpu = 12;
+void set_sweep2_tiles_per_unit(int tpu) { g_sweep2_tpu = tpu < 1 ? 1 : tpu; }
 
-SweepGeometry choose_geometry(int kq, int64_t nelem, int mode)
+SweepGeometry choose_geometry(int kq, int64_t count, int mode)
 {
-    (void)mode;
     const int warps = 4;
     const int ntiles = (kq + TILE_SLABS - 1) / TILE_SLABS;
-    // enough CTAs for ~8 per SM, but at most ~6 tiles per warp (short CTAs balance better, and in
-    // sweep 2 a short unit keeps a neighbour's rows L2-resident until its own CTA reads them)
+    SweepGeometry g;
+    if (mode == MODE_SWEEP2) {
+        // count = strips; every warp walks all tiles of the unit.  Long units amortise the per-CTA
+        // set-up (descriptor, metric, pipeline fill); p.tiles_per_unit_hint overrides for tuning.
+        int64_t tpu = g_sweep2_tpu;
+        const int64_t target_ctas = 148 * 8;
+        if ((ntiles + tpu - 1) / tpu * count < target_ctas) tpu = std::max<int64_t>(1, (int64_t)ntiles * count / target_ctas);
+        if (tpu > ntiles) tpu = ntiles;
+        g.units = (int)((ntiles + tpu - 1) / tpu);
+        g.tiles_per_unit = (int)((ntiles + g.units - 1) / g.units);
+        return g;
+    }
+    // count = elements; the 4 warps of a CTA interleave the unit's tiles.  Enough CTAs for ~8 per
+    // SM, but at most ~6 tiles per warp (short CTAs balance better)
     const int64_t target_ctas = 148 * 8;
-    int64_t tpu = ((int64_t)ntiles * nelem + target_ctas - 1) / target_ctas;
+    int64_t tpu = ((int64_t)ntiles * count + target_ctas - 1) / target_ctas;
     if (tpu < warps) tpu = warps;
     if (tpu > 6 * warps) tpu = 6 * warps;
     if (tpu > ntiles) tpu = ntiles;
-    SweepGeometry g;
     g.units = (int)((ntiles + tpu - 1) / tpu);
     g.tiles_per_unit = (int)((ntiles + g.units - 1) / g.units); // rebalance
     return g;
@@ -420,7 +837,7 @@ SweepGeometry choose_geometry(int kq, int64_t nelem, int mode)
 template <int MODE, int STAGES, int WARPS, int MINB>
 static cudaError_t launch_sweep_t(const SweepParams &p, cudaStream_t st)
 {
-    constexpr int smem = sweep_smem_bytes<MODE, STAGES, WARPS>();
+    constexpr int smem = sweep_smem_bytes<STAGES, WARPS>();
     static bool configured = false;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(sweep_kernel<MODE, STAGES, WARPS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -433,12 +850,29 @@ static cudaError_t launch_sweep_t(const SweepParams &p, cudaStream_t st)
     return cudaGetLastError();
 }
 
+template <int STAGES, int WARPS, int MINB>
+static cudaError_t launch_strip_t(const SweepParams &p, cudaStream_t st)
+{
+    static_assert(WARPS == STRIP_MAX, "one warp per strip element");
+    constexpr int smem = strip_smem_bytes<STAGES, WARPS>();
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(sweep2_strip_kernel<STAGES, WARPS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    if (p.strip_count <= 0 || p.units <= 0) return cudaSuccess;
+    dim3 grid((unsigned)p.strip_count, (unsigned)p.units);
+    sweep2_strip_kernel<STAGES, WARPS, MINB><<<grid, WARPS * 32, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st)
 {
     switch (mode) {
     case MODE_LAPLACE: return launch_sweep_t<MODE_LAPLACE, BWK_CFG_LAPLACE>(p, st);
     case MODE_SWEEP1: return launch_sweep_t<MODE_SWEEP1, BWK_CFG_SWEEP1>(p, st);
-    case MODE_SWEEP2: return launch_sweep_t<MODE_SWEEP2, BWK_CFG_SWEEP2>(p, st);
+    case MODE_SWEEP2: return launch_strip_t<BWK_CFG_SWEEP2>(p, st);
     default: return cudaErrorInvalidValue;
     }
 }
@@ -523,8 +957,8 @@ cudaError_t launch_fold_metric(const double *elem, double *metric, int64_t nelem
 }
 
 // HOMME edgeVpack analogue for the rows that leave this GPU.  Thread = one 16-byte half row.
-__global__ void edge_pack_kernel(const double *__restrict__ tmp, const double *__restrict__ wepack, const int32_t *__restrict__ row_elem,
-                                 const int32_t *__restrict__ row_id, int kq, double *__restrict__ sendbuf)
+__global__ void edge_pack_kernel(const double *__restrict__ tmp, const int32_t *__restrict__ row_elem, const int32_t *__restrict__ row_id, int kq,
+                                 double *__restrict__ sendbuf)
 {
     const int r = blockIdx.y;
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -532,17 +966,23 @@ __global__ void edge_pack_kernel(const double *__restrict__ tmp, const double *_
     const int slab = x >> 1, half = x & 1;
     const int64_t e = row_elem[r];
     const int row = row_id[r];
-    const double *src = row < 4 ? tmp + ((e * kq + slab) * 16 + row * 4 + half * 2) : wepack + (((e * 2 + (row - 4)) * kq + slab) * 4 + half * 2);
-    *reinterpret_cast<double2 *>(sendbuf + (((int64_t)r * kq + slab) * 4 + half * 2)) = *reinterpret_cast<const double2 *>(src);
+    const double *sl = tmp + (e * kq + slab) * 16;
+    double2 v;
+    if (row < 4) v = *reinterpret_cast<const double2 *>(sl + row * 4 + half * 2); // natural j-row
+    else { // W (i=1) / E (i=np) column: stride np
+        const int i = row == ROW_W ? 0 : 3;
+        v = make_double2(sl[i + 4 * (2 * half)], sl[i + 4 * (2 * half + 1)]);
+    }
+    *reinterpret_cast<double2 *>(sendbuf + (((int64_t)r * kq + slab) * 4 + half * 2)) = v;
 }
 
-cudaError_t launch_edge_pack(const double *tmp, const double *wepack, const int32_t *row_elem, const int32_t *row_id, int64_t nrows, int kq,
-                             double *sendbuf, cudaStream_t st)
+cudaError_t launch_edge_pack(const double *tmp, const int32_t *row_elem, const int32_t *row_id, int64_t nrows, int kq, double *sendbuf,
+                             cudaStream_t st)
 {
     for (int64_t r0 = 0; r0 < nrows; r0 += 65535) {
         const int64_t n = nrows - r0 < 65535 ? nrows - r0 : 65535;
         dim3 grid((unsigned)((2 * kq + 255) / 256), (unsigned)n);
-        edge_pack_kernel<<<grid, 256, 0, st>>>(tmp, wepack, row_elem + r0, row_id + r0, kq, sendbuf + r0 * kq * 4);
+        edge_pack_kernel<<<grid, 256, 0, st>>>(tmp, row_elem + r0, row_id + r0, kq, sendbuf + r0 * kq * 4);
     }
     return cudaGetLastError();
 }

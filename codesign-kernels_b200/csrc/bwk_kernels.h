@@ -14,26 +14,30 @@ constexpr int ELEM_DOUBLES = 144;   // element_t, F90:23-27
 
 enum SweepMode : int {
     MODE_LAPLACE = 0, // qtens -> qtens in place              (reference-pinned, F90:186-200)
-    MODE_SWEEP1 = 1,  // qtens -> tmp + W/E edge pack          (laplace + edgeVpack of local edges)
-    MODE_SWEEP2 = 2   // tmp + neighbour rows -> *rspheremp -> laplace -> qtens  (edgeVunpack + second laplace)
+    MODE_SWEEP1 = 1,  // qtens -> tmp                          (first laplace; neighbours read their edges straight from tmp)
+    MODE_SWEEP2 = 2   // tmp + neighbours' edge values -> *rspheremp -> laplace -> qtens  (edgeVunpack + second laplace)
 };
 
 // Everything a sweep launch needs.  Tensor maps are passed by value (__grid_constant__).
 struct SweepParams {
     CUtensorMap map_q;      // qtens   as {16, KQ, nelem}, box {16,32,1}, SWIZZLE_128B
     CUtensorMap map_tmp;    // tmp     same shape (sweep-1 output)
+    CUtensorMap map_rows;   // tmp as {16, KQ, nelem}, box {4,32,1}, SWIZZLE_32B: one edge row (32 B) of 32 consecutive slabs
     const double *metric;   // [nelem][64] folded metric
     const double *rsph;     // [nelem][16]
     const ElemDss *dss;     // [nelem]
-    const double *tmp;      // sweep-1 output, natural layout (neighbours' S/N edge rows are read from here)
-    double *wepack;         // W/E edge pack [nelem][2][KQ][4]: the i=1 / i=np columns, kq-contiguous
+    const double *tmp;      // sweep-1 output, natural layout (neighbours' edge rows/columns are read from here)
     const double *halo;     // received edge rows [nrows][KQ][4]
     const int32_t *elem_list; // optional list of local element indices, else contiguous from elem_first
+    const int32_t *strips;  // MODE_SWEEP2: work units, first*8 + (count-1) (bwk_internal.h); grid x = strip_count
+    const StripReg *strip_reg; // MODE_SWEEP2: one per strip, same order
+    int strip_count;
     int elem_first;         // 0-based first local element (when elem_list == nullptr)
-    int elem_count;         // grid x
+    int elem_count;         // grid x (MODE_LAPLACE / MODE_SWEEP1)
     int kq;                 // nlev*qsize
     int tiles_per_unit;     // tiles (of 32 slabs) per CTA work unit
     int units;              // grid y
+    int dbg;                // timing experiments only (BWK_DBG): 1 no CTA barrier, 2 no neighbour staging, 4 no mate reads -- WRONG RESULTS
 };
 
 // geometry chosen by the host for a given KQ / element count
@@ -41,6 +45,7 @@ struct SweepGeometry {
     int tiles_per_unit, units;
 };
 SweepGeometry choose_geometry(int kq, int64_t nelem, int mode);
+void set_sweep2_tiles_per_unit(int tpu); // tuning knob (BWK_SWEEP2_TPU)
 
 cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st);
 // plain-load variant of MODE_LAPLACE (no TMA, no shared-memory staging); for ncu A/B only
@@ -50,7 +55,7 @@ cudaError_t set_dvv(const double *dvv16_host, cudaStream_t st);
 // folded metric M = -(rrearth^2) * spheremp * Dinv * tensorVisc * Dinv^T per GLL point
 cudaError_t launch_fold_metric(const double *elem, double *metric, int64_t nelem, cudaStream_t st);
 // edge pack: copy rows (local element, row id) x KQ into a contiguous send buffer (HOMME edgeVpack analogue)
-cudaError_t launch_edge_pack(const double *tmp, const double *wepack, const int32_t *row_elem, const int32_t *row_id,
+cudaError_t launch_edge_pack(const double *tmp, const int32_t *row_elem, const int32_t *row_id,
                              int64_t nrows, int kq, double *sendbuf, cudaStream_t st);
 // harness: initialize_data on the device (F90:48-58), table = the 131072 LCG draws
 cudaError_t launch_init_data(const double *table, int64_t nelemd_global, int64_t elem_first, int64_t nelem, int kq,

@@ -282,7 +282,7 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
             if (nb.elem >= lo && nb.elem < hi) {
                 d.edge_src[ed] = (int32_t)(nb.elem - lo);
                 if (nb.edge == EDGE_S || nb.edge == EDGE_N) { d.edge_kind[ed] = SRC_TMP; d.edge_row[ed] = (uint8_t)(nb.edge == EDGE_S ? 0 : 3); }
-                else { d.edge_kind[ed] = SRC_WEPACK; d.edge_row[ed] = (uint8_t)(nb.edge == EDGE_W ? 0 : 1); }
+                else { d.edge_kind[ed] = SRC_TMPCOL; d.edge_row[ed] = (uint8_t)(nb.edge == EDGE_W ? 0 : 1); }
             } else {
                 d.edge_kind[ed] = SRC_HALO;
                 d.edge_row[ed] = 0;
@@ -296,7 +296,7 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
             if (dg.elem >= 0) {
                 d.diag_pos[c] = (uint8_t)(dg.pt / 4); // position along the W/E column = j
                 const int row = dg.pt % 4 == 0 ? ROW_W : ROW_E;
-                if (dg.elem >= lo && dg.elem < hi) { d.diag_kind[c] = SRC_WEPACK; d.diag_row[c] = (uint8_t)(row == ROW_W ? 0 : 1); d.diag_src[c] = (int32_t)(dg.elem - lo); }
+                if (dg.elem >= lo && dg.elem < hi) { d.diag_kind[c] = SRC_TMPCOL; d.diag_row[c] = (uint8_t)(row == ROW_W ? 0 : 1); d.diag_src[c] = (int32_t)(dg.elem - lo); }
                 else { d.diag_kind[c] = SRC_HALO; d.diag_row[c] = 0; d.diag_src[c] = halo_slot({dg.elem, row}); is_dependent[(size_t)le] = 1; }
             }
             // summation order: ascending global point id (== the oracle's order)
@@ -317,6 +317,69 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
     for (int64_t le = 0; le < pl.count; ++le) {
         (is_boundary[(size_t)le] ? pl.boundary_list : pl.interior_list).push_back((int32_t)le);
         (is_dependent[(size_t)le] ? pl.dependent_list : pl.independent_list).push_back((int32_t)le);
+    }
+
+    // ---- sweep-2 strips: runs of consecutive local elements linked E->W with equal orientation
+    auto linked = [&](int32_t a, int32_t b) { // is b == a+1 the E neighbour of a, facing with its W edge, not reversed?
+        const ElemDss &da = pl.dss[(size_t)a];
+        return b == a + 1 && da.edge_src[EDGE_E] == b && da.edge_kind[EDGE_E] == SRC_TMPCOL && da.edge_row[EDGE_E] == 0 && !da.edge_rev[EDGE_E];
+    };
+    // corner_perm of a face-interior element of a row-major patch (must match the kernel's PERM_*)
+    const int std_perm[4] = {3 | (1 << 2) | (2 << 4) | (0 << 6), 1 | (3 << 2) | (0 << 4) | (2 << 6), 2 | (0 << 2) | (3 << 4) | (1 << 6),
+                             0 | (2 << 2) | (1 << 4) | (3 << 6)};
+    auto regular_strip = [&](int32_t first, int n) {
+        StripReg r;
+        std::memset(&r, 0, sizeof r);
+        const int diag_side[4] = {1, 0, 1, 0}, diag_pos[4] = {3, 3, 0, 0}; // SW:pt15 SE:pt12 NW:pt3 NE:pt0
+        for (int w = 0; w < n; ++w) {
+            const ElemDss &d = pl.dss[(size_t)(first + w)];
+            const bool sn_ok = d.edge_src[EDGE_S] >= 0 && d.edge_kind[EDGE_S] == SRC_TMP && d.edge_row[EDGE_S] == 3 && !d.edge_rev[EDGE_S] &&
+                               d.edge_src[EDGE_N] >= 0 && d.edge_kind[EDGE_N] == SRC_TMP && d.edge_row[EDGE_N] == 0 && !d.edge_rev[EDGE_N];
+            const bool we_ok = d.edge_src[EDGE_W] >= 0 && d.edge_kind[EDGE_W] == SRC_TMPCOL && d.edge_row[EDGE_W] == 1 && !d.edge_rev[EDGE_W] &&
+                               d.edge_src[EDGE_E] >= 0 && d.edge_kind[EDGE_E] == SRC_TMPCOL && d.edge_row[EDGE_E] == 0 && !d.edge_rev[EDGE_E];
+            if (!sn_ok || !we_ok) return r;
+            if (w > 0 && d.edge_src[EDGE_W] != first + w - 1) return r;
+            if (w < n - 1 && d.edge_src[EDGE_E] != first + w + 1) return r;
+            for (int c = 0; c < 4; ++c)
+                if (d.corner_n[c] != 4 || d.corner_perm[c] != std_perm[c] || d.diag_src[c] < 0 || d.diag_kind[c] != SRC_TMPCOL ||
+                    d.diag_row[c] != diag_side[c] || d.diag_pos[c] != diag_pos[c])
+                    return r;
+            r.s_src[w] = d.edge_src[EDGE_S];
+            r.n_src[w] = d.edge_src[EDGE_N];
+        }
+        for (int w = 0; w < n; ++w) {
+            const ElemDss &d = pl.dss[(size_t)(first + w)];
+            if (w > 0 && (d.diag_src[0] != r.s_src[w - 1] || d.diag_src[2] != r.n_src[w - 1])) return r;
+            if (w < n - 1 && (d.diag_src[1] != r.s_src[w + 1] || d.diag_src[3] != r.n_src[w + 1])) return r;
+        }
+        const ElemDss &d0 = pl.dss[(size_t)first], &d1 = pl.dss[(size_t)(first + n - 1)];
+        r.w_src = d0.edge_src[EDGE_W];
+        r.e_src = d1.edge_src[EDGE_E];
+        r.dsw = d0.diag_src[0];
+        r.dnw = d0.diag_src[2];
+        r.dse = d1.diag_src[1];
+        r.dne = d1.diag_src[3];
+        r.regular = 1;
+        return r;
+    };
+    auto make_strips = [&](const std::vector<int32_t> &list, std::vector<int32_t> *out, std::vector<StripReg> *reg) {
+        out->clear();
+        reg->clear();
+        size_t i = 0;
+        while (i < list.size()) {
+            int n = 1;
+            while (n < STRIP_MAX && i + n < list.size() && linked(list[i + n - 1], list[i + n])) ++n;
+            out->push_back(list[i] * 8 + (n - 1));
+            reg->push_back(regular_strip(list[i], n));
+            i += (size_t)n;
+        }
+    };
+    {
+        std::vector<int32_t> all((size_t)pl.count);
+        for (int64_t le = 0; le < pl.count; ++le) all[(size_t)le] = (int32_t)le;
+        make_strips(all, &pl.strips_all, &pl.reg_all);
+        make_strips(pl.dependent_list, &pl.strips_dependent, &pl.reg_dependent);
+        make_strips(pl.independent_list, &pl.strips_independent, &pl.reg_independent);
     }
 
     // ---- node groups of the local points (rspheremp, tests)

@@ -142,7 +142,7 @@ int bwk_get_rspheremp(double *rspheremp);
 /* Laplace -> DSS -> *rspheremp -> Laplace on all local elements; asynchronous. */
 int bwk_run_biharmonic(void);
 /* one phase of the above on a single rank, for per-kernel timing and profiling only:
- * 1 = first sweep (laplace + local edge pack), 2 = second sweep (unpack, rspheremp, laplace) */
+ * 1 = first sweep (laplace into the scratch field), 2 = second sweep (unpack, rspheremp, laplace) */
 int bwk_run_biharmonic_phase(int phase);
 /* same through host buffers (upload, both sweeps, download), GPU2-style signature */
 int bwk_biharmonic_wk_scalar_full(const bwk_element_t *elem, double *qtens,
@@ -172,6 +172,11 @@ int bwk_plan_send_list(const bwk_plan_t *, int peer, int64_t *elem, int32_t *row
 int bwk_plan_recv_list(const bwk_plan_t *, int peer, int64_t *elem, int32_t *row);
 int64_t bwk_plan_boundary_elems(const bwk_plan_t *);  /* local elements that feed a peer  */
 int64_t bwk_plan_dependent_elems(const bwk_plan_t *); /* local elements that need a halo */
+/* sweep-2 work units ("strips": up to 4 consecutive local elements chained W->E whose shared edges
+ * are exchanged on chip).  which: 0 = all local elements, 1 = halo-dependent, 2 = halo-independent. */
+int64_t bwk_plan_strip_count(const bwk_plan_t *, int which);
+/* regular[i] = 1 if strip i takes the fully asynchronous structured-patch path (may be NULL) */
+int bwk_plan_strip_list(const bwk_plan_t *, int which, int32_t *first_local_elem, int32_t *count, int32_t *regular);
 /* CPU evaluation of the plan's gather for one slab field (16 doubles per GLOBAL element in
  * `field`): writes the DSS sums of the local elements to out (16*local_count).  Test hook
  * proving the plan equals a node-wise sum; not used by the GPU path. */

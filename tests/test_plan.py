@@ -78,3 +78,39 @@ def test_unsupported_mesh_is_rejected_loudly(bwk):
     g[[0, 16, 32, 48, 64]] = 7
     with pytest.raises(bwk.BwkError):
         bwk.Plan(5, g)
+
+
+@pytest.mark.parametrize("ne,nranks", [(1, 1), (3, 1), (4, 1), (8, 1), (30, 1), (6, 4), (8, 8)])
+def test_strips_tile_the_elements_and_are_west_east_chains(bwk, ne, nranks):
+    """Sweep-2 work units: every local element is in exactly one strip, strips hold <= 4 consecutive
+    elements, and consecutive members share the edge (E column of e == W column of e+1, same
+    orientation) -- read off the gdof ids, independently of the plan."""
+    n = 6 * ne * ne
+    g = bwk.cubed_sphere_gdof(ne).reshape(n, 4, 4)  # [e][j][i]
+    for r in range(nranks):
+        pl = bwk.Plan(n, g.reshape(-1), r, nranks)
+        lo, cnt = pl.local_first, pl.local_count
+        f, c = pl.strips(0)
+        assert np.all((c >= 1) & (c <= 4))
+        assert f[0] == 0 and np.array_equal(f[1:], (f + c)[:-1]) and f[-1] + c[-1] == cnt
+        for a, k in zip(f, c):
+            for e in range(lo + a, lo + a + k - 1):
+                assert np.array_equal(g[e][:, 3], g[e + 1][:, 0])
+        if nranks == 1 and ne % 4 == 0:
+            assert np.all(c == 4)  # face rows are cut into full strips
+        if nranks == 1:
+            # "regular" (fully asynchronous kernel path) <=> every member is a face-interior element
+            reg = pl.strip_regular
+            for a, k, r in zip(f, c, reg):
+                ie = (np.arange(a, a + k) % (ne * ne)) % ne
+                je = (np.arange(a, a + k) % (ne * ne)) // ne
+                interior = np.all((ie > 0) & (ie < ne - 1) & (je > 0) & (je < ne - 1))
+                assert bool(r) == bool(interior), (a, k, r)
+        fd, cd = pl.strips(1)
+        fi, ci = pl.strips(2)
+        assert cd.sum() == pl.dependent_elems and cd.sum() + ci.sum() == cnt
+        covered = np.zeros(cnt, dtype=int)
+        for ff, cc in ((fd, cd), (fi, ci)):
+            for a, k in zip(ff, cc):
+                covered[a : a + k] += 1
+        assert np.all(covered == 1)
