@@ -472,7 +472,6 @@ int bwk_init(int nelemd, int nlev, int qsize)
     if (prop.major != 10) return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", dev, prop.major, prop.minor);
     g = Ctx();
     if (const char *e = std::getenv("BWK_SWEEP2_TPU")) set_sweep2_tiles_per_unit(std::atoi(e));
-    if (const char *e = std::getenv("BWK_DBG")) g.sp.dbg = std::atoi(e);
     g.nelem = nelemd;
     g.nlev = nlev;
     g.qsize = qsize;

@@ -87,6 +87,23 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, int c0, int
                  ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(src)
                  : "memory");
 }
+// one arrival (release at CTA scope: the thread's earlier shared-memory writes are visible to whoever waits on the phase)
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void tma_store_3d_hint(const CUtensorMap *map, int c0, int c1, int c2, uint32_t src, uint64_t pol)
+{
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group.L2::cache_hint [%0, {%1, %2, %3}], [%4], %5;"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(src), "l"(pol)
+                 : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read()
@@ -168,8 +185,8 @@ constexpr int TILE_BYTES = TILE_SLABS * 128;
 template <int STAGES, int WARPS>
 constexpr int sweep_smem_bytes()
 {
-    // 1024 alignment slack + stages + mbarriers + metric
-    return 1024 + WARPS * STAGES * TILE_BYTES + ((WARPS * STAGES * 8 + 15) / 16) * 16 + METRIC_DOUBLES * 8 + 64;
+    // 1024 alignment slack + stages + mbarriers + metric + rspheremp
+    return 1024 + WARPS * STAGES * TILE_BYTES + ((WARPS * STAGES * 8 + 15) / 16) * 16 + METRIC_DOUBLES * 8 + 16 * 8 + 64;
 }
 
 __device__ __forceinline__ void ldg256(const void *ptr, double &a, double &b, double &c, double &d)
@@ -199,6 +216,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
 
     // ---- per-CTA staging of the element's folded metric
     for (int t = threadIdx.x; t < METRIC_DOUBLES; t += WARPS * 32) metric_s[t] = p.metric[(size_t)le * METRIC_DOUBLES + t];
+    double *rsph_s = metric_s + METRIC_DOUBLES;
+    if (MODE == MODE_SWEEP1 && threadIdx.x < 16) rsph_s[threadIdx.x] = p.rsph[(size_t)le * 16 + threadIdx.x];
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
@@ -248,6 +267,17 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
         }
 
         laplace_slab(v, M);
+        if (MODE == MODE_SWEEP1) {
+            // DSS scaling folded into the producer: rspheremp is a property of the NODE (the same in every
+            // element sharing it), so (sum_e q_e) * rspheremp == sum_e (q_e * rspheremp) up to rounding
+            // and sweep 2 only has to add the neighbours' (already scaled) values
+#pragma unroll
+            for (int t = 0; t < 16; t += 2) {
+                const double2 r = *reinterpret_cast<const double2 *>(rsph_s + t);
+                v[t] *= r.x;
+                v[t + 1] *= r.y;
+            }
+        }
 
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
@@ -304,17 +334,21 @@ constexpr int PERM_SW = 3 | (1 << 2) | (2 << 4) | (0 << 6), PERM_SE = 1 | (3 << 
 constexpr int PERM_NW = 2 | (0 << 2) | (3 << 4) | (1 << 6), PERM_NE = 0 | (2 << 2) | (1 << 4) | (3 << 6);
 enum : int { EM_NONE = 0, EM_ROW = 1, EM_COL = 2, EM_MATE_LEFT = 3, EM_MATE_RIGHT = 4 };
 
-// shared memory after the tile ring: tile mbarriers, neighbour-staging mbarriers, per-warp metric and
-// rspheremp, then EITHER the generic path's WarpDss records OR the regular path's staging buffers
-constexpr int ROWBUF_BYTES = 2 * STRIP_MAX * 2 * 32 * 32; // [set][warp][S,N][slab][4 doubles]
-constexpr int COLBUF_BYTES = 2 * 2 * 4 * 32 * 8;          // [set][W end, E end][value t][slab]
-constexpr int DIAGBUF_BYTES = 2 * 4 * 32 * 8;             // [set][SW,NW,SE,NE][slab]
-constexpr int STRIP_EXTRA_BYTES = ROWBUF_BYTES + COLBUF_BYTES + DIAGBUF_BYTES;
-static_assert(STRIP_EXTRA_BYTES >= STRIP_MAX * (int)sizeof(WarpDss) && STRIP_EXTRA_BYTES % 16 == 0, "the generic path's records share the staging area");
+// Shared memory of the strip kernel, in order (offsets from a 1024-byte aligned base):
+//   tiles   [warp][stage][4 KB]                        TMA destination, SWIZZLE_128B, results written in place
+//   rowbuf  [set 2][warp][S,N][32 slabs][32 B]         facing rows of the S/N neighbours, TMA destination, SWIZZLE_32B
+//   endbuf  [set 2][W end,E end][6 values][32 slabs]   facing column + two diagonal corners of the strip-end neighbours (cp.async)
+//   barriers: tile_full [warp][stage], nbr_full [warp][2], cons [warp][2]
+//   metric [warp][64], endsrc [6]
+// The generic path keeps its per-warp descriptors (WarpDss) in the rowbuf area.
+constexpr int ROWBUF_BYTES = 2 * STRIP_MAX * 2 * 32 * 32;
+constexpr int ENDBUF_BYTES = 2 * 2 * 6 * 32 * 8;
+constexpr int STRIP_EXTRA_BYTES = ROWBUF_BYTES + ENDBUF_BYTES;
+static_assert(ROWBUF_BYTES >= STRIP_MAX * (int)sizeof(WarpDss) && STRIP_EXTRA_BYTES % 16 == 0, "the generic path's records share the staging area");
 template <int STAGES, int WARPS>
 constexpr int strip_smem_bytes()
 {
-    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 2) * 8 + WARPS * (METRIC_DOUBLES * 8 + 16 * 8) + 6 * 8 + 64;
+    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 4) * 8 + WARPS * METRIC_DOUBLES * 8 + 6 * 8 + 64;
 }
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t src_bytes)
@@ -331,30 +365,36 @@ __device__ __forceinline__ void cp_async_arrive(uint32_t bar)
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
-// ---- regular path: a strip of face-interior elements (StripReg).  Everything a tile needs from
-// other elements is staged into shared memory with cp.async one tile ahead (double buffered) and
-// tracked by an mbarrier, so the compute phase never waits on a global load:
-//   rowbuf : the facing N row of each member's S neighbour and S row of its N neighbour (2 x 32 B per slab)
-//   colbuf : the facing column of the strip's W-end and E-end neighbours
-//   diagbuf: the four diagonal corner values of the strip ends; interior diagonals are the end
-//            values of the mates' rowbuf rows, interior W/E columns come from the mates' tiles.
-// rowbuf is written by TMA with SWIZZLE_32B: 16-byte chunk c of slab l sits at chunk c ^ ((l >> 2) & 1)
-// (bank-conflict-free 128-bit reads).
+// ---- regular path: a strip of face-interior elements (StripReg).  No CTA-wide barrier inside the
+// tile loop: every warp runs its own pipeline.
+//   * own tile: TMA, STAGES-deep ring, results written in place, TMA store (as in sweep 1);
+//   * facing rows of the S/N neighbours: two TMA boxes {4 doubles, 32 slabs} per tile into rowbuf;
+//   * strip ends: facing column and two diagonal corner values of the outside neighbours, 8-byte cp.async
+//     into endbuf; rowbuf/endbuf are double buffered, refilled two tiles ahead and tracked by nbr_full
+//     (32 cp.async arrivals + lane 0's expect_tx);
+//   * mates: a warp reads the facing column of its mate's tile and the facing ends of the mate's S/N
+//     neighbour rows (= its own diagonal contributors) straight from the mate's shared memory, after
+//     waiting on the MATE's tile_full / nbr_full barriers, and then arrives on the mate's cons barrier
+//     (parity of the tile).  The owner waits on its cons barrier before it overwrites the tile with its
+//     results and before it refills the rowbuf set.  Arrivals depend only on loads having landed, never on
+//     a mate's computation, so the protocol cannot dead-lock; and a mate can run at most one tile ahead
+//     (it needs the owner's arrival for its own tile), so two cons barriers per warp are enough.
 template <int STAGES, int WARPS>
-__device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned char *stages, uint64_t *bars, uint64_t *nbars, double *metric_all,
-                                               double *rsph_all, unsigned char *extra, int first, int cnt, const StripReg &rg)
+__device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, unsigned char *extra,
+                                               int first, int cnt, const StripReg &rg)
 {
     constexpr int SB = TILE_BYTES;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool active = warp < cnt;
     const int le = first + warp;
     double *metric_s = metric_all + warp * METRIC_DOUBLES;
-    double *rsph_s = rsph_all + warp * 16;
-    unsigned char *rowbuf = extra;                       // [set][warp][2][32][32 B]
-    unsigned char *colbuf = extra + ROWBUF_BYTES;        // [set][2][32][32 B]
-    unsigned char *diagbuf = colbuf + COLBUF_BYTES;      // [set][4][32][8 B]
-    const double **endsrc = reinterpret_cast<const double **>(rsph_all + STRIP_MAX * 16); // W col, SW, NW, E col, SE, NE sources (slab 0)
+    unsigned char *rowbuf = extra;                        // [set][warp][2][32][32 B]
+    unsigned char *endbuf = extra + ROWBUF_BYTES;         // [set][2][6][32][8 B]
+    uint64_t *nbars = bars + WARPS * STAGES;              // nbr_full [warp][2]
+    uint64_t *cbars = nbars + WARPS * 2;                  // cons     [warp][2]
+    const double **endsrc = reinterpret_cast<const double **>(metric_all + STRIP_MAX * METRIC_DOUBLES); // W col, SW, NW, E col, SE, NE sources (slab 0)
 
+    const bool w_end = warp == 0, e_end = warp == cnt - 1;
     if (threadIdx.x == 0) {
         const size_t ekq = (size_t)p.kq * 16;
         endsrc[0] = p.tmp + (size_t)rg.w_src * ekq + 3;  // W neighbour's E column
@@ -369,80 +409,76 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
         mbar_init(smem_u32(&nbars[warp * 2]), 33); // 32 cp.async arrivals + lane 0's expect_tx for the two TMA row boxes
         mbar_init(smem_u32(&nbars[warp * 2 + 1]), 33);
+        const uint32_t nmates = (w_end ? 0u : 1u) + (e_end ? 0u : 1u);
+        mbar_init(smem_u32(&cbars[warp * 2]), active && nmates ? 32u * nmates : 1u); // every lane of every mate arrives
+        mbar_init(smem_u32(&cbars[warp * 2 + 1]), active && nmates ? 32u * nmates : 1u);
         fence_barrier_init();
         fence_proxy_async();
     }
-    if (active) { // metric (512 B) and rspheremp (128 B) arrive asynchronously, behind the first tile loads
+    if (active) { // the folded metric (512 B) arrives asynchronously, behind the first tile loads
         cp_async16(smem_u32(metric_s) + lane * 16, p.metric + (size_t)le * METRIC_DOUBLES + lane * 2, 16u);
-        if (lane < 8) cp_async16(smem_u32(rsph_s) + lane * 16, p.rsph + (size_t)le * 16 + lane * 2, 16u);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    __syncthreads();
+    __syncthreads(); // the only CTA-wide barrier: mbarriers initialised, endsrc written
+    if (!active) return;
 
     const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
     const int t0 = blockIdx.y * p.tiles_per_unit;
     const int my_n = min(t0 + p.tiles_per_unit, ntiles) - t0;
-    const size_t kq = (size_t)p.kq;
 
     const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
     const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
     const uint32_t nbar0 = smem_u32(&nbars[warp * 2]);
-    const bool w_end = warp == 0, e_end = warp == cnt - 1;
-    const int swz = (lane >> 2) & 1;
-
-    // sources: S neighbour's N row / N neighbour's S row come as TMA boxes {4 doubles, 32 slabs};
-    // strip-end columns and diagonal corners as 8-byte cp.async (doubles from the start of tmp, slab 0)
+    const uint32_t cbar0 = smem_u32(&cbars[warp * 2]);
+    const int swz = (lane >> 2) & 1; // SWIZZLE_32B: 16-byte chunk c of 32-byte row r sits at chunk c ^ ((r >> 2) & 1)
     const int elemS = rg.s_src[warp & 3], elemN = rg.n_src[warp & 3];
-    // (kept in shared memory, not registers: only the two end warps use them, once per tile)
+    const uint64_t pol_out = l2_policy_evict_first(); // the output is never read again by this kernel
 
     auto issue_tile = [&](int n, int s) {
         const uint32_t dst = stage0 + s * SB, bar = bar0 + s * 8;
         mbar_expect_tx(bar, (uint32_t)TILE_BYTES);
         tma_load_3d(dst, &p.map_tmp, 0, (t0 + n) * TILE_SLABS, le, bar);
     };
-    // all lanes: stage the neighbours' values of tile n into buffer set n & 1
+    // all lanes: stage the outside neighbours' values of tile n into buffer set n & 1
     auto issue_nbr = [&](int n) {
         const int q = n & 1;
         const int kq0 = (t0 + n) * TILE_SLABS;
         const uint32_t nbar = nbar0 + q * 8;
         if (lane == 0) {
-            const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2 * 1024);
+            const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2048);
             mbar_expect_tx(nbar, 2048u);
-            tma_load_3d(rb, &p.map_rows, 12, kq0, elemS, nbar);
-            tma_load_3d(rb + 1024, &p.map_rows, 0, kq0, elemN, nbar);
+            tma_load_3d(rb, &p.map_rows, 12, kq0, elemS, nbar);       // S neighbour's N row
+            tma_load_3d(rb + 1024, &p.map_rows, 0, kq0, elemN, nbar); // N neighbour's S row
         }
         if (w_end || e_end) {
             const uint32_t ok8 = kq0 + lane < p.kq ? 8u : 0u;
             const size_t o = ((size_t)kq0 + lane) * 16;
-            const uint32_t db = smem_u32(diagbuf) + (uint32_t)(q * 1024 + lane * 8);
             if (w_end) {
-                const uint32_t cb = smem_u32(colbuf) + (uint32_t)(q * 2048 + lane * 8);
-                const double *srcW = endsrc[0] + o;
+                const uint32_t eb = smem_u32(endbuf) + (uint32_t)(q * 3072 + lane * 8);
+                const double *src = endsrc[0] + o;
 #pragma unroll
-                for (int t = 0; t < 4; ++t) cp_async8(cb + t * 256, srcW + 4 * t, ok8);
-                cp_async8(db, endsrc[1] + o, ok8);
-                cp_async8(db + 256, endsrc[2] + o, ok8);
+                for (int t = 0; t < 4; ++t) cp_async8(eb + t * 256, src + 4 * t, ok8);
+                cp_async8(eb + 4 * 256, endsrc[1] + o, ok8);
+                cp_async8(eb + 5 * 256, endsrc[2] + o, ok8);
             }
             if (e_end) {
-                const uint32_t cb = smem_u32(colbuf) + (uint32_t)(q * 2048 + 1024 + lane * 8);
-                const double *srcE = endsrc[3] + o;
+                const uint32_t eb = smem_u32(endbuf) + (uint32_t)(q * 3072 + 1536 + lane * 8);
+                const double *src = endsrc[3] + o;
 #pragma unroll
-                for (int t = 0; t < 4; ++t) cp_async8(cb + t * 256, srcE + 4 * t, ok8);
-                cp_async8(db + 512, endsrc[4] + o, ok8);
-                cp_async8(db + 768, endsrc[5] + o, ok8);
+                for (int t = 0; t < 4; ++t) cp_async8(eb + t * 256, src + 4 * t, ok8);
+                cp_async8(eb + 4 * 256, endsrc[4] + o, ok8);
+                cp_async8(eb + 5 * 256, endsrc[5] + o, ok8);
             }
         }
         cp_async_arrive(nbar);
     };
 
-    if (active) {
-        if (lane == 0) {
-            const int pre = my_n < STAGES ? my_n : STAGES;
-            for (int n = 0; n < pre; ++n) issue_tile(n, n);
-        }
-        if (my_n > 0 && !(p.dbg & 2)) issue_nbr(0);
-        if (my_n > 1 && !(p.dbg & 2)) issue_nbr(1);
+    if (lane == 0) {
+        const int pre = my_n < STAGES ? my_n : STAGES;
+        for (int n = 0; n < pre; ++n) issue_tile(n, n);
     }
+    if (my_n > 0) issue_nbr(0);
+    if (my_n > 1) issue_nbr(1);
 
     const SmemMetric M{metric_s};
     const int sw = lane & 7;
@@ -450,69 +486,64 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     for (int n = 0; n < my_n; ++n) {
         const int s = n % STAGES, q = n & 1;
         const int kq0 = (t0 + n) * TILE_SLABS;
-        const uint32_t parity = (uint32_t)((n / STAGES) & 1), nparity = (uint32_t)((n >> 1) & 1);
+        const uint32_t parity = (uint32_t)((n / STAGES) & 1), qparity = (uint32_t)((n >> 1) & 1);
         unsigned char *row = stages + ((size_t)warp * STAGES + s) * SB + lane * 128;
+        const unsigned char *rb = rowbuf + (size_t)((q * STRIP_MAX + warp) * 2048) + lane * 32;
         double v[16], nb[4][4], dg[4];
 
-        if (active) {
-            mbar_wait(bar0 + s * 8, parity);
-            if (!(p.dbg & 2)) mbar_wait(nbar0 + q * 8, nparity);
-            if (n == 0) { // metric / rspheremp staged by this warp's own cp.async group
-                asm volatile("cp.async.wait_all;" ::: "memory");
-                __syncwarp();
-            }
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
-                v[2 * c] = t.x;
-                v[2 * c + 1] = t.y;
-            }
-            const unsigned char *rb = rowbuf + (size_t)((q * STRIP_MAX + warp) * 2 * 1024) + lane * 32;
-            {
-                const double2 a = *reinterpret_cast<const double2 *>(rb + (swz << 4)), b = *reinterpret_cast<const double2 *>(rb + ((1 ^ swz) << 4));
-                nb[EDGE_S][0] = a.x; nb[EDGE_S][1] = a.y; nb[EDGE_S][2] = b.x; nb[EDGE_S][3] = b.y;
-                const double2 c = *reinterpret_cast<const double2 *>(rb + 1024 + (swz << 4)), d = *reinterpret_cast<const double2 *>(rb + 1024 + ((1 ^ swz) << 4));
-                nb[EDGE_N][0] = c.x; nb[EDGE_N][1] = c.y; nb[EDGE_N][2] = d.x; nb[EDGE_N][3] = d.y;
-            }
-            const unsigned char *db = diagbuf + q * 1024 + lane * 8;
-            if (w_end) {
-                const unsigned char *cb = colbuf + q * 2048 + lane * 8;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(cb + t * 256);
-                dg[0] = *reinterpret_cast<const double *>(db);
-                dg[2] = *reinterpret_cast<const double *>(db + 256);
-            } else if (!(p.dbg & 4)) { // mate on the left: E column of its tile, and the east ends of its S/N neighbour rows
-                mbar_wait(bar0 - STAGES * 8 + s * 8, parity);
-                if (!(p.dbg & 2)) mbar_wait(nbar0 - 16 + q * 8, nparity);
-                const unsigned char *mrow = row - STAGES * SB;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(mrow + (((2 * t + 1) ^ sw) << 4) + 8);
-                dg[0] = *reinterpret_cast<const double *>(rb - 2048 + ((1 ^ swz) << 4) + 8);        // mate's S-row value 3
-                dg[2] = *reinterpret_cast<const double *>(rb - 2048 + 1024 + ((1 ^ swz) << 4) + 8); // mate's N-row value 3
-            }
-            if (e_end) {
-                const unsigned char *cb = colbuf + q * 2048 + 1024 + lane * 8;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(cb + t * 256);
-                dg[1] = *reinterpret_cast<const double *>(db + 512);
-                dg[3] = *reinterpret_cast<const double *>(db + 768);
-            } else if (!(p.dbg & 4)) { // mate on the right: W column of its tile, west ends of its S/N neighbour rows
-                mbar_wait(bar0 + STAGES * 8 + s * 8, parity);
-                if (!(p.dbg & 2)) mbar_wait(nbar0 + 16 + q * 8, nparity);
-                const unsigned char *mrow = row + STAGES * SB;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(mrow + (((2 * t) ^ sw) << 4));
-                dg[1] = *reinterpret_cast<const double *>(rb + 2048 + (swz << 4));        // mate's S-row value 0
-                dg[3] = *reinterpret_cast<const double *>(rb + 2048 + 1024 + (swz << 4)); // mate's N-row value 0
-            }
+        mbar_wait(bar0 + s * 8, parity);
+        mbar_wait(nbar0 + q * 8, qparity);
+        if (n == 0) { // the metric staged by this warp's own cp.async group
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            __syncwarp();
         }
-        // every warp has read what it needs from the stage-s tiles and buffer set q
-        if (!(p.dbg & 1)) __syncthreads();
-        if (!active) continue;
-        // buffer set q is free again: stage the neighbours of tile n+2 into it, two tiles ahead
-        if (n + 2 < my_n && !(p.dbg & 2)) issue_nbr(n + 2);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+            v[2 * c] = t.x;
+            v[2 * c + 1] = t.y;
+        }
+        {
+            const double2 a = *reinterpret_cast<const double2 *>(rb + (swz << 4)), b = *reinterpret_cast<const double2 *>(rb + ((1 ^ swz) << 4));
+            nb[EDGE_S][0] = a.x; nb[EDGE_S][1] = a.y; nb[EDGE_S][2] = b.x; nb[EDGE_S][3] = b.y;
+            const double2 c = *reinterpret_cast<const double2 *>(rb + 1024 + (swz << 4)), d = *reinterpret_cast<const double2 *>(rb + 1024 + ((1 ^ swz) << 4));
+            nb[EDGE_N][0] = c.x; nb[EDGE_N][1] = c.y; nb[EDGE_N][2] = d.x; nb[EDGE_N][3] = d.y;
+        }
+        // ---- W side: outside neighbour (strip end) or the left mate's shared memory
+        if (w_end) {
+            const unsigned char *eb = endbuf + q * 3072 + lane * 8;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(eb + t * 256);
+            dg[0] = *reinterpret_cast<const double *>(eb + 4 * 256);
+            dg[2] = *reinterpret_cast<const double *>(eb + 5 * 256);
+        } else { // mate's E column = points 3,7,11,15 = upper halves of chunks 1,3,5,7; east ends of its S/N neighbour rows
+            mbar_wait(bar0 - STAGES * 8 + s * 8, parity);
+            mbar_wait(nbar0 - 16 + q * 8, qparity);
+            const unsigned char *mrow = row - STAGES * SB;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(mrow + (((2 * t + 1) ^ sw) << 4) + 8);
+            dg[0] = *reinterpret_cast<const double *>(rb - 2048 + ((1 ^ swz) << 4) + 8);        // mate's S-row value 3
+            dg[2] = *reinterpret_cast<const double *>(rb - 2048 + 1024 + ((1 ^ swz) << 4) + 8); // mate's N-row value 3
+        }
+        // ---- E side
+        if (e_end) {
+            const unsigned char *eb = endbuf + q * 3072 + 1536 + lane * 8;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(eb + t * 256);
+            dg[1] = *reinterpret_cast<const double *>(eb + 4 * 256);
+            dg[3] = *reinterpret_cast<const double *>(eb + 5 * 256);
+        } else { // mate's W column = points 0,4,8,12 = lower halves of chunks 0,2,4,6; west ends of its S/N neighbour rows
+            mbar_wait(bar0 + STAGES * 8 + s * 8, parity);
+            mbar_wait(nbar0 + 16 + q * 8, qparity);
+            const unsigned char *mrow = row + STAGES * SB;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(mrow + (((2 * t) ^ sw) << 4));
+            dg[1] = *reinterpret_cast<const double *>(rb + 2048 + (swz << 4));        // mate's S-row value 0
+            dg[3] = *reinterpret_cast<const double *>(rb + 2048 + 1024 + (swz << 4)); // mate's N-row value 0
+        }
 
-        // ---- DSS (edgeVunpack): mid-edge points, then corners in ascending global point order
+        // ---- DSS (edgeVunpack): mid-edge points, then corners in ascending global point order.
+        //      (values were scaled by rspheremp in sweep 1)
         v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2];
         v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2];
         v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2];
@@ -521,36 +552,39 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         v[3] = ((nb[EDGE_S][3] + dg[1]) + v[3]) + nb[EDGE_E][0];       // PERM_SE
         v[12] = ((nb[EDGE_W][3] + v[12]) + dg[2]) + nb[EDGE_N][0];     // PERM_NW
         v[15] = ((v[15] + nb[EDGE_E][3]) + nb[EDGE_N][3]) + dg[3];     // PERM_NE
-#pragma unroll
-        for (int t = 0; t < 16; t += 2) {
-            const double2 r = *reinterpret_cast<const double2 *>(rsph_s + t);
-            v[t] *= r.x;
-            v[t + 1] *= r.y;
-        }
+
+        // the mates' values have been consumed (the sums above depend on them): tell the mates.
+        // The asm operand ties the arrival to the corner sums so that it cannot be scheduled above the loads.
+        if (!w_end) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 - 16 + q * 8), "d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]) : "memory");
+        if (!e_end) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 + 16 + q * 8), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
 
         laplace_slab(v, M);
 
+        // both mates must have read this tile's columns and this rowbuf set before they are overwritten
+        if (cnt > 1) mbar_wait(cbar0 + q * 8, qparity);
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
         fence_proxy_async();
-        __syncwarp();
+        __syncwarp(); // all lanes' results are in the tile; all lanes' reads of rowbuf/endbuf set q have been consumed
 
         if (lane == 0) {
-            tma_store_3d(&p.map_q, 0, kq0, le, stage0 + s * SB);
+            tma_store_3d_hint(&p.map_q, 0, kq0, le, stage0 + s * SB, pol_out);
             bulk_commit();
             if (n >= 1 && n - 1 + STAGES < my_n) {
                 bulk_wait_read<1>();
                 issue_tile(n - 1 + STAGES, (n - 1) % STAGES);
             }
         }
+        // buffer set q is free again: stage the outside neighbours of tile n+2 into it
+        if (n + 2 < my_n) issue_nbr(n + 2);
     }
-    if (active && lane == 0) bulk_wait<0>();
+    if (lane == 0) bulk_wait<0>();
 }
 
 // ---- generic path: any connectivity the plan accepts (face edges, cube corners, halo rows, reversed edges)
 template <int STAGES, int WARPS>
-__device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, double *rsph_all,
-                                               unsigned char *extra, int first, int cnt)
+__device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, unsigned char *extra,
+                                               int first, int cnt)
 {
     constexpr int SB = TILE_BYTES;
     WarpDss *wd_all = reinterpret_cast<WarpDss *>(extra);
@@ -558,13 +592,11 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
     const bool active = warp < cnt;
     const int le = first + warp;
     double *metric_s = metric_all + warp * METRIC_DOUBLES;
-    double *rsph_s = rsph_all + warp * 16;
     WarpDss &wd = wd_all[warp];
 
     if (active) {
         metric_s[lane] = p.metric[(size_t)le * METRIC_DOUBLES + lane];
         metric_s[lane + 32] = p.metric[(size_t)le * METRIC_DOUBLES + lane + 32];
-        if (lane < 16) rsph_s[lane] = p.rsph[(size_t)le * 16 + lane];
         if (lane < 4) {
             // lane e decodes edge e and corner e of the element's DSS descriptor
             const ElemDss &d = p.dss[le];
@@ -706,7 +738,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
         __syncthreads();
         if (!active) continue;
 
-        // ---- DSS: add the neighbours' coincident values (edgeVunpack), then * rspheremp
+        // ---- DSS: add the neighbours' coincident values (edgeVunpack; already scaled by rspheremp in sweep 1)
         if (fast) {
             v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2];
             v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2];
@@ -750,14 +782,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
                 v[pt] = sum;
             }
         }
-#pragma unroll
-        for (int t = 0; t < 16; t += 2) {
-            const double2 r = *reinterpret_cast<const double2 *>(rsph_s + t);
-            v[t] *= r.x;
-            v[t + 1] *= r.y;
-        }
-
-        laplace_slab(v, M);
+        laplace_slab(v, M); // (the rspheremp scaling was applied by sweep 1)
 
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
@@ -787,15 +812,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __
     unsigned char *stages = smem;                                  // tile ring, 1024-byte aligned (SWIZZLE_128B)
     unsigned char *extra = smem + WARPS * STAGES * TILE_BYTES;     // staging buffers (1024-aligned, SWIZZLE_32B rows) or WarpDss records
     uint64_t *bars = reinterpret_cast<uint64_t *>(extra + STRIP_EXTRA_BYTES);
-    uint64_t *nbars = bars + WARPS * STAGES;
-    double *metric_all = reinterpret_cast<double *>(nbars + WARPS * 2);
-    double *rsph_all = metric_all + WARPS * METRIC_DOUBLES;
+    double *metric_all = reinterpret_cast<double *>(bars + WARPS * (STAGES + 4)); // after tile_full, nbr_full, exp_full
 
     const int32_t strip = p.strips[blockIdx.x];
     const int first = strip >> 3, cnt = (strip & 7) + 1;
     const StripReg &rg = p.strip_reg[blockIdx.x];
-    if (rg.regular) sweep2_regular<STAGES, WARPS>(p, stages, bars, nbars, metric_all, rsph_all, extra, first, cnt, rg);
-    else sweep2_generic<STAGES, WARPS>(p, stages, bars, metric_all, rsph_all, extra, first, cnt);
+    if (rg.regular) sweep2_regular<STAGES, WARPS>(p, stages, bars, metric_all, extra, first, cnt, rg);
+    else sweep2_generic<STAGES, WARPS>(p, stages, bars, metric_all, extra, first, cnt);
 }
 
 // kernel configurations: (STAGES, WARPS, MINB)

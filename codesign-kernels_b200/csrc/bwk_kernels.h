@@ -37,7 +37,6 @@ struct SweepParams {
     int kq;                 // nlev*qsize
     int tiles_per_unit;     // tiles (of 32 slabs) per CTA work unit
     int units;              // grid y
-    int dbg;                // timing experiments only (BWK_DBG): 1 no CTA barrier, 2 no neighbour staging, 4 no mate reads -- WRONG RESULTS
 };
 
 // geometry chosen by the host for a given KQ / element count
