@@ -117,6 +117,14 @@ struct Ctx {
     cudaEvent_t ev_b = nullptr, ev_halo = nullptr, ev_misc = nullptr;
     cudaEvent_t events[NEVENTS] = {};
     std::vector<cudaEvent_t> chunk_up, chunk_done;
+    // host-buffer pipeline of the full biharmonic (bwk_biharmonic_wk_scalar_full): strips_all re-ordered
+    // by the upload chunk that completes their inputs, see build_e2e_schedule()
+    bool e2e_ready = false;
+    std::vector<int> e2e_bounds;                           // upload chunk boundaries (elements)
+    std::vector<int> e2e_group_start;                      // [nchunks+1] first strip (in the re-ordered list) of each group
+    std::vector<std::vector<std::pair<int, int>>> e2e_runs; // per group: contiguous element runs [first, end) to download
+    int32_t *d_e2e_strips = nullptr;
+    StripReg *d_e2e_reg = nullptr;
 };
 Ctx g;
 
@@ -359,6 +367,7 @@ int install_plan(Plan &&pl)
     g.have_topology = true;
     g.have_rsph = false;
     g.rsph_user = false;
+    g.e2e_ready = false;
     return 0;
 }
 
@@ -422,19 +431,67 @@ std::vector<int> make_chunks(int first0, int count)
     return b;
 }
 
-// the same for sweep 2: boundaries in STRIPS of strips_all (strips tile [0,nelem) in ascending order)
-std::vector<int> make_strip_chunks(const std::vector<int> &elem_bounds)
+// Schedule of the host-buffer pipeline.  Element chunks are uploaded in ascending order and swept
+// (sweep 1) as they arrive.  A strip can run sweep 2 as soon as sweep 1 has produced every element
+// it gathers from -- its members and their edge / corner neighbours -- i.e. after upload chunk
+// need(strip) = max chunk of those elements; strips that read rows of other ranks wait for the last
+// chunk (the halo exchange follows the last sweep 1).  Strips are grouped by need(), each group
+// is launched right after the sweep 1 of its chunk and its elements are downloaded behind it, so the
+// download of the early elements overlaps the upload of the late ones (PCIe is full duplex).  On the
+// cubed sphere only the elements along face edges that touch a later face wait long.
+int build_e2e_schedule()
 {
-    const std::vector<int32_t> &S = g.plan.strips_all;
-    std::vector<int> b;
-    size_t si = 0;
-    for (size_t c = 0; c + 1 < elem_bounds.size(); ++c) {
-        while (si < S.size() && strip_first(S[si]) < elem_bounds[c]) ++si; // first strip starting at or after the boundary
-        if (b.empty() || (int)si > b.back()) b.push_back((int)si);
+    if (g.e2e_ready) return 0;
+    const Plan &P = g.plan;
+    const std::vector<int32_t> &S = P.strips_all;
+    g.e2e_bounds = make_chunks(0, g.nelem);
+    const std::vector<int> &b = g.e2e_bounds;
+    const int nch = (int)b.size() - 1;
+    auto chunk_of = [&](int e) { return (int)(std::upper_bound(b.begin(), b.end(), e) - b.begin()) - 1; };
+    std::vector<int> need(S.size());
+    for (size_t i = 0; i < S.size(); ++i) {
+        const int f = strip_first(S[i]), n = strip_count(S[i]);
+        int hi = f + n - 1;
+        bool halo = false;
+        for (int e = f; e < f + n; ++e) {
+            const ElemDss &d = P.dss[(size_t)e];
+            for (int k = 0; k < 4; ++k) {
+                if (d.edge_src[k] >= 0) { if (d.edge_kind[k] == SRC_HALO) halo = true; else hi = std::max(hi, (int)d.edge_src[k]); }
+                if (d.diag_src[k] >= 0) { if (d.diag_kind[k] == SRC_HALO) halo = true; else hi = std::max(hi, (int)d.diag_src[k]); }
+            }
+        }
+        need[i] = halo ? nch - 1 : chunk_of(hi);
     }
-    if (b.empty() || b.front() != 0) b.insert(b.begin(), 0);
-    b.push_back((int)S.size());
-    return b;
+    std::vector<int> order(S.size());
+    for (size_t i = 0; i < S.size(); ++i) order[i] = (int)i;
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return need[(size_t)x] < need[(size_t)y]; });
+    std::vector<int32_t> hs(S.size());
+    std::vector<StripReg> hr(S.size());
+    g.e2e_group_start.assign((size_t)nch + 1, 0);
+    g.e2e_runs.assign((size_t)nch, {});
+    for (size_t k = 0; k < order.size(); ++k) {
+        const size_t i = (size_t)order[k];
+        hs[k] = S[i];
+        hr[k] = P.reg_all[i];
+        g.e2e_group_start[(size_t)need[i] + 1]++;
+        const int f = strip_first(S[i]), n = strip_count(S[i]);
+        auto &runs = g.e2e_runs[(size_t)need[i]];
+        if (!runs.empty() && runs.back().second == f) runs.back().second = f + n; // strips of a group come in element order
+        else runs.push_back({f, f + n});
+    }
+    for (int c = 0; c < nch; ++c) g.e2e_group_start[(size_t)c + 1] += g.e2e_group_start[(size_t)c];
+    free_dev(g.d_e2e_strips);
+    free_dev(g.d_e2e_reg);
+    g.d_e2e_strips = nullptr;
+    g.d_e2e_reg = nullptr;
+    if (!S.empty()) {
+        CK(cudaMalloc(&g.d_e2e_strips, sizeof(int32_t) * hs.size()));
+        CK(cudaMalloc(&g.d_e2e_reg, sizeof(StripReg) * hr.size()));
+        CK(cudaMemcpy(g.d_e2e_strips, hs.data(), sizeof(int32_t) * hs.size(), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(g.d_e2e_reg, hr.data(), sizeof(StripReg) * hr.size(), cudaMemcpyHostToDevice));
+    }
+    g.e2e_ready = true;
+    return 0;
 }
 
 int ensure_chunk_events(size_t n)
@@ -507,7 +564,7 @@ int bwk_finalize(void)
     free_dev(g.d_q); free_dev(g.d_tmp); free_dev(g.d_elem); free_dev(g.d_metric); free_dev(g.d_rsph);
     free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
     free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);
-    free_dev(g.d_send_elem); free_dev(g.d_send_row); free_dev(g.d_strips_all); free_dev(g.d_strips_dep); free_dev(g.d_strips_indep); free_dev(g.d_reg_all); free_dev(g.d_reg_dep); free_dev(g.d_reg_indep);
+    free_dev(g.d_send_elem); free_dev(g.d_send_row); free_dev(g.d_strips_all); free_dev(g.d_strips_dep); free_dev(g.d_strips_indep); free_dev(g.d_reg_all); free_dev(g.d_reg_dep); free_dev(g.d_reg_indep); free_dev(g.d_e2e_strips); free_dev(g.d_e2e_reg);
     if (g.h_partials) cudaFreeHost(g.h_partials);
     for (cudaEvent_t e : g.chunk_up) cudaEventDestroy(e);
     for (cudaEvent_t e : g.chunk_done) cudaEventDestroy(e);
@@ -604,37 +661,36 @@ int bwk_biharmonic_wk_scalar_full(const bwk_element_t *elem, double *qtens, cons
     if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
     if (upload_metric(elem, deriv, g.s_main)) return 1;
     if (compute_rspheremp()) return 1;
-    const std::vector<int> b = make_chunks(0, g.nelem);
+    if (build_e2e_schedule()) return 1;
+    const std::vector<int> &b = g.e2e_bounds;
     const size_t nch = b.size() - 1;
     if (ensure_chunk_events(nch)) return 1;
     const size_t es = (size_t)16 * g.kq;
-    // phase A: upload chunk c  ||  sweep 1 of chunk c-1
     for (size_t c = 0; c < nch; ++c) {
+        // upload chunk c, sweep 1 on it as soon as it has landed
         const size_t off = es * (size_t)b[c], n = es * (size_t)(b[c + 1] - b[c]);
         CK(cudaMemcpyAsync(g.d_q + off, qtens + off, sizeof(double) * n, cudaMemcpyHostToDevice, g.s_h2d));
         CK(cudaEventRecord(g.chunk_up[c], g.s_h2d));
         CK(cudaStreamWaitEvent(g.s_main, g.chunk_up[c], 0));
         if (sweep(MODE_SWEEP1, b[c], b[c + 1] - b[c], nullptr, g.s_main)) return 1;
-    }
-    if (g.plan.nranks > 1) {
-        CK(cudaEventRecord(g.ev_b, g.s_main));
-        CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
-        if (exchange_halo()) return 1;
-        CK(cudaEventRecord(g.ev_halo, g.s_comm));
-        CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
-    }
-    // phase B: sweep 2 of chunk c  ||  download chunk c-1   (chunks = runs of whole strips)
-    const std::vector<int> sb = make_strip_chunks(b);
-    const std::vector<int32_t> &S = g.plan.strips_all;
-    if (ensure_chunk_events(sb.size())) return 1;
-    for (size_t c = 0; c + 1 < sb.size(); ++c) {
-        const int e0 = strip_first(S[(size_t)sb[c]]);
-        const int e1 = sb[c + 1] < (int)S.size() ? strip_first(S[(size_t)sb[c + 1]]) : g.nelem;
-        const size_t off = es * (size_t)e0, n = es * (size_t)(e1 - e0);
-        if (sweep2(g.d_strips_all + sb[c], g.d_reg_all + sb[c], sb[c + 1] - sb[c], g.s_main)) return 1;
-        CK(cudaEventRecord(g.chunk_done[c], g.s_main));
-        CK(cudaStreamWaitEvent(g.s_d2h, g.chunk_done[c], 0));
-        CK(cudaMemcpyAsync(qtens + off, g.d_q + off, sizeof(double) * n, cudaMemcpyDeviceToHost, g.s_d2h));
+        if (c + 1 == nch && g.plan.nranks > 1) { // every edge row exists now: exchange the halo (bndry_exchangeV)
+            CK(cudaEventRecord(g.ev_b, g.s_main));
+            CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
+            if (exchange_halo()) return 1;
+            CK(cudaEventRecord(g.ev_halo, g.s_comm));
+            CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
+        }
+        // sweep 2 of the strips whose inputs are complete with this chunk, download behind it
+        const int s0 = g.e2e_group_start[c], s1 = g.e2e_group_start[c + 1];
+        if (s1 > s0) {
+            if (sweep2(g.d_e2e_strips + s0, g.d_e2e_reg + s0, s1 - s0, g.s_main)) return 1;
+            CK(cudaEventRecord(g.chunk_done[c], g.s_main));
+            CK(cudaStreamWaitEvent(g.s_d2h, g.chunk_done[c], 0));
+            for (const std::pair<int, int> &r : g.e2e_runs[c]) {
+                const size_t roff = es * (size_t)r.first, rn = es * (size_t)(r.second - r.first);
+                CK(cudaMemcpyAsync(qtens + roff, g.d_q + roff, sizeof(double) * rn, cudaMemcpyDeviceToHost, g.s_d2h));
+            }
+        }
     }
     CK(cudaStreamSynchronize(g.s_d2h));
     CK(cudaStreamSynchronize(g.s_main));
