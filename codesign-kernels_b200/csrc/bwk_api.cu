@@ -231,10 +231,18 @@ int upload_metric(const bwk_element_t *elem, const bwk_derivative_t *deriv, cuda
         g.launches++;
         g.have_metric = true;
         g.gen_nelem_global = -1;
-        g.h_spheremp.resize((size_t)16 * g.nelem);
         const double *e = reinterpret_cast<const double *>(elem);
-        for (int64_t ie = 0; ie < g.nelem; ++ie) std::memcpy(&g.h_spheremp[(size_t)16 * ie], e + ie * ELEM_DOUBLES + 64, 16 * sizeof(double));
-        if (!g.rsph_user) g.have_rsph = false; // a caller-supplied rspheremp (bwk_set_rspheremp) stays in force
+        bool same = g.h_spheremp.size() == (size_t)16 * g.nelem;
+        g.h_spheremp.resize((size_t)16 * g.nelem);
+        for (int64_t ie = 0; ie < g.nelem; ++ie) {
+            double *dst = &g.h_spheremp[(size_t)16 * ie];
+            const double *src = e + ie * ELEM_DOUBLES + 64;
+            if (same && std::memcmp(dst, src, 16 * sizeof(double)) != 0) same = false;
+            std::memcpy(dst, src, 16 * sizeof(double));
+        }
+        // rspheremp = 1/DSS(spheremp) stays valid while spheremp is unchanged (HOMME computes it once at
+        // start-up); a caller-supplied rspheremp (bwk_set_rspheremp) stays in force regardless
+        if (!g.rsph_user && !same) g.have_rsph = false;
     }
     if (deriv) CK(set_dvv(&deriv->Dvv[0][0], st));
     return 0;
@@ -423,7 +431,8 @@ std::vector<int> make_chunks(int first0, int count)
 {
     const double bytes_per_elem = 128.0 * g.kq;
     const double total = bytes_per_elem * count;
-    double chunk_bytes = std::min(128.0 * 1048576.0, std::max(1048576.0, total / 8.0));
+    static const double max_chunk_mb = std::getenv("BWK_CHUNK_MB") ? std::atof(std::getenv("BWK_CHUNK_MB")) : 128.0; // tuning knob
+    double chunk_bytes = std::min(max_chunk_mb * 1048576.0, std::max(1048576.0, total / 8.0));
     int per = (int)std::max(1.0, std::floor(chunk_bytes / bytes_per_elem));
     std::vector<int> b;
     for (int e = first0; e < first0 + count; e += per) b.push_back(e);
@@ -772,7 +781,7 @@ int bwk_initialize_data_device(int64_t nelemd_global, int64_t elem_first, int se
         CK(cudaStreamSynchronize(g.s_main));
         g.h_spheremp.resize((size_t)16 * g.nelem);
         for (int64_t ie = 0; ie < g.nelem; ++ie) std::memcpy(&g.h_spheremp[(size_t)16 * ie], &he[(size_t)(ie * ELEM_DOUBLES + 64)], 16 * sizeof(double));
-        g.have_rsph = false;
+        if (!g.rsph_user) g.have_rsph = false; // a caller-supplied rspheremp stays in force until the topology changes
         g.gen_nelem_global = nelemd_global;
         g.gen_elem_first = elem_first;
         g.gen_seed_mode = seed_mode;
