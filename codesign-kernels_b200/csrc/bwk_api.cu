@@ -144,7 +144,7 @@ int get_encode()
 }
 
 int make_map(CUtensorMap *m, void *base, int rank, const uint64_t *dims, const uint64_t *strides_bytes /*rank-1*/, const uint32_t *box,
-             CUtensorMapSwizzle swz)
+             CUtensorMapSwizzle swz, CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_128B)
 {
     if (get_encode()) return 1;
     cuuint64_t gd[5], gs[4];
@@ -152,7 +152,7 @@ int make_map(CUtensorMap *m, void *base, int rank, const uint64_t *dims, const u
     for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
     for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
     CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, (cuuint32_t)rank, base, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
-                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                          promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with CUresult %d (rank %d, dims %llu %llu %llu)", (int)r, rank,
                                        (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)(rank > 2 ? dims[2] : 0));
     return 0;
@@ -367,6 +367,12 @@ int install_plan(Plan &&pl)
         const uint64_t str[2] = {128, (uint64_t)g.kq * 128};
         const uint32_t box[3] = {4, TILE_SLABS, 1};
         if (make_map(&g.sp.map_rows, g.d_tmp, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+        g.sp.map_halo = g.sp.map_rows;
+        if (nrecv > 0) {
+            const uint64_t hdims[3] = {4, (uint64_t)g.kq, (uint64_t)nrecv};
+            const uint64_t hstr[2] = {32, (uint64_t)g.kq * 32};
+            if (make_map(&g.sp.map_halo, g.d_halo, 3, hdims, hstr, box, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+        }
     }
     g.sp.tmp = g.d_tmp;
     g.sp.halo = g.d_halo;

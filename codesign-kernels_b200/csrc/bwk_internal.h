@@ -34,22 +34,34 @@ struct ElemDss {
 };
 static_assert(sizeof(ElemDss) == 64, "ElemDss must be 64 bytes");
 
-// Gather sources of a REGULAR strip: every member is a face-interior element of a row-major
-// structured patch -- all neighbours local, none reversed, S/N neighbours face us with their N/S
-// rows, strip-end W/E neighbours with their E/W columns, four contributors per corner in the
-// standard order, and the diagonal contributors of interior corners are the S/N neighbours of the
-// strip mates.  Such a strip runs the fully asynchronous (cp.async-staged) sweep-2 path; any other
-// strip runs the generic descriptor-driven path.  Element indices are local.
+// Gather sources of a REGULAR strip, the one the fully asynchronous sweep-2 path can run: every member's
+// S and N neighbour faces it with a natural j-row of a local slab (or with a received halo row) in the
+// same orientation, so the row can be staged by TMA; members are linked W-E through shared memory; the
+// diagonal contributors of interior corners are the ends of the strip mates' S/N neighbour rows.  The two
+// strip ends are free: any source (column or row of a local slab, halo row, either orientation) and any
+// corner multiplicity / summation order, so strips along face edges and partition cuts qualify too.
+// Any other strip runs the generic descriptor-driven path.  Element indices are local.
 struct StripReg {
     int32_t regular;          // 0: use the generic path (other fields unused)
-    int32_t s_src[4];         // S neighbour of member w (its N row is read)
-    int32_t n_src[4];         // N neighbour of member w (its S row is read)
-    int32_t w_src, e_src;     // W neighbour of the first member (E column), E neighbour of the last (W column)
-    int32_t dsw, dnw;         // SW / NW diagonal contributors of the first member (their points 15 / 3)
-    int32_t dse, dne;         // SE / NE diagonal contributors of the last member  (their points 12 / 0)
-    int32_t pad;
+    int32_t s_src[4];         // S neighbour of member w: local element, or halo slot when s_c0 == ROW_IN_HALO
+    int32_t n_src[4];         // N neighbour of member w
+    uint8_t s_c0[4];          // first double of the facing row inside the neighbour's slab (0 or 12), or ROW_IN_HALO
+    uint8_t n_c0[4];
+    uint8_t corner_n[4][4];   // [member][corner SW,SE,NW,NE]: number of contributors (own included)
+    uint8_t corner_perm[4][4];// summation order, as ElemDss::corner_perm
+    int32_t end_src[2];       // W neighbour of the first member / E neighbour of the last: local element or halo slot
+    uint8_t end_kind[2];      // SRC_TMP (a j-row), SRC_TMPCOL (an i-column) or SRC_HALO
+    uint8_t end_row[2];       // row 0/3 (SRC_TMP), side 0=W/1=E (SRC_TMPCOL)
+    uint8_t end_rev[2];       // 1 = runs the other way
+    uint8_t all_std;          // 1 = every corner has four contributors in the row-major interior order (fast sums)
+    uint8_t pad0;
+    int32_t diag_src[4];      // SW, NW of the first member, SE, NE of the last: local element / halo slot, -1 = none
+    uint8_t diag_kind[4];     // SRC_TMPCOL (local slab, diag_pt = point 0..15) or SRC_HALO (diag_pt = position in the row)
+    uint8_t diag_pt[4];
+    uint8_t pad1[12];
 };
-static_assert(sizeof(StripReg) == 64, "StripReg must be 64 bytes");
+static_assert(sizeof(StripReg) == 128, "StripReg must be 128 bytes");
+constexpr int ROW_IN_HALO = 255;
 
 struct RowRef {
     int64_t elem; // global element id

@@ -348,7 +348,7 @@ static_assert(ROWBUF_BYTES >= STRIP_MAX * (int)sizeof(WarpDss) && STRIP_EXTRA_BY
 template <int STAGES, int WARPS>
 constexpr int strip_smem_bytes()
 {
-    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 4) * 8 + WARPS * METRIC_DOUBLES * 8 + 6 * 8 + 64;
+    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 4) * 8 + WARPS * METRIC_DOUBLES * 8 + 6 * 16 + 64;
 }
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t src_bytes)
@@ -365,7 +365,7 @@ __device__ __forceinline__ void cp_async_arrive(uint32_t bar)
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
-// ---- regular path: a strip of face-interior elements (StripReg).  No CTA-wide barrier inside the
+// ---- regular path (StripReg): S/N neighbour rows stageable by TMA, free strip ends.  No CTA-wide barrier inside the
 // tile loop: every warp runs its own pipeline.
 //   * own tile: TMA, STAGES-deep ring, results written in place, TMA store (as in sweep 1);
 //   * facing rows of the S/N neighbours: two TMA boxes {4 doubles, 32 slabs} per tile into rowbuf;
@@ -392,17 +392,30 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     unsigned char *endbuf = extra + ROWBUF_BYTES;         // [set][2][6][32][8 B]
     uint64_t *nbars = bars + WARPS * STAGES;              // nbr_full [warp][2]
     uint64_t *cbars = nbars + WARPS * 2;                  // cons     [warp][2]
-    const double **endsrc = reinterpret_cast<const double **>(metric_all + STRIP_MAX * METRIC_DOUBLES); // W col, SW, NW, E col, SE, NE sources (slab 0)
+    // sources of the two strip ends, decoded once per CTA: [W column, SW, NW, E column, SE, NE]
+    struct EndSrc { const double *p; int32_t sstride, tstride; }; // doubles per slab / per position along the edge
+    EndSrc *endsrc = reinterpret_cast<EndSrc *>(metric_all + STRIP_MAX * METRIC_DOUBLES);
 
     const bool w_end = warp == 0, e_end = warp == cnt - 1;
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 6) {
+        const int k = threadIdx.x, side = k / 3, which = k % 3; // which: 0 column, 1 S-side diagonal, 2 N-side diagonal
         const size_t ekq = (size_t)p.kq * 16;
-        endsrc[0] = p.tmp + (size_t)rg.w_src * ekq + 3;  // W neighbour's E column
-        endsrc[1] = p.tmp + (size_t)rg.dsw * ekq + 15;
-        endsrc[2] = p.tmp + (size_t)rg.dnw * ekq + 3;
-        endsrc[3] = p.tmp + (size_t)rg.e_src * ekq;      // E neighbour's W column
-        endsrc[4] = p.tmp + (size_t)rg.dse * ekq + 12;
-        endsrc[5] = p.tmp + (size_t)rg.dne * ekq;
+        EndSrc e{nullptr, 0, 0};
+        if (which == 0) {
+            const int src = rg.end_src[side], kind = rg.end_kind[side], row = rg.end_row[side];
+            if (kind == SRC_TMPCOL) e = {p.tmp + (size_t)src * ekq + (row ? 3 : 0), 16, 4};
+            else if (kind == SRC_TMP) e = {p.tmp + (size_t)src * ekq + 4 * row, 16, 1};
+            else e = {p.halo + (size_t)src * p.kq * 4, 4, 1};
+            if (rg.end_rev[side]) { e.p += 3 * e.tstride; e.tstride = -e.tstride; }
+        } else {
+            const int d = side * 2 + (which - 1);
+            const int src = rg.diag_src[d];
+            if (src >= 0) {
+                if (rg.diag_kind[d] == SRC_HALO) e = {p.halo + (size_t)src * p.kq * 4 + rg.diag_pt[d], 4, 0};
+                else e = {p.tmp + (size_t)src * ekq + rg.diag_pt[d], 16, 0};
+            }
+        }
+        endsrc[k] = e;
     }
     if (lane == 0) {
 #pragma unroll
@@ -432,6 +445,16 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     const uint32_t cbar0 = smem_u32(&cbars[warp * 2]);
     const int swz = (lane >> 2) & 1; // SWIZZLE_32B: 16-byte chunk c of 32-byte row r sits at chunk c ^ ((r >> 2) & 1)
     const int elemS = rg.s_src[warp & 3], elemN = rg.n_src[warp & 3];
+    const int rawS = rg.s_c0[warp & 3], rawN = rg.n_c0[warp & 3];
+    const CUtensorMap *mapS = rawS == ROW_IN_HALO ? &p.map_halo : &p.map_rows, *mapN = rawN == ROW_IN_HALO ? &p.map_halo : &p.map_rows;
+    const int c0S = rawS == ROW_IN_HALO ? 0 : rawS, c0N = rawN == ROW_IN_HALO ? 0 : rawN;
+    const bool std_corners = rg.all_std != 0;
+    uint32_t cn_pack = 0, cperm_pack = 0; // this member's four corner counts / summation orders, one byte each
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        cn_pack |= (uint32_t)rg.corner_n[warp & 3][c] << (8 * c);
+        cperm_pack |= (uint32_t)rg.corner_perm[warp & 3][c] << (8 * c);
+    }
     const uint64_t pol_out = l2_policy_evict_first(); // the output is never read again by this kernel
 
     auto issue_tile = [&](int n, int s) {
@@ -447,27 +470,22 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         if (lane == 0) {
             const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2048);
             mbar_expect_tx(nbar, 2048u);
-            tma_load_3d(rb, &p.map_rows, 12, kq0, elemS, nbar);       // S neighbour's N row
-            tma_load_3d(rb + 1024, &p.map_rows, 0, kq0, elemN, nbar); // N neighbour's S row
+            tma_load_3d(rb, mapS, c0S, kq0, elemS, nbar);        // the S neighbour's facing row (its N row in a face interior)
+            tma_load_3d(rb + 1024, mapN, c0N, kq0, elemN, nbar); // the N neighbour's facing row
         }
         if (w_end || e_end) {
             const uint32_t ok8 = kq0 + lane < p.kq ? 8u : 0u;
-            const size_t o = ((size_t)kq0 + lane) * 16;
-            if (w_end) {
-                const uint32_t eb = smem_u32(endbuf) + (uint32_t)(q * 3072 + lane * 8);
-                const double *src = endsrc[0] + o;
+            const int64_t slab = (int64_t)kq0 + lane;
 #pragma unroll
-                for (int t = 0; t < 4; ++t) cp_async8(eb + t * 256, src + 4 * t, ok8);
-                cp_async8(eb + 4 * 256, endsrc[1] + o, ok8);
-                cp_async8(eb + 5 * 256, endsrc[2] + o, ok8);
-            }
-            if (e_end) {
-                const uint32_t eb = smem_u32(endbuf) + (uint32_t)(q * 3072 + 1536 + lane * 8);
-                const double *src = endsrc[3] + o;
+            for (int side = 0; side < 2; ++side) {
+                if (side == 0 ? !w_end : !e_end) continue;
+                const uint32_t eb = smem_u32(endbuf) + (uint32_t)(q * 3072 + side * 1536 + lane * 8);
+                const EndSrc c = endsrc[3 * side], d0 = endsrc[3 * side + 1], d1 = endsrc[3 * side + 2];
+                const double *src = c.p + slab * c.sstride;
 #pragma unroll
-                for (int t = 0; t < 4; ++t) cp_async8(eb + t * 256, src + 4 * t, ok8);
-                cp_async8(eb + 4 * 256, endsrc[4] + o, ok8);
-                cp_async8(eb + 5 * 256, endsrc[5] + o, ok8);
+                for (int t = 0; t < 4; ++t) cp_async8(eb + t * 256, src + t * c.tstride, ok8);
+                if (d0.p) cp_async8(eb + 4 * 256, d0.p + slab * d0.sstride, ok8); // absent at a cube corner (three elements)
+                if (d1.p) cp_async8(eb + 5 * 256, d1.p + slab * d1.sstride, ok8);
             }
         }
         cp_async_arrive(nbar);
@@ -548,10 +566,31 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2];
         v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2];
         v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2];
-        v[0] = ((dg[0] + nb[EDGE_S][0]) + nb[EDGE_W][0]) + v[0];       // PERM_SW
-        v[3] = ((nb[EDGE_S][3] + dg[1]) + v[3]) + nb[EDGE_E][0];       // PERM_SE
-        v[12] = ((nb[EDGE_W][3] + v[12]) + dg[2]) + nb[EDGE_N][0];     // PERM_NW
-        v[15] = ((v[15] + nb[EDGE_E][3]) + nb[EDGE_N][3]) + dg[3];     // PERM_NE
+        if (std_corners) {
+            v[0] = ((dg[0] + nb[EDGE_S][0]) + nb[EDGE_W][0]) + v[0];       // PERM_SW
+            v[3] = ((nb[EDGE_S][3] + dg[1]) + v[3]) + nb[EDGE_E][0];       // PERM_SE
+            v[12] = ((nb[EDGE_W][3] + v[12]) + dg[2]) + nb[EDGE_N][0];     // PERM_NW
+            v[15] = ((v[15] + nb[EDGE_E][3]) + nb[EDGE_N][3]) + dg[3];     // PERM_NE
+        } else { // face edges, cube corners, partition cuts: up to four contributors in the plan's order
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int pt = c == 0 ? 0 : (c == 1 ? 3 : (c == 2 ? 12 : 15));
+                const double cv0 = v[pt];
+                const double cv1 = nb[c < 2 ? EDGE_S : EDGE_N][(c & 1) ? 3 : 0];
+                const double cv2 = nb[(c & 1) ? EDGE_E : EDGE_W][c < 2 ? 0 : 3];
+                const double cv3 = dg[c];
+                const int perm = (cperm_pack >> (8 * c)) & 255, cn = (cn_pack >> (8 * c)) & 255;
+                auto pick = [&](int k) {
+                    const int w = (perm >> (2 * k)) & 3;
+                    return w == 0 ? cv0 : (w == 1 ? cv1 : (w == 2 ? cv2 : cv3));
+                };
+                double sum = pick(0);
+                if (cn > 1) sum = sum + pick(1);
+                if (cn > 2) sum = sum + pick(2);
+                if (cn > 3) sum = sum + pick(3);
+                v[pt] = sum;
+            }
+        }
 
         // the mates' values have been consumed (the sums above depend on them): tell the mates.
         // The asm operand ties the arrival to the corner sums so that it cannot be scheduled above the loads.
@@ -636,13 +675,23 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
             if (lane == 0) wd.fast = all_ok == 0xfu ? 1 : 0;
         }
     }
+    // Strip members are linked E->W by construction (bwk_plan.cpp), so warp w reads the facing column of
+    // the tiles of warps w-1 and w+1 and they read its own: same consumed-barrier protocol as the regular path.
+    const bool has_left = active && warp > 0, has_right = active && warp < cnt - 1;
+    uint64_t *cbars = bars + WARPS * STAGES + WARPS * 2; // cons [warp][2]
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
+        const uint32_t nmates = (has_left ? 1u : 0u) + (has_right ? 1u : 0u);
+        mbar_init(smem_u32(&cbars[warp * 2]), nmates ? 32u * nmates : 1u);
+        mbar_init(smem_u32(&cbars[warp * 2 + 1]), nmates ? 32u * nmates : 1u);
         fence_barrier_init();
         fence_proxy_async();
     }
-    __syncthreads();
+    __syncthreads(); // the only CTA-wide barrier
+    if (!active) return;
+    if ((has_left && wd.edge_mode[EDGE_W] != EM_MATE_LEFT) || (has_right && wd.edge_mode[EDGE_E] != EM_MATE_RIGHT)) __trap(); // plan/kernel disagree
+    const uint32_t cbar0 = smem_u32(&cbars[warp * 2]);
 
     // ---- all warps walk the same tiles t0 .. t1-1, each for its own element
     const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
@@ -657,7 +706,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
         mbar_expect_tx(bar, (uint32_t)TILE_BYTES);
         tma_load_3d(dst, &p.map_tmp, 0, (t0 + n) * TILE_SLABS, le, bar);
     };
-    if (active && lane == 0) {
+    if (lane == 0) {
         const int pre = my_n < STAGES ? my_n : STAGES;
         for (int n = 0; n < pre; ++n) issue_load(n, n);
     }
@@ -672,8 +721,10 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
         unsigned char *row = stages + ((size_t)warp * STAGES + s) * SB + lane * 128;
         double v[16], nb[4][4], dg[4];
 
-        const bool fast = active && wd.fast != 0;
-        if (active) {
+        const int q = n & 1;
+        const uint32_t qparity = (uint32_t)((n >> 1) & 1);
+        const bool fast = wd.fast != 0;
+        {
             // ---- contributors that live in global memory: issue the loads before the tile wait
             const bool live = kq0 + lane < p.kq;
             const size_t slab = (size_t)(kq0 + lane);
@@ -734,9 +785,6 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
                 for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(mrow + (((2 * t) ^ sw) << 4));
             }
         }
-        // every warp has read what it needs from the stage-s tiles: they may now be overwritten in place
-        __syncthreads();
-        if (!active) continue;
 
         // ---- DSS: add the neighbours' coincident values (edgeVunpack; already scaled by rspheremp in sweep 1)
         if (fast) {
@@ -782,25 +830,31 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
                 v[pt] = sum;
             }
         }
+        // the mates' columns have been consumed (the sums above depend on them): tell the mates
+        if (has_left) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 - 16 + q * 8), "d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]) : "memory");
+        if (has_right) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 + 16 + q * 8), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
+
         laplace_slab(v, M); // (the rspheremp scaling was applied by sweep 1)
 
+        // both mates must have read this tile's columns before it is overwritten in place
+        if (has_left || has_right) mbar_wait(cbar0 + q * 8, qparity);
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
         fence_proxy_async();
         __syncwarp();
 
         if (lane == 0) {
-            tma_store_3d(&p.map_q, 0, kq0, le, stage0 + s * SB);
+            tma_store_3d_hint(&p.map_q, 0, kq0, le, stage0 + s * SB, l2_policy_evict_first());
             bulk_commit();
             // refill the stage tile n-1 used: its store has read shared memory, and the mates
-            // finished reading it before the __syncthreads of iteration n-1
+            // had consumed it before this warp overwrote it (cons wait of iteration n-1)
             if (n >= 1 && n - 1 + STAGES < my_n) {
                 bulk_wait_read<1>();
                 issue_load(n - 1 + STAGES, (n - 1) % STAGES);
             }
         }
     }
-    if (active && lane == 0) bulk_wait<0>();
+    if (lane == 0) bulk_wait<0>();
 }
 
 template <int STAGES, int WARPS, int MINB>

@@ -23,6 +23,7 @@ struct SweepParams {
     CUtensorMap map_q;      // qtens   as {16, KQ, nelem}, box {16,32,1}, SWIZZLE_128B
     CUtensorMap map_tmp;    // tmp     same shape (sweep-1 output)
     CUtensorMap map_rows;   // tmp as {16, KQ, nelem}, box {4,32,1}, SWIZZLE_32B: one edge row (32 B) of 32 consecutive slabs
+    CUtensorMap map_halo;   // received edge rows as {4, KQ, nrows}, box {4,32,1}, SWIZZLE_32B (aliases map_rows when there is no halo)
     const double *metric;   // [nelem][64] folded metric
     const double *rsph;     // [nelem][16]
     const ElemDss *dss;     // [nelem]

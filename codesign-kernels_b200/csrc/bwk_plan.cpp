@@ -330,35 +330,64 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
     auto regular_strip = [&](int32_t first, int n) {
         StripReg r;
         std::memset(&r, 0, sizeof r);
-        const int diag_side[4] = {1, 0, 1, 0}, diag_pos[4] = {3, 3, 0, 0}; // SW:pt15 SE:pt12 NW:pt3 NE:pt0
+        bool all_std = true;
         for (int w = 0; w < n; ++w) {
             const ElemDss &d = pl.dss[(size_t)(first + w)];
-            const bool sn_ok = d.edge_src[EDGE_S] >= 0 && d.edge_kind[EDGE_S] == SRC_TMP && d.edge_row[EDGE_S] == 3 && !d.edge_rev[EDGE_S] &&
-                               d.edge_src[EDGE_N] >= 0 && d.edge_kind[EDGE_N] == SRC_TMP && d.edge_row[EDGE_N] == 0 && !d.edge_rev[EDGE_N];
-            const bool we_ok = d.edge_src[EDGE_W] >= 0 && d.edge_kind[EDGE_W] == SRC_TMPCOL && d.edge_row[EDGE_W] == 1 && !d.edge_rev[EDGE_W] &&
-                               d.edge_src[EDGE_E] >= 0 && d.edge_kind[EDGE_E] == SRC_TMPCOL && d.edge_row[EDGE_E] == 0 && !d.edge_rev[EDGE_E];
-            if (!sn_ok || !we_ok) return r;
-            if (w > 0 && d.edge_src[EDGE_W] != first + w - 1) return r;
-            if (w < n - 1 && d.edge_src[EDGE_E] != first + w + 1) return r;
-            for (int c = 0; c < 4; ++c)
-                if (d.corner_n[c] != 4 || d.corner_perm[c] != std_perm[c] || d.diag_src[c] < 0 || d.diag_kind[c] != SRC_TMPCOL ||
-                    d.diag_row[c] != diag_side[c] || d.diag_pos[c] != diag_pos[c])
-                    return r;
-            r.s_src[w] = d.edge_src[EDGE_S];
-            r.n_src[w] = d.edge_src[EDGE_N];
+            const ElemTopo &T = topo[(size_t)(first + w)];
+            // S and N: a natural j-row of a local slab, or a halo row, same orientation
+            for (int ed = EDGE_S; ed <= EDGE_N; ++ed) {
+                if (d.edge_src[ed] < 0 || d.edge_rev[ed]) return r;
+                uint8_t c0;
+                if (d.edge_kind[ed] == SRC_TMP) c0 = (uint8_t)(4 * d.edge_row[ed]);
+                else if (d.edge_kind[ed] == SRC_HALO) c0 = (uint8_t)ROW_IN_HALO;
+                else return r; // the neighbour faces us with an i-column: not a TMA row
+                (ed == EDGE_S ? r.s_src : r.n_src)[w] = d.edge_src[ed];
+                (ed == EDGE_S ? r.s_c0 : r.n_c0)[w] = c0;
+            }
+            // interior links are mate links by construction of the strip; re-check
+            if (w > 0 && !(d.edge_src[EDGE_W] == first + w - 1 && d.edge_kind[EDGE_W] == SRC_TMPCOL && d.edge_row[EDGE_W] == 1 && !d.edge_rev[EDGE_W])) return r;
+            if (w < n - 1 && !(d.edge_src[EDGE_E] == first + w + 1 && d.edge_kind[EDGE_E] == SRC_TMPCOL && d.edge_row[EDGE_E] == 0 && !d.edge_rev[EDGE_E])) return r;
+            // interior corners: the diagonal contributor must be the facing end of the mate's S/N neighbour row
+            // (corner_gp[c] = {own, S/N neighbour's point, W/E neighbour's point, diagonal point}, -1 = none)
+            if (w > 0) {
+                const ElemTopo &L = topo[(size_t)(first + w - 1)];
+                if (T.corner_gp[0][3] >= 0 && T.corner_gp[0][3] != L.corner_gp[1][1]) return r; // SW diag == east end of the left mate's S row
+                if (T.corner_gp[2][3] >= 0 && T.corner_gp[2][3] != L.corner_gp[3][1]) return r; // NW diag == east end of its N row
+            }
+            if (w < n - 1) {
+                const ElemTopo &R = topo[(size_t)(first + w + 1)];
+                if (T.corner_gp[1][3] >= 0 && T.corner_gp[1][3] != R.corner_gp[0][1]) return r; // SE diag == west end of the right mate's S row
+                if (T.corner_gp[3][3] >= 0 && T.corner_gp[3][3] != R.corner_gp[2][1]) return r; // NE diag == west end of its N row
+            }
+            for (int c = 0; c < 4; ++c) {
+                r.corner_n[w][c] = d.corner_n[c];
+                r.corner_perm[w][c] = d.corner_perm[c];
+                if (d.corner_n[c] != 4 || d.corner_perm[c] != std_perm[c]) all_std = false;
+            }
         }
-        for (int w = 0; w < n; ++w) {
-            const ElemDss &d = pl.dss[(size_t)(first + w)];
-            if (w > 0 && (d.diag_src[0] != r.s_src[w - 1] || d.diag_src[2] != r.n_src[w - 1])) return r;
-            if (w < n - 1 && (d.diag_src[1] != r.s_src[w + 1] || d.diag_src[3] != r.n_src[w + 1])) return r;
-        }
+        // the two strip ends: any source
         const ElemDss &d0 = pl.dss[(size_t)first], &d1 = pl.dss[(size_t)(first + n - 1)];
-        r.w_src = d0.edge_src[EDGE_W];
-        r.e_src = d1.edge_src[EDGE_E];
-        r.dsw = d0.diag_src[0];
-        r.dnw = d0.diag_src[2];
-        r.dse = d1.diag_src[1];
-        r.dne = d1.diag_src[3];
+        const ElemDss *de[2] = {&d0, &d1};
+        const int end_edge[2] = {EDGE_W, EDGE_E};
+        for (int k = 0; k < 2; ++k) {
+            const ElemDss &d = *de[k];
+            const int ed = end_edge[k];
+            if (d.edge_src[ed] < 0) return r; // open boundary: generic path
+            r.end_src[k] = d.edge_src[ed];
+            r.end_kind[k] = d.edge_kind[ed];
+            r.end_row[k] = d.edge_row[ed];
+            r.end_rev[k] = d.edge_rev[ed];
+        }
+        const int dcorner[4] = {0, 2, 1, 3}; // SW, NW of the first member; SE, NE of the last
+        for (int k = 0; k < 4; ++k) {
+            const ElemDss &d = k < 2 ? d0 : d1;
+            const int c = dcorner[k];
+            r.diag_src[k] = d.diag_src[c];
+            if (d.diag_src[c] < 0) continue;
+            r.diag_kind[k] = d.diag_kind[c];
+            r.diag_pt[k] = d.diag_kind[c] == SRC_HALO ? d.diag_pos[c] : (uint8_t)((d.diag_row[c] ? 3 : 0) + 4 * d.diag_pos[c]);
+        }
+        r.all_std = all_std ? 1 : 0;
         r.regular = 1;
         return r;
     };

@@ -99,20 +99,16 @@ def test_strips_tile_the_elements_and_are_west_east_chains(bwk, ne, nranks):
         if nranks == 1 and ne % 4 == 0:
             assert np.all(c == 4)  # face rows are cut into full strips
         if nranks == 1:
-            # "regular" (fully asynchronous kernel path): every face-interior strip must be regular;
-            # a regular strip must have, for every member, S/N/W/E neighbours facing it with the
-            # opposite edge in the same orientation and four 4-element corners (read off the ids).
-            # Face-edge strips whose cross-face neighbour happens to be aligned (e.g. top row of
-            # face 3 against the bottom row of face 4) qualify as well.
+            # "regular" (fully asynchronous kernel path): every face-interior strip must be regular, and
+            # a regular strip must have, for every member, S and N neighbours that face it with one of
+            # their natural j-rows in the same orientation (so that TMA can stage the row) -- read off
+            # the ids, independently of the plan.  The strip ends are free (face edges qualify).
             reg = pl.strip_regular
             rows = {}
             for e in range(n):
-                rows.setdefault(("S", tuple(g[e][0, :])), []).append(e)
-                rows.setdefault(("N", tuple(g[e][3, :])), []).append(e)
-                rows.setdefault(("W", tuple(g[e][:, 0])), []).append(e)
-                rows.setdefault(("E", tuple(g[e][:, 3])), []).append(e)
-            mult = np.bincount(np.unique(g.reshape(-1), return_inverse=True)[1])
-            inv = np.unique(g.reshape(-1), return_inverse=True)[1].reshape(n, 4, 4)
+                rows.setdefault(tuple(g[e][0, :]), []).append(e)
+                rows.setdefault(tuple(g[e][3, :]), []).append(e)
+            nreg = 0
             for a, k, r in zip(f, c, reg):
                 ie = (np.arange(a, a + k) % (ne * ne)) % ne
                 je = (np.arange(a, a + k) % (ne * ne)) // ne
@@ -120,12 +116,13 @@ def test_strips_tile_the_elements_and_are_west_east_chains(bwk, ne, nranks):
                 if interior:
                     assert r, (a, k, r)
                 if r:
+                    nreg += 1
                     for e in range(a, a + k):
-                        assert len(rows.get(("N", tuple(g[e][0, :])), [])) == 1  # S neighbour faces with its N row
-                        assert len(rows.get(("S", tuple(g[e][3, :])), [])) == 1
-                        assert len(rows.get(("E", tuple(g[e][:, 0])), [])) == 1
-                        assert len(rows.get(("W", tuple(g[e][:, 3])), [])) == 1
-                        assert all(mult[inv[e][j, i]] == 4 for j in (0, 3) for i in (0, 3))
+                        assert len([x for x in rows[tuple(g[e][0, :])] if x != e]) == 1  # S neighbour: same ids, same order, as a j-row
+                        assert len([x for x in rows[tuple(g[e][3, :])] if x != e]) == 1
+            if ne >= 8:
+                # rows 1..ne-2 of every face are entirely regular now (face-edge columns included)
+                assert nreg >= 6 * (ne - 2) * ((ne + 3) // 4)
         fd, cd = pl.strips(1)
         fi, ci = pl.strips(2)
         assert cd.sum() == pl.dependent_elems and cd.sum() + ci.sum() == cnt
