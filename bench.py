@@ -303,10 +303,18 @@ def main():
                     "kernel": dom, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_sweep_local,
                     "step_frac_of_32B_per_update": (2 * bytes_sweep_local) / (ms_per_step * 1e-3) / 1e9 / peak,
                     "frac_of_nominal_8TBs": ach / 8000.0, "kernels": kernels}
+        # DRAM bytes per launch from the committed ncu --set full capture (profiles/traffic.json, taken at a
+        # smaller cubed sphere: ncu replays every kernel ~40x), scaled by the number of slabs of this launch
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             try:
-                roofline["traffic"] = json.load(open(tr)).get(dom.split()[0])
+                tj = json.load(open(tr))
+                want = "sweep2_strip_kernel" if dom.startswith("sweep2") else "sweep_kernel<1"
+                for kname, rec in tj["kernels"].items():
+                    if want in kname:
+                        roofline["traffic"] = rec["dram_bytes_per_slab"] * kq * count
+                        roofline["traffic_note"] = (f"dram__bytes_read+write of {kname} in {tj['source']} ({tj['config']}) = "
+                                                    f"{rec['dram_bytes_per_slab']:.1f} B/slab, scaled to this launch's {kq * count} slabs")
             except Exception:
                 pass
 
