@@ -81,6 +81,12 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
                  : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2, int c3, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+                 : "memory");
+}
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, int c0, int c1, int c2, uint32_t src)
 {
     asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
@@ -337,18 +343,19 @@ enum : int { EM_NONE = 0, EM_ROW = 1, EM_COL = 2, EM_MATE_LEFT = 3, EM_MATE_RIGH
 // Shared memory of the strip kernel, in order (offsets from a 1024-byte aligned base):
 //   tiles   [warp][stage][4 KB]                        TMA destination, SWIZZLE_128B, results written in place
 //   rowbuf  [set 2][warp][S,N][32 slabs][32 B]         facing rows of the S/N neighbours, TMA destination, SWIZZLE_32B
-//   endbuf  [set 2][W end,E end][6 values][32 slabs]   facing column + two diagonal corners of the strip-end neighbours (cp.async)
-//   barriers: tile_full [warp][stage], nbr_full [warp][2], cons [warp][2]
-//   metric [warp][64], endsrc [6]
+//   endbuf  [W end,E end][column: 4 x 512 B | diagonal 512 B | diagonal 512 B]   strip-end neighbours, TMA destination, single buffered
+//   barriers: tile_full [warp][stage], nbr_full [warp][2], cons [warp][2], end_full [warp]
+//   metric [warp][64], endtma [6]
 // The generic path keeps its per-warp descriptors (WarpDss) in the rowbuf area.
 constexpr int ROWBUF_BYTES = 2 * STRIP_MAX * 2 * 32 * 32;
-constexpr int ENDBUF_BYTES = 2 * 2 * 6 * 32 * 8;
+constexpr int END_SIDE_BYTES = 2048 + 2 * 512;
+constexpr int ENDBUF_BYTES = 2 * END_SIDE_BYTES;
 constexpr int STRIP_EXTRA_BYTES = ROWBUF_BYTES + ENDBUF_BYTES;
 static_assert(ROWBUF_BYTES >= STRIP_MAX * (int)sizeof(WarpDss) && STRIP_EXTRA_BYTES % 16 == 0, "the generic path's records share the staging area");
 template <int STAGES, int WARPS>
 constexpr int strip_smem_bytes()
 {
-    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 4) * 8 + WARPS * METRIC_DOUBLES * 8 + 6 * 16 + 64;
+    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 5) * 8 + WARPS * METRIC_DOUBLES * 8 + 6 * 16 + 64;
 }
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t src_bytes)
@@ -369,9 +376,15 @@ __device__ __forceinline__ void cp_async_arrive(uint32_t bar)
 // tile loop: every warp runs its own pipeline.
 //   * own tile: TMA, STAGES-deep ring, results written in place, TMA store (as in sweep 1);
 //   * facing rows of the S/N neighbours: two TMA boxes {4 doubles, 32 slabs} per tile into rowbuf;
-//   * strip ends: facing column and two diagonal corner values of the outside neighbours, 8-byte cp.async
-//     into endbuf; rowbuf/endbuf are double buffered, refilled two tiles ahead and tracked by nbr_full
-//     (32 cp.async arrivals + lane 0's expect_tx);
+//   * strip ends: facing column (or row) and two diagonal corner values of the outside neighbours come by TMA too.
+//     The neighbour's slab is viewed as {i,j,kq,elem}; a box {2,1,32 slabs} picks the 16-byte i-pair that holds one
+//     value of 32 consecutive slabs (16 bytes is the TMA minimum): four of them for a facing column, one per
+//     diagonal; a {4,32} row box when the neighbour faces with a row or sits in the halo.  (Gathering these with
+//     per-lane cp.async cost 32 LSU wavefronts per instruction -- a third of the kernel's shared-memory pipe
+//     traffic; a single swizzled {2,4,32} box is rejected by the hardware: swizzle modes fault when the inner box
+//     is narrower than the swizzle span.)  endbuf is single buffered: its values are in registers a few
+//     instructions into the tile, and the next tile's boxes are issued before the Laplacian, tracked by end_full;
+//   * rowbuf is double buffered, refilled two tiles ahead and tracked by nbr_full (lane 0's expect_tx);
 //   * mates: a warp reads the facing column of its mate's tile and the facing ends of the mate's S/N
 //     neighbour rows (= its own diagonal contributors) straight from the mate's shared memory, after
 //     waiting on the MATE's tile_full / nbr_full barriers, and then arrives on the mate's cons barrier
@@ -379,6 +392,19 @@ __device__ __forceinline__ void cp_async_arrive(uint32_t bar)
 //     results and before it refills the rowbuf set.  Arrivals depend only on loads having landed, never on
 //     a mate's computation, so the protocol cannot dead-lock; and a mate can run at most one tile ahead
 //     (it needs the owner's arrival for its own tile), so two cons barriers per warp are enough.
+enum : int { ET_NONE = 0, ET_COL, ET_ROW, ET_HALOROW, ET_PT, ET_HALOPT };
+struct EndTma {          // one staged source of a strip end (16 bytes)
+    uint8_t kind;        // ET_*
+    uint8_t hi;          // which double of the staged i-pair holds the value (ET_COL, ET_PT, ET_HALOPT)
+    uint8_t rev, pad;    // column/row runs the other way
+    int32_t c0, c1;      // first i (or first double of the row) / j of the box
+    int32_t src;         // local element or halo slot
+};
+__device__ __forceinline__ uint32_t end_box_bytes(int kind)
+{
+    return kind == ET_COL ? 2048u : (kind == ET_ROW || kind == ET_HALOROW) ? 1024u : kind == ET_NONE ? 0u : 512u;
+}
+
 template <int STAGES, int WARPS>
 __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, unsigned char *extra,
                                                int first, int cnt, const StripReg &rg)
@@ -392,36 +418,38 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     unsigned char *endbuf = extra + ROWBUF_BYTES;         // [set][2][6][32][8 B]
     uint64_t *nbars = bars + WARPS * STAGES;              // nbr_full [warp][2]
     uint64_t *cbars = nbars + WARPS * 2;                  // cons     [warp][2]
+    uint64_t *ebars = cbars + WARPS * 2;                  // end_full [warp]
     // sources of the two strip ends, decoded once per CTA: [W column, SW, NW, E column, SE, NE]
-    struct EndSrc { const double *p; int32_t sstride, tstride; }; // doubles per slab / per position along the edge
-    EndSrc *endsrc = reinterpret_cast<EndSrc *>(metric_all + STRIP_MAX * METRIC_DOUBLES);
+    EndTma *endtma = reinterpret_cast<EndTma *>(metric_all + STRIP_MAX * METRIC_DOUBLES);
 
     const bool w_end = warp == 0, e_end = warp == cnt - 1;
     if (threadIdx.x < 6) {
         const int k = threadIdx.x, side = k / 3, which = k % 3; // which: 0 column, 1 S-side diagonal, 2 N-side diagonal
-        const size_t ekq = (size_t)p.kq * 16;
-        EndSrc e{nullptr, 0, 0};
+        EndTma e{ET_NONE, 0, 0, 0, 0, 0, 0};
         if (which == 0) {
-            const int src = rg.end_src[side], kind = rg.end_kind[side], row = rg.end_row[side];
-            if (kind == SRC_TMPCOL) e = {p.tmp + (size_t)src * ekq + (row ? 3 : 0), 16, 4};
-            else if (kind == SRC_TMP) e = {p.tmp + (size_t)src * ekq + 4 * row, 16, 1};
-            else e = {p.halo + (size_t)src * p.kq * 4, 4, 1};
-            if (rg.end_rev[side]) { e.p += 3 * e.tstride; e.tstride = -e.tstride; }
+            const int kind = rg.end_kind[side], row = rg.end_row[side];
+            if (kind == SRC_TMPCOL) e = {ET_COL, (uint8_t)(row ? 1 : 0), 0, 0, row ? 2 : 0, 0, 0}; // column i=1: first of the pair (1,2); i=4: second of (3,4)
+            else if (kind == SRC_TMP) e = {ET_ROW, 0, 0, 0, 4 * row, 0, 0};
+            else e = {ET_HALOROW, 0, 0, 0, 0, 0, 0};
+            e.rev = rg.end_rev[side];
+            e.src = rg.end_src[side];
         } else {
             const int d = side * 2 + (which - 1);
-            const int src = rg.diag_src[d];
-            if (src >= 0) {
-                if (rg.diag_kind[d] == SRC_HALO) e = {p.halo + (size_t)src * p.kq * 4 + rg.diag_pt[d], 4, 0};
-                else e = {p.tmp + (size_t)src * ekq + rg.diag_pt[d], 16, 0};
+            if (rg.diag_src[d] >= 0) {
+                const int pt = rg.diag_pt[d];
+                if (rg.diag_kind[d] == SRC_HALO) e = {ET_HALOPT, (uint8_t)(pt & 1), 0, 0, pt & 2, 0, 0};
+                else e = {ET_PT, (uint8_t)(pt & 1), 0, 0, pt & 2, pt >> 2, 0};
+                e.src = rg.diag_src[d];
             }
         }
-        endsrc[k] = e;
+        endtma[k] = e;
     }
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
-        mbar_init(smem_u32(&nbars[warp * 2]), 33); // 32 cp.async arrivals + lane 0's expect_tx for the two TMA row boxes
-        mbar_init(smem_u32(&nbars[warp * 2 + 1]), 33);
+        mbar_init(smem_u32(&nbars[warp * 2]), 1); // lane 0's expect_tx for the two TMA row boxes
+        mbar_init(smem_u32(&nbars[warp * 2 + 1]), 1);
+        mbar_init(smem_u32(&ebars[warp]), 1);
         const uint32_t nmates = (w_end ? 0u : 1u) + (e_end ? 0u : 1u);
         mbar_init(smem_u32(&cbars[warp * 2]), active && nmates ? 32u * nmates : 1u); // every lane of every mate arrives
         mbar_init(smem_u32(&cbars[warp * 2 + 1]), active && nmates ? 32u * nmates : 1u);
@@ -432,7 +460,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         cp_async16(smem_u32(metric_s) + lane * 16, p.metric + (size_t)le * METRIC_DOUBLES + lane * 2, 16u);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    __syncthreads(); // the only CTA-wide barrier: mbarriers initialised, endsrc written
+    __syncthreads(); // the only CTA-wide barrier: mbarriers initialised, endtma written
     if (!active) return;
 
     const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
@@ -462,41 +490,76 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         mbar_expect_tx(bar, (uint32_t)TILE_BYTES);
         tma_load_3d(dst, &p.map_tmp, 0, (t0 + n) * TILE_SLABS, le, bar);
     };
-    // all lanes: stage the outside neighbours' values of tile n into buffer set n & 1
+    // lane 0: stage the S/N neighbours' facing rows of tile n into buffer set n & 1
     auto issue_nbr = [&](int n) {
         const int q = n & 1;
         const int kq0 = (t0 + n) * TILE_SLABS;
         const uint32_t nbar = nbar0 + q * 8;
-        if (lane == 0) {
-            const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2048);
-            mbar_expect_tx(nbar, 2048u);
-            tma_load_3d(rb, mapS, c0S, kq0, elemS, nbar);        // the S neighbour's facing row (its N row in a face interior)
-            tma_load_3d(rb + 1024, mapN, c0N, kq0, elemN, nbar); // the N neighbour's facing row
-        }
-        if (w_end || e_end) {
-            const uint32_t ok8 = kq0 + lane < p.kq ? 8u : 0u;
-            const int64_t slab = (int64_t)kq0 + lane;
+        const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2048);
+        mbar_expect_tx(nbar, 2048u);
+        tma_load_3d(rb, mapS, c0S, kq0, elemS, nbar);        // the S neighbour's facing row (its N row in a face interior)
+        tma_load_3d(rb + 1024, mapN, c0N, kq0, elemN, nbar); // the N neighbour's facing row
+    };
+    // lane 0 of an end warp: stage the outside neighbour's facing column and the two diagonal corner values of tile n
+    const bool is_end = w_end || e_end;
+    const uint32_t ebar = smem_u32(&ebars[warp]);
+    uint32_t end_bytes = 0;
+    if (is_end) {
 #pragma unroll
-            for (int side = 0; side < 2; ++side) {
-                if (side == 0 ? !w_end : !e_end) continue;
-                const uint32_t eb = smem_u32(endbuf) + (uint32_t)(q * 3072 + side * 1536 + lane * 8);
-                const EndSrc c = endsrc[3 * side], d0 = endsrc[3 * side + 1], d1 = endsrc[3 * side + 2];
-                const double *src = c.p + slab * c.sstride;
+        for (int k = 0; k < 6; ++k)
+            if (k < 3 ? w_end : e_end) end_bytes += end_box_bytes(endtma[k].kind);
+    }
+    auto issue_end = [&](int n) {
+        const int kq0 = (t0 + n) * TILE_SLABS;
+        mbar_expect_tx(ebar, end_bytes);
 #pragma unroll
-                for (int t = 0; t < 4; ++t) cp_async8(eb + t * 256, src + t * c.tstride, ok8);
-                if (d0.p) cp_async8(eb + 4 * 256, d0.p + slab * d0.sstride, ok8); // absent at a cube corner (three elements)
-                if (d1.p) cp_async8(eb + 5 * 256, d1.p + slab * d1.sstride, ok8);
+        for (int side = 0; side < 2; ++side) {
+            if (side == 0 ? !w_end : !e_end) continue;
+#pragma unroll
+            for (int which = 0; which < 3; ++which) {
+                const EndTma e = endtma[3 * side + which];
+                const uint32_t dst = smem_u32(endbuf) + (uint32_t)(side * END_SIDE_BYTES + (which ? 1536 + 512 * which : 0));
+                switch (e.kind) {
+                case ET_COL:
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) tma_load_4d(dst + j * 512, &p.map_pt, e.c0, j, kq0, e.src, ebar);
+                    break;
+                case ET_ROW: tma_load_3d(dst, &p.map_rows, e.c0, kq0, e.src, ebar); break;
+                case ET_HALOROW: tma_load_3d(dst, &p.map_halo, 0, kq0, e.src, ebar); break;
+                case ET_PT: tma_load_4d(dst, &p.map_pt, e.c0, e.c1, kq0, e.src, ebar); break;
+                case ET_HALOPT: tma_load_3d(dst, &p.map_halo_pt, e.c0, kq0, e.src, ebar); break;
+                default: break; // no diagonal contributor (cube corner)
+                }
             }
         }
-        cp_async_arrive(nbar);
+    };
+    // all lanes of an end warp: the four values along the facing edge (own orientation) and the two diagonals
+    auto read_end = [&](int side, double (&col)[4], double &d0, double &d1) {
+        const unsigned char *eb = endbuf + side * END_SIDE_BYTES;
+        const EndTma c = endtma[3 * side];
+        const int rm = c.rev ? 3 : 0; // position t of this element's edge = position t ^ rm of the neighbour's
+        if (c.kind == ET_COL) { // [j][slab][2 doubles]
+            const unsigned char *b = eb + lane * 16 + c.hi * 8;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + ((t ^ rm) << 9));
+        } else { // [slab][4 doubles], SWIZZLE_32B
+            const unsigned char *b = eb + lane * 32;
+            const int x = ((lane >> 2) & 1) ^ (rm >> 1), y = rm & 1;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + (((t >> 1) ^ x) << 4) + (((t & 1) ^ y) << 3));
+        }
+        // [slab][2 doubles]; an absent diagonal (cube corner) leaves the box unwritten and the value unused
+        d0 = *reinterpret_cast<const double *>(eb + 2048 + lane * 16 + endtma[3 * side + 1].hi * 8);
+        d1 = *reinterpret_cast<const double *>(eb + 2560 + lane * 16 + endtma[3 * side + 2].hi * 8);
     };
 
     if (lane == 0) {
         const int pre = my_n < STAGES ? my_n : STAGES;
         for (int n = 0; n < pre; ++n) issue_tile(n, n);
+        if (my_n > 0) issue_nbr(0);
+        if (my_n > 1) issue_nbr(1);
+        if (is_end && my_n > 0) issue_end(0);
     }
-    if (my_n > 0) issue_nbr(0);
-    if (my_n > 1) issue_nbr(1);
 
     const SmemMetric M{metric_s};
     const int sw = lane & 7;
@@ -511,6 +574,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
 
         mbar_wait(bar0 + s * 8, parity);
         mbar_wait(nbar0 + q * 8, qparity);
+        if (is_end) mbar_wait(ebar, (uint32_t)(n & 1));
         if (n == 0) { // the metric staged by this warp's own cp.async group
             asm volatile("cp.async.wait_all;" ::: "memory");
             __syncwarp();
@@ -529,11 +593,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         }
         // ---- W side: outside neighbour (strip end) or the left mate's shared memory
         if (w_end) {
-            const unsigned char *eb = endbuf + q * 3072 + lane * 8;
-#pragma unroll
-            for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(eb + t * 256);
-            dg[0] = *reinterpret_cast<const double *>(eb + 4 * 256);
-            dg[2] = *reinterpret_cast<const double *>(eb + 5 * 256);
+            read_end(0, nb[EDGE_W], dg[0], dg[2]);
         } else { // mate's E column = points 3,7,11,15 = upper halves of chunks 1,3,5,7; east ends of its S/N neighbour rows
             mbar_wait(bar0 - STAGES * 8 + s * 8, parity);
             mbar_wait(nbar0 - 16 + q * 8, qparity);
@@ -545,11 +605,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         }
         // ---- E side
         if (e_end) {
-            const unsigned char *eb = endbuf + q * 3072 + 1536 + lane * 8;
-#pragma unroll
-            for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(eb + t * 256);
-            dg[1] = *reinterpret_cast<const double *>(eb + 4 * 256);
-            dg[3] = *reinterpret_cast<const double *>(eb + 5 * 256);
+            read_end(1, nb[EDGE_E], dg[1], dg[3]);
         } else { // mate's W column = points 0,4,8,12 = lower halves of chunks 0,2,4,6; west ends of its S/N neighbour rows
             mbar_wait(bar0 + STAGES * 8 + s * 8, parity);
             mbar_wait(nbar0 + 16 + q * 8, qparity);
@@ -596,6 +652,13 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         // The asm operand ties the arrival to the corner sums so that it cannot be scheduled above the loads.
         if (!w_end) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 - 16 + q * 8), "d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]) : "memory");
         if (!e_end) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 + 16 + q * 8), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
+        if (is_end) {
+            // endbuf has been consumed by every lane (the sums above depend on its values): refill it for the next tile now,
+            // so that the boxes travel while this tile's Laplacian runs
+            asm volatile("" ::"d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
+            __syncwarp();
+            if (lane == 0 && n + 1 < my_n) issue_end(n + 1);
+        }
 
         laplace_slab(v, M);
 
@@ -613,9 +676,9 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
                 bulk_wait_read<1>();
                 issue_tile(n - 1 + STAGES, (n - 1) % STAGES);
             }
+            // rowbuf set q is free again (own reads and the mates', see the cons wait above): stage tile n+2's rows into it
+            if (n + 2 < my_n) issue_nbr(n + 2);
         }
-        // buffer set q is free again: stage the outside neighbours of tile n+2 into it
-        if (n + 2 < my_n) issue_nbr(n + 2);
     }
     if (lane == 0) bulk_wait<0>();
 }
@@ -866,7 +929,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __
     unsigned char *stages = smem;                                  // tile ring, 1024-byte aligned (SWIZZLE_128B)
     unsigned char *extra = smem + WARPS * STAGES * TILE_BYTES;     // staging buffers (1024-aligned, SWIZZLE_32B rows) or WarpDss records
     uint64_t *bars = reinterpret_cast<uint64_t *>(extra + STRIP_EXTRA_BYTES);
-    double *metric_all = reinterpret_cast<double *>(bars + WARPS * (STAGES + 4)); // after tile_full, nbr_full, exp_full
+    double *metric_all = reinterpret_cast<double *>(bars + WARPS * (STAGES + 5)); // after tile_full, nbr_full, cons, end_full
 
     const int32_t strip = p.strips[blockIdx.x];
     const int first = strip >> 3, cnt = (strip & 7) + 1;

@@ -24,6 +24,8 @@ struct SweepParams {
     CUtensorMap map_tmp;    // tmp     same shape (sweep-1 output)
     CUtensorMap map_rows;   // tmp as {16, KQ, nelem}, box {4,32,1}, SWIZZLE_32B: one edge row (32 B) of 32 consecutive slabs
     CUtensorMap map_halo;   // received edge rows as {4, KQ, nrows}, box {4,32,1}, SWIZZLE_32B (aliases map_rows when there is no halo)
+    CUtensorMap map_pt;     // tmp as {4 (i), 4 (j), KQ, nelem}, box {2,1,32,1}: the 16-byte i-pair holding one point of 32 consecutive slabs
+    CUtensorMap map_halo_pt;// received edge rows as {4, KQ, nrows}, box {2,32,1}: half a halo row (aliases a 3-D view of tmp when there is no halo)
     const double *metric;   // [nelem][64] folded metric
     const double *rsph;     // [nelem][16]
     const ElemDss *dss;     // [nelem]
