@@ -366,14 +366,16 @@ int install_plan(Plan &&pl)
         const uint64_t dims[3] = {16, (uint64_t)g.kq, (uint64_t)g.nelem};
         const uint64_t str[2] = {128, (uint64_t)g.kq * 128};
         const uint32_t box[3] = {4, TILE_SLABS, 1};
-        if (make_map(&g.sp.map_rows, g.d_tmp, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+        CUtensorMapL2promotion npromo = CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+        if (const char *e = std::getenv("BWK_NBR_PROMO")) npromo = (CUtensorMapL2promotion)std::atoi(e); // tuning knob: 0 none, 1 64 B, 2 128 B, 3 256 B
+        if (make_map(&g.sp.map_rows, g.d_tmp, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B, npromo)) return 1;
         g.sp.map_halo = g.sp.map_rows;
         // strip ends of sweep 2: the neighbour's slab as {i, j, KQ, elem}; an i-pair (16 bytes, the TMA minimum) of one j
         // holds one value of a W/E edge column or a corner value
         const uint64_t cdims[4] = {4, 4, (uint64_t)g.kq, (uint64_t)g.nelem};
         const uint64_t cstr[3] = {32, 128, (uint64_t)g.kq * 128};
         const uint32_t pbox[4] = {2, 1, TILE_SLABS, 1}, hpbox[3] = {2, TILE_SLABS, 1};
-        if (make_map(&g.sp.map_pt, g.d_tmp, 4, cdims, cstr, pbox, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+        if (make_map(&g.sp.map_pt, g.d_tmp, 4, cdims, cstr, pbox, CU_TENSOR_MAP_SWIZZLE_NONE, npromo)) return 1;
         if (make_map(&g.sp.map_halo_pt, g.d_tmp, 3, dims, str, hpbox, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
         if (nrecv > 0) {
             const uint64_t hdims[3] = {4, (uint64_t)g.kq, (uint64_t)nrecv};

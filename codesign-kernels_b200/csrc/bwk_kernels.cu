@@ -943,7 +943,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __
 #define BWK_CFG_SWEEP1 3, 4, 3
 #define BWK_CFG_SWEEP2 3, 4, 3
 
-static int g_sweep2_tpu = 12;
+static int g_sweep2_tpu = 15;
 void set_sweep2_tiles_per_unit(int tpu) { g_sweep2_tpu = tpu < 1 ? 1 : tpu; }
 
 SweepGeometry choose_geometry(int kq, int64_t count, int mode)
