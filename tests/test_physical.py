@@ -110,7 +110,11 @@ def test_full_biharmonic_energy_known_answer_cpu(oracle):
 def test_physical_terms_gpu(bwk, oracle, ne):
     """the CUDA path on physical inputs: analytic values, and agreement with the oracle.  Dvv has mixed signs here,
     so the contractions cancel and the elementwise-relative bound of the LCG tests is replaced by a bound relative
-    to the largest magnitude of each slab field (1e-12)."""
+    to the largest magnitude of each (k,q) field: 1e-12 for one Laplacian (measured 3e-15 / 8e-15 at ne 4 / 8).  The
+    second Laplacian differentiates the rounding noise of the first (amplification ~ lambda_max / lambda_l of the
+    discrete operator, growing like ne^2), so the bound for the full biharmonic is derived from the oracle itself: ten
+    times the change of the oracle's result when its own sweep-1 output is perturbed by 1e-14 of the field maximum
+    (measured GPU-vs-oracle: 1.0e-12 at ne=4, 1.1e-11 at ne=8)."""
     dvv, elem, dss, rs, q0, deg, mp = _setup(oracle, ne)
     n = 6 * ne * ne
     ref_lap = oracle.biharmonic_wk_scalar_cpu(elem, q0.copy(order="F"), dvv.reshape(16))
@@ -135,7 +139,17 @@ def test_physical_terms_gpu(bwk, oracle, ne):
         return worst
 
     assert slot_rel(lap, ref_lap) <= 1e-12, slot_rel(lap, ref_lap)
-    assert slot_rel(bih, ref_bih) <= 1e-12, slot_rel(bih, ref_bih)
+    rng = np.random.default_rng(5)
+    pert = ref_lap.copy(order="F")
+    for t in range(QSIZE):
+        for k in range(NLEV):
+            pert[:, :, k, t, :] += 1e-14 * np.abs(ref_lap[:, :, k, t, :]).max() * rng.choice([-1.0, 1.0], size=(4, 4, n))
+    dss.apply(pert)
+    pert *= rs[:, :, None, None, :]
+    oracle.biharmonic_wk_scalar_cpu(elem, pert, dvv.reshape(16))
+    bound = 10.0 * slot_rel(pert, ref_bih) + 1e-12
+    print(f"ne={ne}: GPU vs oracle, relative to max: laplace {slot_rel(lap, ref_lap):.2e}, biharmonic {slot_rel(bih, ref_bih):.2e} (bound {bound:.2e})")
+    assert slot_rel(bih, ref_bih) <= bound, (slot_rel(bih, ref_bih), bound)
     pe = _pointwise_errors(oracle, lap, dss, rs, q0, deg)
     ee = _energy_errors(oracle, bih, q0, deg, mp)
     if ne == 8:
