@@ -450,3 +450,75 @@ void bwko_biharmonic_full(const bwko_dss_t *d, const double *elem, const double 
         for (int ie = 0; ie < nelem; ++ie) element_sweep2(elem + (size_t)ED * ie, rsph + (size_t)16 * ie, qtens + es * ie, dvv, nlev, qsize);
     }
 }
+
+/* ------------------------------------------------------------------------------------------
+ * advance_hypervis_scalar -- NOT in /root/reference: the caller of
+ * biharmonic_wk_scalar in upstream HOMME (prim_advection: advance_hypervis_scalar, limiter2d_zero).
+ * Un-vendored, no pinned version, restated from its published structure; PARITY UNPINNED.
+ * Per subcycle (dt = dt2 / subcycles):
+ *     Qtens = dpdiss * Qdp / dp                           (hyperviscosity acts on the mixing ratio)
+ *     Qtens = biharmonic_wk_scalar(Qtens)                 (Laplace -> DSS -> rspheremp -> Laplace, weak form)
+ *     Qdp   = Qdp * spheremp - dt * nu_q * Qtens
+ *     limiter2d_zero(Qdp(:,:,:,q))                        (optional: clip negatives level by level, keep the level's mass)
+ *     Qdp   = DSS(Qdp) * rspheremp
+ * Qdp(np,np,nlev,qsize,nelemd); dp, dpdiss (np,np,nlev,nelemd).
+ */
+static void limiter2d_zero_level(double *q16)
+{
+    double mass = 0.0;
+    for (int t = 0; t < 16; ++t) mass = mass + q16[t];
+    if (mass < 0.0)
+        for (int t = 0; t < 16; ++t) q16[t] = -q16[t];
+    double mass_added = 0.0;
+    for (int t = 0; t < 16; ++t) {
+        if (q16[t] < 0.0) q16[t] = 0.0;
+        else mass_added = mass_added + q16[t];
+    }
+    if (mass_added > 0.0) {
+        const double scale = fabs(mass) / mass_added;
+        for (int t = 0; t < 16; ++t) q16[t] = q16[t] * scale;
+    }
+    if (mass < 0.0)
+        for (int t = 0; t < 16; ++t) q16[t] = -q16[t];
+}
+
+void bwko_limiter2d_zero(double *q, int64_t nslabs)
+{
+    for (int64_t s = 0; s < nslabs; ++s) limiter2d_zero_level(q + 16 * s);
+}
+
+void bwko_advance_hypervis_scalar(const bwko_dss_t *d, const double *elem, const double *rsph, double *qdp, const double *dp,
+                                  const double *dpdiss, const double *dvv, int nlev, int qsize, double dt2, double nu_q,
+                                  int subcycles, int limiter)
+{
+    const int64_t nelem = d->nelem;
+    const size_t es = (size_t)16 * nlev * qsize;
+    double *qtens = (double *)malloc(sizeof(double) * es * (size_t)nelem);
+    const double dt = dt2 / subcycles;
+    for (int ic = 0; ic < subcycles; ++ic) {
+        for (int64_t ie = 0; ie < nelem; ++ie)
+            for (int q = 0; q < qsize; ++q)
+                for (int k = 0; k < nlev; ++k)
+                    for (int t = 0; t < 16; ++t) {
+                        const size_t a = es * (size_t)ie + (size_t)16 * (k + (size_t)nlev * q) + t;
+                        const size_t b = (size_t)16 * nlev * (size_t)ie + (size_t)16 * k + t;
+                        qtens[a] = dpdiss[b] * qdp[a] / dp[b];
+                    }
+        bwko_biharmonic_full(d, elem, rsph, qtens, dvv, nlev, qsize, 0);
+        for (int64_t ie = 0; ie < nelem; ++ie) {
+            const double *e = elem + (size_t)ED * ie;
+            for (int q = 0; q < qsize; ++q)
+                for (int k = 0; k < nlev; ++k) {
+                    double *slab = qdp + es * (size_t)ie + (size_t)16 * (k + (size_t)nlev * q);
+                    const double *ts = qtens + es * (size_t)ie + (size_t)16 * (k + (size_t)nlev * q);
+                    for (int t = 0; t < 16; ++t) slab[t] = slab[t] * e[64 + t] - dt * nu_q * ts[t];
+                    if (limiter) limiter2d_zero_level(slab);
+                }
+        }
+        dss_apply_impl(d, qdp, nlev, qsize, 0);
+        for (int64_t ie = 0; ie < nelem; ++ie)
+            for (size_t s = 0; s < (size_t)nlev * qsize; ++s)
+                for (int t = 0; t < 16; ++t) qdp[es * (size_t)ie + 16 * s + t] = rsph[(size_t)16 * ie + t] * qdp[es * (size_t)ie + 16 * s + t];
+    }
+    free(qtens);
+}

@@ -99,6 +99,15 @@ void bwko_biharmonic_full(const bwko_dss_t *, const double *elem, const double *
                           double *qtens, const double *dvv, int nlev, int qsize,
                           int use_omp);
 
+/* advance_hypervis_scalar of upstream HOMME (the caller of biharmonic_wk_scalar; NOT in the reference,
+ * parity unpinned): per subcycle Qtens = dpdiss*Qdp/dp -> biharmonic -> Qdp*spheremp - dt*nu_q*Qtens ->
+ * limiter2d_zero (optional) -> DSS -> *rspheremp.  qdp(np,np,nlev,qsize,nelemd); dp, dpdiss (np,np,nlev,nelemd). */
+void bwko_advance_hypervis_scalar(const bwko_dss_t *, const double *elem, const double *rsph, double *qdp,
+                                  const double *dp, const double *dpdiss, const double *dvv, int nlev, int qsize,
+                                  double dt2, double nu_q, int subcycles, int limiter);
+/* limiter2d_zero on nslabs (np x np) levels: negatives clipped, the level's sum preserved */
+void bwko_limiter2d_zero(double *q, int64_t nslabs);
+
 #ifdef __cplusplus
 }
 #endif

@@ -44,6 +44,8 @@ def _load(name):
     L.bwko_dss_apply.argtypes = [p, p, i32, i32]
     L.bwko_biharmonic_full.argtypes = [p, p, p, p, p, i32, i32, i32]
     L.bwko_omp_max_threads.restype = i32
+    L.bwko_advance_hypervis_scalar.argtypes = [p, p, p, p, p, p, p, i32, i32, C.c_double, C.c_double, i32, i32]
+    L.bwko_limiter2d_zero.argtypes = [p, i64]
     return L
 
 
@@ -161,3 +163,15 @@ class Dss:
         else:
             L.bwko_biharmonic_full(self._h, _p(elem), _p(rsph), _p(qtens), _p(dvv), nlev, qsize, 0)
         return qtens
+
+    def advance_hypervis_scalar(self, elem, rsph, qdp, dp, dpdiss, dvv, dt2, nu_q, subcycles=1, limiter=True):
+        """upstream HOMME advance_hypervis_scalar (parity unpinned, see bwk_oracle.c); qdp updated in place"""
+        nlev, qsize, _ = _dims(qdp)
+        lib().bwko_advance_hypervis_scalar(self._h, _p(elem), _p(rsph), _p(qdp), _p(dp), _p(dpdiss), _p(dvv), nlev, qsize,
+                                           float(dt2), float(nu_q), int(subcycles), 1 if limiter else 0)
+        return qdp
+
+
+def limiter2d_zero(q):
+    lib().bwko_limiter2d_zero(_p(q), q.size // 16)
+    return q
