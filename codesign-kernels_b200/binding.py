@@ -80,6 +80,9 @@ def lib():
         "bwk_set_rspheremp": [p],
         "bwk_get_rspheremp": [p],
         "bwk_run_biharmonic": [],
+        "bwk_upload_hypervis_fields": [p, p],
+        "bwk_run_advance_hypervis": [C.c_double, C.c_double, i32, i32],
+        "bwk_advance_hypervis_scalar": [p, p, p, p, p, C.c_double, C.c_double, i32, i32],
         "bwk_run_biharmonic_phase": [i32],
         "bwk_comm_unique_id": [p],
         "bwk_comm_init": [i32, i32, p],
@@ -304,6 +307,18 @@ class KernelUtils:
     # -- upstream HOMME full biharmonic through host arrays
     def biharmonic_wk_scalar_full(self, elem, qtens, deriv):
         _ck(lib().bwk_biharmonic_wk_scalar_full(_ptr(elem), _ptr(qtens), _ptr(deriv)))
+
+    # -- the caller of this path in HOMME (prim_advection advance_hypervis_scalar; not in the reference, bwk_b200.h)
+    def advance_hypervis_scalar(self, elem, qdp, dp, dpdiss, deriv, dt2, nu_q, hypervis_subcycle_q=1, limiter=True):
+        """Qdp(np,np,nlev,qsize,nelemd) updated in place; dp, dpdiss (np,np,nlev,nelemd) Fortran order"""
+        _ck(lib().bwk_advance_hypervis_scalar(_ptr(elem), _ptr(qdp), _ptr(dp), _ptr(dpdiss), _ptr(deriv), float(dt2), float(nu_q),
+                                              int(hypervis_subcycle_q), 1 if limiter else 0))
+
+    def upload_hypervis_fields(self, dp, dpdiss):
+        _ck(lib().bwk_upload_hypervis_fields(_ptr(dp), _ptr(dpdiss)))
+
+    def run_advance_hypervis_device(self, dt2, nu_q, hypervis_subcycle_q=1, limiter=True):
+        _ck(lib().bwk_run_advance_hypervis(float(dt2), float(nu_q), int(hypervis_subcycle_q), 1 if limiter else 0))
 
     def set_topology_cubed_sphere(self, ne, elem_first=0):
         _ck(lib().bwk_set_topology_cubed_sphere(ne, elem_first))

@@ -94,6 +94,8 @@ struct Ctx {
     size_t q_doubles = 0;
     cudaStream_t s_main = nullptr, s_comm = nullptr, s_h2d = nullptr, s_d2h = nullptr;
     double *d_q = nullptr, *d_tmp = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
+    double *d_w = nullptr, *d_ratio = nullptr; // advance_hypervis_scalar: biharmonic work buffer, dpdiss/dp [nelem][nlev][16]
+    CUtensorMap map_w;
     double *d_save = nullptr, *d_table = nullptr, *d_partials = nullptr, *d_halo = nullptr, *d_send = nullptr, *d_dummy = nullptr;
     double *h_partials = nullptr;
     ElemDss *d_dss = nullptr;
@@ -197,17 +199,18 @@ int sweep(int mode, int first, int count, const int32_t *list, cudaStream_t st)
 }
 
 // launch sweep 2 over `count` strips of a device strip list
-int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaStream_t st)
+int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaStream_t st, int mode = MODE_SWEEP2, const CUtensorMap *out = nullptr)
 {
     if (count <= 0) return 0;
     SweepParams p = g.sp;
-    const SweepGeometry geo = choose_geometry(g.kq, count, MODE_SWEEP2);
+    if (out) p.map_out = *out;
+    const SweepGeometry geo = choose_geometry(g.kq, count, mode);
     p.tiles_per_unit = geo.tiles_per_unit;
     p.units = geo.units;
     p.strips = d_strips;
     p.strip_reg = d_reg;
     p.strip_count = (int)count;
-    CK(launch_sweep(MODE_SWEEP2, p, st));
+    CK(launch_sweep(mode, p, st));
     g.launches++;
     return 0;
 }
@@ -420,26 +423,65 @@ int exchange_halo()
     return 0;
 }
 
-int biharmonic_device()
+// One "produce -> DSS -> consume" pass: produce(first, count, list) writes rspheremp-scaled element-local values to tmp,
+// boundary elements first so that their edge rows travel (ncclSend/Recv on s_comm) while the interior is produced; the
+// strip kernel then assembles (and, for MODE_SWEEP2, applies the second Laplacian) into `out`.
+template <class Produce>
+int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
 {
-    if (!g.have_metric) return fail("no element metric on the device");
-    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
-    if (compute_rspheremp()) return 1;
     const Plan &P = g.plan;
     if (P.nranks == 1) {
-        if (sweep(MODE_SWEEP1, 0, g.nelem, nullptr, g.s_main)) return 1;
-        return sweep2(g.d_strips_all, g.d_reg_all, (int64_t)P.strips_all.size(), g.s_main);
+        if (produce(0, g.nelem, (const int32_t *)nullptr)) return 1;
+        return sweep2(g.d_strips_all, g.d_reg_all, (int64_t)P.strips_all.size(), g.s_main, consume_mode, out);
     }
-    // boundary elements first so that their edge rows can travel while the interior is computed
-    if (sweep(MODE_SWEEP1, 0, (int)P.boundary_list.size(), g.d_boundary, g.s_main)) return 1;
+    if (produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary)) return 1;
     CK(cudaEventRecord(g.ev_b, g.s_main));
     CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
     if (exchange_halo()) return 1;
     CK(cudaEventRecord(g.ev_halo, g.s_comm));
-    if (sweep(MODE_SWEEP1, 0, (int)P.interior_list.size(), g.d_interior, g.s_main)) return 1;
-    if (sweep2(g.d_strips_indep, g.d_reg_indep, (int64_t)P.strips_independent.size(), g.s_main)) return 1;
+    if (produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior)) return 1;
+    if (sweep2(g.d_strips_indep, g.d_reg_indep, (int64_t)P.strips_independent.size(), g.s_main, consume_mode, out)) return 1;
     CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
-    return sweep2(g.d_strips_dep, g.d_reg_dep, (int64_t)P.strips_dependent.size(), g.s_main);
+    if (sweep2(g.d_strips_dep, g.d_reg_dep, (int64_t)P.strips_dependent.size(), g.s_main, consume_mode, out)) return 1;
+    // the next pass's exchange overwrites the halo buffer: it must not start before these strips have read it
+    CK(cudaEventRecord(g.ev_misc, g.s_main));
+    CK(cudaStreamWaitEvent(g.s_comm, g.ev_misc, 0));
+    return 0;
+}
+
+int biharmonic_device(int produce_mode = MODE_SWEEP1, const CUtensorMap *out = nullptr)
+{
+    if (!g.have_metric) return fail("no element metric on the device");
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (compute_rspheremp()) return 1;
+    return dss_pass([&](int first, int count, const int32_t *list) { return sweep(produce_mode, first, count, list, g.s_main); }, MODE_SWEEP2, out);
+}
+
+// advance_hypervis_scalar on the device-resident Qdp (d_q); see bwk_b200.h
+int hypervis_device(double dt2, double nu_q, int subcycles, int limiter)
+{
+    if (!g.d_ratio) return fail("no dp / dpdiss on the device: call bwk_upload_hypervis_fields first");
+    if (subcycles < 1) return fail("hypervis_subcycle_q must be >= 1");
+    if (!sweep1_pre_fits(g.nlev)) return fail("nlev = %d: the per-level factors do not fit in shared memory", g.nlev);
+    if (!g.d_w) {
+        CK(cudaMalloc(&g.d_w, sizeof(double) * g.q_doubles));
+        if (make_slab_map(&g.map_w, g.d_w, g.kq, g.nelem)) return 1;
+    }
+    g.sp.prescale = g.d_ratio;
+    g.sp.nlev = g.nlev;
+    const double coef = (dt2 / subcycles) * nu_q;
+    for (int ic = 0; ic < subcycles; ++ic) {
+        // Qtens = biharmonic(dpdiss * Qdp / dp) -> work buffer (Qdp itself is still needed)
+        if (biharmonic_device(MODE_SWEEP1_PRE, &g.map_w)) return 1;
+        // Qdp = DSS(limiter(Qdp * spheremp - dt nu_q Qtens)) * rspheremp
+        auto post = [&](int first, int count, const int32_t *list) {
+            CK(launch_hypervis_post(g.d_q, g.d_w, g.d_tmp, g.d_elem, g.d_rsph, list, first, count, g.kq, coef, limiter, g.s_main));
+            g.launches++;
+            return 0;
+        };
+        if (dss_pass(post, MODE_DSS, &g.sp.map_q)) return 1;
+    }
+    return 0;
 }
 
 // chunk boundaries (in elements) for the host<->device pipelines
@@ -575,6 +617,7 @@ int bwk_init(int nelemd, int nlev, int qsize)
     if (make_slab_map(&g.sp.map_q, g.d_q, g.kq, nelemd)) return 1;
     // until a topology is installed map_tmp aliases map_q (never dereferenced by MODE_LAPLACE)
     g.sp.map_tmp = g.sp.map_q;
+    g.sp.map_out = g.sp.map_q;
     g.sp.metric = g.d_metric;
     g.sp.kq = g.kq;
     g.inited = true;
@@ -587,6 +630,7 @@ int bwk_finalize(void)
     cudaDeviceSynchronize();
     if (g.comm && g_nccl.CommDestroy) g_nccl.CommDestroy(g.comm);
     free_dev(g.d_q); free_dev(g.d_tmp); free_dev(g.d_elem); free_dev(g.d_metric); free_dev(g.d_rsph);
+    free_dev(g.d_w); free_dev(g.d_ratio);
     free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
     free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);
     free_dev(g.d_send_elem); free_dev(g.d_send_row); free_dev(g.d_strips_all); free_dev(g.d_strips_dep); free_dev(g.d_strips_indep); free_dev(g.d_reg_all); free_dev(g.d_reg_dep); free_dev(g.d_reg_indep); free_dev(g.d_e2e_strips); free_dev(g.d_e2e_reg);
@@ -926,6 +970,45 @@ int bwk_run_biharmonic(void)
 {
     if (need_init()) return 1;
     return biharmonic_device();
+}
+
+int bwk_upload_hypervis_fields(const double *dp, const double *dpdiss)
+{
+    if (need_init()) return 1;
+    if (!dp || !dpdiss) return fail("bwk_upload_hypervis_fields: dp and dpdiss are required");
+    const size_t n = (size_t)16 * g.nlev * g.nelem;
+    if (!g.d_ratio) CK(cudaMalloc(&g.d_ratio, sizeof(double) * n));
+    double *d_den = nullptr;
+    CK(cudaMalloc(&d_den, sizeof(double) * n));
+    cudaError_t e = cudaMemcpyAsync(g.d_ratio, dpdiss, sizeof(double) * n, cudaMemcpyHostToDevice, g.s_main);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_den, dp, sizeof(double) * n, cudaMemcpyHostToDevice, g.s_main);
+    if (e == cudaSuccess) e = launch_ratio(g.d_ratio, d_den, g.d_ratio, (int64_t)n, g.s_main);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.s_main);
+    cudaFree(d_den);
+    CK(e);
+    g.launches++;
+    return 0;
+}
+
+int bwk_run_advance_hypervis(double dt2, double nu_q, int hypervis_subcycle_q, int limiter)
+{
+    if (need_init()) return 1;
+    if (!g.have_metric) return fail("no element metric on the device");
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (compute_rspheremp()) return 1;
+    return hypervis_device(dt2, nu_q, hypervis_subcycle_q, limiter);
+}
+
+int bwk_advance_hypervis_scalar(const bwk_element_t *elem, double *Qdp, const double *dp, const double *dpdiss,
+                                const bwk_derivative_t *deriv, double dt2, double nu_q, int hypervis_subcycle_q, int limiter)
+{
+    if (need_init()) return 1;
+    if (!Qdp) return fail("bwk_advance_hypervis_scalar: Qdp is required");
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (bwk_upload(elem, Qdp, deriv)) return 1;
+    if (dp || dpdiss) { if (bwk_upload_hypervis_fields(dp, dpdiss)) return 1; }
+    if (bwk_run_advance_hypervis(dt2, nu_q, hypervis_subcycle_q, limiter)) return 1;
+    return bwk_download(Qdp);
 }
 
 int bwk_run_biharmonic_phase(int phase)

@@ -223,7 +223,18 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
     // ---- per-CTA staging of the element's folded metric
     for (int t = threadIdx.x; t < METRIC_DOUBLES; t += WARPS * 32) metric_s[t] = p.metric[(size_t)le * METRIC_DOUBLES + t];
     double *rsph_s = metric_s + METRIC_DOUBLES;
-    if (MODE == MODE_SWEEP1 && threadIdx.x < 16) rsph_s[threadIdx.x] = p.rsph[(size_t)le * 16 + threadIdx.x];
+    constexpr bool S1 = MODE == MODE_SWEEP1 || MODE == MODE_SWEEP1_PRE;
+    if (S1 && threadIdx.x < 16) rsph_s[threadIdx.x] = p.rsph[(size_t)le * 16 + threadIdx.x];
+    // MODE_SWEEP1_PRE: the element's per-level factors [nlev][16], 16-byte chunk c of level k at chunk c ^ (k & 7) so that
+    // lanes holding consecutive levels read their 128-byte rows without bank conflicts
+    unsigned char *pre_s = reinterpret_cast<unsigned char *>(rsph_s + 16);
+    if (MODE == MODE_SWEEP1_PRE) {
+        const double2 *src = reinterpret_cast<const double2 *>(p.prescale + (size_t)le * p.nlev * 16);
+        for (int t = threadIdx.x; t < p.nlev * 8; t += WARPS * 32) {
+            const int k = t >> 3, c = t & 7;
+            *reinterpret_cast<double2 *>(pre_s + k * 128 + ((c ^ (k & 7)) << 4)) = __ldg(src + t);
+        }
+    }
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
@@ -272,8 +283,18 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
             v[2 * c + 1] = t.y;
         }
 
+        if (MODE == MODE_SWEEP1_PRE) { // Qtens = Qdp * (dpdiss/dp) of this slab's level (lanes past a ragged end compute on clipped zeros)
+            const int k = (kq0 + lane) % p.nlev;
+            const unsigned char *prow = pre_s + k * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double2 r = *reinterpret_cast<const double2 *>(prow + ((c ^ (k & 7)) << 4));
+                v[2 * c] *= r.x;
+                v[2 * c + 1] *= r.y;
+            }
+        }
         laplace_slab(v, M);
-        if (MODE == MODE_SWEEP1) {
+        if (S1) {
             // DSS scaling folded into the producer: rspheremp is a property of the NODE (the same in every
             // element sharing it), so (sum_e q_e) * rspheremp == sum_e (q_e * rspheremp) up to rounding
             // and sweep 2 only has to add the neighbours' (already scaled) values
@@ -291,7 +312,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
         __syncwarp();
 
         if (lane == 0) {
-            tma_store_3d(MODE == MODE_SWEEP1 ? &p.map_tmp : &p.map_q, 0, kq0, le, stage0 + s * SB);
+            tma_store_3d(S1 ? &p.map_tmp : &p.map_q, 0, kq0, le, stage0 + s * SB);
             bulk_commit();
             // refill the stage tile n-1 used, once its store has finished reading shared memory
             if (n >= 1 && n - 1 + STAGES < my_n) {
@@ -405,7 +426,7 @@ __device__ __forceinline__ uint32_t end_box_bytes(int kind)
     return kind == ET_COL ? 2048u : (kind == ET_ROW || kind == ET_HALOROW) ? 1024u : kind == ET_NONE ? 0u : 512u;
 }
 
-template <int STAGES, int WARPS>
+template <int STAGES, int WARPS, bool LAP>
 __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, unsigned char *extra,
                                                int first, int cnt, const StripReg &rg)
 {
@@ -660,7 +681,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
             if (lane == 0 && n + 1 < my_n) issue_end(n + 1);
         }
 
-        laplace_slab(v, M);
+        if (LAP) laplace_slab(v, M); // MODE_DSS stops at the assembled (and already rspheremp-scaled) values
 
         // both mates must have read this tile's columns and this rowbuf set before they are overwritten
         if (cnt > 1) mbar_wait(cbar0 + q * 8, qparity);
@@ -670,7 +691,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         __syncwarp(); // all lanes' results are in the tile; all lanes' reads of rowbuf/endbuf set q have been consumed
 
         if (lane == 0) {
-            tma_store_3d_hint(&p.map_q, 0, kq0, le, stage0 + s * SB, pol_out);
+            tma_store_3d_hint(&p.map_out, 0, kq0, le, stage0 + s * SB, pol_out);
             bulk_commit();
             if (n >= 1 && n - 1 + STAGES < my_n) {
                 bulk_wait_read<1>();
@@ -684,7 +705,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
 }
 
 // ---- generic path: any connectivity the plan accepts (face edges, cube corners, halo rows, reversed edges)
-template <int STAGES, int WARPS>
+template <int STAGES, int WARPS, bool LAP>
 __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, unsigned char *extra,
                                                int first, int cnt)
 {
@@ -897,7 +918,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
         if (has_left) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 - 16 + q * 8), "d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]) : "memory");
         if (has_right) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 + 16 + q * 8), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
 
-        laplace_slab(v, M); // (the rspheremp scaling was applied by sweep 1)
+        if (LAP) laplace_slab(v, M); // (the rspheremp scaling was applied by sweep 1)
 
         // both mates must have read this tile's columns before it is overwritten in place
         if (has_left || has_right) mbar_wait(cbar0 + q * 8, qparity);
@@ -907,7 +928,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
         __syncwarp();
 
         if (lane == 0) {
-            tma_store_3d_hint(&p.map_q, 0, kq0, le, stage0 + s * SB, l2_policy_evict_first());
+            tma_store_3d_hint(&p.map_out, 0, kq0, le, stage0 + s * SB, l2_policy_evict_first());
             bulk_commit();
             // refill the stage tile n-1 used: its store has read shared memory, and the mates
             // had consumed it before this warp overwrote it (cons wait of iteration n-1)
@@ -920,7 +941,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
     if (lane == 0) bulk_wait<0>();
 }
 
-template <int STAGES, int WARPS, int MINB>
+template <int STAGES, int WARPS, int MINB, bool LAP>
 __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __grid_constant__ SweepParams p)
 {
     static_assert(WARPS == STRIP_MAX, "one warp per strip element");
@@ -934,8 +955,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __
     const int32_t strip = p.strips[blockIdx.x];
     const int first = strip >> 3, cnt = (strip & 7) + 1;
     const StripReg &rg = p.strip_reg[blockIdx.x];
-    if (rg.regular) sweep2_regular<STAGES, WARPS>(p, stages, bars, metric_all, extra, first, cnt, rg);
-    else sweep2_generic<STAGES, WARPS>(p, stages, bars, metric_all, extra, first, cnt);
+    if (rg.regular) sweep2_regular<STAGES, WARPS, LAP>(p, stages, bars, metric_all, extra, first, cnt, rg);
+    else sweep2_generic<STAGES, WARPS, LAP>(p, stages, bars, metric_all, extra, first, cnt);
 }
 
 // kernel configurations: (STAGES, WARPS, MINB)
@@ -951,7 +972,7 @@ SweepGeometry choose_geometry(int kq, int64_t count, int mode)
     const int warps = 4;
     const int ntiles = (kq + TILE_SLABS - 1) / TILE_SLABS;
     SweepGeometry g;
-    if (mode == MODE_SWEEP2) {
+    if (mode == MODE_SWEEP2 || mode == MODE_DSS) {
         // count = strips; every warp walks all tiles of the unit.  Long units amortise the per-CTA
         // set-up (descriptor, metric, pipeline fill); p.tiles_per_unit_hint overrides for tuning.
         int64_t tpu = g_sweep2_tpu;
@@ -977,12 +998,12 @@ SweepGeometry choose_geometry(int kq, int64_t count, int mode)
 template <int MODE, int STAGES, int WARPS, int MINB>
 static cudaError_t launch_sweep_t(const SweepParams &p, cudaStream_t st)
 {
-    constexpr int smem = sweep_smem_bytes<STAGES, WARPS>();
-    static bool configured = false;
-    if (!configured) {
+    const int smem = sweep_smem_bytes<STAGES, WARPS>() + (MODE == MODE_SWEEP1_PRE ? p.nlev * 128 : 0);
+    static int configured = 0;
+    if (configured < smem) {
         cudaError_t e = cudaFuncSetAttribute(sweep_kernel<MODE, STAGES, WARPS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        configured = true;
+        configured = smem;
     }
     if (p.elem_count <= 0 || p.units <= 0) return cudaSuccess;
     dim3 grid((unsigned)p.elem_count, (unsigned)p.units);
@@ -990,31 +1011,101 @@ static cudaError_t launch_sweep_t(const SweepParams &p, cudaStream_t st)
     return cudaGetLastError();
 }
 
-template <int STAGES, int WARPS, int MINB>
+template <int STAGES, int WARPS, int MINB, bool LAP>
 static cudaError_t launch_strip_t(const SweepParams &p, cudaStream_t st)
 {
     static_assert(WARPS == STRIP_MAX, "one warp per strip element");
     constexpr int smem = strip_smem_bytes<STAGES, WARPS>();
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(sweep2_strip_kernel<STAGES, WARPS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(sweep2_strip_kernel<STAGES, WARPS, MINB, LAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
     if (p.strip_count <= 0 || p.units <= 0) return cudaSuccess;
     dim3 grid((unsigned)p.strip_count, (unsigned)p.units);
-    sweep2_strip_kernel<STAGES, WARPS, MINB><<<grid, WARPS * 32, smem, st>>>(p);
+    sweep2_strip_kernel<STAGES, WARPS, MINB, LAP><<<grid, WARPS * 32, smem, st>>>(p);
     return cudaGetLastError();
 }
+
+bool sweep1_pre_fits(int nlev) { return sweep_smem_bytes<3, 4>() + nlev * 128 <= 227 * 1024; }
 
 cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st)
 {
     switch (mode) {
     case MODE_LAPLACE: return launch_sweep_t<MODE_LAPLACE, BWK_CFG_LAPLACE>(p, st);
     case MODE_SWEEP1: return launch_sweep_t<MODE_SWEEP1, BWK_CFG_SWEEP1>(p, st);
-    case MODE_SWEEP2: return launch_strip_t<BWK_CFG_SWEEP2>(p, st);
+    case MODE_SWEEP1_PRE: return launch_sweep_t<MODE_SWEEP1_PRE, BWK_CFG_SWEEP1>(p, st);
+    case MODE_SWEEP2: return launch_strip_t<BWK_CFG_SWEEP2, true>(p, st);
+    case MODE_DSS: return launch_strip_t<BWK_CFG_SWEEP2, false>(p, st);
     default: return cudaErrorInvalidValue;
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// advance_hypervis_scalar, pointwise part (upstream HOMME prim_advection; not in the reference):
+//     out = limiter2d_zero(Qdp * spheremp - dt*nu_q * Qtens) * rspheremp
+// (the trailing rspheremp is the DSS scaling, folded into the producer as in sweep 1).  Fully coalesced:
+// a thread owns one 16-byte chunk (2 GLL points), 8 consecutive lanes own one (np x np) level, the
+// limiter's two sums per level are 3-step xor-shuffle reductions inside those 8 lanes.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) hypervis_post_kernel(const double *__restrict__ qdp, const double *__restrict__ qtens, double *__restrict__ out,
+                                                            const double *__restrict__ elem, const double *__restrict__ rsph,
+                                                            const int32_t *__restrict__ list, int first, int64_t nchunks, int kq, double coef, int limiter)
+{
+    const int64_t g = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const bool live = g < nchunks; // nchunks is a multiple of 8: the 8 lanes of a level are live together
+    const int64_t slab = live ? g >> 3 : 0;
+    const int c = (int)(g & 7);
+    const int64_t li = slab / kq;
+    const int le = list ? list[li] : first + (int)li;
+    const size_t off = ((size_t)le * kq + (size_t)(slab - li * kq)) * 16 + 2 * c;
+    const double2 a = *reinterpret_cast<const double2 *>(qdp + off), t = *reinterpret_cast<const double2 *>(qtens + off);
+    const double2 mp = __ldg(reinterpret_cast<const double2 *>(elem + (size_t)le * ELEM_DOUBLES + 64 + 2 * c));
+    const double2 rs = __ldg(reinterpret_cast<const double2 *>(rsph + (size_t)le * 16 + 2 * c));
+    // same roundings as the CPU statement  Qdp*spheremp - (dt*nu_q)*Qtens  (no FMA contraction)
+    double x = __dsub_rn(__dmul_rn(a.x, mp.x), __dmul_rn(coef, t.x));
+    double y = __dsub_rn(__dmul_rn(a.y, mp.y), __dmul_rn(coef, t.y));
+    if (limiter) { // limiter2d_zero on this level: clip negatives, rescale so that the level's sum is unchanged
+        double mass = x + y;
+        mass += __shfl_xor_sync(0xffffffffu, mass, 1);
+        mass += __shfl_xor_sync(0xffffffffu, mass, 2);
+        mass += __shfl_xor_sync(0xffffffffu, mass, 4);
+        const bool neg = mass < 0.0;
+        if (neg) { x = -x; y = -y; }
+        x = x < 0.0 ? 0.0 : x;
+        y = y < 0.0 ? 0.0 : y;
+        double added = x + y;
+        added += __shfl_xor_sync(0xffffffffu, added, 1);
+        added += __shfl_xor_sync(0xffffffffu, added, 2);
+        added += __shfl_xor_sync(0xffffffffu, added, 4);
+        if (added > 0.0) {
+            const double scale = fabs(mass) / added;
+            x *= scale;
+            y *= scale;
+        }
+        if (neg) { x = -x; y = -y; }
+    }
+    if (live) *reinterpret_cast<double2 *>(out + off) = make_double2(x * rs.x, y * rs.y);
+}
+
+cudaError_t launch_hypervis_post(const double *qdp, const double *qtens, double *out, const double *elem, const double *rsph,
+                                 const int32_t *list, int first, int count, int kq, double coef, int limiter, cudaStream_t st)
+{
+    if (count <= 0) return cudaSuccess;
+    const int64_t nchunks = (int64_t)count * kq * 8;
+    hypervis_post_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(qdp, qtens, out, elem, rsph, list, first, nchunks, kq, coef, limiter);
+    return cudaGetLastError();
+}
+
+__global__ void ratio_kernel(const double *__restrict__ num, const double *__restrict__ den, double *__restrict__ ratio, int64_t n)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) ratio[i] = num[i] / den[i];
+}
+cudaError_t launch_ratio(const double *dpdiss, const double *dp, double *ratio, int64_t n, cudaStream_t st)
+{
+    ratio_kernel<<<148 * 8, 256, 0, st>>>(dpdiss, dp, ratio, n);
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------

@@ -15,7 +15,9 @@ constexpr int ELEM_DOUBLES = 144;   // element_t, F90:23-27
 enum SweepMode : int {
     MODE_LAPLACE = 0, // qtens -> qtens in place              (reference-pinned, F90:186-200)
     MODE_SWEEP1 = 1,  // qtens -> tmp                          (first laplace; neighbours read their edges straight from tmp)
-    MODE_SWEEP2 = 2   // tmp + neighbours' edge values -> *rspheremp -> laplace -> qtens  (edgeVunpack + second laplace)
+    MODE_SWEEP2 = 2,  // tmp + neighbours' edge values -> *rspheremp -> laplace -> qtens  (edgeVunpack + second laplace)
+    MODE_SWEEP1_PRE = 3, // as MODE_SWEEP1 on qtens * prescale(:,:,k,ie)  (advance_hypervis_scalar: Qtens = dpdiss*Qdp/dp)
+    MODE_DSS = 4      // as MODE_SWEEP2 without the Laplacian: tmp + neighbours' edge values -> out  (edgeVunpack [+ rspheremp])
 };
 
 // Everything a sweep launch needs.  Tensor maps are passed by value (__grid_constant__).
@@ -26,6 +28,9 @@ struct SweepParams {
     CUtensorMap map_halo;   // received edge rows as {4, KQ, nrows}, box {4,32,1}, SWIZZLE_32B (aliases map_rows when there is no halo)
     CUtensorMap map_pt;     // tmp as {4 (i), 4 (j), KQ, nelem}, box {2,1,32,1}: the 16-byte i-pair holding one point of 32 consecutive slabs
     CUtensorMap map_halo_pt;// received edge rows as {4, KQ, nrows}, box {2,32,1}: half a halo row (aliases a 3-D view of tmp when there is no halo)
+    CUtensorMap map_out;    // where sweep 2 / the DSS-only sweep store their result (qtens, or the hyperviscosity work buffer)
+    const double *prescale; // MODE_SWEEP1_PRE: [nelem][nlev][16] factors applied to the input slab of level k
+    int nlev;               // MODE_SWEEP1_PRE: slab kq belongs to level kq % nlev
     const double *metric;   // [nelem][64] folded metric
     const double *rsph;     // [nelem][16]
     const ElemDss *dss;     // [nelem]
@@ -50,6 +55,14 @@ SweepGeometry choose_geometry(int kq, int64_t nelem, int mode);
 void set_sweep2_tiles_per_unit(int tpu); // tuning knob (BWK_SWEEP2_TPU)
 
 cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st);
+// MODE_SWEEP1_PRE needs nlev*128 more bytes of shared memory per CTA than the other element-local sweeps; false if that does not fit
+bool sweep1_pre_fits(int nlev);
+// advance_hypervis_scalar, pointwise part: out = limiter2d_zero(qdp*spheremp - coef*qtens) * rspheremp over the slabs of
+// local elements [first, first+count) or of a device list (HOMME prim_advection, not in the reference)
+cudaError_t launch_hypervis_post(const double *qdp, const double *qtens, double *out, const double *elem, const double *rsph,
+                                 const int32_t *list, int first, int count, int kq, double coef, int limiter, cudaStream_t st);
+// prescale = dpdiss / dp, n values
+cudaError_t launch_ratio(const double *dpdiss, const double *dp, double *ratio, int64_t n, cudaStream_t st);
 // plain-load variant of MODE_LAPLACE (no TMA, no shared-memory staging); for ncu A/B only
 cudaError_t launch_laplace_plain(double *qtens, const double *metric, int elem_first, int elem_count, int kq, cudaStream_t st);
 

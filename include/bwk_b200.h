@@ -148,6 +148,23 @@ int bwk_run_biharmonic_phase(int phase);
 int bwk_biharmonic_wk_scalar_full(const bwk_element_t *elem, double *qtens,
                                   const bwk_derivative_t *deriv);
 
+/* ---- the caller of this path in HOMME: advance_hypervis_scalar ----------------
+ * NOT in the reference repository (upstream E3SM components/homme/src/share/prim_advection_base.F90, un-vendored, no
+ * pinned version; semantics restated in oracle/bwk_oracle.c, PARITY UNPINNED).  It replaces, per subcycle
+ * (dt = dt2 / hypervis_subcycle_q):
+ *     Qtens = dpdiss * Qdp / dp ; call biharmonic_wk_scalar(elem, Qtens, deriv, edge, hybrid, nets, nete)
+ *     Qdp   = Qdp * spheremp - dt * nu_q * Qtens ; limiter2d_zero(Qdp(:,:,:,q)) ; edgeVpack / bndry_exchangeV /
+ *     edgeVunpack ; Qdp = Qdp * rspheremp
+ * Qdp(np,np,nlev,qsize,nelemd) is the field given to bwk_upload / held in the device buffer; dp and dpdiss are
+ * (np,np,nlev,nelemd): dp = derived%dp - dt2*derived%divdp_proj, dpdiss = derived%dpdiss_ave (or dp0(k) broadcast).
+ * Needs a topology (bwk_set_topology_*).  Allocates a second field-sized work buffer on first use. */
+int bwk_upload_hypervis_fields(const double *dp, const double *dpdiss);
+/* device resident, asynchronous; limiter != 0 applies limiter2d_zero */
+int bwk_run_advance_hypervis(double dt2, double nu_q, int hypervis_subcycle_q, int limiter);
+/* upload (elem, Qdp, dp, dpdiss, deriv), run, download Qdp */
+int bwk_advance_hypervis_scalar(const bwk_element_t *elem, double *Qdp, const double *dp, const double *dpdiss,
+                                const bwk_derivative_t *deriv, double dt2, double nu_q, int hypervis_subcycle_q, int limiter);
+
 /* ---- several GPUs: one process per GPU, contiguous element blocks, NCCL send/recv ---- */
 #define BWK_UNIQUE_ID_BYTES 128
 /* rank 0 creates the id, the launcher broadcasts the bytes (any transport) */

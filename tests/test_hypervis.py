@@ -1,0 +1,174 @@
+"""advance_hypervis_scalar: the caller of biharmonic_wk_scalar in upstream HOMME.
+NOT in the reference repository -> parity unpinned; the oracle (oracle/bwk_oracle.c) restates the published
+structure, and the tests pin it to analytic facts on the physical cubed sphere:
+  * a constant mixing ratio is a fixed point (hyperviscosity of a constant is zero, DSS of a continuous field is the field);
+  * a spherical harmonic of degree l decays by  1 - dt nu_q (l(l+1) rrearth^2)^2  in the mass-weighted projection (O(h^6));
+  * limiter2d_zero removes negatives and keeps every level's sum.
+GPU tests compare libbwk_b200 (C ABI) with the oracle on the same inputs and repeat the analytic checks.
+"""
+import numpy as np
+import pytest
+
+NLEV, QSIZE = 3, 2
+
+
+def _cs():
+    from codesign_kernels_b200 import cubed_sphere
+
+    return cubed_sphere
+
+
+def _slot_rel(a, b):
+    worst = 0.0
+    for t in range(a.shape[3]):
+        for k in range(a.shape[2]):
+            worst = max(worst, float(np.abs(a[:, :, k, t, :] - b[:, :, k, t, :]).max() / np.abs(b[:, :, k, t, :]).max()))
+    return worst
+
+
+def _physical(oracle, ne):
+    cs = _cs()
+    dvv, elem, xyz = cs.physical_elements(ne)
+    n = 6 * ne * ne
+    dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
+    rs = dss.rspheremp(elem)
+    mp = elem[:, 64:80].reshape(n, 4, 4).transpose(2, 1, 0)  # [i][j][e]
+    return dvv, elem, xyz, dss, rs, mp
+
+
+def _smooth_dp(xyz, nlev):
+    """a continuous, positive layer thickness: 1 + 0.1 k + 0.2 * harmonic(2)"""
+    n = xyz.shape[0]
+    dp = np.empty((4, 4, nlev, n), order="F")
+    h2 = np.transpose(_cs().harmonic(xyz, 2), (2, 1, 0))
+    for k in range(nlev):
+        dp[:, :, k, :] = 1.0 + 0.1 * k + 0.2 * h2
+    return dp
+
+
+def _decay_case(oracle, ne):
+    dvv, elem, xyz, dss, rs, mp = _physical(oracle, ne)
+    n = 6 * ne * ne
+    q0, deg = _cs().harmonic_field(xyz, NLEV, QSIZE)
+    ones = np.ones((4, 4, NLEV, n), order="F")
+    rr = oracle.rrearth()
+    coef = 0.05 / (42.0 * rr * rr) ** 2  # dt*nu_q: 5 % decay of the degree-6 harmonic
+    return dvv, elem, dss, rs, mp, q0, deg, ones, coef, rr
+
+
+def _decay_errors(qnew, q0, deg, mp, coef, rr):
+    out = {}
+    for t in range(QSIZE):
+        for k in range(NLEV):
+            lam = deg[k, t] * (deg[k, t] + 1) * rr * rr
+            f = q0[:, :, k, t, :]
+            ratio = (mp * f * qnew[:, :, k, t, :]).sum() / (mp * f * f).sum()
+            out[int(deg[k, t])] = float((1.0 - ratio) / (coef * lam * lam) - 1.0)
+    return out
+
+
+def test_limiter2d_zero_properties(oracle):
+    rng = np.random.default_rng(11)
+    q = rng.standard_normal((4, 4, 500)).copy(order="F")
+    q[:, :, 0] = 0.0
+    q[:, :, 1] = -np.abs(q[:, :, 1])          # all negative: flipped, nothing to clip
+    q[:, :, 2] = np.abs(q[:, :, 2])           # all positive: untouched
+    before = q.copy(order="F")
+    mass0 = q.sum(axis=(0, 1))
+    oracle.limiter2d_zero(q)
+    mass1 = q.sum(axis=(0, 1))
+    assert np.allclose(mass1, mass0, rtol=1e-13, atol=1e-15)
+    pos = mass0 >= 0
+    assert q[:, :, pos].min() >= 0.0 and q[:, :, ~pos].max() <= 0.0
+    assert np.array_equal(q[:, :, 0], before[:, :, 0]) and np.allclose(q[:, :, 1:3], before[:, :, 1:3], rtol=1e-15)
+
+
+def test_constant_mixing_ratio_is_a_fixed_point_cpu(oracle):
+    ne = 4
+    dvv, elem, xyz, dss, rs, mp = _physical(oracle, ne)
+    n = 6 * ne * ne
+    dp = _smooth_dp(xyz, NLEV)
+    dp0 = np.ones_like(dp, order="F") * (1.0 + np.arange(NLEV))[None, None, :, None]
+    qdp = np.empty((4, 4, NLEV, QSIZE, n), order="F")
+    for t in range(QSIZE):
+        qdp[:, :, :, t, :] = (0.3 + t) * dp
+    ref = qdp.copy(order="F")
+    rr = oracle.rrearth()
+    dss.advance_hypervis_scalar(elem, rs, qdp, dp, dp0, dvv.reshape(16), dt2=2.0, nu_q=0.05 / (42 * rr * rr) ** 2, subcycles=2, limiter=True)
+    assert _slot_rel(qdp, ref) < 1e-10
+
+
+def test_harmonic_decay_rate_cpu(oracle):
+    errs = {}
+    for ne in (4, 8):
+        dvv, elem, dss, rs, mp, q0, deg, ones, coef, rr = _decay_case(oracle, ne)
+        q = q0.copy(order="F")
+        dss.advance_hypervis_scalar(elem, rs, q, ones, ones, dvv.reshape(16), dt2=1.0, nu_q=coef, subcycles=1, limiter=False)
+        errs[ne] = _decay_errors(q, q0, deg, mp, coef, rr)
+    for l in range(1, 7):
+        assert abs(errs[8][l]) < 3e-5 and abs(errs[8][l]) < abs(errs[4][l]) / 10.0, (l, errs[4][l], errs[8][l])
+
+
+def _lcg_case(oracle, ne, nlev, qsize):
+    n = 6 * ne * ne
+    dvv, elem, q = oracle.initialize_data(n, nlev, qsize)
+    dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
+    rs = dss.rspheremp(elem)
+    rng = np.random.default_rng(3)
+    dp = (0.5 + rng.random((4, 4, nlev, n))).copy(order="F")
+    dpd = (0.5 + rng.random((4, 4, nlev, n))).copy(order="F")
+    # dt*nu_q such that the diffusion term is comparable with Qdp*spheremp (the noise metric gives a tiny biharmonic)
+    b = dss.biharmonic_full(elem, rs, (q * (dpd / dp)[:, :, :, None, :]).copy(order="F"), dvv)
+    coef = 0.25 / np.abs(b).max()
+    return n, dvv, elem, q, dss, rs, dp, dpd, coef
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ne,nlev,qsize,sub,lim", [(2, 8, 3, 1, True), (3, 72, 2, 2, True), (4, 33, 1, 1, False), (8, 16, 4, 3, True)])
+def test_advance_hypervis_gpu_vs_oracle(bwk, oracle, ne, nlev, qsize, sub, lim):
+    """tolerance: 1e-12 of each (k,q) field's maximum per subcycle (the update subtracts two terms of similar size, so an
+    elementwise-relative bound is not meaningful; same operator drift as the biharmonic tests otherwise)"""
+    n, dvv, elem, q, dss, rs, dp, dpd, coef = _lcg_case(oracle, ne, nlev, qsize)
+    ref = dss.advance_hypervis_scalar(elem, rs, q.copy(order="F"), dp, dpd, dvv, dt2=2.0, nu_q=coef / 2.0 * sub, subcycles=sub, limiter=lim)
+    with bwk.KernelUtils(n, nlev, qsize).allocate_data() as ku:
+        ku.initialize_data()
+        assert np.array_equal(ku.qtens, q)
+        ku.set_topology_cubed_sphere(ne)
+        ku.advance_hypervis_scalar(ku.elem, ku.qtens, dp, dpd, ku.deriv, 2.0, coef / 2.0 * sub, sub, lim)
+        got = ku.qtens.copy(order="F")
+        # device-resident entry: same bits
+        ku.initialize_data()
+        ku.update_device()
+        ku.upload_hypervis_fields(dp, dpd)
+        ku.run_advance_hypervis_device(2.0, coef / 2.0 * sub, sub, lim)
+        ku.update_host()
+        assert np.array_equal(ku.qtens, got)
+    err = _slot_rel(got, ref)
+    print(f"ne={ne} sub={sub} limiter={lim}: GPU vs oracle {err:.2e} of the field maximum")
+    assert err <= 1e-12 * sub, err
+    if lim:
+        assert got.min() >= 0.0  # LCG data: every level has positive mass, so the limiter leaves no negatives
+
+
+@pytest.mark.gpu
+def test_advance_hypervis_analytic_gpu(bwk, oracle):
+    ne = 8
+    n = 6 * ne * ne
+    dvv, elem, dss, rs, mp, q0, deg, ones, coef, rr = _decay_case(oracle, ne)
+    with bwk.KernelUtils(n, NLEV, QSIZE).allocate_data() as ku:
+        ku.elem.view(np.float64).reshape(n, 144)[...] = elem
+        ku.deriv["Dvv"] = dvv
+        ku.set_topology_cubed_sphere(ne)
+        ku.qtens[...] = q0
+        ku.advance_hypervis_scalar(ku.elem, ku.qtens, ones, ones, ku.deriv, 1.0, coef, 1, False)
+        errs = _decay_errors(ku.qtens, q0, deg, mp, coef, rr)
+        assert max(abs(v) for v in errs.values()) < 3e-5, errs
+        # constant mixing ratio: fixed point
+        xyz = _cs().physical_elements(ne)[2]
+        dp = _smooth_dp(xyz, NLEV)
+        dp0 = np.ones_like(dp, order="F") * (1.0 + np.arange(NLEV))[None, None, :, None]
+        for t in range(QSIZE):
+            ku.qtens[:, :, :, t, :] = (0.3 + t) * dp
+        ref = ku.qtens.copy(order="F")
+        ku.advance_hypervis_scalar(ku.elem, ku.qtens, dp, dp0, ku.deriv, 2.0, coef, 2, True)
+        assert _slot_rel(ku.qtens, ref) < 1e-10
