@@ -171,4 +171,6 @@ def test_advance_hypervis_analytic_gpu(bwk, oracle):
             ku.qtens[:, :, :, t, :] = (0.3 + t) * dp
         ref = ku.qtens.copy(order="F")
         ku.advance_hypervis_scalar(ku.elem, ku.qtens, dp, dp0, ku.deriv, 2.0, coef, 2, True)
-        assert _slot_rel(ku.qtens, ref) < 1e-10
+        # not exactly zero: dp0*Qdp/dp is constant only up to rounding, and dt*nu_q*biharmonic amplifies that noise by
+        # ~ 0.05 (lambda_max/lambda_6)^2 ~ 1e6..1e7 at ne=8 (measured 6.7e-10; 1e-10 bound holds at ne=4)
+        assert _slot_rel(ku.qtens, ref) < 1e-8
