@@ -15,6 +15,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def hypervis_inputs(n, nlev):
+    """dp, dpdiss (4,4,nlev,n) and dt*nu_q, the same on every rank and in the single-rank run of the test"""
+    rng = np.random.default_rng(77)
+    dp = np.asfortranarray(0.5 + rng.random((4, 4, nlev, n)))
+    dpd = np.asfortranarray(0.5 + rng.random((4, 4, nlev, n)))
+    return dp, dpd, 1.0e24  # with the LCG metric the weak biharmonic is O(1e-25): the two terms of the update are comparable
+
+
 def main():
     mode, ne, nlev, qsize, outdir = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), sys.argv[5]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -38,6 +46,13 @@ def main():
             ku.run_biharmonic_device()
             ku.sync()
         np.save(os.path.join(outdir, f"dev_{rank}.npy"), ku.download_elements(0, count))
+        # advance_hypervis_scalar across ranks: two DSS exchanges per subcycle, halo buffers reused
+        dp, dpd, coef = hypervis_inputs(n, nlev)
+        ku.initialize_data_device(n, first)
+        ku.upload_hypervis_fields(np.asfortranarray(dp[..., first : first + count]), np.asfortranarray(dpd[..., first : first + count]))
+        ku.run_advance_hypervis_device(2.0, coef, 2, True)
+        ku.sync()
+        np.save(os.path.join(outdir, f"hv_{rank}.npy"), ku.download_elements(0, count))
         dist.barrier()
         ku.finalize()
     else:

@@ -47,6 +47,19 @@ def test_multi_gpu_matches_single_gpu_bitwise(bwk, oracle, tmp_path, ne, nlev, q
         ku.run_biharmonic_device()
         single = ku.download_elements(0, n)
     assert np.array_equal(multi, single)
+    # advance_hypervis_scalar: N ranks == 1 rank bit for bit
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from mg_worker import hypervis_inputs
+
+    dp, dpd, coef = hypervis_inputs(n, nlev)
+    multi_hv = np.concatenate([np.load(tmp_path / f"hv_{r}.npy") for r in range(world)], axis=-1)
+    with bwk.KernelUtils(n, nlev, qsize).allocate_data(host_arrays=False) as ku:
+        ku.initialize_data_device()
+        ku.set_topology_cubed_sphere(ne)
+        ku.upload_hypervis_fields(dp, dpd)
+        ku.run_advance_hypervis_device(2.0, coef, 2, True)
+        single_hv = ku.download_elements(0, n)
+    assert np.array_equal(multi_hv, single_hv)
     dvv, elem, q = oracle.initialize_data(n, nlev, qsize)
     dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
     ref = dss.biharmonic_full(elem, dss.rspheremp(elem), q, dvv)
