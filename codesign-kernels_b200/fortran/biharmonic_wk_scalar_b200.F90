@@ -20,6 +20,8 @@ module biharmonic_wk_scalar_b200
 
   public :: biharmonic_wk_scalar
   public :: biharmonic_wk_scalar_cpusig
+  public :: advance_hypervis_scalar
+  public :: b200_set_topology_gdof
   public :: b200_init
   public :: b200_finalize
 
@@ -47,6 +49,20 @@ module biharmonic_wk_scalar_b200
       integer(c_int), intent(in) :: nets_c, nete_c
       integer(c_int) :: rc
     end function bwk_biharmonic_wk_scalar_nets
+    function bwk_set_topology_gdof(nelem_global_c, gdof_c, elem_first_c) bind(c, name="bwk_set_topology_gdof") result(rc)
+      use iso_c_binding
+      integer(c_int64_t), value :: nelem_global_c, elem_first_c
+      type(c_ptr), value :: gdof_c
+      integer(c_int) :: rc
+    end function bwk_set_topology_gdof
+    function bwk_advance_hypervis_scalar(elem_c, qdp_c, dp_c, dpdiss_c, deriv_c, dt2_c, nu_q_c, subcycle_c, limiter_c) &
+        bind(c, name="bwk_advance_hypervis_scalar") result(rc)
+      use iso_c_binding
+      type(c_ptr), value :: elem_c, qdp_c, dp_c, dpdiss_c, deriv_c
+      real(c_double), value :: dt2_c, nu_q_c
+      integer(c_int), value :: subcycle_c, limiter_c
+      integer(c_int) :: rc
+    end function bwk_advance_hypervis_scalar
   end interface
 
 contains
@@ -61,6 +77,37 @@ contains
     implicit none
     if (bwk_finalize() /= 0) error stop "bwk_finalize failed"
   end subroutine b200_finalize
+
+  !! HOMME global dof ids per GLL point, gdof(np,np,nelemd) (the information edgeVpack/edgeVunpack's maps carry):
+  !! needed once before the DSS-containing calls below
+  subroutine b200_set_topology_gdof(gdof, nelem_global, elem_first)
+    implicit none
+    integer(c_int64_t), intent(in), target :: gdof(np,np,nelemd)
+    integer(c_int64_t), intent(in) :: nelem_global, elem_first
+    if (bwk_set_topology_gdof(nelem_global, c_loc(gdof), elem_first) /= 0) error stop "bwk_set_topology_gdof failed"
+  end subroutine b200_set_topology_gdof
+
+  !! The caller of this path in HOMME (prim_advection: advance_hypervis_scalar), kernel-extraction style: the state the
+  !! upstream routine reads through elem(ie)%state / elem(ie)%derived is passed as plain arrays.
+  !!   Qdp(np,np,nlev,qsize,nelemd) = elem(:)%state%Qdp(:,:,:,:,nt_qdp)          (updated in place)
+  !!   dp (np,np,nlev,nelemd)       = derived%dp - dt2*derived%divdp_proj
+  !!   dpdiss(np,np,nlev,nelemd)    = derived%dpdiss_ave, or dp0(k) broadcast
+  subroutine advance_hypervis_scalar(elem,Qdp,dp,dpdiss,deriv,dt2,nu_q,hypervis_subcycle_q,limiter)
+    implicit none
+    type (element_t)     , intent(in   ), target :: elem(:)
+    real (kind=real_kind), intent(inout), target :: Qdp(np,np,nlev,qsize,nelemd)
+    real (kind=real_kind), intent(in   ), target :: dp(np,np,nlev,nelemd)
+    real (kind=real_kind), intent(in   ), target :: dpdiss(np,np,nlev,nelemd)
+    type (derivative_t)  , intent(in   ), target :: deriv
+    real (kind=real_kind), intent(in   ) :: dt2, nu_q
+    integer              , intent(in   ) :: hypervis_subcycle_q
+    logical              , intent(in   ) :: limiter
+    integer(c_int) :: rc
+    rc = bwk_advance_hypervis_scalar(c_loc(elem(1)), c_loc(Qdp), c_loc(dp), c_loc(dpdiss), c_loc(deriv), &
+                                     real(dt2,c_double), real(nu_q,c_double), int(hypervis_subcycle_q,c_int), &
+                                     merge(1_c_int, 0_c_int, limiter))
+    if (rc /= 0) error stop "bwk_advance_hypervis_scalar failed"
+  end subroutine advance_hypervis_scalar
 
   !! same dummy arguments as the push-loop variant, F90:525-531
   subroutine biharmonic_wk_scalar(elem,qtens,grads,deriv,nets,nete)
