@@ -186,6 +186,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-hv", action="store_true", help="skip the advance_hypervis_scalar (caller, SURVEY 8(f)1) timing")
     ap.add_argument("--variant", type=int, default=0)
     args = ap.parse_args()
 
@@ -255,6 +256,7 @@ def main():
             ku.sync()
             if world > 1:
                 dist.barrier()
+                ku.comm_barrier()  # device-side: the ranks' streams start the step within one NCCL latency of each other
             la = ku.launch_count()
             ku.event_record(0)
             run()
@@ -320,6 +322,22 @@ def main():
 
     clocks = sampler.summary(*wall) if sampler else None
 
+    # ---- the caller of the path (upstream HOMME advance_hypervis_scalar), one subcycle, device resident
+    hv = None
+    if not args.no_hv:
+        try:
+            rng = np.random.default_rng(1 + rank)
+            dp = np.asfortranarray(0.5 + rng.random((4, 4, nlev, count)))
+            ku.upload_hypervis_fields(dp, np.asfortranarray(dp[::-1]))
+            del dp
+            hv_ms, hv_launches, _ = timed_steps(lambda: ku.run_advance_hypervis_device(2.0, 1.0e24, 1, True), 1, max(3, min(args.steps, 5)))
+            hv_ms /= max(3, min(args.steps, 5))
+            hv = {"value": updates_global / (hv_ms * 1e-3), "unit": UNIT, "ms_per_step": hv_ms, "bytes_per_update": 72,
+                  "GBps_of_its_traffic": 72.0 * updates_global / world / (hv_ms * 1e-3) / 1e9,
+                  "note": "Qtens=dpdiss*Qdp/dp -> biharmonic -> Qdp*spheremp-dt*nu_q*Qtens -> limiter2d_zero -> DSS -> *rspheremp (4 launches)"}
+        except Exception as ex:
+            hv = {"value": None, "error": str(ex)[:200]}
+
     # ---- e2e: host buffers through the drop-in call (H2D + D2H inside the timed region)
     e2e = None
     if not args.no_e2e:
@@ -380,7 +398,7 @@ def main():
             "config": {"workload": f"ne{ne}np4 L{nlev} q{qsize}, {nglob} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
                        "partition": f"contiguous element blocks over {world} rank(s)", "l2": "working set >> L2 (no flush needed); inputs re-generated before every step",
                        "variant": args.variant},
-            "laplace_only": lap, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "laplace_only": lap, "advance_hypervis_scalar": hv, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     ku.finalize()

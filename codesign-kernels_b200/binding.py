@@ -87,6 +87,7 @@ def lib():
         "bwk_comm_unique_id": [p],
         "bwk_comm_init": [i32, i32, p],
         "bwk_comm_finalize": [],
+        "bwk_comm_barrier": [],
         "bwk_partition": [i64, i32, i32, C.POINTER(i64), C.POINTER(i64)],
         "bwk_plan_apply_host": [p, p, p],
         "bwk_plan_send_list": [p, i32, p, p],
@@ -293,6 +294,10 @@ class KernelUtils:
 
     def sync(self):
         _ck(lib().bwk_sync())
+
+    def comm_barrier(self):
+        """device-side barrier across ranks on the library's stream (no-op on one rank)"""
+        _ck(lib().bwk_comm_barrier())
 
     # -- the reference's subroutine, GPU2 signature F90:525-531 (host arrays in, host arrays out)
     def biharmonic_wk_scalar(self, elem, qtens, grads, deriv, nets, nete):

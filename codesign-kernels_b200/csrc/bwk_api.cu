@@ -18,6 +18,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -434,6 +435,26 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
         if (produce(0, g.nelem, (const int32_t *)nullptr)) return 1;
         return sweep2(g.d_strips_all, g.d_reg_all, (int64_t)P.strips_all.size(), g.s_main, consume_mode, out);
     }
+    static const bool trace = std::getenv("BWK_TRACE") != nullptr; // debugging aid: serialised phases with their durations on stderr
+    if (trace) {
+        auto lap = [&](const char *what, cudaStream_t st, auto &&fn) -> int {
+            CK(cudaDeviceSynchronize());
+            const auto t0 = std::chrono::steady_clock::now();
+            if (fn()) return 1;
+            CK(cudaStreamSynchronize(st));
+            const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+            std::fprintf(stderr, "[bwk trace rank %d] %-28s %9.1f us\n", P.rank, what, us);
+            return 0;
+        };
+        if (lap("produce(boundary)", g.s_main, [&] { return produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary); })) return 1;
+        if (g.comm && lap("pack + ncclSend/Recv", g.s_comm, [&] { return exchange_halo(); })) return 1;
+        if (lap("produce(interior)", g.s_main, [&] { return produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior); })) return 1;
+        if (lap("consume(independent strips)", g.s_main, [&] { return sweep2(g.d_strips_indep, g.d_reg_indep, (int64_t)P.strips_independent.size(), g.s_main, consume_mode, out); })) return 1;
+        if (lap("consume(dependent strips)", g.s_main, [&] { return sweep2(g.d_strips_dep, g.d_reg_dep, (int64_t)P.strips_dependent.size(), g.s_main, consume_mode, out); })) return 1;
+        std::fprintf(stderr, "[bwk trace rank %d] boundary %zu interior %zu elements; independent %zu dependent %zu strips\n", P.rank,
+                     P.boundary_list.size(), P.interior_list.size(), P.strips_independent.size(), P.strips_dependent.size());
+        return 0;
+    }
     if (produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary)) return 1;
     CK(cudaEventRecord(g.ev_b, g.s_main));
     CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
@@ -596,13 +617,22 @@ int bwk_init(int nelemd, int nlev, int qsize)
     if (prop.major != 10) return fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", dev, prop.major, prop.minor);
     g = Ctx();
     if (const char *e = std::getenv("BWK_SWEEP2_TPU")) set_sweep2_tiles_per_unit(std::atoi(e));
+    // profiling aid: plan and launch lists of rank r of n on ONE GPU without a communicator ("r,n"; only with BWK_TRACE,
+    // halo rows are never filled, results are meaningless)
+    if (const char *e = std::getenv("BWK_FAKE_RANKS")) std::sscanf(e, "%d,%d", &g.rank, &g.nranks);
     g.nelem = nelemd;
     g.nlev = nlev;
     g.qsize = qsize;
     g.kq = nlev * qsize;
     g.q_doubles = (size_t)16 * g.kq * nelemd;
     CK(cudaStreamCreateWithFlags(&g.s_main, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&g.s_comm, cudaStreamNonBlocking));
+    {
+        // the halo pack and the NCCL send/recv kernels must be dispatched as soon as CTA slots free up, not behind the
+        // whole interior grid that is already queued on s_main: highest priority for the comm stream
+        int prio_lo = 0, prio_hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        CK(cudaStreamCreateWithPriority(&g.s_comm, cudaStreamNonBlocking, prio_hi));
+    }
     CK(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&g.ev_b, cudaEventDisableTiming));
@@ -1046,6 +1076,23 @@ int bwk_comm_init(int rank, int nranks, const void *id_bytes)
     ncclUniqueId id;
     std::memcpy(&id, id_bytes, sizeof id);
     NK(g_nccl.CommInitRank(&g.comm, nranks, id, rank));
+    return 0;
+}
+
+// device-side barrier on the library's stream: every rank exchanges 8 bytes with every other rank, so work enqueued
+// after it starts within one NCCL latency on all ranks (a host barrier leaves hundreds of microseconds of skew)
+int bwk_comm_barrier(void)
+{
+    if (need_init()) return 1;
+    if (g.nranks == 1 || !g.comm) return 0;
+    if (!g.d_dummy) CK(cudaMalloc(&g.d_dummy, sizeof(double) * 2 * 1024));
+    NK(g_nccl.GroupStart());
+    for (int p = 0; p < g.nranks; ++p) {
+        if (p == g.rank) continue;
+        NK(g_nccl.Send(g.d_dummy + g.rank, 1, ncclDouble, p, g.comm, g.s_main));
+        NK(g_nccl.Recv(g.d_dummy + 1024 + p, 1, ncclDouble, p, g.comm, g.s_main));
+    }
+    NK(g_nccl.GroupEnd());
     return 0;
 }
 

@@ -170,6 +170,8 @@ int bwk_advance_hypervis_scalar(const bwk_element_t *elem, double *Qdp, const do
 /* rank 0 creates the id, the launcher broadcasts the bytes (any transport) */
 int bwk_comm_unique_id(void *id_bytes);
 int bwk_comm_init(int rank, int nranks, const void *id_bytes);
+/* device-side barrier across ranks on the library's stream (benchmark bracketing); no-op on one rank */
+int bwk_comm_barrier(void);
 int bwk_comm_finalize(void);
 /* contiguous block partition used by every rank: [first, first+count) */
 int bwk_partition(int64_t nelem_global, int rank, int nranks, int64_t *first, int64_t *count);
