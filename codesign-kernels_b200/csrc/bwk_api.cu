@@ -20,6 +20,7 @@
 #include <cstdlib>
 #include <chrono>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -199,19 +200,59 @@ int sweep(int mode, int first, int count, const int32_t *list, cudaStream_t st)
     return 0;
 }
 
-// launch sweep 2 over `count` strips of a device strip list
+// Unit length of the strip sweeps, tuned per launch shape.  The best number of tiles per CTA depends on how long the
+// neighbouring CTAs stay in step (L2 residency of shared lines) against the per-CTA pipeline fill, and that moves with the
+// strip count and the mesh (measured: 15 tiles best at ne120/ne60/ne30 on one rank, 9 tiles 6-8 % faster at ne84, ne100 and
+// on the per-rank blocks of a 2- or 8-rank run).  So the first calls of a shape measure both with CUDA events (results do
+// not depend on the unit length): call 0 runs candidate 0 untimed (cold), calls 1 and 2 time candidates 0 and 1, later
+// calls use the faster one.
+struct StripTune {
+    int calls = 0, best = -1;
+    cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+};
+constexpr int TUNE_CAND[2] = {15, 9};
+std::map<uint64_t, StripTune> g_tune;
+
+// launch sweep 2 (or the DSS-only sweep) over `count` strips of a device strip list
 int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaStream_t st, int mode = MODE_SWEEP2, const CUtensorMap *out = nullptr)
 {
     if (count <= 0) return 0;
     SweepParams p = g.sp;
     if (out) p.map_out = *out;
-    const SweepGeometry geo = choose_geometry(g.kq, count, mode);
+    int hint = 0, timed = -1;
+    StripTune *t = nullptr;
+    if (sweep2_tiles_per_unit_forced() == 0 && count * ((g.kq + TILE_SLABS - 1) / TILE_SLABS) >= 148 * 64 && g_tune.size() < 4096) {
+        t = &g_tune[((uint64_t)mode << 56) ^ ((uint64_t)count << 20) ^ (uint64_t)g.kq];
+        if (t->best >= 0) hint = TUNE_CAND[t->best];
+        else if (t->calls <= 1) { hint = TUNE_CAND[0]; timed = t->calls == 1 ? 0 : -1; }
+        else if (t->calls == 2) { hint = TUNE_CAND[1]; timed = 1; }
+        else {
+            float ms[2] = {0.f, 0.f};
+            for (int c = 0; c < 2; ++c) {
+                CK(cudaEventSynchronize(t->ev[c][1]));
+                CK(cudaEventElapsedTime(&ms[c], t->ev[c][0], t->ev[c][1]));
+                CK(cudaEventDestroy(t->ev[c][0]));
+                CK(cudaEventDestroy(t->ev[c][1]));
+                t->ev[c][0] = t->ev[c][1] = nullptr;
+            }
+            t->best = ms[1] < ms[0] ? 1 : 0;
+            hint = TUNE_CAND[t->best];
+        }
+        t->calls++;
+    }
+    const SweepGeometry geo = choose_geometry(g.kq, count, mode, hint);
     p.tiles_per_unit = geo.tiles_per_unit;
     p.units = geo.units;
     p.strips = d_strips;
     p.strip_reg = d_reg;
     p.strip_count = (int)count;
+    if (timed >= 0) {
+        CK(cudaEventCreate(&t->ev[timed][0]));
+        CK(cudaEventCreate(&t->ev[timed][1]));
+        CK(cudaEventRecord(t->ev[timed][0], st));
+    }
     CK(launch_sweep(mode, p, st));
+    if (timed >= 0) CK(cudaEventRecord(t->ev[timed][1], st));
     g.launches++;
     return 0;
 }
@@ -660,6 +701,11 @@ int bwk_finalize(void)
     cudaDeviceSynchronize();
     if (g.comm && g_nccl.CommDestroy) g_nccl.CommDestroy(g.comm);
     free_dev(g.d_q); free_dev(g.d_tmp); free_dev(g.d_elem); free_dev(g.d_metric); free_dev(g.d_rsph);
+    for (auto &kv : g_tune)
+        for (int c = 0; c < 2; ++c)
+            for (int e = 0; e < 2; ++e)
+                if (kv.second.ev[c][e]) cudaEventDestroy(kv.second.ev[c][e]);
+    g_tune.clear();
     free_dev(g.d_w); free_dev(g.d_ratio);
     free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
     free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);

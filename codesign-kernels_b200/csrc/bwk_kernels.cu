@@ -964,10 +964,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __
 #define BWK_CFG_SWEEP1 3, 4, 3
 #define BWK_CFG_SWEEP2 3, 4, 3
 
-static int g_sweep2_tpu = 15;
-void set_sweep2_tiles_per_unit(int tpu) { g_sweep2_tpu = tpu < 1 ? 1 : tpu; }
+static int g_sweep2_tpu = 0; // 0: caller's hint / default; > 0: forced (BWK_SWEEP2_TPU)
+void set_sweep2_tiles_per_unit(int tpu) { g_sweep2_tpu = tpu < 0 ? 0 : tpu; }
+int sweep2_tiles_per_unit_forced() { return g_sweep2_tpu; }
 
-SweepGeometry choose_geometry(int kq, int64_t count, int mode)
+SweepGeometry choose_geometry(int kq, int64_t count, int mode, int tpu_hint)
 {
     const int warps = 4;
     const int ntiles = (kq + TILE_SLABS - 1) / TILE_SLABS;
@@ -975,7 +976,7 @@ SweepGeometry choose_geometry(int kq, int64_t count, int mode)
     if (mode == MODE_SWEEP2 || mode == MODE_DSS) {
         // count = strips; every warp walks all tiles of the unit.  Long units amortise the per-CTA
         // set-up (descriptor, metric, pipeline fill); p.tiles_per_unit_hint overrides for tuning.
-        int64_t tpu = g_sweep2_tpu;
+        int64_t tpu = g_sweep2_tpu > 0 ? g_sweep2_tpu : (tpu_hint > 0 ? tpu_hint : 15);
         const int64_t target_ctas = 148 * 8;
         if ((ntiles + tpu - 1) / tpu * count < target_ctas) tpu = std::max<int64_t>(1, (int64_t)ntiles * count / target_ctas);
         if (tpu > ntiles) tpu = ntiles;

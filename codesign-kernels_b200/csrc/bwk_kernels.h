@@ -51,8 +51,10 @@ struct SweepParams {
 struct SweepGeometry {
     int tiles_per_unit, units;
 };
-SweepGeometry choose_geometry(int kq, int64_t nelem, int mode);
-void set_sweep2_tiles_per_unit(int tpu); // tuning knob (BWK_SWEEP2_TPU)
+// tpu_hint: tiles per unit wanted for the strip sweeps (0 = default 15)
+SweepGeometry choose_geometry(int kq, int64_t nelem, int mode, int tpu_hint = 0);
+void set_sweep2_tiles_per_unit(int tpu); // tuning knob (BWK_SWEEP2_TPU): > 0 forces the unit length and disables the autotuner
+int sweep2_tiles_per_unit_forced();
 
 cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st);
 // MODE_SWEEP1_PRE needs nlev*128 more bytes of shared memory per CTA than the other element-local sweeps; false if that does not fit

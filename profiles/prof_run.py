@@ -15,7 +15,7 @@ ku = bwk.KernelUtils(n, nlev, qsize).allocate_data(host_arrays=False)
 ku.initialize_data_device()
 ku.set_topology_cubed_sphere(ne)
 ku.get_rspheremp()
-for rep in range(2):
+for rep in range(5):
     ku.initialize_data_device()
     ku.sync()
     ku.event_record(0); ku.run_device(1, n); ku.event_record(1)

@@ -11,7 +11,7 @@ ku = bwk.KernelUtils(count, nlev, qsize).allocate_data(host_arrays=False)
 ku.initialize_data_device(n, first)
 ku.set_topology_cubed_sphere(ne, first)
 ku.get_rspheremp()
-for rep in range(2):
+for rep in range(5):
     ku.initialize_data_device(n, first)
     ku.run_biharmonic_device()
     ku.sync()
