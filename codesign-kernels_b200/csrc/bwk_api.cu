@@ -235,7 +235,7 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
                 CK(cudaEventDestroy(t->ev[c][1]));
                 t->ev[c][0] = t->ev[c][1] = nullptr;
             }
-            t->best = ms[1] < ms[0] ? 1 : 0;
+            t->best = ms[1] < 0.975f * ms[0] ? 1 : 0; // single samples: the default keeps the shape unless the alternative wins clearly
             hint = TUNE_CAND[t->best];
         }
         t->calls++;
