@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
             }
         }
     }
-    if (lane == 0) bulk_wait<0>();
+    if (lane == 0) bulk_wait_read<0>(); // shared memory may be released once the stores have READ it; the writes complete on their own (kernel end flushes them)
 }
 
 // ------------------------------------------------------------------------------------------
@@ -444,6 +444,35 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     EndTma *endtma = reinterpret_cast<EndTma *>(metric_all + STRIP_MAX * METRIC_DOUBLES);
 
     const bool w_end = warp == 0, e_end = warp == cnt - 1;
+    const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
+    const int t0 = blockIdx.y * p.tiles_per_unit;
+    const int my_n = min(t0 + p.tiles_per_unit, ntiles) - t0;
+    const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
+    const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
+        mbar_init(smem_u32(&nbars[warp * 2]), 1); // lane 0's expect_tx for the two TMA row boxes
+        mbar_init(smem_u32(&nbars[warp * 2 + 1]), 1);
+        mbar_init(smem_u32(&ebars[warp]), 1);
+        const uint32_t nmates = (w_end ? 0u : 1u) + (e_end ? 0u : 1u);
+        mbar_init(smem_u32(&cbars[warp * 2]), active && nmates ? 32u * nmates : 1u); // every lane of every mate arrives
+        mbar_init(smem_u32(&cbars[warp * 2 + 1]), active && nmates ? 32u * nmates : 1u);
+        fence_barrier_init();
+        fence_proxy_async();
+        // this warp's first tiles need nothing but its own barriers: get them on their way before the descriptor decode
+        if (active) {
+            const int pre = my_n < STAGES ? my_n : STAGES;
+            for (int n = 0; n < pre; ++n) {
+                mbar_expect_tx(bar0 + n * 8, (uint32_t)TILE_BYTES);
+                tma_load_3d(stage0 + n * SB, &p.map_tmp, 0, (t0 + n) * TILE_SLABS, le, bar0 + n * 8);
+            }
+        }
+    }
+    if (active) { // the folded metric (512 B) arrives asynchronously, behind the first tile loads
+        cp_async16(smem_u32(metric_s) + lane * 16, p.metric + (size_t)le * METRIC_DOUBLES + lane * 2, 16u);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
     if (threadIdx.x < 6) {
         const int k = threadIdx.x, side = k / 3, which = k % 3; // which: 0 column, 1 S-side diagonal, 2 N-side diagonal
         EndTma e{ET_NONE, 0, 0, 0, 0, 0, 0};
@@ -465,31 +494,9 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         }
         endtma[k] = e;
     }
-    if (lane == 0) {
-#pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
-        mbar_init(smem_u32(&nbars[warp * 2]), 1); // lane 0's expect_tx for the two TMA row boxes
-        mbar_init(smem_u32(&nbars[warp * 2 + 1]), 1);
-        mbar_init(smem_u32(&ebars[warp]), 1);
-        const uint32_t nmates = (w_end ? 0u : 1u) + (e_end ? 0u : 1u);
-        mbar_init(smem_u32(&cbars[warp * 2]), active && nmates ? 32u * nmates : 1u); // every lane of every mate arrives
-        mbar_init(smem_u32(&cbars[warp * 2 + 1]), active && nmates ? 32u * nmates : 1u);
-        fence_barrier_init();
-        fence_proxy_async();
-    }
-    if (active) { // the folded metric (512 B) arrives asynchronously, behind the first tile loads
-        cp_async16(smem_u32(metric_s) + lane * 16, p.metric + (size_t)le * METRIC_DOUBLES + lane * 2, 16u);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    }
     __syncthreads(); // the only CTA-wide barrier: mbarriers initialised, endtma written
     if (!active) return;
 
-    const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
-    const int t0 = blockIdx.y * p.tiles_per_unit;
-    const int my_n = min(t0 + p.tiles_per_unit, ntiles) - t0;
-
-    const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
-    const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
     const uint32_t nbar0 = smem_u32(&nbars[warp * 2]);
     const uint32_t cbar0 = smem_u32(&cbars[warp * 2]);
     const int swz = (lane >> 2) & 1; // SWIZZLE_32B: 16-byte chunk c of 32-byte row r sits at chunk c ^ ((r >> 2) & 1)
@@ -574,9 +581,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         d1 = *reinterpret_cast<const double *>(eb + 2560 + lane * 16 + endtma[3 * side + 2].hi * 8);
     };
 
-    if (lane == 0) {
-        const int pre = my_n < STAGES ? my_n : STAGES;
-        for (int n = 0; n < pre; ++n) issue_tile(n, n);
+    if (lane == 0) { // (the first tile loads were issued before the decode)
         if (my_n > 0) issue_nbr(0);
         if (my_n > 1) issue_nbr(1);
         if (is_end && my_n > 0) issue_end(0);
@@ -701,7 +706,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
             if (n + 2 < my_n) issue_nbr(n + 2);
         }
     }
-    if (lane == 0) bulk_wait<0>();
+    if (lane == 0) bulk_wait_read<0>(); // shared memory may be released once the stores have READ it; the writes complete on their own (kernel end flushes them)
 }
 
 // ---- generic path: any connectivity the plan accepts (face edges, cube corners, halo rows, reversed edges)
@@ -938,7 +943,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
             }
         }
     }
-    if (lane == 0) bulk_wait<0>();
+    if (lane == 0) bulk_wait_read<0>(); // shared memory may be released once the stores have READ it; the writes complete on their own (kernel end flushes them)
 }
 
 template <int STAGES, int WARPS, int MINB, bool LAP>
