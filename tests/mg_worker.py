@@ -31,7 +31,34 @@ def main():
 
     n = 6 * ne * ne
     first, count = bwk.partition(n, rank, world)
-    if mode == "gpu":
+    if mode == "big":
+        # BASELINE config 5 (ne512np4 L128 q10 on 8 GPUs, 32 GB of qtens per rank): device-generated data, full biharmonic
+        # with the NCCL halo, twice (determinism); every rank saves a few of its elements for the patch oracle of the test
+        import torch
+
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        ku = bwk.KernelUtils(count, nlev, qsize).allocate_data(host_arrays=False)
+        idb = [bwk.KernelUtils.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(idb, src=0)
+        bwk.KernelUtils.comm_init(rank, world, idb[0])
+        ku.initialize_data_device(n, first)
+        ku.run_device(1, count)  # reference-pinned single Laplacian
+        ku.sync()
+        picks = [0, ne + 3, count // 2 + 7, count - 1]  # first row of the block (S neighbours on another rank), interior, last element
+        np.save(os.path.join(outdir, f"big_lap_{rank}.npy"), np.stack([ku.download_elements(e, 1) for e in picks], axis=0))
+        ku.set_topology_cubed_sphere(ne, first)
+        sums = []
+        for rep in range(2):
+            ku.initialize_data_device(n, first)
+            ku.run_biharmonic_device()
+            ku.sync()
+            sums.append(ku.checksum())
+        assert sums[0] == sums[1], sums
+        np.save(os.path.join(outdir, f"big_bih_{rank}.npy"), np.stack([ku.download_elements(e, 1) for e in picks], axis=0))
+        np.save(os.path.join(outdir, f"big_picks_{rank}.npy"), np.array([first + e for e in picks], dtype=np.int64))
+        dist.barrier()
+        ku.finalize()
+    elif mode == "gpu":
         import torch
 
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))

@@ -64,3 +64,58 @@ def test_multi_gpu_matches_single_gpu_bitwise(bwk, oracle, tmp_path, ne, nlev, q
     dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
     ref = dss.biharmonic_full(elem, dss.rspheremp(elem), q, dvv)
     assert oracle.max_rel(np.asfortranarray(multi), ref) <= 1e-12
+
+
+def _patch_oracle_full(oracle, ne, nlev, qsize, gd, e):
+    """Full biharmonic of ONE element e of a big cubed sphere from the oracle's pieces: the CPU-order Laplacian
+    (F90:109-200) of e and of every element sharing a node with it, the DSS sum over coincident points in ascending
+    global point order, rspheremp from the same sums of spheremp, then the Laplacian of e again."""
+    n = 6 * ne * ne
+    keys = gd[e]
+    nbrs = np.unique(np.nonzero(np.isin(gd, keys))[0])
+    lap, sph = {}, {}
+    for m in nbrs:
+        dvv, elem, q = oracle.initialize_subset(n, nlev, qsize, int(m), 1)
+        sph[int(m)] = elem[0, 64:80].copy()
+        lap[int(m)] = oracle.biharmonic_wk_scalar_cpu(elem, q, dvv).reshape(16, nlev * qsize, order="F")
+        if m == e:
+            dvv_e, elem_e = dvv, elem
+    out = np.empty((16, nlev * qsize))
+    for pt in range(16):
+        members = [(int(m), int(t)) for m in nbrs for t in np.nonzero(gd[m] == keys[pt])[0]]
+        members.sort()
+        s = None
+        w = None
+        for m, t in members:
+            s = lap[m][t].copy() if s is None else s + lap[m][t]
+            w = sph[m][t] if w is None else w + sph[m][t]
+        out[pt] = s  # the oracle scales by rspheremp inside its second sweep (element_sweep2)
+        out[pt] *= 1.0 / w
+    q2 = np.asfortranarray(out.reshape((4, 4, nlev, qsize, 1), order="F"))
+    return oracle.biharmonic_wk_scalar_cpu(elem_e, q2, dvv_e)
+
+
+@pytest.mark.gpu
+def test_ne512_l128_q10_on_8_gpus(bwk, oracle, tmp_path):
+    """BASELINE config 5: ne512np4 nlev=128 qsize=10 (1,572,864 elements, 257.7 GB of qtens) on 8 GPUs.  The single
+    Laplacian and the full biharmonic of elements at block edges (halo path) and in the interior are compared with
+    the oracle evaluated on the element's own neighbourhood; two runs give bit-identical checksums."""
+    import torch
+
+    if torch.cuda.device_count() < 8:
+        pytest.skip("needs 8 GPUs")
+    ne, nlev, qsize, world = 512, 128, 10, 8
+    n = 6 * ne * ne
+    _launch(world, ["big", ne, nlev, qsize, tmp_path], 29541)
+    gd = oracle.cubed_sphere_gdof(ne).reshape(n, 16)
+    for r in (0, 3, 7):
+        picks = np.load(tmp_path / f"big_picks_{r}.npy")
+        lap = np.load(tmp_path / f"big_lap_{r}.npy")
+        bih = np.load(tmp_path / f"big_bih_{r}.npy")
+        for k, e in enumerate(picks):
+            dvv, elem, q = oracle.initialize_subset(n, nlev, qsize, int(e), 1)
+            ref = oracle.biharmonic_wk_scalar_cpu(elem, q, dvv)
+            assert oracle.max_rel(np.asfortranarray(lap[k]), ref) <= 1e-12
+            if k in (0, 2):
+                ref2 = _patch_oracle_full(oracle, ne, nlev, qsize, gd, int(e))
+                assert oracle.max_rel(np.asfortranarray(bih[k]), ref2) <= 1e-12, (r, int(e))
