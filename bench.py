@@ -165,7 +165,8 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * tot / len(times), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic (reference LCG, F90:77-91)",
-        "config": {"workload": f"ne{args.ne}np4 L{args.nlev} q{args.qsize} full biharmonic", "sample": res["sample"]},
+        "config": {"workload": f"ne{args.ne}np4 L{args.nlev} q{args.qsize}, {6 * args.ne * args.ne} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
+                   "sample": res["sample"]},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": res["cores"], "kind": "port", "sample": res["sample"]},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
