@@ -97,7 +97,8 @@ struct Ctx {
     cudaStream_t s_main = nullptr, s_comm = nullptr, s_h2d = nullptr, s_d2h = nullptr;
     double *d_q = nullptr, *d_tmp = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
     double *d_w = nullptr, *d_ratio = nullptr; // advance_hypervis_scalar: biharmonic work buffer, dpdiss/dp [nelem][nlev][16]
-    CUtensorMap map_w;
+    CUtensorMap map_w, map_w_rows, map_w_pt; // the work buffer seen as slabs / edge rows / i-pairs (strip sweeps reading it)
+    bool src_is_w = false;                  // strip sweeps and the halo pack read the work buffer instead of tmp
     double *d_save = nullptr, *d_table = nullptr, *d_partials = nullptr, *d_halo = nullptr, *d_send = nullptr, *d_dummy = nullptr;
     double *h_partials = nullptr;
     ElemDss *d_dss = nullptr;
@@ -219,6 +220,12 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
     if (count <= 0) return 0;
     SweepParams p = g.sp;
     if (out) p.map_out = *out;
+    if (g.src_is_w) {
+        p.tmp = g.d_w;
+        p.map_tmp = g.map_w;
+        p.map_rows = g.map_w_rows;
+        p.map_pt = g.map_w_pt;
+    }
     int hint = 0, timed = -1;
     StripTune *t = nullptr;
     if (sweep2_tiles_per_unit_forced() == 0 && count * ((g.kq + TILE_SLABS - 1) / TILE_SLABS) >= 148 * 64 && g_tune.size() < 4096) {
@@ -449,7 +456,7 @@ int exchange_halo()
     if (P.nranks == 1) return 0;
     if (!g.comm) return fail("topology spans %d ranks but bwk_comm_init was not called", P.nranks);
     if (nsend > 0) {
-        CK(launch_edge_pack(g.d_tmp, g.d_send_elem, g.d_send_row, nsend, g.kq, g.d_send, g.s_comm));
+        CK(launch_edge_pack(g.src_is_w ? g.d_w : g.d_tmp, g.d_send_elem, g.d_send_row, nsend, g.kq, g.d_send, g.s_comm));
         g.launches += (nsend + 65534) / 65535;
     }
     const size_t row_doubles = (size_t)4 * g.kq;
@@ -511,12 +518,12 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
     return 0;
 }
 
-int biharmonic_device(int produce_mode = MODE_SWEEP1, const CUtensorMap *out = nullptr)
+int biharmonic_device(int produce_mode = MODE_SWEEP1, const CUtensorMap *out = nullptr, int consume_mode = MODE_SWEEP2)
 {
     if (!g.have_metric) return fail("no element metric on the device");
     if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
     if (compute_rspheremp()) return 1;
-    return dss_pass([&](int first, int count, const int32_t *list) { return sweep(produce_mode, first, count, list, g.s_main); }, MODE_SWEEP2, out);
+    return dss_pass([&](int first, int count, const int32_t *list) { return sweep(produce_mode, first, count, list, g.s_main); }, consume_mode, out);
 }
 
 // advance_hypervis_scalar on the device-resident Qdp (d_q); see bwk_b200.h
@@ -528,20 +535,42 @@ int hypervis_device(double dt2, double nu_q, int subcycles, int limiter)
     if (!g.d_w) {
         CK(cudaMalloc(&g.d_w, sizeof(double) * g.q_doubles));
         if (make_slab_map(&g.map_w, g.d_w, g.kq, g.nelem)) return 1;
+        const uint64_t dims[3] = {16, (uint64_t)g.kq, (uint64_t)g.nelem}, str[2] = {128, (uint64_t)g.kq * 128};
+        const uint32_t box[3] = {4, TILE_SLABS, 1};
+        if (make_map(&g.map_w_rows, g.d_w, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+        const uint64_t cdims[4] = {4, 4, (uint64_t)g.kq, (uint64_t)g.nelem}, cstr[3] = {32, 128, (uint64_t)g.kq * 128};
+        const uint32_t pbox[4] = {2, 1, TILE_SLABS, 1};
+        if (make_map(&g.map_w_pt, g.d_w, 4, cdims, cstr, pbox, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
     }
     g.sp.prescale = g.d_ratio;
     g.sp.nlev = g.nlev;
+    g.sp.elem = g.d_elem;
     const double coef = (dt2 / subcycles) * nu_q;
+    g.sp.hv_coef = coef;
+    g.sp.hv_limiter = limiter;
+    static const bool unfused = std::getenv("BWK_HV_UNFUSED") != nullptr; // A/B knob: the 4-launch form with a separate update kernel
     for (int ic = 0; ic < subcycles; ++ic) {
-        // Qtens = biharmonic(dpdiss * Qdp / dp) -> work buffer (Qdp itself is still needed)
-        if (biharmonic_device(MODE_SWEEP1_PRE, &g.map_w)) return 1;
-        // Qdp = DSS(limiter(Qdp * spheremp - dt nu_q Qtens)) * rspheremp
-        auto post = [&](int first, int count, const int32_t *list) {
-            CK(launch_hypervis_post(g.d_q, g.d_w, g.d_tmp, g.d_elem, g.d_rsph, list, first, count, g.kq, coef, limiter, g.s_main));
-            g.launches++;
-            return 0;
-        };
-        if (dss_pass(post, MODE_DSS, &g.sp.map_q)) return 1;
+        if (unfused) {
+            // Qtens = biharmonic(dpdiss * Qdp / dp) -> work buffer (Qdp itself is still needed)
+            if (biharmonic_device(MODE_SWEEP1_PRE, &g.map_w)) return 1;
+            // Qdp = DSS(limiter(Qdp * spheremp - dt nu_q Qtens)) * rspheremp
+            auto post = [&](int first, int count, const int32_t *list) {
+                CK(launch_hypervis_post(g.d_q, g.d_w, g.d_tmp, g.d_elem, g.d_rsph, list, first, count, g.kq, coef, limiter, g.s_main));
+                g.launches++;
+                return 0;
+            };
+            if (dss_pass(post, MODE_DSS, &g.sp.map_q)) return 1;
+            continue;
+        }
+        // pass 1: sweep 1 on dpdiss*Qdp/dp, then the strip sweep with the update fused in (it TMA-loads the slab of Qdp into
+        // the tile's own stage while the second Laplacian runs): work buffer = limiter(Qdp*spheremp - dt nu_q Qtens)*rspheremp
+        if (biharmonic_device(MODE_SWEEP1_PRE, &g.map_w, MODE_SWEEP2_POST)) return 1;
+        // pass 2: DSS of the work buffer -> Qdp.  Nothing to produce: the halo exchange starts as soon as pass 1 is done and
+        // overlaps the independent strips.
+        g.src_is_w = true;
+        const int rc = dss_pass([](int, int, const int32_t *) { return 0; }, MODE_DSS, &g.sp.map_q);
+        g.src_is_w = false;
+        if (rc) return 1;
     }
     return 0;
 }

@@ -339,6 +339,44 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep_kernel(const __grid_co
 // CTAs apart -- so they are served by the 126 MB L2 and DRAM sees each slab once.
 // Corners are summed in ascending global point order (bit-identical for any rank count).
 // ------------------------------------------------------------------------------------------
+// what the strip kernel does after assembling the DSS sums
+enum : int { SK_DSS = 0,   // nothing: edgeVunpack only (values were scaled by rspheremp by their producer)
+             SK_LAP = 1,   // second laplace_sphere_wk
+             SK_POST = 2 };// second Laplacian, then advance_hypervis_scalar's update fused in: the slab of Qdp is TMA-loaded into
+                           // the tile's own stage while the Laplacian runs, out = limiter2d_zero(Qdp*spheremp - coef*lap)*rspheremp
+
+// Qdp*spheremp - coef*Qtens with the CPU statement's roundings, limiter2d_zero in the CPU order (a thread owns the level)
+__device__ __forceinline__ void hypervis_update_slab(double (&v)[16], const double (&a)[16], const double *mp, const double *rs, double coef, int limiter)
+{
+    double x[16];
+#pragma unroll
+    for (int t = 0; t < 16; ++t) x[t] = __dsub_rn(__dmul_rn(a[t], mp[t]), __dmul_rn(coef, v[t]));
+    if (limiter) {
+        double mass = 0.0;
+#pragma unroll
+        for (int t = 0; t < 16; ++t) mass = __dadd_rn(mass, x[t]);
+        const bool neg = mass < 0.0;
+        double added = 0.0;
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+            if (neg) x[t] = -x[t];
+            if (x[t] < 0.0) x[t] = 0.0;
+            else added = __dadd_rn(added, x[t]);
+        }
+        if (added > 0.0) {
+            const double scale = fabs(mass) / added;
+#pragma unroll
+            for (int t = 0; t < 16; ++t) x[t] = __dmul_rn(x[t], scale);
+        }
+        if (neg) {
+#pragma unroll
+            for (int t = 0; t < 16; ++t) x[t] = -x[t];
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < 16; ++t) v[t] = x[t] * rs[t];
+}
+
 struct WarpDss {                  // per warp in shared memory, built once per CTA (112 bytes)
     const unsigned char *edge_ptr[4]; // S,N,W,E: address of value 0 for slab 0
     const unsigned char *diag_ptr[4]; // corners (1,1),(4,1),(1,4),(4,4): address for slab 0, nullptr = none
@@ -376,7 +414,7 @@ static_assert(ROWBUF_BYTES >= STRIP_MAX * (int)sizeof(WarpDss) && STRIP_EXTRA_BY
 template <int STAGES, int WARPS>
 constexpr int strip_smem_bytes()
 {
-    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 5) * 8 + WARPS * METRIC_DOUBLES * 8 + 6 * 16 + 64;
+    return 1024 + WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + WARPS * (STAGES + 6) * 8 + WARPS * METRIC_DOUBLES * 8 + 6 * 16 + WARPS * 32 * 8 + 64;
 }
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t src_bytes)
@@ -426,7 +464,7 @@ __device__ __forceinline__ uint32_t end_box_bytes(int kind)
     return kind == ET_COL ? 2048u : (kind == ET_ROW || kind == ET_HALOROW) ? 1024u : kind == ET_NONE ? 0u : 512u;
 }
 
-template <int STAGES, int WARPS, bool LAP>
+template <int STAGES, int WARPS, int KIND>
 __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, unsigned char *extra,
                                                int first, int cnt, const StripReg &rg)
 {
@@ -455,6 +493,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         mbar_init(smem_u32(&nbars[warp * 2]), 1); // lane 0's expect_tx for the two TMA row boxes
         mbar_init(smem_u32(&nbars[warp * 2 + 1]), 1);
         mbar_init(smem_u32(&ebars[warp]), 1);
+        mbar_init(smem_u32(&ebars[WARPS + warp]), 1); // qdp_full (SK_POST)
         const uint32_t nmates = (w_end ? 0u : 1u) + (e_end ? 0u : 1u);
         mbar_init(smem_u32(&cbars[warp * 2]), active && nmates ? 32u * nmates : 1u); // every lane of every mate arrives
         mbar_init(smem_u32(&cbars[warp * 2 + 1]), active && nmates ? 32u * nmates : 1u);
@@ -469,6 +508,9 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
             }
         }
     }
+    double *hv_s = reinterpret_cast<double *>(endtma + 6) + warp * 32; // SK_POST: this element's spheremp, rspheremp
+    const uint32_t qbar = smem_u32(&ebars[WARPS + warp]);
+    if (KIND == SK_POST && active) hv_s[lane] = lane < 16 ? p.elem[(size_t)le * ELEM_DOUBLES + 64 + lane] : p.rsph[(size_t)le * 16 + lane - 16];
     if (active) { // the folded metric (512 B) arrives asynchronously, behind the first tile loads
         cp_async16(smem_u32(metric_s) + lane * 16, p.metric + (size_t)le * METRIC_DOUBLES + lane * 2, 16u);
         asm volatile("cp.async.commit_group;" ::: "memory");
@@ -686,10 +728,33 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
             if (lane == 0 && n + 1 < my_n) issue_end(n + 1);
         }
 
-        if (LAP) laplace_slab(v, M); // MODE_DSS stops at the assembled (and already rspheremp-scaled) values
+        if (KIND == SK_POST) {
+            // This warp holds the tile in registers and, once cons fires, the mates have read its columns: the stage is free
+            // for the slab of Qdp, which travels while the Laplacian runs.
+            if (cnt > 1) mbar_wait(cbar0 + q * 8, qparity);
+            asm volatile("" ::"d"(v[5]), "d"(v[6]), "d"(v[9]), "d"(v[10]) : "memory");
+            __syncwarp();
+            if (lane == 0) {
+                mbar_expect_tx(qbar, (uint32_t)TILE_BYTES);
+                tma_load_3d(stage0 + s * SB, &p.map_q, 0, kq0, le, qbar);
+            }
+        }
+        if (KIND != SK_DSS) laplace_slab(v, M); // MODE_DSS stops at the assembled (and already rspheremp-scaled) values
 
-        // both mates must have read this tile's columns and this rowbuf set before they are overwritten
-        if (cnt > 1) mbar_wait(cbar0 + q * 8, qparity);
+        if (KIND == SK_POST) {
+            mbar_wait(qbar, (uint32_t)(n & 1));
+            double a[16];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+                a[2 * c] = t.x;
+                a[2 * c + 1] = t.y;
+            }
+            hypervis_update_slab(v, a, hv_s, hv_s + 16, p.hv_coef, p.hv_limiter);
+        } else if (cnt > 1) {
+            // both mates must have read this tile's columns and this rowbuf set before they are overwritten
+            mbar_wait(cbar0 + q * 8, qparity);
+        }
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
         fence_proxy_async();
@@ -710,7 +775,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
 }
 
 // ---- generic path: any connectivity the plan accepts (face edges, cube corners, halo rows, reversed edges)
-template <int STAGES, int WARPS, bool LAP>
+template <int STAGES, int WARPS, int KIND>
 __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned char *stages, uint64_t *bars, double *metric_all, unsigned char *extra,
                                                int first, int cnt)
 {
@@ -774,9 +839,14 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
         const uint32_t nmates = (has_left ? 1u : 0u) + (has_right ? 1u : 0u);
         mbar_init(smem_u32(&cbars[warp * 2]), nmates ? 32u * nmates : 1u);
         mbar_init(smem_u32(&cbars[warp * 2 + 1]), nmates ? 32u * nmates : 1u);
+        mbar_init(smem_u32(&cbars[WARPS * 2 + WARPS + warp]), 1); // qdp_full (SK_POST), same slot as in the regular path
         fence_barrier_init();
         fence_proxy_async();
     }
+    // SK_POST: this element's spheremp, rspheremp (behind the metric and the six strip-end records of the regular path)
+    double *hv_s = reinterpret_cast<double *>(reinterpret_cast<unsigned char *>(metric_all + STRIP_MAX * METRIC_DOUBLES) + 6 * 16) + warp * 32;
+    const uint32_t qbar = smem_u32(&cbars[WARPS * 2 + WARPS + warp]);
+    if (KIND == SK_POST && active) hv_s[lane] = lane < 16 ? p.elem[(size_t)le * ELEM_DOUBLES + 64 + lane] : p.rsph[(size_t)le * 16 + lane - 16];
     __syncthreads(); // the only CTA-wide barrier
     if (!active) return;
     if ((has_left && wd.edge_mode[EDGE_W] != EM_MATE_LEFT) || (has_right && wd.edge_mode[EDGE_E] != EM_MATE_RIGHT)) __trap(); // plan/kernel disagree
@@ -923,10 +993,31 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
         if (has_left) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 - 16 + q * 8), "d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]) : "memory");
         if (has_right) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 + 16 + q * 8), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
 
-        if (LAP) laplace_slab(v, M); // (the rspheremp scaling was applied by sweep 1)
+        if (KIND == SK_POST) { // as in the regular path: the stage takes the slab of Qdp while the Laplacian runs
+            if (has_left || has_right) mbar_wait(cbar0 + q * 8, qparity);
+            asm volatile("" ::"d"(v[5]), "d"(v[6]), "d"(v[9]), "d"(v[10]) : "memory");
+            __syncwarp();
+            if (lane == 0) {
+                mbar_expect_tx(qbar, (uint32_t)TILE_BYTES);
+                tma_load_3d(stage0 + s * SB, &p.map_q, 0, kq0, le, qbar);
+            }
+        }
+        if (KIND != SK_DSS) laplace_slab(v, M); // (the rspheremp scaling was applied by sweep 1)
 
-        // both mates must have read this tile's columns before it is overwritten in place
-        if (has_left || has_right) mbar_wait(cbar0 + q * 8, qparity);
+        if (KIND == SK_POST) {
+            mbar_wait(qbar, (uint32_t)(n & 1));
+            double a[16];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+                a[2 * c] = t.x;
+                a[2 * c + 1] = t.y;
+            }
+            hypervis_update_slab(v, a, hv_s, hv_s + 16, p.hv_coef, p.hv_limiter);
+        } else if (has_left || has_right) {
+            // both mates must have read this tile's columns before it is overwritten in place
+            mbar_wait(cbar0 + q * 8, qparity);
+        }
 #pragma unroll
         for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
         fence_proxy_async();
@@ -946,7 +1037,7 @@ __device__ __forceinline__ void sweep2_generic(const SweepParams &p, unsigned ch
     if (lane == 0) bulk_wait_read<0>(); // shared memory may be released once the stores have READ it; the writes complete on their own (kernel end flushes them)
 }
 
-template <int STAGES, int WARPS, int MINB, bool LAP>
+template <int STAGES, int WARPS, int MINB, int KIND>
 __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __grid_constant__ SweepParams p)
 {
     static_assert(WARPS == STRIP_MAX, "one warp per strip element");
@@ -955,13 +1046,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __
     unsigned char *stages = smem;                                  // tile ring, 1024-byte aligned (SWIZZLE_128B)
     unsigned char *extra = smem + WARPS * STAGES * TILE_BYTES;     // staging buffers (1024-aligned, SWIZZLE_32B rows) or WarpDss records
     uint64_t *bars = reinterpret_cast<uint64_t *>(extra + STRIP_EXTRA_BYTES);
-    double *metric_all = reinterpret_cast<double *>(bars + WARPS * (STAGES + 5)); // after tile_full, nbr_full, cons, end_full
+    double *metric_all = reinterpret_cast<double *>(bars + WARPS * (STAGES + 6)); // after tile_full, nbr_full, cons, end_full, qdp_full
 
     const int32_t strip = p.strips[blockIdx.x];
     const int first = strip >> 3, cnt = (strip & 7) + 1;
     const StripReg &rg = p.strip_reg[blockIdx.x];
-    if (rg.regular) sweep2_regular<STAGES, WARPS, LAP>(p, stages, bars, metric_all, extra, first, cnt, rg);
-    else sweep2_generic<STAGES, WARPS, LAP>(p, stages, bars, metric_all, extra, first, cnt);
+    if (rg.regular) sweep2_regular<STAGES, WARPS, KIND>(p, stages, bars, metric_all, extra, first, cnt, rg);
+    else sweep2_generic<STAGES, WARPS, KIND>(p, stages, bars, metric_all, extra, first, cnt);
 }
 
 // kernel configurations: (STAGES, WARPS, MINB)
@@ -978,7 +1069,7 @@ SweepGeometry choose_geometry(int kq, int64_t count, int mode, int tpu_hint)
     const int warps = 4;
     const int ntiles = (kq + TILE_SLABS - 1) / TILE_SLABS;
     SweepGeometry g;
-    if (mode == MODE_SWEEP2 || mode == MODE_DSS) {
+    if (mode == MODE_SWEEP2 || mode == MODE_DSS || mode == MODE_SWEEP2_POST) {
         // count = strips; every warp walks all tiles of the unit.  Long units amortise the per-CTA
         // set-up (descriptor, metric, pipeline fill); p.tiles_per_unit_hint overrides for tuning.
         int64_t tpu = g_sweep2_tpu > 0 ? g_sweep2_tpu : (tpu_hint > 0 ? tpu_hint : 15);
@@ -1017,20 +1108,20 @@ static cudaError_t launch_sweep_t(const SweepParams &p, cudaStream_t st)
     return cudaGetLastError();
 }
 
-template <int STAGES, int WARPS, int MINB, bool LAP>
+template <int STAGES, int WARPS, int MINB, int KIND>
 static cudaError_t launch_strip_t(const SweepParams &p, cudaStream_t st)
 {
     static_assert(WARPS == STRIP_MAX, "one warp per strip element");
     constexpr int smem = strip_smem_bytes<STAGES, WARPS>();
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(sweep2_strip_kernel<STAGES, WARPS, MINB, LAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(sweep2_strip_kernel<STAGES, WARPS, MINB, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
     if (p.strip_count <= 0 || p.units <= 0) return cudaSuccess;
     dim3 grid((unsigned)p.strip_count, (unsigned)p.units);
-    sweep2_strip_kernel<STAGES, WARPS, MINB, LAP><<<grid, WARPS * 32, smem, st>>>(p);
+    sweep2_strip_kernel<STAGES, WARPS, MINB, KIND><<<grid, WARPS * 32, smem, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -1042,8 +1133,9 @@ cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st)
     case MODE_LAPLACE: return launch_sweep_t<MODE_LAPLACE, BWK_CFG_LAPLACE>(p, st);
     case MODE_SWEEP1: return launch_sweep_t<MODE_SWEEP1, BWK_CFG_SWEEP1>(p, st);
     case MODE_SWEEP1_PRE: return launch_sweep_t<MODE_SWEEP1_PRE, BWK_CFG_SWEEP1>(p, st);
-    case MODE_SWEEP2: return launch_strip_t<BWK_CFG_SWEEP2, true>(p, st);
-    case MODE_DSS: return launch_strip_t<BWK_CFG_SWEEP2, false>(p, st);
+    case MODE_SWEEP2: return launch_strip_t<BWK_CFG_SWEEP2, SK_LAP>(p, st);
+    case MODE_DSS: return launch_strip_t<BWK_CFG_SWEEP2, SK_DSS>(p, st);
+    case MODE_SWEEP2_POST: return launch_strip_t<BWK_CFG_SWEEP2, SK_POST>(p, st);
     default: return cudaErrorInvalidValue;
     }
 }

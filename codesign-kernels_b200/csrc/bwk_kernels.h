@@ -17,7 +17,8 @@ enum SweepMode : int {
     MODE_SWEEP1 = 1,  // qtens -> tmp                          (first laplace; neighbours read their edges straight from tmp)
     MODE_SWEEP2 = 2,  // tmp + neighbours' edge values -> *rspheremp -> laplace -> qtens  (edgeVunpack + second laplace)
     MODE_SWEEP1_PRE = 3, // as MODE_SWEEP1 on qtens * prescale(:,:,k,ie)  (advance_hypervis_scalar: Qtens = dpdiss*Qdp/dp)
-    MODE_DSS = 4      // as MODE_SWEEP2 without the Laplacian: tmp + neighbours' edge values -> out  (edgeVunpack [+ rspheremp])
+    MODE_DSS = 4,     // as MODE_SWEEP2 without the Laplacian: tmp + neighbours' edge values -> out  (edgeVunpack [+ rspheremp])
+    MODE_SWEEP2_POST = 5 // MODE_SWEEP2 with advance_hypervis_scalar's update fused in: out = limiter(Qdp*spheremp - coef*lap)*rspheremp
 };
 
 // Everything a sweep launch needs.  Tensor maps are passed by value (__grid_constant__).
@@ -31,6 +32,9 @@ struct SweepParams {
     CUtensorMap map_out;    // where sweep 2 / the DSS-only sweep store their result (qtens, or the hyperviscosity work buffer)
     const double *prescale; // MODE_SWEEP1_PRE: [nelem][nlev][16] factors applied to the input slab of level k
     int nlev;               // MODE_SWEEP1_PRE: slab kq belongs to level kq % nlev
+    const double *elem;     // MODE_SWEEP2_POST: element records [nelem][144] (spheremp at +64); Qdp is read through map_q
+    double hv_coef;         // MODE_SWEEP2_POST: dt * nu_q
+    int hv_limiter;         // MODE_SWEEP2_POST: apply limiter2d_zero
     const double *metric;   // [nelem][64] folded metric
     const double *rsph;     // [nelem][16]
     const ElemDss *dss;     // [nelem]
