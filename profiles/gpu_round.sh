@@ -16,3 +16,8 @@ ncu --set full --clock-control none --import-source on -k regex:sweep -s 3 -c 3 
   python profiles/prof_run.py 30 72 40 > gpurun_out/${tag}_ncu_full.log 2>&1
 tail -2 gpurun_out/${tag}_ncu_full.log
 ls -la gpurun_out
+# the caller (advance_hypervis_scalar): timing at ne120, ncu --set full of its three launches at ne30
+python profiles/prof_hv.py > gpurun_out/${tag}_prof_hv_ne120.log 2>&1; tail -3 gpurun_out/${tag}_prof_hv_ne120.log
+ncu --set full --clock-control none --import-source on -k regex:sweep -s 6 -c 3 -o gpurun_out/${tag}_full_ne30_hv \
+  python profiles/prof_hv.py 30 72 40 > gpurun_out/${tag}_ncu_full_hv.log 2>&1
+tail -2 gpurun_out/${tag}_ncu_full_hv.log
