@@ -489,8 +489,10 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
     if (lane == 0) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), 1);
-        mbar_init(smem_u32(&nbars[warp * 2]), 1); // lane 0's expect_tx for the two TMA row boxes
+        // one barrier per tile in flight collects everything that tile needs: the tile itself, the S/N rows and, for an end
+        // warp, the strip-end boxes -- three separate expect_tx arrivals (issued 3, 2 and 1 tiles ahead), one wait
+        for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), (w_end || e_end) ? 3u : 2u);
+        mbar_init(smem_u32(&nbars[warp * 2]), 1); // (unused)
         mbar_init(smem_u32(&nbars[warp * 2 + 1]), 1);
         mbar_init(smem_u32(&ebars[warp]), 1);
         mbar_init(smem_u32(&ebars[WARPS + warp]), 1); // qdp_full (SK_POST)
@@ -539,7 +541,6 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     __syncthreads(); // the only CTA-wide barrier: mbarriers initialised, endtma written
     if (!active) return;
 
-    const uint32_t nbar0 = smem_u32(&nbars[warp * 2]);
     const uint32_t cbar0 = smem_u32(&cbars[warp * 2]);
     const int swz = (lane >> 2) & 1; // SWIZZLE_32B: 16-byte chunk c of 32-byte row r sits at chunk c ^ ((r >> 2) & 1)
     const int elemS = rg.s_src[warp & 3], elemN = rg.n_src[warp & 3];
@@ -564,7 +565,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     auto issue_nbr = [&](int n) {
         const int q = n & 1;
         const int kq0 = (t0 + n) * TILE_SLABS;
-        const uint32_t nbar = nbar0 + q * 8;
+        const uint32_t nbar = bar0 + (n % STAGES) * 8;
         const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2048);
         mbar_expect_tx(nbar, 2048u);
         tma_load_3d(rb, mapS, c0S, kq0, elemS, nbar);        // the S neighbour's facing row (its N row in a face interior)
@@ -572,7 +573,6 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     };
     // lane 0 of an end warp: stage the outside neighbour's facing column and the two diagonal corner values of tile n
     const bool is_end = w_end || e_end;
-    const uint32_t ebar = smem_u32(&ebars[warp]);
     uint32_t end_bytes = 0;
     if (is_end) {
 #pragma unroll
@@ -581,6 +581,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     }
     auto issue_end = [&](int n) {
         const int kq0 = (t0 + n) * TILE_SLABS;
+        const uint32_t ebar = bar0 + (n % STAGES) * 8;
         mbar_expect_tx(ebar, end_bytes);
 #pragma unroll
         for (int side = 0; side < 2; ++side) {
@@ -641,8 +642,6 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         double v[16], nb[4][4], dg[4];
 
         mbar_wait(bar0 + s * 8, parity);
-        mbar_wait(nbar0 + q * 8, qparity);
-        if (is_end) mbar_wait(ebar, (uint32_t)(n & 1));
         if (n == 0) { // the metric staged by this warp's own cp.async group
             asm volatile("cp.async.wait_all;" ::: "memory");
             __syncwarp();
@@ -664,7 +663,6 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
             read_end(0, nb[EDGE_W], dg[0], dg[2]);
         } else { // mate's E column = points 3,7,11,15 = upper halves of chunks 1,3,5,7; east ends of its S/N neighbour rows
             mbar_wait(bar0 - STAGES * 8 + s * 8, parity);
-            mbar_wait(nbar0 - 16 + q * 8, qparity);
             const unsigned char *mrow = row - STAGES * SB;
 #pragma unroll
             for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(mrow + (((2 * t + 1) ^ sw) << 4) + 8);
@@ -676,7 +674,6 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
             read_end(1, nb[EDGE_E], dg[1], dg[3]);
         } else { // mate's W column = points 0,4,8,12 = lower halves of chunks 0,2,4,6; west ends of its S/N neighbour rows
             mbar_wait(bar0 + STAGES * 8 + s * 8, parity);
-            mbar_wait(nbar0 + 16 + q * 8, qparity);
             const unsigned char *mrow = row + STAGES * SB;
 #pragma unroll
             for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(mrow + (((2 * t) ^ sw) << 4));
