@@ -308,6 +308,16 @@ def main():
                     "frac_of_nominal_8TBs": ach / 8000.0, "kernels": kernels}
         # DRAM bytes per launch from the committed ncu --set full capture (profiles/traffic.json, taken at a
         # smaller cubed sphere: ncu replays every kernel ~40x), scaled by the number of slabs of this launch
+        # FP64 side: 64 flop per point-update per Laplacian (the reference's CPU operation count) against a
+        # DFMA rate measured on this GPU; the kernels execute 40 FMA-class instructions per point (folded metric)
+        try:
+            fp64_peak = ku.measure_fp64_peak()
+            roofline["fp64"] = {"peak_TFLOPs_measured_dfma": fp64_peak,
+                                "algorithmic_TFLOPs": 2 * 64.0 * updates_global / (ms_per_step * 1e-3) / 1e12,
+                                "executed_TFLOPs": 2 * 40.0 * updates_global / (ms_per_step * 1e-3) / 1e12,
+                                "executed_frac_of_peak": 2 * 40.0 * updates_global / (ms_per_step * 1e-3) / 1e12 / fp64_peak}
+        except Exception as ex:
+            roofline["fp64"] = {"error": str(ex)[:120]}
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             try:

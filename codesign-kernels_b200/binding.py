@@ -88,6 +88,7 @@ def lib():
         "bwk_comm_init": [i32, i32, p],
         "bwk_comm_finalize": [],
         "bwk_comm_barrier": [],
+        "bwk_measure_fp64_peak": [C.POINTER(C.c_double)],
         "bwk_partition": [i64, i32, i32, C.POINTER(i64), C.POINTER(i64)],
         "bwk_plan_apply_host": [p, p, p],
         "bwk_plan_send_list": [p, i32, p, p],
@@ -294,6 +295,12 @@ class KernelUtils:
 
     def sync(self):
         _ck(lib().bwk_sync())
+
+    def measure_fp64_peak(self):
+        """measured DFMA rate of this GPU, TFLOP/s"""
+        v = C.c_double()
+        _ck(lib().bwk_measure_fp64_peak(C.byref(v)))
+        return v.value
 
     def comm_barrier(self):
         """device-side barrier across ranks on the library's stream (no-op on one rank)"""

@@ -1077,6 +1077,28 @@ int bwk_run_biharmonic(void)
     return biharmonic_device();
 }
 
+int bwk_measure_fp64_peak(double *tflops)
+{
+    if (need_init()) return 1;
+    if (!g.d_dummy) CK(cudaMalloc(&g.d_dummy, sizeof(double) * 2 * 1024));
+    const int blocks = 148 * 32;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    CK(launch_dfma_peak(g.d_dummy, blocks, g.s_main)); // warm-up
+    CK(cudaEventRecord(e0, g.s_main));
+    for (int r = 0; r < 5; ++r) CK(launch_dfma_peak(g.d_dummy, blocks, g.s_main));
+    CK(cudaEventRecord(e1, g.s_main));
+    CK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    g.launches += 6;
+    *tflops = 5.0 * blocks * 256.0 * 8.0 * 4096.0 * 2.0 / (ms * 1e-3) / 1e12;
+    return 0;
+}
+
 int bwk_upload_hypervis_fields(const double *dp, const double *dpdiss)
 {
     if (need_init()) return 1;

@@ -1197,6 +1197,28 @@ __global__ void ratio_kernel(const double *__restrict__ num, const double *__res
 {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) ratio[i] = num[i] / den[i];
 }
+// FP64 issue-rate microbenchmark (there is no FP64 peak in MEASURED_PEAKS.json, so the pipe utilisation
+// ncu reports is put against a measured DFMA rate): 8 independent FMA chains per thread, 4096 FMAs each.
+__global__ void __launch_bounds__(256) dfma_peak_kernel(double *out, double a, double b)
+{
+    double x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = threadIdx.x + i;
+    for (int it = 0; it < 4096; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = fma(x[i], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += x[i];
+    if (s == 12345.678) out[0] = s; // never true: keeps the chains alive
+}
+cudaError_t launch_dfma_peak(double *out, int blocks, cudaStream_t st)
+{
+    dfma_peak_kernel<<<blocks, 256, 0, st>>>(out, 0.999999, 1e-9);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_ratio(const double *dpdiss, const double *dp, double *ratio, int64_t n, cudaStream_t st)
 {
     ratio_kernel<<<148 * 8, 256, 0, st>>>(dpdiss, dp, ratio, n);

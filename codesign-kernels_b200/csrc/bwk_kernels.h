@@ -67,6 +67,8 @@ bool sweep1_pre_fits(int nlev);
 // local elements [first, first+count) or of a device list (HOMME prim_advection, not in the reference)
 cudaError_t launch_hypervis_post(const double *qdp, const double *qtens, double *out, const double *elem, const double *rsph,
                                  const int32_t *list, int first, int count, int kq, double coef, int limiter, cudaStream_t st);
+// FP64 FMA issue-rate microbenchmark: blocks x 256 threads x 8 chains x 4096 FMAs
+cudaError_t launch_dfma_peak(double *out, int blocks, cudaStream_t st);
 // prescale = dpdiss / dp, n values
 cudaError_t launch_ratio(const double *dpdiss, const double *dp, double *ratio, int64_t n, cudaStream_t st);
 // plain-load variant of MODE_LAPLACE (no TMA, no shared-memory staging); for ncu A/B only

@@ -170,6 +170,8 @@ int bwk_advance_hypervis_scalar(const bwk_element_t *elem, double *Qdp, const do
 /* rank 0 creates the id, the launcher broadcasts the bytes (any transport) */
 int bwk_comm_unique_id(void *id_bytes);
 int bwk_comm_init(int rank, int nranks, const void *id_bytes);
+/* harness: measured FP64 FMA rate of this GPU in TFLOP/s (DFMA microbenchmark), the denominator for FP64 pipe utilisation */
+int bwk_measure_fp64_peak(double *tflops);
 /* device-side barrier across ranks on the library's stream (benchmark bracketing); no-op on one rank */
 int bwk_comm_barrier(void);
 int bwk_comm_finalize(void);
