@@ -403,8 +403,9 @@ enum : int { EM_NONE = 0, EM_ROW = 1, EM_COL = 2, EM_MATE_LEFT = 3, EM_MATE_RIGH
 //   tiles   [warp][stage][4 KB]                        TMA destination, SWIZZLE_128B, results written in place
 //   rowbuf  [set 2][warp][S,N][32 slabs][32 B]         facing rows of the S/N neighbours, TMA destination, SWIZZLE_32B
 //   endbuf  [W end,E end][column: 4 x 512 B | diagonal 512 B | diagonal 512 B]   strip-end neighbours, TMA destination, single buffered
-//   barriers: tile_full [warp][stage], nbr_full [warp][2], cons [warp][2], end_full [warp]
-//   metric [warp][64], endtma [6]
+//   barriers: full [warp][stage] (tile + S/N rows + strip-end boxes of one tile), 2 spare slots per warp, cons [warp][2],
+//             1 spare slot per warp, qdp_full [warp] (SK_POST)
+//   metric [warp][64], endtma [6], spheremp + rspheremp [warp][32] (SK_POST)
 // The generic path keeps its per-warp descriptors (WarpDss) in the rowbuf area.
 constexpr int ROWBUF_BYTES = 2 * STRIP_MAX * 2 * 32 * 32;
 constexpr int END_SIDE_BYTES = 2048 + 2 * 512;
@@ -475,7 +476,7 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
     double *metric_s = metric_all + warp * METRIC_DOUBLES;
     unsigned char *rowbuf = extra;                        // [set][warp][2][32][32 B]
     unsigned char *endbuf = extra + ROWBUF_BYTES;         // [set][2][6][32][8 B]
-    uint64_t *nbars = bars + WARPS * STAGES;              // nbr_full [warp][2]
+    uint64_t *nbars = bars + WARPS * STAGES;              // (two spare slots per warp)
     uint64_t *cbars = nbars + WARPS * 2;                  // cons     [warp][2]
     uint64_t *ebars = cbars + WARPS * 2;                  // end_full [warp]
     // sources of the two strip ends, decoded once per CTA: [W column, SW, NW, E column, SE, NE]
@@ -492,9 +493,6 @@ __device__ __forceinline__ void sweep2_regular(const SweepParams &p, unsigned ch
         // one barrier per tile in flight collects everything that tile needs: the tile itself, the S/N rows and, for an end
         // warp, the strip-end boxes -- three separate expect_tx arrivals (issued 3, 2 and 1 tiles ahead), one wait
         for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&bars[warp * STAGES + s]), (w_end || e_end) ? 3u : 2u);
-        mbar_init(smem_u32(&nbars[warp * 2]), 1); // (unused)
-        mbar_init(smem_u32(&nbars[warp * 2 + 1]), 1);
-        mbar_init(smem_u32(&ebars[warp]), 1);
         mbar_init(smem_u32(&ebars[WARPS + warp]), 1); // qdp_full (SK_POST)
         const uint32_t nmates = (w_end ? 0u : 1u) + (e_end ? 0u : 1u);
         mbar_init(smem_u32(&cbars[warp * 2]), active && nmates ? 32u * nmates : 1u); // every lane of every mate arrives
