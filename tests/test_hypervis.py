@@ -124,7 +124,7 @@ def _lcg_case(oracle, ne, nlev, qsize):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("ne,nlev,qsize,sub,lim", [(2, 8, 3, 1, True), (3, 72, 2, 2, True), (4, 33, 1, 1, False), (8, 16, 4, 3, True)])
+@pytest.mark.parametrize("ne,nlev,qsize,sub,lim", [(2, 8, 3, 1, True), (3, 72, 2, 2, True), (4, 33, 1, 1, False), (8, 16, 4, 3, True), (2, 128, 2, 1, True)])
 def test_advance_hypervis_gpu_vs_oracle(bwk, oracle, ne, nlev, qsize, sub, lim):
     """tolerance: 1e-12 of each (k,q) field's maximum per subcycle (the update subtracts two terms of similar size, so an
     elementwise-relative bound is not meaningful; same operator drift as the biharmonic tests otherwise)"""
@@ -174,3 +174,24 @@ def test_advance_hypervis_analytic_gpu(bwk, oracle):
         # not exactly zero: dp0*Qdp/dp is constant only up to rounding, and dt*nu_q*biharmonic amplifies that noise by
         # ~ 0.05 (lambda_max/lambda_6)^2 ~ 1e6..1e7 at ne=8 (measured 6.7e-10; 1e-10 bound holds at ne=4)
         assert _slot_rel(ku.qtens, ref) < 1e-8
+
+
+@pytest.mark.gpu
+def test_advance_hypervis_signed_field_limiter_branches_gpu(bwk, oracle):
+    """Qdp of both signs, so that limiter2d_zero meets levels of negative mass (the flip branch), levels it clips and
+    levels it leaves alone; GPU vs oracle at 1e-12 of the field maximum, plus the limiter's own guarantees on the
+    pre-DSS quantity are implied by the oracle agreement."""
+    ne, nlev, qsize = 3, 20, 3
+    n, dvv, elem, q, dss, rs, dp, dpd, coef = _lcg_case(oracle, ne, nlev, qsize)
+    q = np.asfortranarray(q - 0.5)
+    q[:, :, 3, 1, :] = -np.abs(q[:, :, 3, 1, :])  # a level that is negative everywhere
+    ref = dss.advance_hypervis_scalar(elem, rs, q.copy(order="F"), dp, dpd, dvv, dt2=1.0, nu_q=coef, subcycles=1, limiter=True)
+    ref_nolim = dss.advance_hypervis_scalar(elem, rs, q.copy(order="F"), dp, dpd, dvv, dt2=1.0, nu_q=coef, subcycles=1, limiter=False)
+    assert np.abs(ref - ref_nolim).max() > 1e-3 * np.abs(ref).max()  # the limiter did something on this input
+    with bwk.KernelUtils(n, nlev, qsize).allocate_data() as ku:
+        ku.initialize_data()
+        ku.qtens[...] = q
+        ku.set_topology_cubed_sphere(ne)
+        ku.advance_hypervis_scalar(ku.elem, ku.qtens, dp, dpd, ku.deriv, 1.0, coef, 1, True)
+        err = _slot_rel(ku.qtens, ref)
+    assert err <= 1e-12, err
