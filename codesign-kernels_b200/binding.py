@@ -83,6 +83,9 @@ def lib():
         "bwk_upload_hypervis_fields": [p, p],
         "bwk_run_advance_hypervis": [C.c_double, C.c_double, i32, i32],
         "bwk_advance_hypervis_scalar": [p, p, p, p, p, C.c_double, C.c_double, i32, i32],
+        "bwk_upload_vec_sphere2cart": [p],
+        "bwk_run_biharmonic_dp3d": [i32, i32],
+        "bwk_biharmonic_wk_dp3d": [p, p, p, p, p, p, i32, i32],
         "bwk_run_biharmonic_phase": [i32],
         "bwk_comm_unique_id": [p],
         "bwk_comm_init": [i32, i32, p],
@@ -125,7 +128,7 @@ def _ck(rc):
 
 
 def _ptr(a):
-    return a.ctypes.data_as(C.c_void_p)
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
 def cubed_sphere_gdof(ne):
@@ -331,6 +334,23 @@ class KernelUtils:
 
     def run_advance_hypervis_device(self, dt2, nu_q, hypervis_subcycle_q=1, limiter=True):
         _ck(lib().bwk_run_advance_hypervis(float(dt2), float(nu_q), int(hypervis_subcycle_q), 1 if limiter else 0))
+
+    # -- upstream HOMME biharmonic_wk_dp3d with the Cartesian vlaplace_sphere_wk (not in the reference, bwk_b200.h); the
+    #    KernelUtils must have been made with qsize = 4
+    def biharmonic_wk_dp3d(self, elem, vec_sphere2cart, dptens, ttens, vtens, deriv, var_coef1=True, undamprrcart=True):
+        """dptens, ttens (np,np,nlev,nelemd) and vtens (np,np,2,nlev,nelemd), Fortran order, hold dp3d, T and v on entry and
+        the weak biharmonic on return; vec_sphere2cart (np,np,3,2,nelemd)"""
+        for a in (dptens, ttens, vtens):
+            if not (isinstance(a, np.ndarray) and a.flags.f_contiguous and a.dtype == np.float64):
+                raise ValueError("biharmonic_wk_dp3d needs Fortran-ordered float64 arrays")
+        _ck(lib().bwk_biharmonic_wk_dp3d(_ptr(elem), _ptr(vec_sphere2cart), _ptr(dptens), _ptr(ttens), _ptr(vtens), _ptr(deriv),
+                                         1 if var_coef1 else 0, 1 if undamprrcart else 0))
+
+    def upload_vec_sphere2cart(self, vec_sphere2cart):
+        _ck(lib().bwk_upload_vec_sphere2cart(_ptr(vec_sphere2cart)))
+
+    def run_biharmonic_dp3d_device(self, var_coef1=True, undamprrcart=True):
+        _ck(lib().bwk_run_biharmonic_dp3d(1 if var_coef1 else 0, 1 if undamprrcart else 0))
 
     def set_topology_cubed_sphere(self, ne, elem_first=0):
         _ck(lib().bwk_set_topology_cubed_sphere(ne, elem_first))

@@ -99,6 +99,8 @@ struct Ctx {
     double *d_w = nullptr, *d_ratio = nullptr; // advance_hypervis_scalar: biharmonic work buffer, dpdiss/dp [nelem][nlev][16]
     CUtensorMap map_w, map_w_rows, map_w_pt; // the work buffer seen as slabs / edge rows / i-pairs (strip sweeps reading it)
     bool src_is_w = false;                  // strip sweeps and the halo pack read the work buffer instead of tmp
+    double *d_v2c = nullptr, *d_metric_plain = nullptr; // biharmonic_wk_dp3d: vec_sphere2cart [nelem][96]; folded metric without tensorVisc
+    bool have_v2c = false, have_metric_plain = false;
     double *d_save = nullptr, *d_table = nullptr, *d_partials = nullptr, *d_halo = nullptr, *d_send = nullptr, *d_dummy = nullptr;
     double *h_partials = nullptr;
     ElemDss *d_dss = nullptr;
@@ -282,6 +284,7 @@ int upload_metric(const bwk_element_t *elem, const bwk_derivative_t *deriv, cuda
         CK(launch_fold_metric(g.d_elem, g.d_metric, g.nelem, st));
         g.launches++;
         g.have_metric = true;
+        g.have_metric_plain = false;
         g.gen_nelem_global = -1;
         const double *e = reinterpret_cast<const double *>(elem);
         bool same = g.h_spheremp.size() == (size_t)16 * g.nelem;
@@ -575,6 +578,37 @@ int hypervis_device(double dt2, double nu_q, int subcycles, int limiter)
     return 0;
 }
 
+// biharmonic_wk_dp3d on the device-resident fields (d_q in HOMME's edge-buffer order: T, v, dp3d; the context was made with
+// qsize = 4): element-local sweep (-> tmp, rspheremp-scaled, boundary elements first so their rows travel early), DSS strip
+// sweep (-> d_q), element-local sweep in place.  See bwk_b200.h
+int dp3d_device(int var_coef1, int undamp)
+{
+    if (g.qsize != 4) return fail("biharmonic_wk_dp3d needs a context made with qsize = 4 (T, v(1), v(2), dp3d per level); this one has qsize = %d", g.qsize);
+    if (!g.have_metric) return fail("no element metric on the device");
+    if (!g.have_v2c) return fail("no vec_sphere2cart on the device: call bwk_upload_vec_sphere2cart first");
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (compute_rspheremp()) return 1;
+    const double *metric1 = g.d_metric;
+    if (!var_coef1) {
+        if (!g.d_metric_plain) CK(cudaMalloc(&g.d_metric_plain, sizeof(double) * METRIC_DOUBLES * g.nelem));
+        if (!g.have_metric_plain) {
+            CK(launch_fold_metric(g.d_elem, g.d_metric_plain, g.nelem, g.s_main, 0));
+            g.launches++;
+            g.have_metric_plain = true;
+        }
+        metric1 = g.d_metric_plain;
+    }
+    auto produce = [&](int first, int count, const int32_t *list) {
+        CK(launch_dp3d_laplace(true, g.d_q, g.d_tmp, metric1, g.d_v2c, g.d_elem, g.d_rsph, list, first, count, g.nlev, undamp, g.s_main));
+        if (count > 0) g.launches++;
+        return 0;
+    };
+    if (dss_pass(produce, MODE_DSS, &g.sp.map_q)) return 1;
+    CK(launch_dp3d_laplace(false, g.d_q, g.d_q, g.d_metric, g.d_v2c, g.d_elem, g.d_rsph, nullptr, 0, g.nelem, g.nlev, undamp, g.s_main));
+    g.launches++;
+    return 0;
+}
+
 // chunk boundaries (in elements) for the host<->device pipelines
 std::vector<int> make_chunks(int first0, int count)
 {
@@ -735,7 +769,7 @@ int bwk_finalize(void)
             for (int e = 0; e < 2; ++e)
                 if (kv.second.ev[c][e]) cudaEventDestroy(kv.second.ev[c][e]);
     g_tune.clear();
-    free_dev(g.d_w); free_dev(g.d_ratio);
+    free_dev(g.d_w); free_dev(g.d_ratio); free_dev(g.d_v2c); free_dev(g.d_metric_plain);
     free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
     free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);
     free_dev(g.d_send_elem); free_dev(g.d_send_row); free_dev(g.d_strips_all); free_dev(g.d_strips_dep); free_dev(g.d_strips_indep); free_dev(g.d_reg_all); free_dev(g.d_reg_dep); free_dev(g.d_reg_indep); free_dev(g.d_e2e_strips); free_dev(g.d_e2e_reg);
@@ -1136,6 +1170,52 @@ int bwk_advance_hypervis_scalar(const bwk_element_t *elem, double *Qdp, const do
     if (dp || dpdiss) { if (bwk_upload_hypervis_fields(dp, dpdiss)) return 1; }
     if (bwk_run_advance_hypervis(dt2, nu_q, hypervis_subcycle_q, limiter)) return 1;
     return bwk_download(Qdp);
+}
+
+int bwk_upload_vec_sphere2cart(const double *vec_sphere2cart)
+{
+    if (need_init()) return 1;
+    if (!vec_sphere2cart) return fail("bwk_upload_vec_sphere2cart: the array is required");
+    if (!g.d_v2c) CK(cudaMalloc(&g.d_v2c, sizeof(double) * 96 * g.nelem));
+    CK(cudaMemcpyAsync(g.d_v2c, vec_sphere2cart, sizeof(double) * 96 * g.nelem, cudaMemcpyHostToDevice, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    g.have_v2c = true;
+    return 0;
+}
+
+int bwk_run_biharmonic_dp3d(int var_coef1, int undamprrcart)
+{
+    if (need_init()) return 1;
+    return dp3d_device(var_coef1, undamprrcart);
+}
+
+// host arrays in HOMME's layouts <-> the fused device field (per element: T | v | dp3d, 4*nlev slabs)
+static int dp3d_copy(double *dptens, double *ttens, double *vtens, bool to_device)
+{
+    const size_t lev = (size_t)g.nlev * 128, pitch = 4 * lev;
+    char *base = reinterpret_cast<char *>(g.d_q);
+    struct Part { double *host; size_t off, width; } parts[3] = {{ttens, 0, lev}, {vtens, lev, 2 * lev}, {dptens, 3 * lev, lev}};
+    for (const Part &p : parts) {
+        if (to_device) CK(cudaMemcpy2DAsync(base + p.off, pitch, p.host, p.width, p.width, (size_t)g.nelem, cudaMemcpyHostToDevice, g.s_main));
+        else CK(cudaMemcpy2DAsync(p.host, p.width, base + p.off, pitch, p.width, (size_t)g.nelem, cudaMemcpyDeviceToHost, g.s_main));
+    }
+    return 0;
+}
+
+int bwk_biharmonic_wk_dp3d(const bwk_element_t *elem, const double *vec_sphere2cart, double *dptens, double *ttens, double *vtens,
+                           const bwk_derivative_t *deriv, int var_coef1, int undamprrcart)
+{
+    if (need_init()) return 1;
+    if (!dptens || !ttens || !vtens) return fail("bwk_biharmonic_wk_dp3d: dptens, ttens and vtens are required");
+    if (g.qsize != 4) return fail("biharmonic_wk_dp3d needs a context made with qsize = 4; this one has qsize = %d", g.qsize);
+    if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
+    if (upload_metric(elem, deriv, g.s_main)) return 1;
+    if (vec_sphere2cart && bwk_upload_vec_sphere2cart(vec_sphere2cart)) return 1;
+    if (dp3d_copy(dptens, ttens, vtens, true)) return 1;
+    if (dp3d_device(var_coef1, undamprrcart)) return 1;
+    if (dp3d_copy(dptens, ttens, vtens, false)) return 1;
+    CK(cudaStreamSynchronize(g.s_main));
+    return 0;
 }
 
 int bwk_run_biharmonic_phase(int phase)

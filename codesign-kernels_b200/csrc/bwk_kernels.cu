@@ -1264,6 +1264,157 @@ cudaError_t launch_laplace_plain(double *qtens, const double *metric, int elem_f
 }
 
 // ------------------------------------------------------------------------------------------
+// biharmonic_wk_dp3d (upstream HOMME): the element-local part of one application, for the four
+// fields of a level at once.  Field layout of an element = HOMME's edge-buffer order: T at slab k, v at nlev + m + 2k
+// (m = lat-lon component), dp3d at 3 nlev + k.  One thread per (level, element):
+//   T, dp3d : laplace_sphere_wk
+//   v       : vlaplace_sphere_wk in the Cartesian form -- three Cartesian components through vec_sphere2cart(np,np,3,2),
+//             laplace_sphere_wk on each, back with the transpose, + 2 spheremp v rrearth^2 (rigid rotation is not damped)
+// PRODUCE: src -> dst, scaled by rspheremp (what the DSS strip sweep expects); otherwise in place and unscaled.
+// Every thread moves whole 128-byte lines: its four slabs come in by cp.async (512 bytes per thread in flight before any
+// arithmetic starts), results leave by 128-bit stores; the Cartesian components live in shared memory around the three
+// Laplacians, which keeps the kernel at ~120 registers.  Not TMA-tiled.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+
+// shared memory: element constants [192 doubles], then five 128-byte slots per thread, slot r / 16-byte chunk c of thread tid
+// at ((r * 8 + c) * blockDim.x + tid) * 16 bytes (conflict-free).  Slots 0..3 receive T, dp3d, v(1), v(2) by cp.async -- all
+// 512 bytes of a thread in flight at once --; the Cartesian components take slots 0, 1 (free once the scalars are done) and 4.
+template <bool PRODUCE>
+__global__ void __launch_bounds__(128) dp3d_laplace_kernel(const double *src, double *dst, const double *__restrict__ metric,
+                                                           const double *__restrict__ v2c, const double *__restrict__ elem,
+                                                           const double *__restrict__ rsph, const int32_t *__restrict__ list, int elem_first, int nlev,
+                                                           int undamp)
+{
+    extern __shared__ __align__(16) double dp3d_s[];
+    const int le = list ? list[blockIdx.x] : elem_first + (int)blockIdx.x;
+    const int nt = blockDim.x, tid = threadIdx.x;
+    const int k = (int)blockIdx.y * nt + tid; // one level per thread (a loop over levels makes the compiler hoist all 128 element constants into registers)
+    double2 *slots = reinterpret_cast<double2 *>(dp3d_s + 192);
+    const size_t base = (size_t)le * 4 * nlev;
+    const size_t slab_t = (base + k) * 16, slab_dp = (base + 3 * (size_t)nlev + k) * 16, slab_v = (base + nlev + 2 * (size_t)k) * 16;
+    if (k < nlev) {
+        const uint32_t s0 = smem_u32(slots + tid);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            cp_async16(s0 + (uint32_t)((0 * 8 + c) * nt) * 16u, src + slab_t + 2 * c);
+            cp_async16(s0 + (uint32_t)((1 * 8 + c) * nt) * 16u, src + slab_dp + 2 * c);
+            cp_async16(s0 + (uint32_t)((2 * 8 + c) * nt) * 16u, src + slab_v + 2 * c);
+            cp_async16(s0 + (uint32_t)((3 * 8 + c) * nt) * 16u, src + slab_v + 16 + 2 * c);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    // per-element constants through shared memory (uniform-address reads): folded metric, vec_sphere2cart, rspheremp, spheremp
+    for (int t = tid; t < 192; t += nt)
+        dp3d_s[t] = t < 64 ? metric[(size_t)le * METRIC_DOUBLES + t]
+                  : t < 160 ? v2c[(size_t)le * 96 + (t - 64)]
+                  : t < 176 ? rsph[(size_t)le * 16 + (t - 160)]
+                            : elem[(size_t)le * ELEM_DOUBLES + 64 + (t - 176)];
+    __syncthreads();
+    if (k >= nlev) return;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    const SmemMetric M{dp3d_s};
+    const double *E = dp3d_s + 64, *rs = dp3d_s + 160, *sp = dp3d_s + 176;
+    auto slot = [&](int r, int c) -> double2 & { return slots[(r * 8 + c) * nt + tid]; };
+#pragma unroll 1
+    for (int f = 0; f < 2; ++f) {
+        asm volatile("" ::: "memory"); // keeps the loop-invariant metric reads inside the loop (hoisted, they cost 128 registers)
+        double s[16];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const double2 t = slot(f, c);
+            s[2 * c] = t.x;
+            s[2 * c + 1] = t.y;
+        }
+        laplace_slab(s, M);
+        if (PRODUCE) {
+#pragma unroll
+            for (int t = 0; t < 16; ++t) s[t] *= rs[t];
+        }
+        double2 *out = reinterpret_cast<double2 *>(dst + (f ? slab_dp : slab_t));
+#pragma unroll
+        for (int c = 0; c < 8; ++c) out[c] = make_double2(s[2 * c], s[2 * c + 1]);
+    }
+    // vector: lat-lon -> three Cartesian components (slots 0, 1, 4), the Laplacian of each in place, then back
+#pragma unroll 2
+    for (int h = 0; h < 8; ++h) {
+        const double2 u = slot(2, h), v = slot(3, h);
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            slot(c < 2 ? c : 4, h) = make_double2(fma(E[2 * h + 16 * c + 48], v.x, E[2 * h + 16 * c] * u.x),
+                                                  fma(E[2 * h + 1 + 16 * c + 48], v.y, E[2 * h + 1 + 16 * c] * u.y));
+    }
+#pragma unroll 1
+    for (int c = 0; c < 3; ++c) {
+        asm volatile("" ::: "memory");
+        const int r = c < 2 ? c : 4;
+        double s[16];
+#pragma unroll
+        for (int h = 0; h < 8; ++h) {
+            const double2 t = slot(r, h);
+            s[2 * h] = t.x;
+            s[2 * h + 1] = t.y;
+        }
+        laplace_slab(s, M);
+#pragma unroll
+        for (int h = 0; h < 8; ++h) slot(r, h) = make_double2(s[2 * h], s[2 * h + 1]);
+    }
+    const double und = undamp ? 2.0 * (BWK_RREARTH * BWK_RREARTH) : 0.0;
+    double2 *vout = reinterpret_cast<double2 *>(dst + slab_v);
+#pragma unroll 2
+    for (int h = 0; h < 8; ++h) {
+        const double2 uu = slot(2, h), vv = slot(3, h);
+        const double2 l0 = slot(0, h), l1 = slot(1, h), l2 = slot(4, h);
+        double o[4]; // u(2h), u(2h+1), v(2h), v(2h+1)
+#pragma unroll
+        for (int x = 0; x < 2; ++x) {
+            const int t = 2 * h + x;
+            const double w = und * sp[t];
+            double ou = w * (x ? uu.y : uu.x), ov = w * (x ? vv.y : vv.x);
+            const double l[3] = {x ? l0.y : l0.x, x ? l1.y : l1.x, x ? l2.y : l2.x};
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                ou = fma(l[c], E[t + 16 * c], ou);
+                ov = fma(l[c], E[t + 16 * c + 48], ov);
+            }
+            if (PRODUCE) {
+                ou *= rs[t];
+                ov *= rs[t];
+            }
+            o[x] = ou;
+            o[2 + x] = ov;
+        }
+        vout[h] = make_double2(o[0], o[1]);
+        vout[8 + h] = make_double2(o[2], o[3]);
+    }
+}
+
+cudaError_t launch_dp3d_laplace(bool produce, const double *src, double *dst, const double *metric, const double *v2c, const double *elem,
+                                const double *rsph, const int32_t *list, int elem_first, int elem_count, int nlev, int undamp, cudaStream_t st)
+{
+    if (elem_count <= 0) return cudaSuccess;
+    const int threads = nlev >= 128 ? 128 : ((nlev + 31) / 32) * 32;
+    const size_t smem = ((size_t)80 * threads + 192) * sizeof(double);
+    const dim3 grid((unsigned)elem_count, (unsigned)((nlev + threads - 1) / threads));
+    static bool attr_set = false;
+    if (!attr_set) {
+        const int max_smem = (80 * 128 + 192) * (int)sizeof(double); // above the 48 KB default
+        cudaError_t e = cudaFuncSetAttribute(dp3d_laplace_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(dp3d_laplace_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    if (produce)
+        dp3d_laplace_kernel<true><<<grid, threads, smem, st>>>(src, dst, metric, v2c, elem, rsph, list, elem_first, nlev, undamp);
+    else
+        dp3d_laplace_kernel<false><<<grid, threads, smem, st>>>(src, dst, metric, v2c, elem, rsph, list, elem_first, nlev, undamp);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
 // Setup / harness kernels
 // ------------------------------------------------------------------------------------------
 cudaError_t set_dvv(const double *dvv16_host, cudaStream_t st)
@@ -1272,7 +1423,7 @@ cudaError_t set_dvv(const double *dvv16_host, cudaStream_t st)
 }
 
 // One thread per (element, GLL point).  element_t layout F90:23-27 flattened.
-__global__ void fold_metric_kernel(const double *__restrict__ elem, double *__restrict__ metric, int64_t nelem)
+__global__ void fold_metric_kernel(const double *__restrict__ elem, double *__restrict__ metric, int64_t nelem, int use_tensor)
 {
     const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= nelem * 16) return;
@@ -1281,7 +1432,9 @@ __global__ void fold_metric_kernel(const double *__restrict__ elem, double *__re
     const double *E = elem + e * ELEM_DOUBLES;
     const double D11 = E[pt], D21 = E[16 + pt], D12 = E[32 + pt], D22 = E[48 + pt]; // Dinv(i,j,c,a) at 16c+32a
     const double sp = E[64 + pt];
-    const double T11 = E[80 + pt], T21 = E[96 + pt], T12 = E[112 + pt], T22 = E[128 + pt];
+    // use_tensor = 0: laplace_sphere_wk with var_coef = .false. (upstream HOMME's first application under tensor hyperviscosity)
+    const double T11 = use_tensor ? E[80 + pt] : 1.0, T21 = use_tensor ? E[96 + pt] : 0.0;
+    const double T12 = use_tensor ? E[112 + pt] : 0.0, T22 = use_tensor ? E[128 + pt] : 1.0;
     // g = T * D^T * (dx,dy)  (F90:128-133 then F90:175-178)
     const double G1x = T11 * D11 + T12 * D12, G1y = T11 * D21 + T12 * D22;
     const double G2x = T21 * D11 + T22 * D12, G2y = T21 * D21 + T22 * D22;
@@ -1294,11 +1447,11 @@ __global__ void fold_metric_kernel(const double *__restrict__ elem, double *__re
     M[3] = f * (D21 * G1y + D22 * G2y);
 }
 
-cudaError_t launch_fold_metric(const double *elem, double *metric, int64_t nelem, cudaStream_t st)
+cudaError_t launch_fold_metric(const double *elem, double *metric, int64_t nelem, cudaStream_t st, int use_tensor)
 {
     if (nelem <= 0) return cudaSuccess;
     const int64_t n = nelem * 16;
-    fold_metric_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(elem, metric, nelem);
+    fold_metric_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(elem, metric, nelem, use_tensor);
     return cudaGetLastError();
 }
 

@@ -76,7 +76,10 @@ cudaError_t launch_laplace_plain(double *qtens, const double *metric, int elem_f
 
 cudaError_t set_dvv(const double *dvv16_host, cudaStream_t st);
 // folded metric M = -(rrearth^2) * spheremp * Dinv * tensorVisc * Dinv^T per GLL point
-cudaError_t launch_fold_metric(const double *elem, double *metric, int64_t nelem, cudaStream_t st);
+cudaError_t launch_fold_metric(const double *elem, double *metric, int64_t nelem, cudaStream_t st, int use_tensor = 1);
+// element-local part of biharmonic_wk_dp3d over [elem_first, elem_first+elem_count) or a device list (see bwk_kernels.cu)
+cudaError_t launch_dp3d_laplace(bool produce, const double *src, double *dst, const double *metric, const double *v2c, const double *elem,
+                                const double *rsph, const int32_t *list, int elem_first, int elem_count, int nlev, int undamp, cudaStream_t st);
 // edge pack: copy rows (local element, row id) x KQ into a contiguous send buffer (HOMME edgeVpack analogue)
 cudaError_t launch_edge_pack(const double *tmp, const int32_t *row_elem, const int32_t *row_id,
                              int64_t nrows, int kq, double *sendbuf, cudaStream_t st);

@@ -59,12 +59,23 @@ _FACE = (
 )
 
 
-def physical_elements(ne):
-    """-> (dvv (4,4), elem (6 ne^2, 144) float64 records in element_t order (F90:23-27), xyz (6 ne^2, 4[j], 4[i], 3))."""
+def physical_elements(ne, axis=None, with_frame=False):
+    """-> (dvv (4,4), elem (6 ne^2, 144) float64 records in element_t order (F90:23-27), xyz (6 ne^2, 4[j], 4[i], 3)).
+
+    axis=None: the tangent frame is local to each face (e_1 along dP/dxi_1) -- enough for scalar fields, whose operator does
+    not depend on the frame.  axis=(ax,ay,az): a GLOBAL frame, e_1 = axis x P (east about that axis), e_2 = P x e_1 (north),
+    the same at every copy of a shared node, so that vector components can be summed by the DSS (HOMME's lat-lon
+    components; the axis is tilted off the cube's symmetry axes so that its poles are not GLL nodes).
+    with_frame=True appends (vec_sphere2cart (6 ne^2, 96) in Fortran order (np,np,3,2), e1, e2 (6 ne^2, 4, 4, 3))."""
     x, w, d = gll4()
+    if axis is not None:
+        axis = np.asarray(axis, float) / np.linalg.norm(axis)
     n = 6 * ne * ne
     elem = np.zeros((n, 144))
     xyz = np.zeros((n, NP, NP, 3))
+    v2c = np.zeros((n, 96))
+    f1 = np.zeros((n, NP, NP, 3))
+    f2 = np.zeros((n, NP, NP, 3))
     dalpha = np.pi / (4.0 * ne)  # d(alpha)/d(xi)
     for f in range(6):
         cfun, cu, cv = _FACE[f]
@@ -83,8 +94,16 @@ def physical_elements(ne):
                 # covariant basis a_c = dP/dxi_c (tangent to the unit sphere)
                 a1 = (cu - P * (P @ cu)[..., None]) / r * ((1 + X * X) * dalpha)[..., None]
                 a2 = (cv - P * (P @ cv)[..., None]) / r * ((1 + Y * Y) * dalpha)[..., None]
-                e1 = a1 / np.linalg.norm(a1, axis=-1, keepdims=True)
+                if axis is None:
+                    e1 = a1 / np.linalg.norm(a1, axis=-1, keepdims=True)
+                else:
+                    e1 = np.cross(axis, P)
+                    e1 = e1 / np.linalg.norm(e1, axis=-1, keepdims=True)
                 e2 = np.cross(P, e1)
+                f1[e], f2[e] = e1, e2
+                for c in range(3):  # vec_sphere2cart(i,j,c,m) at i + 4j + 16c + 48m
+                    v2c[e, 16 * c:16 * c + 16] = e1[..., c].reshape(16)
+                    v2c[e, 48 + 16 * c:48 + 16 * c + 16] = e2[..., c].reshape(16)
                 D = np.empty((NP, NP, 2, 2))
                 D[..., 0, 0] = np.sum(e1 * a1, -1)
                 D[..., 0, 1] = np.sum(e1 * a2, -1)
@@ -103,7 +122,24 @@ def physical_elements(ne):
                         rec[16 * a + 32 * b:16 * a + 32 * b + 16] = Di[..., a, b].reshape(16)
                         rec[80 + 16 * a + 32 * b:80 + 16 * a + 32 * b + 16] = 1.0 if a == b else 0.0
                 rec[64:80] = (np.abs(det) * w[None, :] * w[:, None]).reshape(16)
+    if with_frame:
+        return d.copy(), elem, xyz, v2c, f1, f2
     return d.copy(), elem, xyz
+
+
+TILTED_AXIS = (0.31, 0.52, 0.79)
+
+
+def harmonic_vector(xyz, l, e1, e2, rotational=False):
+    """(u, v) components, in the frame (e1, e2), of the tangent gradient of harmonic(l) -- or of its rotation by 90 degrees
+    (P x grad).  Both are eigenfunctions of the vector Laplacian (grad div - curl curl) with eigenvalue -l(l+1); the
+    rotational l = 1 field is a rigid rotation.  -> array (..., 2)"""
+    z = (xyz[..., 0] + 1j * xyz[..., 1]) ** (l - 1)
+    g = np.stack([l * z.real, -l * z.imag, 0 * z.real], axis=-1)
+    g = g - xyz * np.sum(xyz * g, axis=-1, keepdims=True)
+    if rotational:
+        g = np.cross(xyz, g)
+    return np.stack([np.sum(g * e1, -1), np.sum(g * e2, -1)], axis=-1)
 
 
 def harmonic(xyz, l):

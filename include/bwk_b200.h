@@ -165,6 +165,30 @@ int bwk_run_advance_hypervis(double dt2, double nu_q, int hypervis_subcycle_q, i
 int bwk_advance_hypervis_scalar(const bwk_element_t *elem, double *Qdp, const double *dp, const double *dpdiss,
                                 const bwk_derivative_t *deriv, double dt2, double nu_q, int hypervis_subcycle_q, int limiter);
 
+/* ---- biharmonic_wk_dp3d: the momentum / temperature / layer-thickness counterpart ----
+ * NOT in the reference repository (upstream HOMME viscosity_mod: biharmonic_wk_dp3d(elem, dptens, dpflux, ttens, vtens,
+ * deriv, edge3, hybrid, nt, nets, nete); derivative_mod: vlaplace_sphere_wk / vlaplace_sphere_wk_cartesian; un-vendored,
+ * no pinned version; semantics restated in oracle/bwk_oracle.c, PARITY UNPINNED, pinned to analytic eigenvalues by
+ * tests/test_dp3d.py).  It replaces
+ *     ttens = laplace_sphere_wk(T) ; dptens = laplace_sphere_wk(dp3d) ; vtens = vlaplace_sphere_wk(v)    [var_coef1]
+ *     edgeVpack(ttens @0, vtens @nlev, dptens @3 nlev) / bndry_exchangeV / edgeVunpack ; * rspheremp
+ *     the same three operators again                                                                      [var_coef = .true.]
+ * with vlaplace_sphere_wk in its tensor-hyperviscosity (Cartesian) form: lat-lon components -> three Cartesian components
+ * through vec_sphere2cart(np,np,3,2), laplace_sphere_wk (F90:164-182) on each, back with the transpose, and, when
+ * undamprrcart != 0, + 2*spheremp*v*rrearth**2 so that rigid rotation is not damped.  var_coef1 = 0 leaves tensorVisc out
+ * of the first application (upstream does that when hypervis_scaling > 0); the contravariant (grad-div / curl-vorticity)
+ * form and the dpflux output are not provided.
+ * The context must be made with bwk_init(nelemd, nlev, 4): the device field holds, per element, T(np,np,nlev),
+ * v(np,np,2,nlev), dp3d(np,np,nlev) in that order (HOMME's edge-buffer order).  On entry ttens / dptens / vtens hold T /
+ * dp3d / v (as qtens holds the input of biharmonic_wk_scalar), on return the weak biharmonic. */
+int bwk_upload_vec_sphere2cart(const double *vec_sphere2cart /* (np,np,3,2,nelemd) */);
+/* device resident (the fused field is the one bwk_upload / bwk_download move), asynchronous */
+int bwk_run_biharmonic_dp3d(int var_coef1, int undamprrcart);
+/* upload (elem, vec_sphere2cart, fields, deriv), run, download; ttens, dptens (np,np,nlev,nelemd), vtens (np,np,2,nlev,nelemd);
+ * elem / vec_sphere2cart / deriv may be NULL to keep what is on the device */
+int bwk_biharmonic_wk_dp3d(const bwk_element_t *elem, const double *vec_sphere2cart, double *dptens, double *ttens, double *vtens,
+                           const bwk_derivative_t *deriv, int var_coef1, int undamprrcart);
+
 /* ---- several GPUs: one process per GPU, contiguous element blocks, NCCL send/recv ---- */
 #define BWK_UNIQUE_ID_BYTES 128
 /* rank 0 creates the id, the launcher broadcasts the bytes (any transport) */

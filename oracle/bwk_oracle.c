@@ -522,3 +522,94 @@ void bwko_advance_hypervis_scalar(const bwko_dss_t *d, const double *elem, const
     }
     free(qtens);
 }
+
+/* ------------------------------------------------------------------------------------------
+ * biharmonic_wk_dp3d / vlaplace_sphere_wk -- NOT in /root/reference: the momentum /
+ * temperature / layer-thickness counterpart of biharmonic_wk_scalar in upstream HOMME (viscosity_mod:
+ * biharmonic_wk_dp3d; derivative_mod: vlaplace_sphere_wk, vlaplace_sphere_wk_cartesian).  Un-vendored, no pinned
+ * version, restated from its published structure; PARITY UNPINNED (pinned to analytic eigenvalues by tests/test_dp3d.py).
+ *
+ *   ttens  = laplace_sphere_wk(T),  dptens = laplace_sphere_wk(dp3d),  vtens = vlaplace_sphere_wk(v)      [var_coef = var_coef1]
+ *   DSS of all four fields (one edge buffer: T at 0, v at nlev, dp3d at 3 nlev), * rspheremp
+ *   the same three operators again                                                                          [var_coef = .true.]
+ *
+ * vlaplace_sphere_wk in its tensor-hyperviscosity form (the branch the reference's laplace_sphere_wk, F90:164-182,
+ * belongs to) is the Cartesian one: the lat-lon vector goes to three Cartesian components with vec_sphere2cart(np,np,3,2),
+ * each component gets laplace_sphere_wk, the result comes back with the transpose, and 2*spheremp*v*rrearth^2 is added so
+ * that rigid rotation is not damped ("undamprrcart").  var_coef = 0 applies the operator without tensorVisc (upstream
+ * passes var_coef1 = .false. on the first application when hypervis_scaling > 0); upstream's other branch (the
+ * contravariant grad-div / curl-vorticity form) is not restated here.
+ * Layouts: ttens, dptens (np,np,nlev,nelemd); vtens (np,np,2,nlev,nelemd); vec_sphere2cart (np,np,3,2,nelemd).
+ */
+static void laplace_sphere_wk_vc(const double *s, const double *dvv, const double *e, int var_coef, double *laplace)
+{
+    if (var_coef) {
+        laplace_sphere_wk_cpu(s, dvv, e, laplace);
+        return;
+    }
+    double grads[32];
+    gradient_sphere_cpu(s, dvv, e, grads);
+    divergence_sphere_wk_cpu(grads, dvv, e, laplace);
+}
+
+static void vlaplace_cartesian_cpu(const double *v, const double *dvv, const double *e, const double *v2c, int var_coef, int undamp, double *lap)
+{
+    const double rrearth = bwko_rrearth();
+    double cart[3][16], lc[3][16];
+    for (int c = 0; c < 3; ++c)
+        for (int t = 0; t < 16; ++t) cart[c][t] = v2c[t + 16 * c] * v[t] + v2c[t + 16 * c + 48] * v[16 + t];
+    for (int c = 0; c < 3; ++c) laplace_sphere_wk_vc(cart[c], dvv, e, var_coef, lc[c]);
+    for (int m = 0; m < 2; ++m)
+        for (int t = 0; t < 16; ++t)
+            lap[16 * m + t] = lc[0][t] * v2c[t + 48 * m] + lc[1][t] * v2c[t + 16 + 48 * m] + lc[2][t] * v2c[t + 32 + 48 * m];
+    if (undamp)
+        for (int m = 0; m < 2; ++m)
+            for (int t = 0; t < 16; ++t) lap[16 * m + t] = lap[16 * m + t] + 2 * e[64 + t] * v[16 * m + t] * (rrearth * rrearth);
+}
+
+void bwko_vlaplace_sphere_wk(const double *elem, const double *v2c, double *v, const double *dvv, int nlev, int64_t nelem, int var_coef,
+                             int undamp)
+{
+    for (int64_t ie = 0; ie < nelem; ++ie)
+        for (int k = 0; k < nlev; ++k) {
+            double *slab = v + ((size_t)nlev * ie + k) * 32;
+            double in[32], out[32];
+            memcpy(in, slab, sizeof in);
+            vlaplace_cartesian_cpu(in, dvv, elem + (size_t)ED * ie, v2c + (size_t)96 * ie, var_coef, undamp, out);
+            memcpy(slab, out, sizeof out);
+        }
+}
+
+static void dp3d_sweep(const double *elem, const double *v2c, const double *rsph, double *dptens, double *ttens, double *vtens, const double *dvv,
+                       int nlev, int64_t nelem, int var_coef, int undamp)
+{
+    for (int64_t ie = 0; ie < nelem; ++ie) {
+        const double *e = elem + (size_t)ED * ie;
+        for (int k = 0; k < nlev; ++k) {
+            double *sl[2] = {ttens + ((size_t)nlev * ie + k) * 16, dptens + ((size_t)nlev * ie + k) * 16};
+            for (int f = 0; f < 2; ++f) {
+                double s[16], lap[16];
+                for (int t = 0; t < 16; ++t) s[t] = rsph ? rsph[(size_t)16 * ie + t] * sl[f][t] : sl[f][t];
+                laplace_sphere_wk_vc(s, dvv, e, var_coef, lap);
+                memcpy(sl[f], lap, sizeof lap);
+            }
+            double *vs = vtens + ((size_t)nlev * ie + k) * 32;
+            double in[32], out[32];
+            for (int m = 0; m < 2; ++m)
+                for (int t = 0; t < 16; ++t) in[16 * m + t] = rsph ? rsph[(size_t)16 * ie + t] * vs[16 * m + t] : vs[16 * m + t];
+            vlaplace_cartesian_cpu(in, dvv, e, v2c + (size_t)96 * ie, var_coef, undamp, out);
+            memcpy(vs, out, sizeof out);
+        }
+    }
+}
+
+void bwko_biharmonic_wk_dp3d(const bwko_dss_t *d, const double *elem, const double *v2c, const double *rsph, double *dptens, double *ttens,
+                             double *vtens, const double *dvv, int nlev, int var_coef1, int undamp)
+{
+    const int64_t nelem = d->nelem;
+    dp3d_sweep(elem, v2c, NULL, dptens, ttens, vtens, dvv, nlev, nelem, var_coef1, undamp);
+    dss_apply_impl(d, ttens, nlev, 1, 0);
+    dss_apply_impl(d, vtens, 2 * nlev, 1, 0);
+    dss_apply_impl(d, dptens, nlev, 1, 0);
+    dp3d_sweep(elem, v2c, rsph, dptens, ttens, vtens, dvv, nlev, nelem, 1, undamp);
+}

@@ -108,6 +108,15 @@ void bwko_advance_hypervis_scalar(const bwko_dss_t *, const double *elem, const 
 /* limiter2d_zero on nslabs (np x np) levels: negatives clipped, the level's sum preserved */
 void bwko_limiter2d_zero(double *q, int64_t nslabs);
 
+/* biharmonic_wk_dp3d / vlaplace_sphere_wk (Cartesian form) of upstream HOMME (NOT in the reference, parity unpinned; see
+ * bwk_oracle.c).  ttens, dptens (np,np,nlev,nelemd) hold T and dp3d on entry, vtens (np,np,2,nlev,nelemd) holds v; all are
+ * overwritten with the weak biharmonic.  v2c = vec_sphere2cart (np,np,3,2,nelemd). */
+void bwko_biharmonic_wk_dp3d(const bwko_dss_t *, const double *elem, const double *v2c, const double *rsph, double *dptens,
+                             double *ttens, double *vtens, const double *dvv, int nlev, int var_coef1, int undamp);
+/* one vlaplace_sphere_wk (Cartesian form) per (level, element), in place on v (np,np,2,nlev,nelemd) */
+void bwko_vlaplace_sphere_wk(const double *elem, const double *v2c, double *v, const double *dvv, int nlev, int64_t nelem,
+                             int var_coef, int undamp);
+
 #ifdef __cplusplus
 }
 #endif

@@ -46,6 +46,8 @@ def _load(name):
     L.bwko_omp_max_threads.restype = i32
     L.bwko_advance_hypervis_scalar.argtypes = [p, p, p, p, p, p, p, i32, i32, C.c_double, C.c_double, i32, i32]
     L.bwko_limiter2d_zero.argtypes = [p, i64]
+    L.bwko_biharmonic_wk_dp3d.argtypes = [p, p, p, p, p, p, p, p, i32, i32, i32]
+    L.bwko_vlaplace_sphere_wk.argtypes = [p, p, p, p, i32, i64, i32, i32]
     return L
 
 
@@ -170,6 +172,21 @@ class Dss:
         lib().bwko_advance_hypervis_scalar(self._h, _p(elem), _p(rsph), _p(qdp), _p(dp), _p(dpdiss), _p(dvv), nlev, qsize,
                                            float(dt2), float(nu_q), int(subcycles), 1 if limiter else 0)
         return qdp
+
+    def biharmonic_wk_dp3d(self, elem, v2c, rsph, dptens, ttens, vtens, dvv, var_coef1=True, undamp=True):
+        """upstream HOMME biharmonic_wk_dp3d with the Cartesian vlaplace_sphere_wk (parity unpinned, see bwk_oracle.c);
+        dptens, ttens (4,4,nlev,nelem) and vtens (4,4,2,nlev,nelem) Fortran order, updated in place"""
+        nlev = ttens.shape[2]
+        assert vtens.shape == (4, 4, 2, nlev, self.nelem) and dptens.shape == ttens.shape == (4, 4, nlev, self.nelem)
+        lib().bwko_biharmonic_wk_dp3d(self._h, _p(elem), _p(v2c), _p(rsph), _p(dptens), _p(ttens), _p(vtens), _p(dvv), nlev,
+                                      1 if var_coef1 else 0, 1 if undamp else 0)
+        return dptens, ttens, vtens
+
+
+def vlaplace_sphere_wk(elem, v2c, v, dvv, var_coef=True, undamp=True):
+    """one Cartesian-form vlaplace_sphere_wk per (level, element), in place on v (4,4,2,nlev,nelem)"""
+    lib().bwko_vlaplace_sphere_wk(_p(elem), _p(v2c), _p(v), _p(dvv), v.shape[3], v.shape[4], 1 if var_coef else 0, 1 if undamp else 0)
+    return v
 
 
 def limiter2d_zero(q):
