@@ -1271,39 +1271,48 @@ cudaError_t launch_laplace_plain(double *qtens, const double *metric, int elem_f
 //   v       : vlaplace_sphere_wk in the Cartesian form -- three Cartesian components through vec_sphere2cart(np,np,3,2),
 //             laplace_sphere_wk on each, back with the transpose, + 2 spheremp v rrearth^2 (rigid rotation is not damped)
 // PRODUCE: src -> dst, scaled by rspheremp (what the DSS strip sweep expects); otherwise in place and unscaled.
-// Every thread moves whole 128-byte lines: its four slabs come in by cp.async (512 bytes per thread in flight before any
-// arithmetic starts), results leave by 128-bit stores; the Cartesian components live in shared memory around the three
-// Laplacians, which keeps the kernel at ~120 registers.  Not TMA-tiled.
+// Slabs move between global and shared memory warp-cooperatively (coalesced, cp.async on the way in); the Cartesian
+// components live in shared memory around the three Laplacians, which keeps the kernel at ~128 registers.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
-// shared memory: element constants [192 doubles], then five 128-byte slots per thread, slot r / 16-byte chunk c of thread tid
-// at ((r * 8 + c) * blockDim.x + tid) * 16 bytes (conflict-free).  Slots 0..3 receive T, dp3d, v(1), v(2) by cp.async -- all
-// 512 bytes of a thread in flight at once --; the Cartesian components take slots 0, 1 (free once the scalars are done) and 4.
+// shared memory: element constants [192 doubles], then five 128-byte slots per level; 16-byte chunk c of slot r of the level
+// owned by thread o sits at double2 index (r * 8 + c) * cs + o, cs = slots + 4: the owner's accesses are conflict-free, and
+// so are the warp-cooperative copies below (chunk stride = 64 bytes mod 128).  A warp's 32 levels are contiguous in
+// global memory in each of the three regions (T, v, dp3d), so the warp copies them in and out with fully coalesced 16-byte
+// accesses (cp.async in, all 2 KB of a warp in flight before any arithmetic); slots 0..3 hold T, dp3d, v(1), v(2), the
+// Cartesian components take slots 0, 1 (free once the scalars are stored) and 4.
 template <bool PRODUCE>
 __global__ void __launch_bounds__(128) dp3d_laplace_kernel(const double *src, double *dst, const double *__restrict__ metric,
                                                            const double *__restrict__ v2c, const double *__restrict__ elem,
                                                            const double *__restrict__ rsph, const int32_t *__restrict__ list, int elem_first, int nlev,
-                                                           int undamp)
+                                                           int nslot, int undamp)
 {
     extern __shared__ __align__(16) double dp3d_s[];
     const int le = list ? list[blockIdx.x] : elem_first + (int)blockIdx.x;
-    const int nt = blockDim.x, tid = threadIdx.x;
-    const int k = (int)blockIdx.y * nt + tid; // one level per thread (a loop over levels makes the compiler hoist all 128 element constants into registers)
+    const int nt = blockDim.x, tid = threadIdx.x, lane = tid & 31, wbase = tid & ~31;
+    const int kw = (int)blockIdx.y * nt + wbase;                 // first level of this warp
+    const int nw = nlev - kw < 32 ? (nlev - kw > 0 ? nlev - kw : 0) : 32; // levels this warp owns (one per lane)
+    const int cs = nslot + 4;
     double2 *slots = reinterpret_cast<double2 *>(dp3d_s + 192);
-    const size_t base = (size_t)le * 4 * nlev;
-    const size_t slab_t = (base + k) * 16, slab_dp = (base + 3 * (size_t)nlev + k) * 16, slab_v = (base + nlev + 2 * (size_t)k) * 16;
-    if (k < nlev) {
-        const uint32_t s0 = smem_u32(slots + tid);
+    const size_t ebase = (size_t)le * 4 * nlev * 16;
+    const size_t off_t = ebase + (size_t)kw * 16, off_dp = ebase + ((size_t)3 * nlev + kw) * 16, off_v = ebase + ((size_t)nlev + 2 * (size_t)kw) * 16;
+    if (nw > 0) {
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            cp_async16(s0 + (uint32_t)((0 * 8 + c) * nt) * 16u, src + slab_t + 2 * c);
-            cp_async16(s0 + (uint32_t)((1 * 8 + c) * nt) * 16u, src + slab_dp + 2 * c);
-            cp_async16(s0 + (uint32_t)((2 * 8 + c) * nt) * 16u, src + slab_v + 2 * c);
-            cp_async16(s0 + (uint32_t)((3 * 8 + c) * nt) * 16u, src + slab_v + 16 + 2 * c);
+        for (int i = 0; i < 8; ++i) {
+            const int g = i * 32 + lane;
+            if (g < nw * 8) {
+                cp_async16(smem_u32(slots + (0 * 8 + (g & 7)) * cs + wbase + (g >> 3)), src + off_t + 2 * g);
+                cp_async16(smem_u32(slots + (1 * 8 + (g & 7)) * cs + wbase + (g >> 3)), src + off_dp + 2 * g);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int g = i * 32 + lane; // chunk of the warp's 2 nw contiguous v slabs: slab g/8 = component + 2 * level
+            if (g < nw * 16) cp_async16(smem_u32(slots + ((2 + ((g >> 3) & 1)) * 8 + (g & 7)) * cs + wbase + (g >> 4)), src + off_v + 2 * g);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
@@ -1314,81 +1323,101 @@ __global__ void __launch_bounds__(128) dp3d_laplace_kernel(const double *src, do
                   : t < 176 ? rsph[(size_t)le * 16 + (t - 160)]
                             : elem[(size_t)le * ELEM_DOUBLES + 64 + (t - 176)];
     __syncthreads();
-    if (k >= nlev) return;
+    if (nw == 0) return; // the whole warp
     asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    const bool active = lane < nw;
     const SmemMetric M{dp3d_s};
     const double *E = dp3d_s + 64, *rs = dp3d_s + 160, *sp = dp3d_s + 176;
-    auto slot = [&](int r, int c) -> double2 & { return slots[(r * 8 + c) * nt + tid]; };
+    auto slot = [&](int r, int c) -> double2 & { return slots[(r * 8 + c) * cs + tid]; };
+    if (active) {
 #pragma unroll 1
-    for (int f = 0; f < 2; ++f) {
-        asm volatile("" ::: "memory"); // keeps the loop-invariant metric reads inside the loop (hoisted, they cost 128 registers)
-        double s[16];
+        for (int f = 0; f < 2; ++f) {
+            asm volatile("" ::: "memory"); // keeps the loop-invariant metric reads inside the loop (hoisted, they cost 128 registers)
+            double s[16];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            const double2 t = slot(f, c);
-            s[2 * c] = t.x;
-            s[2 * c + 1] = t.y;
-        }
-        laplace_slab(s, M);
-        if (PRODUCE) {
-#pragma unroll
-            for (int t = 0; t < 16; ++t) s[t] *= rs[t];
-        }
-        double2 *out = reinterpret_cast<double2 *>(dst + (f ? slab_dp : slab_t));
-#pragma unroll
-        for (int c = 0; c < 8; ++c) out[c] = make_double2(s[2 * c], s[2 * c + 1]);
-    }
-    // vector: lat-lon -> three Cartesian components (slots 0, 1, 4), the Laplacian of each in place, then back
-#pragma unroll 2
-    for (int h = 0; h < 8; ++h) {
-        const double2 u = slot(2, h), v = slot(3, h);
-#pragma unroll
-        for (int c = 0; c < 3; ++c)
-            slot(c < 2 ? c : 4, h) = make_double2(fma(E[2 * h + 16 * c + 48], v.x, E[2 * h + 16 * c] * u.x),
-                                                  fma(E[2 * h + 1 + 16 * c + 48], v.y, E[2 * h + 1 + 16 * c] * u.y));
-    }
-#pragma unroll 1
-    for (int c = 0; c < 3; ++c) {
-        asm volatile("" ::: "memory");
-        const int r = c < 2 ? c : 4;
-        double s[16];
-#pragma unroll
-        for (int h = 0; h < 8; ++h) {
-            const double2 t = slot(r, h);
-            s[2 * h] = t.x;
-            s[2 * h + 1] = t.y;
-        }
-        laplace_slab(s, M);
-#pragma unroll
-        for (int h = 0; h < 8; ++h) slot(r, h) = make_double2(s[2 * h], s[2 * h + 1]);
-    }
-    const double und = undamp ? 2.0 * (BWK_RREARTH * BWK_RREARTH) : 0.0;
-    double2 *vout = reinterpret_cast<double2 *>(dst + slab_v);
-#pragma unroll 2
-    for (int h = 0; h < 8; ++h) {
-        const double2 uu = slot(2, h), vv = slot(3, h);
-        const double2 l0 = slot(0, h), l1 = slot(1, h), l2 = slot(4, h);
-        double o[4]; // u(2h), u(2h+1), v(2h), v(2h+1)
-#pragma unroll
-        for (int x = 0; x < 2; ++x) {
-            const int t = 2 * h + x;
-            const double w = und * sp[t];
-            double ou = w * (x ? uu.y : uu.x), ov = w * (x ? vv.y : vv.x);
-            const double l[3] = {x ? l0.y : l0.x, x ? l1.y : l1.x, x ? l2.y : l2.x};
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                ou = fma(l[c], E[t + 16 * c], ou);
-                ov = fma(l[c], E[t + 16 * c + 48], ov);
+            for (int c = 0; c < 8; ++c) {
+                const double2 t = slot(f, c);
+                s[2 * c] = t.x;
+                s[2 * c + 1] = t.y;
             }
+            laplace_slab(s, M);
             if (PRODUCE) {
-                ou *= rs[t];
-                ov *= rs[t];
+#pragma unroll
+                for (int t = 0; t < 16; ++t) s[t] *= rs[t];
             }
-            o[x] = ou;
-            o[2 + x] = ov;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) slot(f, c) = make_double2(s[2 * c], s[2 * c + 1]);
         }
-        vout[h] = make_double2(o[0], o[1]);
-        vout[8 + h] = make_double2(o[2], o[3]);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int g = i * 32 + lane;
+        if (g < nw * 8) {
+            reinterpret_cast<double2 *>(dst + off_t)[g] = slots[(0 * 8 + (g & 7)) * cs + wbase + (g >> 3)];
+            reinterpret_cast<double2 *>(dst + off_dp)[g] = slots[(1 * 8 + (g & 7)) * cs + wbase + (g >> 3)];
+        }
+    }
+    __syncwarp(); // slots 0 and 1 are reused below
+    if (active) {
+        // vector: lat-lon -> three Cartesian components (slots 0, 1, 4), the Laplacian of each in place, then back
+#pragma unroll 2
+        for (int h = 0; h < 8; ++h) {
+            const double2 u = slot(2, h), v = slot(3, h);
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                slot(c < 2 ? c : 4, h) = make_double2(fma(E[2 * h + 16 * c + 48], v.x, E[2 * h + 16 * c] * u.x),
+                                                      fma(E[2 * h + 1 + 16 * c + 48], v.y, E[2 * h + 1 + 16 * c] * u.y));
+        }
+#pragma unroll 1
+        for (int c = 0; c < 3; ++c) {
+            asm volatile("" ::: "memory");
+            const int r = c < 2 ? c : 4;
+            double s[16];
+#pragma unroll
+            for (int h = 0; h < 8; ++h) {
+                const double2 t = slot(r, h);
+                s[2 * h] = t.x;
+                s[2 * h + 1] = t.y;
+            }
+            laplace_slab(s, M);
+#pragma unroll
+            for (int h = 0; h < 8; ++h) slot(r, h) = make_double2(s[2 * h], s[2 * h + 1]);
+        }
+        const double und = undamp ? 2.0 * (BWK_RREARTH * BWK_RREARTH) : 0.0;
+#pragma unroll 2
+        for (int h = 0; h < 8; ++h) {
+            const double2 uu = slot(2, h), vv = slot(3, h);
+            const double2 l0 = slot(0, h), l1 = slot(1, h), l2 = slot(4, h);
+            double o[4]; // u(2h), u(2h+1), v(2h), v(2h+1)
+#pragma unroll
+            for (int x = 0; x < 2; ++x) {
+                const int t = 2 * h + x;
+                const double w = und * sp[t];
+                double ou = w * (x ? uu.y : uu.x), ov = w * (x ? vv.y : vv.x);
+                const double l[3] = {x ? l0.y : l0.x, x ? l1.y : l1.x, x ? l2.y : l2.x};
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    ou = fma(l[c], E[t + 16 * c], ou);
+                    ov = fma(l[c], E[t + 16 * c + 48], ov);
+                }
+                if (PRODUCE) {
+                    ou *= rs[t];
+                    ov *= rs[t];
+                }
+                o[x] = ou;
+                o[2 + x] = ov;
+            }
+            slot(2, h) = make_double2(o[0], o[1]);
+            slot(3, h) = make_double2(o[2], o[3]);
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int g = i * 32 + lane;
+        if (g < nw * 16) reinterpret_cast<double2 *>(dst + off_v)[g] = slots[((2 + ((g >> 3) & 1)) * 8 + (g & 7)) * cs + wbase + (g >> 4)];
     }
 }
 
@@ -1397,20 +1426,21 @@ cudaError_t launch_dp3d_laplace(bool produce, const double *src, double *dst, co
 {
     if (elem_count <= 0) return cudaSuccess;
     const int threads = nlev >= 128 ? 128 : ((nlev + 31) / 32) * 32;
-    const size_t smem = ((size_t)80 * threads + 192) * sizeof(double);
+    const int nslot = nlev >= 128 ? 128 : ((nlev + 7) / 8) * 8; // slots only for the levels a block really has (72 -> 4 blocks per SM)
+    const size_t smem = (192 + (size_t)5 * 8 * (nslot + 4) * 2) * sizeof(double);
     const dim3 grid((unsigned)elem_count, (unsigned)((nlev + threads - 1) / threads));
     static bool attr_set = false;
     if (!attr_set) {
-        const int max_smem = (80 * 128 + 192) * (int)sizeof(double); // above the 48 KB default
+        const int max_smem = (192 + 5 * 8 * (128 + 4) * 2) * (int)sizeof(double); // above the 48 KB default
         cudaError_t e = cudaFuncSetAttribute(dp3d_laplace_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(dp3d_laplace_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
     if (produce)
-        dp3d_laplace_kernel<true><<<grid, threads, smem, st>>>(src, dst, metric, v2c, elem, rsph, list, elem_first, nlev, undamp);
+        dp3d_laplace_kernel<true><<<grid, threads, smem, st>>>(src, dst, metric, v2c, elem, rsph, list, elem_first, nlev, nslot, undamp);
     else
-        dp3d_laplace_kernel<false><<<grid, threads, smem, st>>>(src, dst, metric, v2c, elem, rsph, list, elem_first, nlev, undamp);
+        dp3d_laplace_kernel<false><<<grid, threads, smem, st>>>(src, dst, metric, v2c, elem, rsph, list, elem_first, nlev, nslot, undamp);
     return cudaGetLastError();
 }
 
