@@ -23,6 +23,11 @@ def hypervis_inputs(n, nlev):
     return dp, dpd, 1.0e24  # with the LCG metric the weak biharmonic is O(1e-25): the two terms of the update are comparable
 
 
+def dp3d_v2c(n):
+    """vec_sphere2cart stand-in (n, 96), the same on every rank and in the single-rank run of the test"""
+    return np.random.default_rng(78).random((n, 96))
+
+
 def main():
     mode, ne, nlev, qsize, outdir = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), sys.argv[5]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -56,6 +61,25 @@ def main():
         assert sums[0] == sums[1], sums
         np.save(os.path.join(outdir, f"big_bih_{rank}.npy"), np.stack([ku.download_elements(e, 1) for e in picks], axis=0))
         np.save(os.path.join(outdir, f"big_picks_{rank}.npy"), np.array([first + e for e in picks], dtype=np.int64))
+        dist.barrier()
+        ku.finalize()
+    elif mode == "dp3d":
+        # biharmonic_wk_dp3d across ranks (context with qsize = 4: T, v, dp3d per level); device-generated numbers as fields
+        import torch
+
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        ku = bwk.KernelUtils(count, nlev, 4).allocate_data(host_arrays=False)
+        idb = [bwk.KernelUtils.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(idb, src=0)
+        bwk.KernelUtils.comm_init(rank, world, idb[0])
+        ku.initialize_data_device(n, first)
+        ku.set_topology_cubed_sphere(ne, first)
+        ku.upload_vec_sphere2cart(np.ascontiguousarray(dp3d_v2c(n)[first : first + count]))
+        for rep in range(2):  # twice: the halo buffers are reused across steps
+            ku.initialize_data_device(n, first)
+            ku.run_biharmonic_dp3d_device(rep == 1, True)
+            ku.sync()
+        np.save(os.path.join(outdir, f"dp3d_{rank}.npy"), ku.download_elements(0, count))
         dist.barrier()
         ku.finalize()
     elif mode == "gpu":

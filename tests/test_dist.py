@@ -66,6 +66,32 @@ def test_multi_gpu_matches_single_gpu_bitwise(bwk, oracle, tmp_path, ne, nlev, q
     assert oracle.max_rel(np.asfortranarray(multi), ref) <= 1e-12
 
 
+@pytest.mark.gpu
+def test_dp3d_multi_gpu_matches_single_gpu_bitwise(bwk, tmp_path):
+    """biharmonic_wk_dp3d: N ranks == 1 rank bit for bit (the element-local sweeps run boundary elements first and the DSS
+    strip sweep reads the NCCL halo, as the scalar path does)"""
+    import torch
+
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
+        pytest.skip("needs at least 2 GPUs")
+    world = 2 if ngpu < 4 else 4
+    ne, nlev = 6, 40
+    n = 6 * ne * ne
+    _launch(world, ["dp3d", ne, nlev, 4, tmp_path], 29537)
+    multi = np.concatenate([np.load(tmp_path / f"dp3d_{r}.npy") for r in range(world)], axis=-1)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from mg_worker import dp3d_v2c
+
+    with bwk.KernelUtils(n, nlev, 4).allocate_data(host_arrays=False) as ku:
+        ku.initialize_data_device()
+        ku.set_topology_cubed_sphere(ne)
+        ku.upload_vec_sphere2cart(dp3d_v2c(n))
+        ku.run_biharmonic_dp3d_device(True, True)
+        single = ku.download_elements(0, n)
+    assert np.array_equal(multi, single)
+
+
 def _patch_oracle_full(oracle, ne, nlev, qsize, gd, e):
     """Full biharmonic of ONE element e of a big cubed sphere from the oracle's pieces: the CPU-order Laplacian
     (F90:109-200) of e and of every element sharing a node with it, the DSS sum over coincident points in ascending
