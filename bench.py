@@ -188,6 +188,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-hv", action="store_true", help="skip the advance_hypervis_scalar (caller, SURVEY 8(f)1) timing")
+    ap.add_argument("--no-dp3d", action="store_true", help="skip the biharmonic_wk_dp3d (SURVEY 8(f)3) timing")
     ap.add_argument("--variant", type=int, default=0)
     args = ap.parse_args()
 
@@ -401,6 +402,39 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args.cpu_ne, nlev, qsize, 3, want_serial=True)
 
+    # ---- biharmonic_wk_dp3d: T, v, dp3d of every level, its own context (qsize = 4), device resident
+    dp3d = None
+    if world == 1 and not args.no_dp3d:
+        ku.finalize()
+        try:
+            kd = bwk.KernelUtils(count, nlev, 4).allocate_data(host_arrays=False)
+            kd.initialize_data_device(nglob, first)
+            kd.set_topology_cubed_sphere(ne, first)
+            kd.get_rspheremp()
+            kd.upload_vec_sphere2cart(np.random.default_rng(1).random((count, 96)))
+            nd = max(3, min(args.steps, 5))
+            tot = 0.0
+            for i in range(1 + nd):
+                kd.initialize_data_device(nglob, first)
+                kd.sync()
+                l0 = kd.launch_count()
+                kd.event_record(0)
+                kd.run_biharmonic_dp3d_device(True, True)
+                kd.event_record(1)
+                kd.sync()
+                if i >= 1:
+                    tot += kd.event_elapsed_ms(0, 1)
+                    d_launches = kd.launch_count() - l0
+            d_ms = tot / nd
+            pts = 16.0 * nlev * 4 * count
+            dp3d = {"value": pts / (d_ms * 1e-3), "unit": "field-point updates/s (4 fields per level: T, v(1), v(2), dp3d)", "ms_per_step": d_ms,
+                    "bytes_per_update": 48, "GBps_of_its_traffic": 48.0 * pts / (d_ms * 1e-3) / 1e9, "launches_per_step": d_launches,
+                    "note": "laplace_sphere_wk(T, dp3d) + Cartesian vlaplace_sphere_wk(v) -> DSS -> *rspheremp -> the same operators again "
+                            "(3 launches: element-local sweep, DSS strip sweep, element-local sweep in place; a fused form would need 32 B/update)"}
+            kd.finalize()
+        except Exception as ex:
+            dp3d = {"value": None, "error": str(ex)[:200]}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -409,7 +443,7 @@ def main():
             "config": {"workload": f"ne{ne}np4 L{nlev} q{qsize}, {nglob} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
                        "partition": f"contiguous element blocks over {world} rank(s)", "l2": "working set >> L2 (no flush needed); inputs re-generated before every step",
                        "variant": args.variant},
-            "laplace_only": lap, "advance_hypervis_scalar": hv, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "laplace_only": lap, "advance_hypervis_scalar": hv, "biharmonic_wk_dp3d": dp3d, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     ku.finalize()

@@ -21,6 +21,7 @@ module biharmonic_wk_scalar_b200
   public :: biharmonic_wk_scalar
   public :: biharmonic_wk_scalar_cpusig
   public :: advance_hypervis_scalar
+  public :: biharmonic_wk_dp3d
   public :: b200_set_topology_gdof
   public :: b200_init
   public :: b200_finalize
@@ -63,6 +64,13 @@ module biharmonic_wk_scalar_b200
       integer(c_int), value :: subcycle_c, limiter_c
       integer(c_int) :: rc
     end function bwk_advance_hypervis_scalar
+    function bwk_biharmonic_wk_dp3d(elem_c, v2c_c, dptens_c, ttens_c, vtens_c, deriv_c, var_coef1_c, undamprrcart_c) &
+        bind(c, name="bwk_biharmonic_wk_dp3d") result(rc)
+      use iso_c_binding
+      type(c_ptr), value :: elem_c, v2c_c, dptens_c, ttens_c, vtens_c, deriv_c
+      integer(c_int), value :: var_coef1_c, undamprrcart_c
+      integer(c_int) :: rc
+    end function bwk_biharmonic_wk_dp3d
   end interface
 
 contains
@@ -108,6 +116,26 @@ contains
                                      merge(1_c_int, 0_c_int, limiter))
     if (rc /= 0) error stop "bwk_advance_hypervis_scalar failed"
   end subroutine advance_hypervis_scalar
+
+  !! Upstream HOMME biharmonic_wk_dp3d (viscosity_mod), kernel-extraction style: the state the upstream routine reads through
+  !! elem(ie)%state is passed in the output arrays (ttens = T, dptens = dp3d, vtens = v on entry, as qtens is the input
+  !! of biharmonic_wk_scalar), elem(ie)%vec_sphere2cart as a plain array.  Needs b200_init(nelemd, nlev, 4) and a topology.
+  !!   dptens, ttens (np,np,nlev,nelemd) ; vtens (np,np,2,nlev,nelemd) ; vec_sphere2cart (np,np,3,2,nelemd)
+  !!   var_coef1 = .false.: no tensorVisc in the first application (hypervis_scaling > 0 upstream)
+  subroutine biharmonic_wk_dp3d(elem,vec_sphere2cart,dptens,ttens,vtens,deriv,var_coef1,undamprrcart)
+    implicit none
+    type (element_t)     , intent(in   ), target :: elem(:)
+    real (kind=real_kind), intent(in   ), target :: vec_sphere2cart(np,np,3,2,nelemd)
+    real (kind=real_kind), intent(inout), target :: dptens(np,np,nlev,nelemd)
+    real (kind=real_kind), intent(inout), target :: ttens(np,np,nlev,nelemd)
+    real (kind=real_kind), intent(inout), target :: vtens(np,np,2,nlev,nelemd)
+    type (derivative_t)  , intent(in   ), target :: deriv
+    logical              , intent(in   )         :: var_coef1, undamprrcart
+    integer(c_int) :: rc
+    rc = bwk_biharmonic_wk_dp3d(c_loc(elem(1)), c_loc(vec_sphere2cart), c_loc(dptens), c_loc(ttens), c_loc(vtens), c_loc(deriv), &
+                                merge(1_c_int, 0_c_int, var_coef1), merge(1_c_int, 0_c_int, undamprrcart))
+    if (rc /= 0) error stop "bwk_biharmonic_wk_dp3d failed"
+  end subroutine biharmonic_wk_dp3d
 
   !! same dummy arguments as the push-loop variant, F90:525-531
   subroutine biharmonic_wk_scalar(elem,qtens,grads,deriv,nets,nete)

@@ -73,6 +73,7 @@ def test_fortran_wrapper_matches_reference_signature():
     assert subs["biharmonic_wk_scalar"]["args"] == ["elem", "qtens", "grads", "deriv", "nets", "nete"]
     assert subs["biharmonic_wk_scalar_cpusig"]["args"] == ["elem", "qtens", "deriv", "nets", "nete"]
     assert subs["advance_hypervis_scalar"]["args"] == ["elem", "qdp", "dp", "dpdiss", "deriv", "dt2", "nu_q", "hypervis_subcycle_q", "limiter"]
+    assert subs["biharmonic_wk_dp3d"]["args"] == ["elem", "vec_sphere2cart", "dptens", "ttens", "vtens", "deriv", "var_coef1", "undamprrcart"]
     text = open(path).read()
     for sym in re.findall(r'bind\(c,\s*name="(bwk_[a-z0-9_]+)"\)', text, flags=re.I):
         assert sym in open(os.path.join(ROOT, "include", "bwk_b200.h")).read(), sym
