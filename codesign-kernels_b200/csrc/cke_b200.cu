@@ -1,0 +1,318 @@
+// cke_b200.cu -- libcke_b200.so: the nested_loops mini-app's flux kernel for B200 (sm_100a) behind
+// the reference's own C interface (nested_loops/cke.hpp:7-23; include/cke_b200.h).
+//
+// Data layout in HBM (all copies of the caller's Fortran arrays, unchanged):
+//   tracerCur, cellMask          [nCells][nvldim]  doubles, level fastest
+//   normalThicknessFlux, advMaskHighOrder, highOrderFlx   [nEdges][nvldim]
+//   advCellsForEdge (1-based) / advCoefs / advCoefs3rd     [nEdges][nAdv]
+//
+// One launch computes every (level, edge) point of highOrderFlx.  A CTA owns EB consecutive
+// edges: phase A stages their (cell, coef1+coef3, coef1-coef3[, kmin, kmax]) records in shared
+// memory once; phase B streams the edge rows with 128-bit loads (two levels per thread when
+// nvldim is even) and gathers the tracer rows of the contributing cells through the read-only
+// path -- at the reference sizes tracerCur is 2.2 MB and lives in L2, so the compulsory DRAM
+// traffic is 24 B per point (two 8 B reads, one 8 B write) + 20 B per (edge, cell) record.
+//
+// Bit-exact against the CPU forms: the sum keeps the reference order (i = 1..nAdvCellsForEdge),
+// every product and sum is an explicit round-to-nearest operation (no FMA contraction), and
+// coef1 + coef3*csgn with csgn = +-1 is exactly coef1 +- coef3, so selecting one of two staged
+// sums changes no bit.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "cke_b200.h"
+#include "cke_kernels.cuh"
+
+namespace {
+
+using namespace cke_dev;
+
+struct Ctx {
+    bool live = false;
+    Problem p{};
+    cudaStream_t stream = nullptr;
+    int sm_count = 0;
+    int edges_per_cta = 0;
+    size_t smem = 0;
+    long long launches = 0;
+};
+
+Ctx g;
+char g_err[512];
+bool g_failed = false;
+bool g_abort = true;
+
+void fail(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    g_failed = true;
+    fprintf(stderr, "libcke_b200: %s\n", g_err);
+    if (g_abort) abort();
+}
+
+#define CK(call)                                                                      \
+    do {                                                                              \
+        cudaError_t e_ = (call);                                                      \
+        if (e_ != cudaSuccess) {                                                      \
+            fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return;                                                                   \
+        }                                                                             \
+    } while (0)
+#define CKI(call)                                                                     \
+    do {                                                                              \
+        cudaError_t e_ = (call);                                                      \
+        if (e_ != cudaSuccess) {                                                      \
+            fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return 1;                                                                 \
+        }                                                                             \
+    } while (0)
+
+template <typename T> bool upload(T **dst, const T *src, size_t n) {
+    if (cudaMalloc((void **)dst, (n ? n : 1) * sizeof(T)) != cudaSuccess) {
+        fail("cudaMalloc of %zu bytes failed: %s", n * sizeof(T), cudaGetErrorString(cudaGetLastError()));
+        return false;
+    }
+    if (n && cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) {
+        fail("host-to-device copy of %zu bytes failed: %s", n * sizeof(T), cudaGetErrorString(cudaGetLastError()));
+        return false;
+    }
+    return true;
+}
+
+void release() {
+    Problem &p = g.p;
+    void *ptrs[] = {p.nAdvCellsForEdge, p.minLevelCell,     p.maxLevelCell, p.advCellsForEdge, p.tracerCur,   p.cellMask,
+                    p.normalThicknessFlux, p.advMaskHighOrder, p.advCoefs,     p.advCoefs3rd,     p.highOrderFlx};
+    for (void *q : ptrs)
+        if (q) cudaFree(q);
+    if (g.stream) cudaStreamDestroy(g.stream);
+    g = Ctx{};
+}
+
+bool select_device() {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        fail("no CUDA device (%s); this library has no CPU path", e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        return false;
+    }
+    int dev = 0;
+    if (const char *lr = getenv("LOCAL_RANK")) {
+        dev = atoi(lr) % ndev;
+        if (cudaSetDevice(dev) != cudaSuccess) {
+            fail("cudaSetDevice(%d) failed", dev);
+            return false;
+        }
+    } else if (cudaGetDevice(&dev) != cudaSuccess) {
+        fail("cudaGetDevice failed");
+        return false;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+        fail("cudaGetDeviceProperties failed");
+        return false;
+    }
+    if (prop.major != 10) {
+        fail("device %d is sm_%d%d; this library is built for sm_100a (B200) only", dev, prop.major, prop.minor);
+        return false;
+    }
+    g.sm_count = prop.multiProcessorCount;
+    return true;
+}
+
+// one iteration of implementation `impl` on the library stream; false on a launch error
+bool launch_iteration(int impl) {
+    const Problem &p = g.p;
+    if (p.nEdges == 0) return true;
+    const int nblocks = (p.nEdges + g.edges_per_cta - 1) / g.edges_per_cta;
+    const int grid = nblocks < g.sm_count * kCtasPerSm ? nblocks : g.sm_count * kCtasPerSm;
+    const bool vec2 = (p.nvldim % 2) == 0;
+    if (impl == 1) {
+        const size_t n = (size_t)p.nCells * p.nvldim;
+        if (n) {
+            const size_t want = (n + kThreads - 1) / kThreads;
+            const int mg = (int)(want < (size_t)g.sm_count * kCtasPerSm ? want : (size_t)g.sm_count * kCtasPerSm);
+            mask_tracer_kernel<<<mg, kThreads, 0, g.stream>>>(p.tracerCur, p.cellMask, n);
+            ++g.launches;
+        }
+        if (vec2) flux_kernel<2, false><<<grid, kThreads, g.smem, g.stream>>>(p, g.edges_per_cta);
+        else flux_kernel<1, false><<<grid, kThreads, g.smem, g.stream>>>(p, g.edges_per_cta);
+    } else {
+        if (vec2) flux_kernel<2, true><<<grid, kThreads, g.smem, g.stream>>>(p, g.edges_per_cta);
+        else flux_kernel<1, true><<<grid, kThreads, g.smem, g.stream>>>(p, g.edges_per_cta);
+    }
+    ++g.launches;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fail("kernel launch failed: %s", cudaGetErrorString(e));
+        return false;
+    }
+    return true;
+}
+
+void run(int impl) {
+    if (!g.live) {
+        fail("cke_impl%d_run called before a successful cke_init", impl);
+        return;
+    }
+    for (int it = 0; it < g.p.nIters; ++it)
+        if (!launch_iteration(impl)) return;
+    CK(cudaStreamSynchronize(g.stream));  // Kokkos::fence(), cke_impl1.cpp:36
+}
+
+}  // namespace
+
+extern "C" {
+
+void cke_b200_set_abort_on_error(int on) { g_abort = on != 0; }
+const char *cke_b200_last_error(void) { return g_failed ? g_err : nullptr; }
+long long cke_b200_launch_count(void) { return g.launches; }
+
+void kokkos_init(void) {
+    g_failed = false;
+    if (!select_device()) return;
+    CK(cudaFree(0));
+}
+
+void kokkos_finalize(void) {}
+
+void cke_init(const Int nIters, const Int nEdges, const Int nCells, const Int nVertLevels, const Int nvldim,
+              const Int nAdv, const Int *nAdvCellsForEdge, const Int *minLevelCell, const Int *maxLevelCell,
+              const Int *advCellsForEdge, Real *tracerCur, const Real *normalThicknessFlux,
+              const Real *advMaskHighOrder, const Real *cellMask, const Real *advCoefs, const Real *advCoefs3rd,
+              const Real coef3rdOrder, Real *highOrderFlx) {
+    (void)highOrderFlx;
+    g_failed = false;
+    if (g.live) release();
+    if (nIters < 0 || nEdges < 0 || nCells < 0 || nVertLevels < 0 || nvldim < nVertLevels || nAdv < 0) {
+        fail("cke_init: bad sizes nIters=%d nEdges=%d nCells=%d nVertLevels=%d nvldim=%d nAdv=%d", nIters, nEdges,
+             nCells, nVertLevels, nvldim, nAdv);
+        return;
+    }
+    if (!select_device()) return;
+    // range checks the device code relies on (the reference trusts its caller; an out-of-range
+    // cell would be a wild read there too)
+    for (long long t = 0; t < (long long)nEdges; ++t) {
+        const int n = nAdvCellsForEdge[t] < nAdv ? nAdvCellsForEdge[t] : nAdv;
+        for (int i = 0; i < n; ++i) {
+            const int c = advCellsForEdge[t * nAdv + i];
+            if (c < 1 || c > nCells) {
+                fail("cke_init: advCellsForEdge(%d,%lld) = %d is outside 1..%d", i + 1, t + 1, c, nCells);
+                return;
+            }
+        }
+    }
+    for (int c = 0; c < nCells; ++c)
+        if (minLevelCell[c] < 1 || maxLevelCell[c] > nvldim) {
+            fail("cke_init: level range %d..%d of cell %d is outside 1..%d", minLevelCell[c], maxLevelCell[c], c + 1, nvldim);
+            return;
+        }
+    Problem &p = g.p;
+    p.nIters = nIters; p.nEdges = nEdges; p.nCells = nCells; p.nVertLevels = nVertLevels;
+    p.nvldim = nvldim; p.nAdv = nAdv; p.coef3rdOrder = coef3rdOrder;
+    // edges per CTA: as many as keep the staged records within 40 KB of shared memory
+    int eb = kMaxEdgesPerCta;
+    while (eb > 1 && (size_t)eb * nAdv * sizeof(Rec) + eb * sizeof(int) > 40 * 1024) eb >>= 1;
+    g.edges_per_cta = eb;
+    g.smem = (size_t)eb * nAdv * sizeof(Rec) + eb * sizeof(int);
+    if (g.smem > 40 * 1024) {
+        fail("cke_init: nAdv = %d needs %zu bytes of shared memory per edge (limit 40 KB)", nAdv, g.smem);
+        release();
+        return;
+    }
+    const size_t ncl = (size_t)nCells * nvldim, ned = (size_t)nEdges * nvldim, nad = (size_t)nEdges * nAdv;
+    bool ok = upload(&p.nAdvCellsForEdge, nAdvCellsForEdge, (size_t)nEdges) &&
+              upload(&p.minLevelCell, minLevelCell, (size_t)nCells) && upload(&p.maxLevelCell, maxLevelCell, (size_t)nCells) &&
+              upload(&p.advCellsForEdge, advCellsForEdge, nad) && upload(&p.tracerCur, (const double *)tracerCur, ncl) &&
+              upload(&p.cellMask, cellMask, ncl) && upload(&p.normalThicknessFlux, normalThicknessFlux, ned) &&
+              upload(&p.advMaskHighOrder, advMaskHighOrder, ned) && upload(&p.advCoefs, advCoefs, nad) &&
+              upload(&p.advCoefs3rd, advCoefs3rd, nad);
+    if (ok && cudaMalloc((void **)&p.highOrderFlx, (ned ? ned : 1) * sizeof(double)) != cudaSuccess) {
+        fail("cudaMalloc of highOrderFlx failed: %s", cudaGetErrorString(cudaGetLastError()));
+        ok = false;
+    }
+    if (ok && cudaMemset(p.highOrderFlx, 0, (ned ? ned : 1) * sizeof(double)) != cudaSuccess) {
+        fail("cudaMemset of highOrderFlx failed");
+        ok = false;
+    }
+    if (ok && cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking) != cudaSuccess) {
+        fail("cudaStreamCreate failed");
+        ok = false;
+    }
+    if (!ok) {
+        release();
+        return;
+    }
+    // the uploads and the memset ran on the legacy default stream; the library stream is non-blocking
+    if (cudaDeviceSynchronize() != cudaSuccess) {
+        fail("cudaDeviceSynchronize after the uploads failed");
+        release();
+        return;
+    }
+    g.launches = 0;
+    g.live = true;
+}
+
+void cke_impl1_run(void) { run(1); }
+void cke_impl2_run(void) { run(2); }
+
+void cke_get_results(const Int, const Int, Real *highOrderFlx) {
+    if (!g.live) {
+        fail("cke_get_results called before a successful cke_init");
+        return;
+    }
+    const size_t bytes = (size_t)g.p.nEdges * g.p.nvldim * sizeof(double);
+    if (!bytes) return;
+    CK(cudaMemcpyAsync(highOrderFlx, g.p.highOrderFlx, bytes, cudaMemcpyDeviceToHost, g.stream));
+    CK(cudaMemsetAsync(g.p.highOrderFlx, 0, bytes, g.stream));  // deep_copy(d->highOrderFlx, 0), cke.cpp:159
+    CK(cudaStreamSynchronize(g.stream));
+}
+
+void cke_cleanup(void) {
+    if (g.live) release();
+}
+
+int cke_b200_time_ms(int impl, int iters, double *ms_per_iter) {
+    if (!g.live) {
+        fail("cke_b200_time_ms called before a successful cke_init");
+        return 1;
+    }
+    if ((impl != 1 && impl != 2) || iters < 1 || !ms_per_iter) {
+        fail("cke_b200_time_ms: impl must be 1 or 2, iters >= 1");
+        return 1;
+    }
+    cudaEvent_t a, b;
+    CKI(cudaEventCreate(&a));
+    CKI(cudaEventCreate(&b));
+    CKI(cudaEventRecord(a, g.stream));
+    for (int it = 0; it < iters; ++it)
+        if (!launch_iteration(impl)) return 1;
+    CKI(cudaEventRecord(b, g.stream));
+    CKI(cudaEventSynchronize(b));
+    float ms = 0.f;
+    CKI(cudaEventElapsedTime(&ms, a, b));
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    *ms_per_iter = (double)ms / iters;
+    return 0;
+}
+
+int cke_b200_get_tracer(Real *tracerCur) {
+    if (!g.live) {
+        fail("cke_b200_get_tracer called before a successful cke_init");
+        return 1;
+    }
+    const size_t bytes = (size_t)g.p.nCells * g.p.nvldim * sizeof(double);
+    if (!bytes) return 0;
+    CKI(cudaStreamSynchronize(g.stream));
+    CKI(cudaMemcpy(tracerCur, g.p.tracerCur, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,336 @@
+"""nested_loops mini-app: the MPAS-Ocean high-order flux loop behind the reference's
+own C interface (nested_loops/cke.hpp:7-23).
+
+PARITY UNPINNED: the reference holds no outputs for this kernel (inputs come from the compiler's
+random_number).  What it holds is its acceptance test -- every loop form within errTol = 1e-10 of
+the original CPU form (nested_vars.F90:33, nested.F90:267-279) -- reproduced here for the oracle's
+forms, for the host emulation of the device source, and (GPU) for the CUDA path, which is also
+required to be BIT-IDENTICAL to the oracle's cke_impl1 / cke_impl2 restatements.
+
+This file sorts last on purpose: the -m gpu tests here are the newest in the suite.
+"""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+@pytest.fixture(scope="module")
+def nested(bwk):
+    from codesign_kernels_b200 import nested as m
+
+    return m
+
+
+@pytest.fixture(scope="module")
+def cko():
+    import cke_oracle_py
+
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, stdout=subprocess.DEVNULL)
+    return cke_oracle_py
+
+
+def numpy_reference(prob):
+    """Independent restatement of nested.F90:119-157 (vectorised over edges and levels, loop over
+    the contributing cells in order) -- same operation order per point, so bitwise comparable."""
+    nv, ne = prob.nvldim, prob.nEdges
+    ntf = prob.normalThicknessFlux
+    wgt = ntf * prob.advMaskHighOrder
+    sgn = np.copysign(1.0, ntf)
+    out = np.zeros((nv, ne), order="F")
+    lev = np.arange(1, nv + 1)[:, None]
+    for i in range(prob.nAdv):
+        use = i < prob.nAdvCellsForEdge
+        c = np.where(use, prob.advCellsForEdge[i], 1) - 1
+        coef1 = prob.advCoefs[i][None, :]
+        coef3 = (prob.advCoefs3rd[i] * prob.coef3rdOrder)[None, :]
+        inside = (lev >= prob.minLevelCell[c][None, :]) & (lev <= prob.maxLevelCell[c][None, :]) & use[None, :]
+        inside &= lev <= prob.nVertLevels
+        term = (prob.tracerCur[:, c] * wgt) * (coef1 + coef3 * sgn)
+        out = np.where(inside, out + term, out)
+    return out
+
+
+CASES = {
+    # name: (nEdges, nCells, nVertLevels, nAdv, packn)
+    "namelist_shape_small": (640, 70, 100, 10, 1),
+    "gpu_target_pack8": (300, 40, 100, 10, 8),  # Makefile:110 F90_PACK_SIZE=8 -> nvldim 104
+    "odd_levels_scalar_path": (257, 33, 37, 7, 1),  # nvldim odd -> the one-level-per-thread kernels
+    "single_edge_single_cell": (1, 1, 5, 3, 1),
+    "no_contributing_cells": (19, 4, 12, 0, 1),
+}
+
+
+def make(nested, name, ragged=False, seed=3):
+    ne, nc, nl, na, pk = CASES[name]
+    prob = nested.NestedProblem(nEdges=ne, nCells=nc, nVertLevels=nl, nAdv=na, nIters=1, packn=pk, seed=seed)
+    if ragged and na:
+        rng = np.random.default_rng(seed + 100)
+        prob.nAdvCellsForEdge = rng.integers(0, na + 1, size=ne).astype(np.int32)
+        prob.minLevelCell = rng.integers(1, 4, size=nc).astype(np.int32)  # ice-shelf case, nested.F90:62
+        lev = np.arange(1, prob.nvldim + 1)[:, None]
+        active = (lev >= prob.minLevelCell[None, :]) & (lev <= prob.maxLevelCell[None, :])
+        prob.tracerCur = np.asfortranarray(np.where(active, prob.tracerCur, 0.0))
+        prob.cellMask = np.asfortranarray(active.astype(np.float64))
+        prob.advMaskHighOrder[: prob.nVertLevels] = rng.integers(0, 2, size=(prob.nVertLevels, ne)).astype(np.float64)
+        prob.normalThicknessFlux[3 % prob.nVertLevels, :: 5] = 0.0  # sign(1, 0) = +1
+    return prob
+
+
+# ------------------------------------------------------------------------------------------ CPU
+
+
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("ragged", [False, True])
+def test_oracle_forms_agree_like_the_reference_check(nested, cko, name, ragged):
+    prob = make(nested, name, ragged)
+    ref = cko.original_cpu(prob)
+    assert np.array_equal(ref, numpy_reference(prob)), "C restatement differs from the numpy restatement"
+    for label, flx in (
+        ("gpu_optimized", cko.gpu_optimized(prob)),
+        ("impl1", cko.impl1(prob)[0]),
+        ("impl2", cko.impl2(prob)),
+    ):
+        bad, worst = cko.check(flx, ref, prob, nested.ERR_TOL)
+        assert bad == 0, (label, bad, worst)
+        # with 0/1 masks and tracers that vanish outside the level range the forms are equal bit for bit
+        assert np.array_equal(flx[: prob.nVertLevels], ref[: prob.nVertLevels]), label
+
+
+def test_oracle_known_answer_by_hand(nested, cko):
+    """Two cells, one edge, three levels, worked by hand from nested.F90:130-155."""
+    prob = nested.NestedProblem(nEdges=1, nCells=2, nVertLevels=3, nAdv=2, nIters=1, seed=0)
+    prob.minLevelCell[:] = [1, 2]
+    prob.maxLevelCell[:] = [3, 2]
+    prob.tracerCur = np.asfortranarray(np.array([[1.0, 0.0], [2.0, 5.0], [4.0, 0.0]]))
+    prob.cellMask = np.asfortranarray((prob.tracerCur != 0).astype(np.float64))
+    prob.advCellsForEdge = np.asfortranarray(np.array([[1], [2]], dtype=np.int32))
+    prob.advCoefs = np.asfortranarray(np.array([[0.5], [0.25]]))
+    prob.advCoefs3rd = np.asfortranarray(np.array([[1.0], [2.0]]))
+    prob.coef3rdOrder = 2.0
+    prob.normalThicknessFlux = np.asfortranarray(np.array([[3.0], [-2.0], [1.0]]))
+    prob.advMaskHighOrder = np.asfortranarray(np.array([[1.0], [1.0], [0.0]]))
+    # level 1: 1*3*(0.5+2)            = 7.5
+    # level 2: 2*(-2)*(0.5-2) + 5*(-2)*(0.25-4) = 6 + 37.5 = 43.5
+    # level 3: mask 0                 = 0
+    want = np.array([[7.5], [43.5], [0.0]])
+    assert np.array_equal(cko.original_cpu(prob), want)
+    assert np.array_equal(cko.impl1(prob)[0], want)
+    assert np.array_equal(cko.impl2(prob), want)
+
+
+def test_coef3rdorder_is_the_float32_literal(nested):
+    # nested_vars.F90:32 assigns the default-real literal 2.14 to a double
+    p = nested.NestedProblem(nEdges=1, nCells=1, nVertLevels=3, nAdv=1)
+    assert p.coef3rdOrder == 2.1400001049041748 and p.coef3rdOrder != 2.14
+
+
+def test_generator_follows_the_reference_recipe(nested):
+    p = nested.NestedProblem(nEdges=500, nCells=400, nVertLevels=100, nAdv=10, packn=8, seed=1)
+    assert p.nvldim == 104 and p.nvlpk == 13  # nested_vars.F90:107-108
+    assert p.minLevelCell.min() == 1 and p.maxLevelCell.min() >= 3 and p.maxLevelCell.max() == 100
+    assert 0.35 < np.mean(p.maxLevelCell == 100) < 0.65  # "a good fraction (half?) at the max depth"
+    assert p.advCellsForEdge.min() >= 1 and p.advCellsForEdge.max() <= 400
+    assert np.all((p.tracerCur != 0) <= (p.cellMask == 1)) and p.tracerCur.max() < 15.0
+    assert np.all(p.tracerCur[100:] == 0) and np.all(p.normalThicknessFlux[100:] == 0)
+    assert np.abs(p.normalThicknessFlux).max() <= 7.5 and np.all(p.advMaskHighOrder[:100] == 1)
+
+
+def test_library_exports_every_declared_symbol(nested):
+    L = nested.lib()
+    names = nested.declared_symbols()
+    assert {"kokkos_init", "kokkos_finalize", "cke_init", "cke_get_results", "cke_cleanup", "cke_impl1_run",
+            "cke_impl2_run"} <= set(names)
+    for n in names:
+        assert hasattr(L, n), n
+
+
+def test_header_repeats_the_reference_interface(nested):
+    """Argument lists of include/cke_b200.h == nested_loops/cke.hpp:7-23 (only where the reference
+    tree is present: this container, never the GPU box)."""
+    ref = "/root/reference/nested_loops/cke.hpp"
+    if not os.path.exists(ref):
+        pytest.skip("reference tree not present")
+
+    def protos(text):
+        text = re.sub(r"/\*.*?\*/|//[^\n]*", "", text, flags=re.S)
+        out = {}
+        for m in re.finditer(r"void\s+((?:cke|kokkos)_\w+)\s*\(([^)]*)\)\s*;", text):
+            args = [re.sub(r"\s+", " ", a).strip() for a in m.group(2).split(",")]
+            args = [re.sub(r"\s*\*\s*", "* ", a).strip() for a in args if a not in ("", "void")]
+            out[m.group(1)] = args
+        return out
+
+    mine = protos(open(os.path.join(ROOT, "include", "cke_b200.h")).read())
+    theirs = protos(open(ref).read())
+    assert len(theirs) == 7
+    for name, args in theirs.items():
+        assert mine.get(name) == args, (name, mine.get(name), args)
+
+
+def test_no_cpu_fallback_without_a_device(nested):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    prob = make(nested, "single_edge_single_cell")
+    nl = nested.NestedLoops()
+    with pytest.raises(nested.CkeError, match="no CUDA device|no CPU path|sm_"):
+        nl.cke_init(prob)
+    with pytest.raises(nested.CkeError, match="before a successful cke_init"):
+        nl.cke_impl1_run()
+
+
+@pytest.fixture(scope="module")
+def emul():
+    drv = os.path.join(ROOT, "tests", "driver")
+    subprocess.run(["make", "-C", drv, "libcke_emul.so"], check=True, stdout=subprocess.DEVNULL)
+    L = C.CDLL(os.path.join(drv, "libcke_emul.so"))
+    i32, p = C.c_int, C.c_void_p
+    L.cke_emul_iteration.argtypes = [i32] * 9 + [p] * 10 + [C.c_double, p]
+    L.cke_emul_iteration.restype = i32
+
+    def run(prob, impl, grid, block, edges_per_cta, tracer=None):
+        f = lambda x, dt: np.asfortranarray(x, dtype=dt)  # noqa: E731
+        tr = np.array(prob.tracerCur if tracer is None else tracer, dtype=np.float64, order="F", copy=True)
+        out = np.full((prob.nvldim, prob.nEdges), np.nan, order="F")
+        keep = [f(prob.nAdvCellsForEdge, np.int32), f(prob.minLevelCell, np.int32), f(prob.maxLevelCell, np.int32),
+                f(prob.advCellsForEdge, np.int32), tr, f(prob.normalThicknessFlux, np.float64),
+                f(prob.advMaskHighOrder, np.float64), f(prob.cellMask, np.float64), f(prob.advCoefs, np.float64),
+                f(prob.advCoefs3rd, np.float64)]
+        rc = L.cke_emul_iteration(impl, grid, block, edges_per_cta, prob.nEdges, prob.nCells, prob.nVertLevels,
+                                  prob.nvldim, prob.nAdv, *[k.ctypes.data for k in keep], prob.coef3rdOrder,
+                                  out.ctypes.data)
+        assert rc == 0
+        return out, tr
+
+    return run
+
+
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("ragged", [False, True])
+@pytest.mark.parametrize("geom", [(3, 32, 8), (5, 64, 4), (1, 16, 1)])
+def test_device_source_emulated_on_host_is_bit_identical_to_the_oracle(nested, cko, emul, name, ragged, geom):
+    """The kernel source of libcke_b200.so (cke_kernels.cuh), compiled for the host with threads and
+    a barrier standing in for a CTA, against the oracle: grid-stride over edge blocks, staging,
+    the two-levels-per-thread and scalar paths, ragged nAdvCellsForEdge, level ranges."""
+    grid, block, epc = geom
+    prob = make(nested, name, ragged)
+    if prob.nEdges > 300:
+        prob.nEdges = 300  # keep the thread emulation quick: the first 300 edges of the same arrays
+        for a in ("nAdvCellsForEdge",):
+            setattr(prob, a, getattr(prob, a)[:300].copy())
+        for a in ("advCellsForEdge", "advCoefs", "advCoefs3rd", "normalThicknessFlux", "advMaskHighOrder", "highOrderFlx"):
+            setattr(prob, a, np.asfortranarray(getattr(prob, a)[:, :300]))
+    want1, want_tr = cko.impl1(prob)
+    got1, got_tr = emul(prob, 1, grid, block, epc)
+    assert np.array_equal(got1, want1)
+    assert np.array_equal(got_tr, want_tr)
+    got2, _ = emul(prob, 2, grid, block, epc)
+    assert np.array_equal(got2, cko.impl2(prob))
+    bad, worst = cko.check(got1, cko.original_cpu(prob), prob, nested.ERR_TOL)
+    assert bad == 0, worst
+
+
+def test_emulated_device_source_with_general_masks(nested, cko, emul):
+    """Masks that are not 0/1 and tracers that do not vanish outside the level range: the forms
+    then differ from each other, and the device source must still follow ITS form bit for bit
+    (impl1 masks in place every iteration, impl2 honours the level range)."""
+    prob = make(nested, "odd_levels_scalar_path", ragged=True)
+    rng = np.random.default_rng(9)
+    prob.cellMask = np.asfortranarray(rng.random(prob.cellMask.shape))
+    prob.tracerCur = np.asfortranarray(15.0 * rng.random(prob.tracerCur.shape))
+    w1, tr1 = cko.impl1(prob)
+    g1, gtr1 = emul(prob, 1, 4, 32, 8)
+    assert np.array_equal(g1, w1) and np.array_equal(gtr1, tr1)
+    w1b, tr2 = cko.impl1(prob, tracer=tr1)  # second iteration: mask applied twice
+    g1b, gtr2 = emul(prob, 1, 4, 32, 8, tracer=gtr1)
+    assert np.array_equal(g1b, w1b) and np.array_equal(gtr2, tr2) and not np.array_equal(w1b, w1)
+    g2, _ = emul(prob, 2, 4, 32, 8)
+    assert np.array_equal(g2, cko.impl2(prob))
+
+
+# ------------------------------------------------------------------------------------------ GPU
+
+
+def _run_gpu(nested, prob, impl, iters=1):
+    nl = nested.NestedLoops()
+    nl.kokkos_init()
+    nl.cke_init(prob, nIters=iters)
+    try:
+        (nl.cke_impl1_run if impl == 1 else nl.cke_impl2_run)()
+        launches = nl.launch_count()
+        out = nl.cke_get_results(np.full((prob.nvldim, prob.nEdges), np.nan, order="F"))
+        tracer = nl.get_tracer()
+        again = nl.cke_get_results(np.full((prob.nvldim, prob.nEdges), np.nan, order="F"))
+    finally:
+        nl.cke_cleanup()
+        nl.kokkos_finalize()
+    return out, tracer, again, launches
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("ragged", [False, True])
+def test_gpu_bit_identical_to_the_oracle(nested, cko, name, ragged):
+    prob = make(nested, name, ragged)
+    ref = cko.original_cpu(prob)
+    want1, want_tr = cko.impl1(prob)
+    out, tracer, again, launches = _run_gpu(nested, prob, 1)
+    assert launches == (2 if prob.nEdges else 0)
+    assert np.array_equal(out, want1)
+    assert np.array_equal(tracer, want_tr)
+    assert np.all(again == 0.0)  # cke_get_results zeroes the device copy, cke.cpp:159
+    bad, worst = cko.check(out, ref, prob, nested.ERR_TOL)  # the reference's own test, nested.F90:417-431
+    assert bad == 0, worst
+    out2, _, _, launches2 = _run_gpu(nested, prob, 2)
+    assert launches2 == 1
+    assert np.array_equal(out2, cko.impl2(prob))
+    bad, worst = cko.check(out2, ref, prob, nested.ERR_TOL)
+    assert bad == 0, worst
+
+
+@pytest.mark.gpu
+def test_gpu_namelist_problem_many_iterations(nested, cko):
+    """nested.nml:2-6 as shipped (25,600 edges, 2,800 cells, 100 levels, nAdv 10), at the GPU
+    target's padding (F90_PACK_SIZE=8, Makefile:110), nIters iterations inside one run call."""
+    prob = nested.NestedProblem(packn=8, seed=11)
+    ref = cko.original_cpu(prob)
+    want1, want_tr = cko.impl1(prob)
+    out, tracer, _, launches = _run_gpu(nested, prob, 1, iters=7)
+    assert launches == 14
+    assert np.array_equal(out, want1) and np.array_equal(tracer, want_tr)  # 0/1 masks: iterations are idempotent
+    bad, worst = cko.check(out, ref, prob, nested.ERR_TOL)
+    assert bad == 0, worst
+    out2, _, _, _ = _run_gpu(nested, prob, 2, iters=3)
+    assert np.array_equal(out2, cko.impl2(prob))
+
+
+@pytest.mark.gpu
+def test_gpu_general_masks_follow_each_form(nested, cko):
+    prob = make(nested, "gpu_target_pack8", ragged=True)
+    rng = np.random.default_rng(5)
+    prob.cellMask = np.asfortranarray(rng.random(prob.cellMask.shape))
+    prob.tracerCur = np.asfortranarray(15.0 * rng.random(prob.tracerCur.shape))
+    w, tr = cko.impl1(prob)
+    w, tr = cko.impl1(prob, tracer=tr)  # two iterations: the mask is applied twice
+    out, tracer, _, _ = _run_gpu(nested, prob, 1, iters=2)
+    assert np.array_equal(out, w) and np.array_equal(tracer, tr)
+    out2, _, _, _ = _run_gpu(nested, prob, 2)
+    assert np.array_equal(out2, cko.impl2(prob))
+
+
+@pytest.mark.gpu
+def test_gpu_rejects_bad_connectivity(nested):
+    prob = make(nested, "single_edge_single_cell")
+    prob.advCellsForEdge[0, 0] = 7
+    nl = nested.NestedLoops()
+    with pytest.raises(nested.CkeError, match="outside 1.."):
+        nl.cke_init(prob)
