@@ -17,7 +17,7 @@ struct Problem {
 };
 
 constexpr int kThreads = 256;
-constexpr int kMaxEdgesPerCta = 8;
+constexpr int kMaxEdgesPerCta = 16;
 constexpr int kCtasPerSm = 8;  // 256 threads x 8 = 2048 resident threads per SM
 
 // per (edge, contributing cell) record staged in shared memory
@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(kThreads) mask_tracer_kernel(double *__restric
 
 // RANGE = false: pass 2 of cke_impl1.cpp:18-36 (collapsed (edge, level) loop, nested.F90:332-349)
 // RANGE = true : cke_impl2.cpp:27-68 at pack size 1 (per-cell level range, tracer*cellMask)
-template <int VEC, bool RANGE>
+template <int VEC, bool RANGE, int U>
 __global__ void __launch_bounds__(kThreads) flux_kernel(const Problem p, const int edges_per_cta) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Rec *rec = reinterpret_cast<Rec *>(smem_raw);                  // [edges_per_cta][nAdv]
@@ -107,24 +107,45 @@ __global__ void __launch_bounds__(kThreads) flux_kernel(const Problem p, const i
             }
             const Rec *er = rec + (size_t)el * p.nAdv;
             const int n = nadv[el];
-            for (int i = 0; i < n; ++i) {
-                const Rec r = er[i];
-                const size_t trow = (size_t)r.cell * p.nvldim + (size_t)kg * VEC;
-                typename V::T tr = V::ldg(p.tracerCur + trow);
-                if (RANGE) {
-                    const typename V::T cm = V::ldg(p.cellMask + trow);
+            // U gathers in flight per thread: the records and tracer rows of a batch are all loaded
+            // before the first is consumed (the sum itself stays in the reference order i = 1..n)
+            for (int i0 = 0; i0 < n; i0 += U) {
+                typename V::T tr[U];
 #pragma unroll
-                    for (int s = 0; s < VEC; ++s) V::set(tr, s, __dmul_rn(V::get(tr, s), V::get(cm, s)));
+                for (int u = 0; u < U; ++u) {
+                    const Rec *ru = er + min(i0 + u, n - 1);  // a clamped duplicate is loaded and ignored
+                    const size_t trow = (size_t)ru->cell * p.nvldim + (size_t)kg * VEC;
+                    if (RANGE) {
+                        // rows of cells whose level range misses this group are not fetched at all
+                        const int k0 = (int)kg * VEC;
+                        if (k0 + VEC - 1 >= ru->kmin && k0 <= ru->kmax) {
+                            tr[u] = V::ldg(p.tracerCur + trow);
+                            const typename V::T cm = V::ldg(p.cellMask + trow);
+#pragma unroll
+                            for (int s = 0; s < VEC; ++s) V::set(tr[u], s, __dmul_rn(V::get(tr[u], s), V::get(cm, s)));
+                        } else {
+#pragma unroll
+                            for (int s = 0; s < VEC; ++s) V::set(tr[u], s, 0.0);
+                        }
+                    } else {
+                        tr[u] = V::ldg(p.tracerCur + trow);
+                    }
                 }
 #pragma unroll
-                for (int s = 0; s < VEC; ++s) {
-                    const double sel = neg[s] ? r.cm : r.cp;
-                    const double term = __dmul_rn(__dmul_rn(V::get(tr, s), coef2[s]), sel);
-                    if (RANGE) {
-                        const int k = (int)kg * VEC + s;
-                        if (k >= r.kmin && k <= r.kmax) acc[s] = __dadd_rn(acc[s], term);
-                    } else {
-                        acc[s] = __dadd_rn(acc[s], term);
+                for (int u = 0; u < U; ++u) {
+                    if (i0 + u < n) {
+                        const Rec r = er[i0 + u];  // re-read from shared memory: cheaper than U records in registers
+#pragma unroll
+                        for (int s = 0; s < VEC; ++s) {
+                            const double sel = neg[s] ? r.cm : r.cp;
+                            const double term = __dmul_rn(__dmul_rn(V::get(tr[u], s), coef2[s]), sel);
+                            if (RANGE) {
+                                const int k = (int)kg * VEC + s;
+                                if (k >= r.kmin && k <= r.kmax) acc[s] = __dadd_rn(acc[s], term);
+                            } else {
+                                acc[s] = __dadd_rn(acc[s], term);
+                            }
+                        }
                     }
                 }
             }

@@ -59,6 +59,7 @@ def lib():
     L.cke_b200_last_error.argtypes, L.cke_b200_last_error.restype = [], C.c_char_p
     L.cke_b200_launch_count.argtypes, L.cke_b200_launch_count.restype = [], C.c_longlong
     L.cke_b200_time_ms.argtypes, L.cke_b200_time_ms.restype = [i32, i32, C.POINTER(f64)], i32
+    L.cke_b200_time_cold_ms.argtypes, L.cke_b200_time_cold_ms.restype = [i32, i32, C.POINTER(f64)], i32
     L.cke_b200_get_tracer.argtypes, L.cke_b200_get_tracer.restype = [p], i32
     # Python callers get exceptions instead of the reference's abort-on-assert
     L.cke_b200_set_abort_on_error(0)
@@ -184,6 +185,12 @@ class NestedLoops:
         ms = C.c_double(0.0)
         if self.L.cke_b200_time_ms(impl, iters, C.byref(ms)):
             _check(self.L, "cke_b200_time_ms")
+        return ms.value
+
+    def time_cold_ms(self, impl, reps):
+        ms = C.c_double(0.0)
+        if self.L.cke_b200_time_cold_ms(impl, reps, C.byref(ms)):
+            _check(self.L, "cke_b200_time_cold_ms")
         return ms.value
 
     def launch_count(self):

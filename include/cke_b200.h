@@ -70,6 +70,9 @@ long long cke_b200_launch_count(void);
 /* Runs `iters` iterations of implementation `impl` (1 or 2) on the library stream between two
  * CUDA events and returns the mean milliseconds per iteration in *ms_per_iter; 0 on success. */
 int cke_b200_time_ms(int impl, int iters, double *ms_per_iter);
+/* Same, one iteration at a time with the L2 flushed before each (a 256 MB memset on the same
+ * stream); returns the median of `reps` single-iteration times in *median_ms; 0 on success. */
+int cke_b200_time_cold_ms(int impl, int reps, double *median_ms);
 /* Copies the device tracerCur(nvldim,nCells) back (implementation 1 masks it in place). */
 int cke_b200_get_tracer(Real *tracerCur);
 

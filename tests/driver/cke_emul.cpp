@@ -62,13 +62,13 @@ template <typename F> static void launch(unsigned grid, unsigned block, F kernel
 
 // One iteration of implementation `impl` exactly as cke_b200.cu's launch_iteration issues it,
 // on host pointers.  tracerCur is masked in place by impl 1.  Returns 0, or 1 on bad arguments.
-extern "C" int cke_emul_iteration(int impl, int grid, int block, int edges_per_cta, int nEdges, int nCells,
+extern "C" int cke_emul_iteration(int unroll, int impl, int grid, int block, int edges_per_cta, int nEdges, int nCells,
                                   int nVertLevels, int nvldim, int nAdv, const int *nAdvCellsForEdge,
                                   const int *minLevelCell, const int *maxLevelCell, const int *advCellsForEdge,
                                   double *tracerCur, const double *normalThicknessFlux, const double *advMaskHighOrder,
                                   const double *cellMask, const double *advCoefs, const double *advCoefs3rd,
                                   double coef3rdOrder, double *highOrderFlx) {
-    if ((impl != 1 && impl != 2) || grid < 1 || block < edges_per_cta || edges_per_cta < 1) return 1;
+    if ((unroll != 1 && unroll != 5 && unroll != 10) || (impl != 1 && impl != 2) || grid < 1 || block < edges_per_cta || edges_per_cta < 1) return 1;
     if ((size_t)edges_per_cta * nAdv * sizeof(Rec) + edges_per_cta * sizeof(int) > sizeof smem_raw) return 1;
     Problem p;
     p.nIters = 1; p.nEdges = nEdges; p.nCells = nCells; p.nVertLevels = nVertLevels; p.nvldim = nvldim; p.nAdv = nAdv;
@@ -88,11 +88,14 @@ extern "C" int cke_emul_iteration(int impl, int grid, int block, int edges_per_c
     if (impl == 1) {
         const size_t n = (size_t)nCells * nvldim;
         launch((unsigned)grid, (unsigned)block, [=] { mask_tracer_kernel(p.tracerCur, p.cellMask, n); });
-        if (vec2) launch((unsigned)grid, (unsigned)block, [=] { flux_kernel<2, false>(p, edges_per_cta); });
-        else launch((unsigned)grid, (unsigned)block, [=] { flux_kernel<1, false>(p, edges_per_cta); });
-    } else {
-        if (vec2) launch((unsigned)grid, (unsigned)block, [=] { flux_kernel<2, true>(p, edges_per_cta); });
-        else launch((unsigned)grid, (unsigned)block, [=] { flux_kernel<1, true>(p, edges_per_cta); });
     }
+#define EMUL_CASE(V_, R_, U_)                                                                              \
+    if (vec2 == (V_ == 2) && (impl == 2) == R_ && unroll == U_)                                            \
+        launch((unsigned)grid, (unsigned)block, [=] { flux_kernel<V_, R_, U_>(p, edges_per_cta); });
+    EMUL_CASE(1, false, 1) EMUL_CASE(1, false, 5) EMUL_CASE(1, false, 10)
+    EMUL_CASE(2, false, 1) EMUL_CASE(2, false, 5) EMUL_CASE(2, false, 10)
+    EMUL_CASE(1, true, 1) EMUL_CASE(1, true, 5) EMUL_CASE(1, true, 10)
+    EMUL_CASE(2, true, 1) EMUL_CASE(2, true, 5) EMUL_CASE(2, true, 10)
+#undef EMUL_CASE
     return 0;
 }

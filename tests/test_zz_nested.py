@@ -194,10 +194,10 @@ def emul():
     subprocess.run(["make", "-C", drv, "libcke_emul.so"], check=True, stdout=subprocess.DEVNULL)
     L = C.CDLL(os.path.join(drv, "libcke_emul.so"))
     i32, p = C.c_int, C.c_void_p
-    L.cke_emul_iteration.argtypes = [i32] * 9 + [p] * 10 + [C.c_double, p]
+    L.cke_emul_iteration.argtypes = [i32] * 10 + [p] * 10 + [C.c_double, p]
     L.cke_emul_iteration.restype = i32
 
-    def run(prob, impl, grid, block, edges_per_cta, tracer=None):
+    def run(prob, impl, grid, block, edges_per_cta, tracer=None, unroll=5):
         f = lambda x, dt: np.asfortranarray(x, dtype=dt)  # noqa: E731
         tr = np.array(prob.tracerCur if tracer is None else tracer, dtype=np.float64, order="F", copy=True)
         out = np.full((prob.nvldim, prob.nEdges), np.nan, order="F")
@@ -205,7 +205,7 @@ def emul():
                 f(prob.advCellsForEdge, np.int32), tr, f(prob.normalThicknessFlux, np.float64),
                 f(prob.advMaskHighOrder, np.float64), f(prob.cellMask, np.float64), f(prob.advCoefs, np.float64),
                 f(prob.advCoefs3rd, np.float64)]
-        rc = L.cke_emul_iteration(impl, grid, block, edges_per_cta, prob.nEdges, prob.nCells, prob.nVertLevels,
+        rc = L.cke_emul_iteration(unroll, impl, grid, block, edges_per_cta, prob.nEdges, prob.nCells, prob.nVertLevels,
                                   prob.nvldim, prob.nAdv, *[k.ctypes.data for k in keep], prob.coef3rdOrder,
                                   out.ctypes.data)
         assert rc == 0
@@ -216,12 +216,12 @@ def emul():
 
 @pytest.mark.parametrize("name", list(CASES))
 @pytest.mark.parametrize("ragged", [False, True])
-@pytest.mark.parametrize("geom", [(3, 32, 8), (5, 64, 4), (1, 16, 1)])
+@pytest.mark.parametrize("geom", [(3, 32, 8, 5), (5, 64, 4, 1), (1, 16, 1, 10), (2, 256, 14, 5)])
 def test_device_source_emulated_on_host_is_bit_identical_to_the_oracle(nested, cko, emul, name, ragged, geom):
     """The kernel source of libcke_b200.so (cke_kernels.cuh), compiled for the host with threads and
     a barrier standing in for a CTA, against the oracle: grid-stride over edge blocks, staging,
     the two-levels-per-thread and scalar paths, ragged nAdvCellsForEdge, level ranges."""
-    grid, block, epc = geom
+    grid, block, epc, unroll = geom
     prob = make(nested, name, ragged)
     if prob.nEdges > 300:
         prob.nEdges = 300  # keep the thread emulation quick: the first 300 edges of the same arrays
@@ -230,10 +230,10 @@ def test_device_source_emulated_on_host_is_bit_identical_to_the_oracle(nested, c
         for a in ("advCellsForEdge", "advCoefs", "advCoefs3rd", "normalThicknessFlux", "advMaskHighOrder", "highOrderFlx"):
             setattr(prob, a, np.asfortranarray(getattr(prob, a)[:, :300]))
     want1, want_tr = cko.impl1(prob)
-    got1, got_tr = emul(prob, 1, grid, block, epc)
+    got1, got_tr = emul(prob, 1, grid, block, epc, unroll=unroll)
     assert np.array_equal(got1, want1)
     assert np.array_equal(got_tr, want_tr)
-    got2, _ = emul(prob, 2, grid, block, epc)
+    got2, _ = emul(prob, 2, grid, block, epc, unroll=unroll)
     assert np.array_equal(got2, cko.impl2(prob))
     bad, worst = cko.check(got1, cko.original_cpu(prob), prob, nested.ERR_TOL)
     assert bad == 0, worst
