@@ -1,0 +1,199 @@
+// libmpdata_b200.so -- host side of the MMF MPDATA tracer step (include/mpdata_b200.h).
+// sm_100a only, no CPU fallback: every entry point fails without a B200-class device.
+// Compiled with -fmad=false (see mpdata_kernels.cuh: the result is bit-identical to the CPU order).
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "../../include/mpdata_b200.h"
+#include "mpdata_kernels.cuh"
+
+namespace {
+
+struct State {
+    bool ready = false, uploaded = false;
+    int ns = 0, nx = 0, nz = 0;
+    size_t nf = 0, nu = 0, nw = 0, n2m = 0, n2 = 0;  // element counts of the arrays
+    double *f = nullptr, *f0 = nullptr, *u = nullptr, *w = nullptr, *rho = nullptr, *rhow = nullptr, *adz = nullptr,
+           *flux = nullptr, *flush = nullptr;
+    size_t flush_bytes = 0;
+    cudaStream_t stream = nullptr;
+    int block = 1024, grid = 0, sms = 0;
+    size_t smem = 0;
+} g;
+
+char g_err[512];
+bool g_failed = false;
+long long g_launches = 0;
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    g_failed = true;
+    return code;
+}
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) return fail(4, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+int release() {
+    double **ptrs[] = {&g.f, &g.f0, &g.u, &g.w, &g.rho, &g.rhow, &g.adz, &g.flux, &g.flush};
+    for (double **p : ptrs) {
+        if (*p) cudaFree(*p);
+        *p = nullptr;
+    }
+    if (g.stream) cudaStreamDestroy(g.stream);
+    g.stream = nullptr;
+    g.ready = g.uploaded = false;
+    return 0;
+}
+
+int launch_step() {
+    mpd_dev::Problem p{g.ns, g.nx, g.nz, g.f, g.u, g.w, g.rho, g.rhow, g.adz, g.flux};
+    mpd_dev::advect_kernel<<<g.grid, g.block, g.smem, g.stream>>>(p);
+    ++g_launches;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *mpdata_last_error(void) { return g_failed ? g_err : nullptr; }
+long long mpdata_launch_count(void) { return g_launches; }
+long long mpdata_slice_smem_bytes(int nx, int nz) {
+    if (nx < 1 || nz < 3) return -1;
+    return (long long)(mpd_dev::slice_doubles(nx, nz) * sizeof(double));
+}
+
+int mpdata_set_block(int threads) {
+    if (threads < 32 || threads > 1024 || threads % 32) return fail(2, "mpdata_set_block: %d is not a multiple of 32 in 32..1024", threads);
+    g.block = threads;
+    return 0;
+}
+
+int mpdata_init(int nslices, int nx, int nz) {
+    g_failed = false;
+    if (nslices < 1 || nx < 1 || nz < 3) return fail(2, "mpdata_init: bad sizes nslices=%d nx=%d nz=%d (need >=1, >=1, >=3)", nslices, nx, nz);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+        return fail(1, "mpdata_init: no CUDA device (this library has no CPU fallback)");
+    int dev = 0;
+    if (const char *lr = getenv("LOCAL_RANK")) dev = atoi(lr) % ndev;
+    CU(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10) return fail(1, "mpdata_init: device %d is sm_%d%d, this library is built for sm_100a only", dev, prop.major, prop.minor);
+    const size_t smem = mpd_dev::slice_doubles(nx, nz) * sizeof(double);
+    if (smem > (size_t)prop.sharedMemPerBlockOptin)
+        return fail(3, "mpdata_init: one slice needs %zu B of shared memory (nx=%d nz=%d), the SM has %zu", smem, nx, nz,
+                    (size_t)prop.sharedMemPerBlockOptin);
+    release();
+    g.ns = nslices; g.nx = nx; g.nz = nz;
+    const size_t nzm = nz - 1;
+    g.nf = (size_t)nslices * (nx + 6) * nzm;
+    g.nu = (size_t)nslices * (nx + 5) * nzm;
+    g.nw = (size_t)nslices * (nx + 4) * nz;
+    g.n2m = (size_t)nslices * nzm;
+    g.n2 = (size_t)nslices * nz;
+    g.smem = smem;
+    g.sms = prop.multiProcessorCount;
+    // one CTA per slice; beyond (resident CTAs per SM x SMs) slices a CTA walks several
+    const int per_sm = (int)(prop.sharedMemPerMultiprocessor / (smem + 1024)) > 0 ? (int)(prop.sharedMemPerMultiprocessor / (smem + 1024)) : 1;
+    const long long resident = (long long)per_sm * g.sms;
+    g.grid = (int)(nslices < resident ? nslices : resident);
+    CU(cudaFuncSetAttribute(mpd_dev::advect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    CU(cudaMalloc(&g.f, g.nf * 8));
+    CU(cudaMalloc(&g.f0, g.nf * 8));
+    CU(cudaMalloc(&g.u, g.nu * 8));
+    CU(cudaMalloc(&g.w, g.nw * 8));
+    CU(cudaMalloc(&g.rho, g.n2m * 8));
+    CU(cudaMalloc(&g.rhow, g.n2 * 8));
+    CU(cudaMalloc(&g.adz, g.n2m * 8));
+    CU(cudaMalloc(&g.flux, g.n2 * 8));
+    CU(cudaMemsetAsync(g.flux, 0, g.n2 * 8, g.stream));
+    g.ready = true;
+    return 0;
+}
+
+int mpdata_upload(const double *f, const double *u, const double *w, const double *rho, const double *rhow,
+                  const double *adz, const double *flux) {
+    if (!g.ready) return fail(5, "mpdata_upload before mpdata_init");
+    if (!f || !u || !w || !rho || !rhow || !adz) return fail(2, "mpdata_upload: null array");
+    CU(cudaMemcpyAsync(g.f, f, g.nf * 8, cudaMemcpyHostToDevice, g.stream));
+    CU(cudaMemcpyAsync(g.u, u, g.nu * 8, cudaMemcpyHostToDevice, g.stream));
+    CU(cudaMemcpyAsync(g.w, w, g.nw * 8, cudaMemcpyHostToDevice, g.stream));
+    CU(cudaMemcpyAsync(g.rho, rho, g.n2m * 8, cudaMemcpyHostToDevice, g.stream));
+    CU(cudaMemcpyAsync(g.rhow, rhow, g.n2 * 8, cudaMemcpyHostToDevice, g.stream));
+    CU(cudaMemcpyAsync(g.adz, adz, g.n2m * 8, cudaMemcpyHostToDevice, g.stream));
+    if (flux) CU(cudaMemcpyAsync(g.flux, flux, g.n2 * 8, cudaMemcpyHostToDevice, g.stream));
+    CU(cudaMemcpyAsync(g.f0, g.f, g.nf * 8, cudaMemcpyDeviceToDevice, g.stream));
+    g.uploaded = true;
+    return 0;
+}
+
+int mpdata_run(void) {
+    if (!g.ready || !g.uploaded) return fail(5, "mpdata_run before mpdata_init/mpdata_upload");
+    return launch_step();
+}
+
+int mpdata_download(double *f, double *flux) {
+    if (!g.ready || !g.uploaded) return fail(5, "mpdata_download before mpdata_init/mpdata_upload");
+    if (f) CU(cudaMemcpyAsync(f, g.f, g.nf * 8, cudaMemcpyDeviceToHost, g.stream));
+    if (flux) CU(cudaMemcpyAsync(flux, g.flux, g.n2m * 8, cudaMemcpyDeviceToHost, g.stream));  // levels 1..nzm only
+    CU(cudaStreamSynchronize(g.stream));
+    return 0;
+}
+
+int mpdata_finalize(void) { return release(); }
+
+int mpdata_advect_scalar2D(int nslices, int nx, int nz, double *f, const double *u, const double *w, const double *rho,
+                           const double *rhow, const double *adz, double *flux) {
+    if (!f || !flux) return fail(2, "mpdata_advect_scalar2D: null array");
+    if (!g.ready || g.ns != nslices || g.nx != nx || g.nz != nz) {
+        if (int rc = mpdata_init(nslices, nx, nz)) return rc;
+    }
+    if (int rc = mpdata_upload(f, u, w, rho, rhow, adz, nullptr)) return rc;
+    if (int rc = launch_step()) return rc;
+    return mpdata_download(f, flux);
+}
+
+int mpdata_time_steps(int iters, int flush_l2, float *ms_per_step) {
+    if (!g.ready || !g.uploaded) return fail(5, "mpdata_time_steps before mpdata_init/mpdata_upload");
+    if (iters < 1 || !ms_per_step) return fail(2, "mpdata_time_steps: bad arguments");
+    if (flush_l2 && !g.flush) {
+        g.flush_bytes = (size_t)256 << 20;  // > the 126 MB L2
+        CU(cudaMalloc(&g.flush, g.flush_bytes));
+    }
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    double total = 0.0;
+    for (int it = 0; it < iters; ++it) {
+        CU(cudaMemcpyAsync(g.f, g.f0, g.nf * 8, cudaMemcpyDeviceToDevice, g.stream));
+        if (flush_l2) CU(cudaMemsetAsync(g.flush, it & 0xff, g.flush_bytes, g.stream));
+        CU(cudaEventRecord(a, g.stream));
+        if (int rc = launch_step()) return rc;
+        CU(cudaEventRecord(b, g.stream));
+        CU(cudaEventSynchronize(b));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, a, b));
+        total += ms;
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    *ms_per_step = (float)(total / iters);
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,72 @@
+"""GPU-box script (run under gpurun): timing of the MPDATA tracer step (libmpdata_b200.so) at the
+reference sizes and at production-like slice counts, with the CPU port timed beside it.
+
+    python profiles/prof_mpdata.py [--slices 48,1184,18944] [--flush] > gpurun_out/mpdata_prof.json
+
+Prints one JSON object: per slice count the mean kernel time (CUDA events on the library stream),
+point-updates/s, algorithmic GB/s against the measured HBM peak, the GPU-vs-oracle check (bitwise),
+and at the reference sizes the oracle timed on the host cores (serial, as the reference runs it, and
+OpenMP over blocks of slices).  The oracle is used here only as checker and CPU baseline.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--slices", default="48,1184,18944")
+    ap.add_argument("--iters", type=int, default=50)
+    ap.add_argument("--flush", action="store_true")
+    ap.add_argument("--block", type=int, default=1024)
+    args = ap.parse_args()
+    import __graft_entry__ as ge
+
+    ge.build()
+    from codesign_kernels_b200 import mpdata
+    import mpdata_oracle_py as mpo
+
+    peak = 6553.6
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
+    out = {"hbm_peak_GBs": peak, "block": args.block, "flush_l2": args.flush, "runs": []}
+    nx, nz = mpdata.NX, mpdata.NZ
+    for ns in [int(s) for s in args.slices.split(",")]:
+        P = mpdata.TestAdvect(ns, nx, nz).init(seed=100)
+        f, fl = P.f.copy(order="F"), P.flux.copy(order="F")
+        t0 = time.perf_counter()
+        mpo.advect_scalar2D_cpu(ns, nx, nz, f, P.u, P.w, P.rho, P.rhow, P.adz, fl, omp_block=8)
+        cpu_omp = time.perf_counter() - t0
+        ms = mpdata.time_steps(P, iters=args.iters, flush_l2=args.flush, block=args.block)
+        fo, flo = np.empty_like(P.f), P.flux.copy(order="F")
+        assert mpdata.lib().mpdata_download(fo.ctypes.data, flo.ctypes.data) == 0
+        pts = ns * nx * (nz - 1)
+        b = mpdata.algorithmic_bytes(ns, nx, nz)
+        run = {"nslices": ns, "nx": nx, "nz": nz, "points": pts, "algorithmic_bytes": b, "ms_per_step": ms,
+               "points_per_s": pts / (ms * 1e-3), "alg_GBs": b / (ms * 1e-3) / 1e9, "frac_of_hbm": b / (ms * 1e-3) / 1e9 / peak,
+               "bitwise_equal_to_oracle": bool(np.array_equal(fo, f) and np.array_equal(flo, fl)),
+               "cpu_omp": {"s": cpu_omp, "points_per_s": pts / cpu_omp, "cores": os.cpu_count(), "kind": "port",
+                           "sample": "one step, blocks of 8 slices on OpenMP threads"}}
+        if ns == mpdata.NSLICES:
+            f2, fl2 = P.f.copy(order="F"), P.flux.copy(order="F")
+            t0 = time.perf_counter()
+            mpo.advect_scalar2D_cpu(ns, nx, nz, f2, P.u, P.w, P.rho, P.rhow, P.adz, fl2)
+            s = time.perf_counter() - t0
+            run["cpu_serial"] = {"s": s, "points_per_s": pts / s, "cores": 1, "kind": "port",
+                                 "sample": "one step of advect_scalar2D_cpu (A:477-642), the reference's own timed region"}
+        out["runs"].append(run)
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

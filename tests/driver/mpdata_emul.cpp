@@ -1,0 +1,58 @@
+// TEST INFRASTRUCTURE ONLY -- compiles the device source of libmpdata_b200.so
+// (codesign-kernels_b200/csrc/mpdata_kernels.cuh, unmodified) for the HOST: the CUDA vocabulary is
+// mapped onto blockDim.x host threads and a barrier, CTAs run one after another.  This is how the
+// kernel's indexing, phase ordering (barrier-phased in-place updates in shared memory) and
+// operation order are checked against the oracle on a box without a GPU; it is not a CPU path of
+// the product (nothing in the package builds or loads it).
+#include <barrier>
+#include <cmath>
+#include <cstddef>
+#include <thread>
+#include <vector>
+
+struct emu_dim3 {
+    unsigned x = 1, y = 1, z = 1;
+};
+static thread_local emu_dim3 threadIdx, blockIdx;
+static emu_dim3 blockDim, gridDim;
+static std::barrier<> *emu_barrier = nullptr;
+static inline void __syncthreads() { emu_barrier->arrive_and_wait(); }
+
+#define __global__
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __launch_bounds__(a, b)
+#define __align__(n) __attribute__((aligned(n)))
+#define __shared__
+
+namespace mpd_dev {
+alignas(16) unsigned char smem_raw[227 * 1024];  // the block-scope `extern ... smem_raw[]` of the kernel binds to this
+}
+#include "../../codesign-kernels_b200/csrc/mpdata_kernels.cuh"
+
+// One step exactly as mpdata_b200.cu's launch_step issues it (grid CTAs of `block` threads), on
+// host pointers.  Returns 0, 1 on bad arguments, 3 if a slice does not fit the shared memory.
+extern "C" int mpdata_emul_step(int grid, int block, int ns, int nx, int nz, double *f, const double *u, const double *w,
+                                const double *rho, const double *rhow, const double *adz, double *flux) {
+    if (grid < 1 || block < 1 || block > 1024 || ns < 1 || nx < 1 || nz < 3) return 1;
+    if (mpd_dev::slice_doubles(nx, nz) * sizeof(double) > sizeof mpd_dev::smem_raw) return 3;
+    mpd_dev::Problem p{ns, nx, nz, f, u, w, rho, rhow, adz, flux};
+    blockDim.x = (unsigned)block;
+    gridDim.x = (unsigned)grid;
+    std::barrier<> bar((std::ptrdiff_t)block);
+    emu_barrier = &bar;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < block; ++t)
+        pool.emplace_back([=, &bar] {
+            threadIdx.x = (unsigned)t;
+            for (int b = 0; b < grid; ++b) {
+                blockIdx.x = (unsigned)b;
+                mpd_dev::advect_kernel(p);
+                bar.arrive_and_wait();  // CTAs share the one shared-memory buffer: run them in turn
+            }
+        });
+    for (auto &th : pool) th.join();
+    emu_barrier = nullptr;
+    return 0;
+}

@@ -1,0 +1,321 @@
+"""mmf-mpdata-tracer mini-app: the MMF MPDATA tracer step behind include/mpdata_b200.h.
+
+Reference: mmf-mpdata-tracer/advect_scalar2D_pushncols_openacc.F90 (cited as A:<line>).
+
+PARITY UNPINNED: the reference holds no outputs for this kernel (its inputs come from the compiler's
+random_number, A:645-665).  What it holds is its acceptance test -- relative L1 error of f and flux
+against advect_scalar2D_cpu (A:679-683), printed as exactly 0 by every CPU build under results/ and as
+2.2e-16 / 8.2e-17 by the one GPU build (results/advect.pgiacc.17.7).  Here the CUDA path is required to
+be BIT-IDENTICAL to the C restatement of advect_scalar2D_cpu, which is itself checked bitwise against
+an independent numpy restatement written from the Fortran, and the device source is run on the host
+(tests/driver/mpdata_emul.cpp) to check indexing and phase ordering without a GPU.
+
+This file sorts last on purpose: its -m gpu tests are the newest in the suite and have not yet run on a B200.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+@pytest.fixture(scope="module")
+def mpdata(bwk):
+    from codesign_kernels_b200 import mpdata as m
+
+    return m
+
+
+@pytest.fixture(scope="module")
+def mpo():
+    import mpdata_oracle_py
+
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, stdout=subprocess.DEVNULL)
+    return mpdata_oracle_py
+
+
+@pytest.fixture(scope="module")
+def emul():
+    subprocess.run(["make", "-C", os.path.join(ROOT, "tests", "driver"), "libmpdata_emul.so"], check=True, stdout=subprocess.DEVNULL)
+    E = C.CDLL(os.path.join(ROOT, "tests", "driver", "libmpdata_emul.so"))
+    E.mpdata_emul_step.argtypes = [C.c_int] * 5 + [C.c_void_p] * 7
+    E.mpdata_emul_step.restype = C.c_int
+    return E
+
+
+def numpy_reference(ns, nx, nz, f, u, w, rho, rhow, adz, flux):
+    """Independent restatement of A:477-642, vectorised over slices and x (python loop over levels only
+    where the Fortran has a level dependence).  Same operation order per point -> bitwise comparable.
+    Arrays are (ns, x, nlev) views with the halo offsets applied by the index helpers."""
+    nzm = nz - 1
+    f = f.reshape(ns, nx + 6, nzm, order="F").copy(order="F")
+    u = u.reshape(ns, nx + 5, nzm, order="F")
+    w = w.reshape(ns, nx + 4, nz, order="F")
+    flux = flux.copy(order="F")
+    eps = np.float64(np.float32(1.0e-10))
+    F = lambda a, b: slice(a + 2, b + 3)  # x range a..b of f
+    V = lambda a, b: slice(a + 1, b + 2)  # x range a..b of u, w, uuu, www
+    kk = np.arange(1, nzm + 1)
+    kb = np.maximum(1, kk - 1) - 1  # 0-based level indices
+    kc = np.minimum(nzm, kk + 1) - 1
+    k0 = kk - 1
+    uuu = np.zeros((ns, nx + 5, nzm))
+    www = np.zeros((ns, nx + 4, nz))
+
+    def extrema(op, extra=None):
+        r = op(f[:, F(-1, nx), :], f[:, F(1, nx + 2), :])
+        r = op(r, f[:, F(0, nx + 1), :][:, :, kb])
+        r = op(r, f[:, F(0, nx + 1), :][:, :, kc])
+        r = op(r, f[:, F(0, nx + 1), :])
+        return r if extra is None else op(r, extra)
+
+    mx, mn = extrema(np.maximum), extrema(np.minimum)  # x = 0..nx+1
+    uuu[:, V(-1, nx + 3), :] = np.maximum(0.0, u) * f[:, F(-2, nx + 2), :] + np.minimum(0.0, u) * f[:, F(-1, nx + 3), :]
+    wv = w[:, :, :nzm]
+    www[:, :, :nzm] = np.maximum(0.0, wv) * f[:, F(-1, nx + 2), :][:, :, kb] + np.minimum(0.0, wv) * f[:, F(-1, nx + 2), :]
+    fl = np.zeros((ns, nzm))
+    for i in range(1, nx + 1):
+        fl = fl + www[:, i + 1, :nzm]
+    irho, iadz = 1.0 / rho, 1.0 / adz
+    f[:, F(-1, nx + 2), :] = f[:, F(-1, nx + 2), :] - (
+        uuu[:, V(0, nx + 3), :] - uuu[:, V(-1, nx + 2), :] + (www[:, :, 1:] - www[:, :, :nzm]) * iadz[:, None, :]
+    ) * irho[:, None, :]
+    irhow = 1.0 / (rhow[:, :nzm] * adz)
+    dd = (2.0 / (kc - kb).astype(np.float64))[None, :] / adz
+
+    def andiff(x1, x2, a, b):
+        return (np.abs(a) - a * a * b) * 0.5 * (x2 - x1)
+
+    def across(x1, a1, a2):
+        return 0.03125 * a1 * a2 * x1
+
+    fi, fib = f[:, F(0, nx + 2), :], f[:, F(-1, nx + 1), :]
+    ui = u[:, V(0, nx + 2), :]
+    wi, wib = w[:, V(0, nx + 2), :], w[:, V(-1, nx + 1), :]
+    new_uuu = andiff(fib, fi, ui, irho[:, None, :]) - across(
+        dd[:, None, :] * (fib[:, :, kc] + fi[:, :, kc] - fib[:, :, kb] - fi[:, :, kb]),
+        ui,
+        wib[:, :, k0] + wib[:, :, kc] + wi[:, :, k0] + wi[:, :, kc],
+    ) * irho[:, None, :]
+    fi, fib, fic = f[:, F(0, nx + 1), :], f[:, F(-1, nx), :], f[:, F(1, nx + 2), :]
+    wi = w[:, V(0, nx + 1), :nzm]
+    ui, uic = u[:, V(0, nx + 1), :], u[:, V(1, nx + 2), :]
+    new_www = andiff(fi[:, :, kb], fi, wi, irhow[:, None, :]) - across(
+        fic[:, :, kb] + fic - fib[:, :, kb] - fib, wi, ui[:, :, kb] + ui + uic + uic[:, :, kb]
+    ) * irho[:, None, :]
+    uuu[:, V(0, nx + 2), :] = new_uuu
+    www[:, V(0, nx + 1), :nzm] = new_www
+    www[:, :, 0] = 0.0
+    mx, mn = extrema(np.maximum, mx), extrema(np.minimum, mn)
+    pp = lambda y: np.maximum(0.0, y)
+    pn = lambda y: -np.minimum(0.0, y)
+    f0 = f[:, F(0, nx + 1), :]
+    u_i, u_ic = uuu[:, V(0, nx + 1), :], uuu[:, V(1, nx + 2), :]
+    w_k = www[:, V(0, nx + 1), :nzm]
+    w_kc = w_k[:, :, kc]
+    r = rho[:, None, :]
+    mx = r * (mx - f0) / (pn(u_ic) + pp(u_i) + iadz[:, None, :] * (pn(w_kc) + pp(w_k)) + eps)
+    mn = r * (f0 - mn) / (pp(u_ic) + pn(u_i) + iadz[:, None, :] * (pp(w_kc) + pn(w_k)) + eps)
+    ul = uuu[:, V(1, nx + 1), :]
+    uuu[:, V(1, nx + 1), :] = pp(ul) * np.minimum(np.minimum(1.0, mx[:, 1:, :]), mn[:, :-1, :]) - pn(ul) * np.minimum(
+        np.minimum(1.0, mx[:, :-1, :]), mn[:, 1:, :]
+    )
+    wl = www[:, V(1, nx), :nzm]
+    mxi, mni = mx[:, 1 : nx + 1, :], mn[:, 1 : nx + 1, :]
+    www[:, V(1, nx), :nzm] = pp(wl) * np.minimum(np.minimum(1.0, mxi), mni[:, :, kb]) - pn(wl) * np.minimum(
+        np.minimum(1.0, mxi[:, :, kb]), mni
+    )
+    for i in range(1, nx + 1):
+        fl = fl + www[:, i + 1, :nzm]
+    flux[:, :nzm] = fl
+    f[:, F(1, nx), :] = np.maximum(
+        0.0,
+        f[:, F(1, nx), :]
+        - (uuu[:, V(2, nx + 1), :] - uuu[:, V(1, nx), :] + (www[:, V(1, nx), 1:] - www[:, V(1, nx), :nzm]) * iadz[:, None, :])
+        * irho[:, None, :],
+    )
+    return f.reshape(ns, nx + 6, 1, nzm, order="F"), flux
+
+
+CASES = [  # nslices, nx, nz, signed velocities
+    (48, 32, 58, False),  # the reference's sizes and input distribution (A:6-8, A:654-660)
+    (48, 32, 58, True),
+    (5, 7, 4, True),
+    (3, 1, 3, True),  # smallest sizes the algorithm admits
+    (11, 13, 9, False),
+]
+
+
+def _run_oracle(mpo, P):
+    f, fl = P.f.copy(order="F"), P.flux.copy(order="F")
+    mpo.advect_scalar2D_cpu(P.nslices, P.nx, P.nz, f, P.u, P.w, P.rho, P.rhow, P.adz, fl)
+    return f, fl
+
+
+# ------------------------------------------------------------------------------------------ CPU
+
+
+@pytest.mark.parametrize("ns,nx,nz,signed", CASES)
+def test_oracle_matches_numpy_restatement_bitwise(mpdata, mpo, ns, nx, nz, signed):
+    P = mpdata.TestAdvect(ns, nx, nz).init(seed=7, signed_velocity=signed)
+    f, fl = _run_oracle(mpo, P)
+    fn, fln = numpy_reference(ns, nx, nz, P.f, P.u, P.w, P.rho, P.rhow, P.adz, P.flux)
+    assert np.array_equal(f, fn)
+    assert np.array_equal(fl, fln)
+    # the reference never writes flux(:,nz) nor the outermost halo columns of f
+    assert np.array_equal(fl[:, -1], P.flux[:, -1])
+    assert np.array_equal(f[:, [0, -1]], P.f[:, [0, -1]])
+    assert np.all(f[:, 3 : nx + 3] >= 0.0)  # positive definite (A:634)
+    assert not np.array_equal(f, P.f)
+
+
+def test_oracle_known_answer_uniform_field(mpdata, mpo):
+    """Hand-checkable case: f = c everywhere, u = u0 > 0, w = 0, rho = adz = rhow = 1.  First-order
+    fluxes are u0*c (no divergence -> f unchanged), every antidiffusive flux is 0 (x2 - x1 = 0,
+    cross terms have zero differences), flux = 0, so the step returns f = c exactly."""
+    ns, nx, nz = 4, 6, 5
+    P = mpdata.TestAdvect(ns, nx, nz).init(seed=1)
+    P.f[:] = 0.75
+    P.u[:] = 0.25
+    P.w[:] = 0.0
+    P.rho[:] = P.rhow[:] = P.adz[:] = 1.0
+    f, fl = _run_oracle(mpo, P)
+    assert np.array_equal(f, P.f)
+    assert np.all(fl[:, :-1] == 0.0)
+
+
+def test_oracle_omp_blocks_equal_serial(mpdata, mpo):
+    P = mpdata.TestAdvect(48, 32, 58).init(seed=3, signed_velocity=True)
+    f, fl = _run_oracle(mpo, P)
+    f2, fl2 = P.f.copy(order="F"), P.flux.copy(order="F")
+    mpo.advect_scalar2D_cpu(48, 32, 58, f2, P.u, P.w, P.rho, P.rhow, P.adz, fl2, omp_block=5)
+    assert np.array_equal(f, f2) and np.array_equal(fl, fl2)
+    assert mpo.relative_l1(f2, f) == 0.0
+
+
+@pytest.mark.parametrize("ns,nx,nz,signed", CASES)
+@pytest.mark.parametrize("block,grid", [(64, 1000), (96, 2), (32, 1)])
+def test_device_source_on_host_bit_identical_to_oracle(mpdata, mpo, emul, ns, nx, nz, signed, block, grid):
+    P = mpdata.TestAdvect(ns, nx, nz).init(seed=11, signed_velocity=signed)
+    f, fl = _run_oracle(mpo, P)
+    fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
+    grid = min(grid, ns)
+    rc = emul.mpdata_emul_step(grid, block, ns, nx, nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)])
+    assert rc == 0
+    assert np.array_equal(fe, f)
+    assert np.array_equal(fle, fl)
+
+
+def test_device_source_on_host_full_block(mpdata, mpo, emul):
+    """1024 threads per CTA (the launch default) at the reference sizes, CTAs walking several slices."""
+    P = mpdata.TestAdvect().init(seed=100)
+    f, fl = _run_oracle(mpo, P)
+    fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
+    assert emul.mpdata_emul_step(5, 1024, P.nslices, P.nx, P.nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)]) == 0
+    assert np.array_equal(fe, f) and np.array_equal(fle, fl)
+
+
+def test_abi_exports_and_no_fallback(mpdata):
+    L = mpdata.lib()
+    names = mpdata.declared_symbols()
+    assert "mpdata_advect_scalar2D" in names and len(names) == 11
+    for n in names:
+        assert hasattr(L, n), n
+    # shared-memory budget at the reference sizes: one slice = 7 planes + columns
+    assert L.mpdata_slice_smem_bytes(32, 58) == 8 * (38 * 57 + 2 * 37 * 57 + 2 * 36 * 58 + 2 * 34 * 57 + 6 * 58) == 118272
+    assert L.mpdata_slice_smem_bytes(32, 2) == -1
+    assert L.mpdata_set_block(100) != 0 and b"multiple of 32" in L.mpdata_last_error()
+    assert L.mpdata_set_block(1024) == 0
+    # no CPU fallback: the product source never mentions the oracle, and without a device init fails
+    src = open(os.path.join(ROOT, "codesign-kernels_b200", "mpdata.py")).read() + open(
+        os.path.join(ROOT, "codesign-kernels_b200", "csrc", "mpdata_b200.cu")
+    ).read()
+    assert "oracle" not in src.replace("the oracle", "")
+    import torch
+
+    if not torch.cuda.is_available():
+        assert L.mpdata_init(48, 32, 58) == 1
+        assert b"no CPU fallback" in L.mpdata_last_error()
+        with pytest.raises(mpdata.MpdataError):
+            mpdata.TestAdvect(3, 4, 5).init().advect_scalar2D()
+    assert mpdata.algorithmic_bytes() == 8 * 48 * (38 * 57 + 37 * 57 + 36 * 58 + 3 * 57 + 36 * 57 + 57)
+
+
+# ------------------------------------------------------------------------------------------ GPU
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ns,nx,nz,signed", CASES + [(1000, 32, 58, True), (300, 60, 40, True)])
+def test_gpu_bit_identical_to_oracle(mpdata, mpo, ns, nx, nz, signed):
+    P = mpdata.TestAdvect(ns, nx, nz).init(seed=100, signed_velocity=signed)
+    f, fl = _run_oracle(mpo, P)
+    n0 = mpdata.lib().mpdata_launch_count()
+    P.advect_scalar2D()
+    assert mpdata.lib().mpdata_launch_count() == n0 + 1  # the whole step is one launch
+    assert np.array_equal(P.f, f)
+    assert np.array_equal(P.flux, fl)
+    # the reference's own acceptance quantities (A:679-683)
+    P.f_save, P.flux_save = f, fl
+    assert P.compare() == (0.0, 0.0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("block", [128, 512, 1024])
+def test_gpu_result_independent_of_block_size(mpdata, mpo, block):
+    L = mpdata.lib()
+    P = mpdata.TestAdvect().init(seed=5, signed_velocity=True)
+    f, fl = _run_oracle(mpo, P)
+    try:
+        assert L.mpdata_set_block(block) == 0
+        P.advect_scalar2D()
+    finally:
+        L.mpdata_set_block(1024)
+    assert np.array_equal(P.f, f) and np.array_equal(P.flux, fl)
+
+
+@pytest.mark.gpu
+def test_gpu_life_cycle_and_errors(mpdata, mpo):
+    L = mpdata.lib()
+    P = mpdata.TestAdvect(20, 16, 12).init(seed=9, signed_velocity=True)
+    assert L.mpdata_finalize() == 0
+    assert L.mpdata_run() == 5  # call order
+    assert L.mpdata_init(20, 16, 12) == 0
+    assert L.mpdata_run() == 5  # nothing uploaded yet
+    ptr = lambda a: a.ctypes.data
+    assert L.mpdata_upload(ptr(P.f), ptr(P.u), ptr(P.w), ptr(P.rho), ptr(P.rhow), ptr(P.adz), ptr(P.flux)) == 0
+    # two device-resident steps == two oracle steps
+    f, fl = P.f.copy(order="F"), P.flux.copy(order="F")
+    for _ in range(2):
+        assert L.mpdata_run() == 0
+        mpo.advect_scalar2D_cpu(20, 16, 12, f, P.u, P.w, P.rho, P.rhow, P.adz, fl)
+    fo, flo = np.empty_like(P.f), P.flux.copy(order="F")
+    assert L.mpdata_download(ptr(fo), ptr(flo)) == 0
+    assert np.array_equal(fo, f) and np.array_equal(flo, fl)
+    # a slice that cannot fit an SM's shared memory is refused, not silently run elsewhere
+    assert L.mpdata_init(4, 256, 128) == 3 and b"shared memory" in L.mpdata_last_error()
+    assert L.mpdata_init(4, 32, 2) == 2
+    ms = mpdata.time_steps(mpdata.TestAdvect().init(), iters=5)
+    assert 0.0 < ms < 5.0
+    assert L.mpdata_finalize() == 0
+
+
+def test_fortran_module_argument_lists():
+    """The shipped ISO_C_BINDING module (no Fortran compiler here: lint with f2py's parser) keeps the
+    reference's argument order (f,u,w,rho,rhow,flux | A:72) and binds the C names the header declares."""
+    import numpy.f2py.crackfortran as cf
+
+    cf.verbose = 0
+    path = os.path.join(ROOT, "codesign-kernels_b200", "fortran", "mpdata_b200_mod.F90")
+    mod = cf.crackfortran([path])[0]
+    assert mod["name"] == "mpdata_b200_mod"
+    subs = {b["name"]: b for b in mod["body"] if b["block"] == "subroutine"}
+    assert subs["advect_scalar2d_b200"]["args"] == ["f", "u", "w", "rho", "rhow", "flux", "adz", "nslices", "nx", "nz"]
+    text = open(path).read()
+    assert "bind(c, name='mpdata_advect_scalar2D')" in text and "bind(c, name='mpdata_last_error')" in text
+    header = open(os.path.join(ROOT, "include", "mpdata_b200.h")).read()
+    assert "int mpdata_advect_scalar2D(int nslices, int nx, int nz, double *f, const double *u, const double *w, const double *rho," in header
