@@ -189,6 +189,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-hv", action="store_true", help="skip the advance_hypervis_scalar (caller, SURVEY 8(f)1) timing")
     ap.add_argument("--no-dp3d", action="store_true", help="skip the biharmonic_wk_dp3d (SURVEY 8(f)3) timing")
+    ap.add_argument("--no-mini", action="store_true", help="skip the two mini-app timings (nested_loops, mmf-mpdata-tracer; SURVEY 8(f)4)")
     ap.add_argument("--variant", type=int, default=0)
     args = ap.parse_args()
 
@@ -435,6 +436,19 @@ def main():
         except Exception as ex:
             dp3d = {"value": None, "error": str(ex)[:200]}
 
+    # ---- the reference repo's two other mini-apps, each in its own process (own library, own
+    #      CUDA context; a failure there cannot touch this line's numbers), bounded to two minutes each
+    mini = None
+    if rank == 0 and world == 1 and not args.no_mini:
+        mini = {}
+        for name, script in (("nested_loops", "prof_nested.py"), ("mmf_mpdata_tracer", "prof_mpdata.py")):
+            try:
+                r = subprocess.run([sys.executable, os.path.join(ROOT, "profiles", script)], capture_output=True, text=True, timeout=120)
+                last = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+                mini[name] = json.loads(last[-1]) if r.returncode == 0 and last else {"error": (r.stderr or r.stdout)[-300:]}
+            except Exception as ex:
+                mini[name] = {"error": str(ex)[:200]}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -443,7 +457,7 @@ def main():
             "config": {"workload": f"ne{ne}np4 L{nlev} q{qsize}, {nglob} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
                        "partition": f"contiguous element blocks over {world} rank(s)", "l2": "working set >> L2 (no flush needed); inputs re-generated before every step",
                        "variant": args.variant},
-            "laplace_only": lap, "advance_hypervis_scalar": hv, "biharmonic_wk_dp3d": dp3d, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "laplace_only": lap, "advance_hypervis_scalar": hv, "biharmonic_wk_dp3d": dp3d, "mini_apps": mini, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     ku.finalize()

@@ -1,7 +1,7 @@
 """GPU-box script (run under gpurun): timing of the MPDATA tracer step (libmpdata_b200.so) at the
 reference sizes and at production-like slice counts, with the CPU port timed beside it.
 
-    python profiles/prof_mpdata.py [--slices 48,1184,18944] [--flush] > gpurun_out/mpdata_prof.json
+    python profiles/prof_mpdata.py [--slices 48,1184,9472] [--flush] > gpurun_out/mpdata_prof.json
 
 Prints one JSON object: per slice count the mean kernel time (CUDA events on the library stream),
 point-updates/s, algorithmic GB/s against the measured HBM peak, the GPU-vs-oracle check (bitwise),
@@ -23,7 +23,7 @@ sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--slices", default="48,1184,18944")
+    ap.add_argument("--slices", default="48,1184,9472")
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--block", type=int, default=1024)
