@@ -319,3 +319,78 @@ def test_fortran_module_argument_lists():
     assert "bind(c, name='mpdata_advect_scalar2D')" in text and "bind(c, name='mpdata_last_error')" in text
     header = open(os.path.join(ROOT, "include", "mpdata_b200.h")).read()
     assert "int mpdata_advect_scalar2D(int nslices, int nx, int nz, double *f, const double *u, const double *w, const double *rho," in header
+
+
+# ------------------------------------------------------------------- physical invariants (no oracle needed)
+
+
+def physical_problem(mpdata, ns, nx, nz, seed=0, cfl=0.6):
+    """Closed box, discretely non-divergent flow (stream function vanishing on the walls), rho = adz = 1,
+    smooth positive tracer.  For such a flow MPDATA with the non-oscillatory option conserves the total
+    tracer, keeps it positive and creates no new extrema -- properties of the algorithm that hold at any
+    size and pin what is computed independently of the builder's restatement."""
+    nzm = nz - 1
+    rng = np.random.default_rng(seed)
+    P = mpdata.TestAdvect(ns, nx, nz)
+    sh = P.shapes
+    X = np.clip((np.arange(-1, nx + 4) - 1) / nx, 0, 1)  # u faces x = -1..nx+3: 0 at face 1, 1 at face nx+1
+    Z = (np.arange(1, nz + 1) - 1) / nzm  # w faces: 0 at face 1, 1 at face nz
+    amp = cfl * rng.uniform(0.5, 1.0, ns) * nx / (2 * np.pi)
+    psi = amp[:, None, None] * (np.sin(np.pi * X) ** 2)[None, :, None] * (np.sin(np.pi * Z) ** 2)[None, None, :]
+    P.u = np.asfortranarray((-(psi[:, :, 1:] - psi[:, :, :-1])).reshape(sh["u"], order="F"))
+    P.w = np.asfortranarray((psi[:, 1:, :] - psi[:, :-1, :]).reshape(sh["w"], order="F"))
+    P.rho, P.rhow, P.adz = (np.ones(sh[n], order="F") for n in ("rho", "rhow", "adz"))
+    xc, zc = np.arange(-2, nx + 4), np.arange(1, nz)
+    blob = np.exp(-(((xc[None, :, None] - nx * 0.4) / (nx * 0.15)) ** 2 + ((zc[None, None, :] - nzm * 0.5) / (nzm * 0.2)) ** 2))
+    f = 1.0 + 0.8 * blob * rng.uniform(0.5, 1.0, ns)[:, None, None]
+    P.f = np.asfortranarray(f.reshape(sh["f"], order="F"))
+    P.flux = np.zeros(sh["flux"], order="F")
+    return P
+
+
+def check_invariants(f0, f1, nx):
+    old, new = f0[:, :, 0, :], f1[:, :, 0, :]
+    interior = slice(3, nx + 3)  # x = 1..nx
+    m0, m1 = old[:, interior, :].sum(axis=(1, 2)), new[:, interior, :].sum(axis=(1, 2))
+    assert np.abs(m1 - m0).max() <= 1e-13 * m0.max()  # conservation (closed box)
+    assert new[:, interior, :].min() > 0.0  # positivity, and the clip at 0 (A:634) never acted
+    lev = np.pad(old, ((0, 0), (0, 0), (1, 1)), mode="edge")  # kb = max(1,k-1), kc = min(nzm,k+1)
+    c, west, east = old[:, interior, :], old[:, 2 : nx + 2, :], old[:, 4 : nx + 4, :]
+    below, above = lev[:, interior, :-2], lev[:, interior, 2:]
+    hi = np.maximum.reduce([c, west, east, below, above])
+    lo = np.minimum.reduce([c, west, east, below, above])
+    n = new[:, interior, :]
+    tol = 1e-9  # the limiter's eps = 1e-10 in the denominators (A:606-609) lets the bound slip by O(eps)
+    assert (n - hi).max() <= tol and (lo - n).max() <= tol  # no new extrema
+    assert np.abs(n - c).max() > 1e-3  # and something did move
+
+
+def test_oracle_physical_invariants(mpdata, mpo):
+    P = physical_problem(mpdata, 6, 32, 58, seed=2)
+    f, fl = _run_oracle(mpo, P)
+    check_invariants(P.f, f, 32)
+    # several steps keep them (the field keeps moving)
+    f0 = P.f.copy(order="F")
+    for _ in range(5):
+        mpo.advect_scalar2D_cpu(6, 32, 58, f, P.u, P.w, P.rho, P.rhow, P.adz, fl)
+    m0, m5 = f0[:, 3:35].sum(), f[:, 3:35].sum()
+    assert abs(m5 - m0) <= 1e-13 * m0 and f[:, 3:35].min() > 0.0
+
+
+@pytest.mark.gpu
+def test_gpu_physical_invariants_at_production_slice_count(mpdata, mpo):
+    """4,736 slices (32 per SM): conservation, positivity and monotonicity on every slice; bitwise
+    against the oracle on a strided subset (slices are independent, so the oracle can run on a subset)."""
+    ns, nx, nz = 4736, 32, 58
+    P = physical_problem(mpdata, ns, nx, nz, seed=4)
+    f0 = P.f.copy(order="F")
+    P.advect_scalar2D()
+    check_invariants(f0, P.f, nx)
+    pick = np.arange(0, ns, 37)
+    sub = mpdata.TestAdvect(len(pick), nx, nz)
+    for name, src in (("f", f0), ("u", P.u), ("w", P.w), ("rho", P.rho), ("rhow", P.rhow), ("adz", P.adz)):
+        setattr(sub, name, np.asfortranarray(src[pick]))
+    sub.flux = np.zeros(sub.shapes["flux"], order="F")
+    f, fl = _run_oracle(mpo, sub)
+    assert np.array_equal(P.f[pick], f)
+    assert np.array_equal(P.flux[pick][:, :-1], fl[:, :-1])
