@@ -38,6 +38,14 @@ __device__ __forceinline__ double across(double x1, double a1, double a2) { retu
 __device__ __forceinline__ double pp(double y) { return fmax(0.0, y); }
 __device__ __forceinline__ double pn(double y) { return -fmin(0.0, y); }
 
+// q -> (k = q / W, i = q % W) without an integer division: exact for q < 65536, W < 16384
+// (checked exhaustively in tests/test_zzz_mpdata.py); a plane never has more than 29,056 points
+// (227 KB of shared memory), so every index this kernel splits is in range.
+__device__ __forceinline__ void split(int q, int W, float invW, int &k, int &i) {
+    k = (int)(((float)q + 0.5f) * invW);
+    i = q - k * W;
+}
+
 __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int nx = p.nx, nz = p.nz, nzm = nz - 1, ns = p.ns;
@@ -45,6 +53,8 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
     const int nxp1 = nx + 1, nxp2 = nx + 2;
     const int tid = threadIdx.x, nth = blockDim.x;
     const double eps = (double)1.e-10f;  // default-real literal assigned to a double (A:509)
+    const float invUX = 1.0f / (float)UX, invWX = 1.0f / (float)WX, invMW = 1.0f / (float)MW;
+    const float invP3 = 1.0f / (float)(nx + 3), invP5 = 1.0f / (float)nxp1;
 
     double *sf = reinterpret_cast<double *>(smem_raw);  // f   [k-1][i+2]
     double *su = sf + FX * nzm;                         // u   [k-1][i+1]
@@ -54,7 +64,7 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
     double *smx = swww + WX * nz;                       // mx  [k-1][i]
     double *smn = smx + MW * nzm;                       // mn  [k-1][i]
     double *srho = smn + MW * nzm;                      // per-level columns, nz each
-    double *sadz = srho + nz, *sirho = sadz + nz, *siadz = sirho + nz, *sirhow = siadz + nz, *sflux = sirhow + nz;
+    double *sdd = srho + nz, *sirho = sdd + nz, *siadz = sirho + nz, *sirhow = siadz + nz, *sflux = sirhow + nz;
 
 #define SF(i, k) sf[((i) + 2) + FX * ((k)-1)]
 #define SU(i, k) su[((i) + 1) + UX * ((k)-1)]
@@ -71,8 +81,9 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
         for (int q = tid; q < WX * nz; q += nth) sw[q] = p.w[sl + (size_t)ns * q];
         for (int k = tid + 1; k <= nzm; k += nth) {
             const double r = p.rho[sl + (size_t)ns * (k - 1)], a = p.adz[sl + (size_t)ns * (k - 1)];
+            const int kb = k > 1 ? k - 1 : 1, kc = k < nzm ? k + 1 : nzm;
             srho[k - 1] = r;
-            sadz[k - 1] = a;
+            sdd[k - 1] = 2.0 / (double)(kc - kb) / a;                           // A:569, the same for every x
             sirho[k - 1] = 1.0 / r;                                             // A:552
             siadz[k - 1] = 1.0 / a;                                             // A:553
             sirhow[k - 1] = 1.0 / (p.rhow[sl + (size_t)ns * (k - 1)] * a);      // A:565
@@ -81,7 +92,9 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
 
         // ---- P1: first-order (upwind) fluxes and the local extrema of f (A:511-541)
         for (int q = tid; q < UX * nzm; q += nth) {
-            const int k = q / UX + 1, i = q % UX - 1;  // i = -1..nx+3
+            int k, i;
+            split(q, UX, invUX, k, i);
+            k += 1, i -= 1;  // i = -1..nx+3
             const double uu = SU(i, k);
             SUUU(i, k) = fmax(0.0, uu) * SF(i - 1, k) + fmin(0.0, uu) * SF(i, k);
             if (i <= nxp2) {
@@ -109,17 +122,21 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
             }
         }
         for (int q = tid; q < WX * nzm; q += nth) {
-            const int k = q / WX + 1, i = q % WX - 1;  // i = -1..nx+2
+            int k, i;
+            split(q, WX, invWX, k, i);
+            k += 1, i -= 1;  // i = -1..nx+2
             SF(i, k) = SF(i, k) - (SUUU(i + 1, k) - SUUU(i, k) + (SWWW(i, k + 1) - SWWW(i, k)) * siadz[k - 1]) * sirho[k - 1];
         }
         __syncthreads();
 
         // ---- P3: antidiffusive fluxes from the updated f (A:561-586) and its extrema (A:589-600)
         for (int q = tid; q < (nx + 3) * nzm; q += nth) {
-            const int k = q / (nx + 3) + 1, i = q % (nx + 3);  // i = 0..nx+2
+            int k, i;
+            split(q, nx + 3, invP3, k, i);
+            k += 1;  // i = 0..nx+2
             const int kb = k > 1 ? k - 1 : 1, kc = k < nzm ? k + 1 : nzm;
             const int ib = i - 1, ic = i + 1;
-            const double dd = 2.0 / (double)(kc - kb) / sadz[k - 1];
+            const double dd = sdd[k - 1];
             SUUU(i, k) = andiff(SF(ib, k), SF(i, k), SU(i, k), sirho[k - 1]) -
                          across(dd * (SF(ib, kc) + SF(i, kc) - SF(ib, kb) - SF(i, kb)), SU(i, k),
                                 SW(ib, k) + SW(ib, kc) + SW(i, k) + SW(i, kc)) * sirho[k - 1];
@@ -138,7 +155,9 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
 
         // ---- P4: limiter ratios (A:601-612), in place
         for (int q = tid; q < MW * nzm; q += nth) {
-            const int k = q / MW + 1, i = q % MW;  // i = 0..nx+1
+            int k, i;
+            split(q, MW, invMW, k, i);
+            k += 1;  // i = 0..nx+1
             const int kc = k < nzm ? k + 1 : nzm, ic = i + 1;
             const double fk = SF(i, k), r = srho[k - 1], ia = siadz[k - 1];
             const double ui = SUUU(i, k), uc = SUUU(ic, k), wk = SWWW(i, k), wc = SWWW(i, kc);
@@ -149,7 +168,9 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
 
         // ---- P5: limited fluxes (A:613-625), in place (each reads only its own flux)
         for (int q = tid; q < nxp1 * nzm; q += nth) {
-            const int k = q / nxp1 + 1, i = q % nxp1 + 1;  // i = 1..nx+1
+            int k, i;
+            split(q, nxp1, invP5, k, i);
+            k += 1, i += 1;  // i = 1..nx+1
             const int kb = k > 1 ? k - 1 : 1, ib = i - 1;
             const double uu = SUUU(i, k);
             SUUU(i, k) = pp(uu) * fmin(fmin(1.0, SMX(i, k)), SMN(ib, k)) - pn(uu) * fmin(fmin(1.0, SMX(ib, k)), SMN(i, k));
@@ -169,7 +190,9 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
             }
         }
         for (int q = tid; q < WX * nzm; q += nth) {
-            const int k = q / WX + 1, i = q % WX - 1;  // i = -1..nx+2: every point of f the step changes
+            int k, i;
+            split(q, WX, invWX, k, i);
+            k += 1, i -= 1;  // i = -1..nx+2: every point of f the step changes
             double v = SF(i, k);
             if (i >= 1 && i <= nx)
                 v = fmax(0.0, v - (SUUU(i + 1, k) - SUUU(i, k) + (SWWW(i, k + 1) - SWWW(i, k)) * siadz[k - 1]) * sirho[k - 1]);

@@ -394,3 +394,13 @@ def test_gpu_physical_invariants_at_production_slice_count(mpdata, mpo):
     f, fl = _run_oracle(mpo, sub)
     assert np.array_equal(P.f[pick], f)
     assert np.array_equal(P.flux[pick][:, :-1], fl[:, :-1])
+
+
+def test_index_split_is_exact():
+    """mpdata_kernels.cuh::split replaces q / W, q % W by one float multiply: k = int((q + 0.5f) * (1.0f / W)).
+    Exactness over everything the kernel can ask for (a plane has < 29,056 points: 227 KB of shared memory)."""
+    q = np.arange(0, 1 << 15, dtype=np.int64)
+    qf = q.astype(np.float32) + np.float32(0.5)
+    for W in list(range(1, 1200)) + list(range(1200, 16384, 7)):
+        k = (qf * (np.float32(1.0) / np.float32(W))).astype(np.int64)
+        assert np.array_equal(k, q // W), W
