@@ -32,11 +32,16 @@ __host__ __device__ inline size_t slice_doubles(int nx, int nz) {
            6 * (size_t)nz;
 }
 
+// Fortran MAX/MIN as compare-select, in the oracle's argument order (so even the sign of a zero
+// agrees).  CUDA's fmax/fmin cost ~8 instructions each on sm_100a (DSETP pair, two selects, the
+// NaN-quieting LOP3s and register moves); these are DSETP + two selects.
+__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+__device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
 // statement functions A:500-503 (left-to-right products, as Fortran evaluates them)
 __device__ __forceinline__ double andiff(double x1, double x2, double a, double b) { return (fabs(a) - a * a * b) * 0.5 * (x2 - x1); }
 __device__ __forceinline__ double across(double x1, double a1, double a2) { return 0.03125 * a1 * a2 * x1; }
-__device__ __forceinline__ double pp(double y) { return fmax(0.0, y); }
-__device__ __forceinline__ double pn(double y) { return -fmin(0.0, y); }
+__device__ __forceinline__ double pp(double y) { return dmax(0.0, y); }
+__device__ __forceinline__ double pn(double y) { return -dmin(0.0, y); }
 
 // q -> (k = q / W, i = q % W) without an integer division: exact for q < 65536, W < 16384
 // (checked exhaustively in tests/test_zzz_mpdata.py); a plane never has more than 29,056 points
@@ -96,18 +101,18 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
             split(q, UX, invUX, k, i);
             k += 1, i -= 1;  // i = -1..nx+3
             const double uu = SU(i, k);
-            SUUU(i, k) = fmax(0.0, uu) * SF(i - 1, k) + fmin(0.0, uu) * SF(i, k);
+            SUUU(i, k) = dmax(0.0, uu) * SF(i - 1, k) + dmin(0.0, uu) * SF(i, k);
             if (i <= nxp2) {
                 const int kb = k > 1 ? k - 1 : 1;
                 const double ww = SW(i, k);
-                SWWW(i, k) = fmax(0.0, ww) * SF(i, kb) + fmin(0.0, ww) * SF(i, k);
+                SWWW(i, k) = dmax(0.0, ww) * SF(i, kb) + dmin(0.0, ww) * SF(i, k);
                 if (k == 1) SWWW(i, nz) = 0.0;
             }
             if (i >= 0 && i <= nxp1) {
                 const int kb = k > 1 ? k - 1 : 1, kc = k < nzm ? k + 1 : nzm;
                 const double a = SF(i - 1, k), b = SF(i + 1, k), c = SF(i, kb), d = SF(i, kc), e = SF(i, k);
-                SMX(i, k) = fmax(fmax(fmax(fmax(a, b), c), d), e);
-                SMN(i, k) = fmin(fmin(fmin(fmin(a, b), c), d), e);
+                SMX(i, k) = dmax(dmax(dmax(dmax(a, b), c), d), e);
+                SMN(i, k) = dmin(dmin(dmin(dmin(a, b), c), d), e);
             }
         }
         __syncthreads();
@@ -146,8 +151,8 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
                                         SU(i, kb) + SU(i, k) + SU(ic, k) + SU(ic, kb)) * sirho[k - 1];
                 SWWW(i, k) = k == 1 ? 0.0 : v;  // www(:,:,:,1) = 0 (A:586)
                 const double a = SF(ib, k), b = SF(ic, k), c = SF(i, kb), d = SF(i, kc), e = SF(i, k);
-                SMX(i, k) = fmax(fmax(fmax(fmax(fmax(a, b), c), d), e), SMX(i, k));
-                SMN(i, k) = fmin(fmin(fmin(fmin(fmin(a, b), c), d), e), SMN(i, k));
+                SMX(i, k) = dmax(dmax(dmax(dmax(dmax(a, b), c), d), e), SMX(i, k));
+                SMN(i, k) = dmin(dmin(dmin(dmin(dmin(a, b), c), d), e), SMN(i, k));
             }
         }
         if (tid < 2) SWWW(tid == 0 ? -1 : nxp2, 1) = 0.0;  // the two columns of level 1 the loop above does not visit
@@ -173,10 +178,10 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
             k += 1, i += 1;  // i = 1..nx+1
             const int kb = k > 1 ? k - 1 : 1, ib = i - 1;
             const double uu = SUUU(i, k);
-            SUUU(i, k) = pp(uu) * fmin(fmin(1.0, SMX(i, k)), SMN(ib, k)) - pn(uu) * fmin(fmin(1.0, SMX(ib, k)), SMN(i, k));
+            SUUU(i, k) = pp(uu) * dmin(dmin(1.0, SMX(i, k)), SMN(ib, k)) - pn(uu) * dmin(dmin(1.0, SMX(ib, k)), SMN(i, k));
             if (i <= nx) {
                 const double ww = SWWW(i, k);
-                SWWW(i, k) = pp(ww) * fmin(fmin(1.0, SMX(i, k)), SMN(i, kb)) - pn(ww) * fmin(fmin(1.0, SMX(i, kb)), SMN(i, k));
+                SWWW(i, k) = pp(ww) * dmin(dmin(1.0, SMX(i, k)), SMN(i, kb)) - pn(ww) * dmin(dmin(1.0, SMX(i, kb)), SMN(i, k));
             }
         }
         __syncthreads();
@@ -195,7 +200,7 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p) {
             k += 1, i -= 1;  // i = -1..nx+2: every point of f the step changes
             double v = SF(i, k);
             if (i >= 1 && i <= nx)
-                v = fmax(0.0, v - (SUUU(i + 1, k) - SUUU(i, k) + (SWWW(i, k + 1) - SWWW(i, k)) * siadz[k - 1]) * sirho[k - 1]);
+                v = dmax(0.0, v - (SUUU(i + 1, k) - SUUU(i, k) + (SWWW(i, k + 1) - SWWW(i, k)) * siadz[k - 1]) * sirho[k - 1]);
             p.f[sl + (size_t)ns * (((i) + 2) + FX * (k - 1))] = v;
         }
         __syncthreads();  // the next slice of this CTA reuses the planes
