@@ -47,12 +47,14 @@ def main():
         t0 = time.perf_counter()
         mpo.advect_scalar2D_cpu(ns, nx, nz, f, P.u, P.w, P.rho, P.rhow, P.adz, fl, omp_block=8)
         cpu_omp = time.perf_counter() - t0
+        by_block = {str(b): mpdata.time_steps(P, iters=max(5, args.iters // 5), flush_l2=args.flush, block=b) for b in (256, 512)}
         ms = mpdata.time_steps(P, iters=args.iters, flush_l2=args.flush, block=args.block)
+        by_block[str(args.block)] = ms
         fo, flo = np.empty_like(P.f), P.flux.copy(order="F")
         assert mpdata.lib().mpdata_download(fo.ctypes.data, flo.ctypes.data) == 0
         pts = ns * nx * (nz - 1)
         b = mpdata.algorithmic_bytes(ns, nx, nz)
-        run = {"nslices": ns, "nx": nx, "nz": nz, "points": pts, "algorithmic_bytes": b, "ms_per_step": ms,
+        run = {"nslices": ns, "nx": nx, "nz": nz, "points": pts, "algorithmic_bytes": b, "ms_per_step": ms, "ms_per_step_by_block": by_block,
                "points_per_s": pts / (ms * 1e-3), "alg_GBs": b / (ms * 1e-3) / 1e9, "frac_of_hbm": b / (ms * 1e-3) / 1e9 / peak,
                "bitwise_equal_to_oracle": bool(np.array_equal(fo, f) and np.array_equal(flo, fl)),
                "cpu_omp": {"s": cpu_omp, "points_per_s": pts / cpu_omp, "cores": os.cpu_count(), "kind": "port",
