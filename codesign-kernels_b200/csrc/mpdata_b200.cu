@@ -17,11 +17,12 @@ struct State {
     bool ready = false, uploaded = false;
     int ns = 0, nx = 0, nz = 0;
     size_t nf = 0, nu = 0, nw = 0, n2m = 0, n2 = 0;  // element counts of the arrays
-    double *f = nullptr, *f0 = nullptr, *u = nullptr, *w = nullptr, *rho = nullptr, *rhow = nullptr, *adz = nullptr,
+    double *f = nullptr, *f1 = nullptr, *f0 = nullptr, *u = nullptr, *w = nullptr, *rho = nullptr, *rhow = nullptr, *adz = nullptr,
            *flux = nullptr, *flush = nullptr;
     size_t flush_bytes = 0;
     cudaStream_t stream = nullptr;
-    int block = 1024, grid = 0, sms = 0;
+    int block = 0, chunks = 0;  // 0 = chosen by the library (see plan_launch)
+    int use_block = 1024, use_chunks = 1, nlmax = 0, grid = 0, sms = 0, smem_optin = 0, smem_sm = 0;
     size_t smem = 0;
 } g;
 
@@ -45,7 +46,7 @@ int fail(int code, const char *fmt, ...) {
     } while (0)
 
 int release() {
-    double **ptrs[] = {&g.f, &g.f0, &g.u, &g.w, &g.rho, &g.rhow, &g.adz, &g.flux, &g.flush};
+    double **ptrs[] = {&g.f, &g.f1, &g.f0, &g.u, &g.w, &g.rho, &g.rhow, &g.adz, &g.flux, &g.flush};
     for (double **p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -56,11 +57,51 @@ int release() {
     return 0;
 }
 
+// Work decomposition for the current sizes.  chunks: a slice's levels are split (with a halo of 3
+// recomputed levels, mpdata_kernels.cuh) only while there are fewer slices than SMs, so that
+// slices x chunks fills the SMs once (48 slices -> 3 chunks -> 144 CTAs on 148 SMs); block: about two
+// points of the widest plane per thread.  Results do not depend on either.
+int plan_launch() {
+    const int nzm = g.nz - 1;
+    int chunks = g.chunks;
+    if (chunks <= 0) {
+        chunks = g.sms / g.ns;
+        if (chunks > nzm / 8) chunks = nzm / 8;
+    }
+    if (chunks > nzm) chunks = nzm;
+    if (chunks < 1) chunks = 1;
+    int nlmax = mpd_dev::max_local_levels(nzm, chunks);
+    size_t smem = mpd_dev::item_doubles(g.nx, nlmax) * sizeof(double);
+    while (smem > (size_t)g.smem_optin && chunks < nzm) {  // a whole slice does not fit: more, shorter chunks
+        ++chunks;
+        nlmax = mpd_dev::max_local_levels(nzm, chunks);
+        smem = mpd_dev::item_doubles(g.nx, nlmax) * sizeof(double);
+    }
+    if (smem > (size_t)g.smem_optin)
+        return fail(3, "one level range of a slice needs %zu B of shared memory (nx=%d), the SM has %d", smem, g.nx, g.smem_optin);
+    int block = g.block;
+    if (block <= 0) {
+        const long long pts = (long long)(g.nx + 6) * nlmax;
+        block = pts >= 1536 ? 1024 : pts >= 640 ? 512 : pts >= 192 ? 256 : 64;
+    }
+    g.use_chunks = chunks; g.use_block = block; g.nlmax = nlmax; g.smem = smem;
+    // the kernel is compiled for 64 registers per thread: 64 K registers hold 1024 threads per SM
+    int per_sm = (int)((size_t)g.smem_sm / (smem + 1024));
+    if (per_sm > 1024 / block) per_sm = 1024 / block;
+    if (per_sm < 1) per_sm = 1;
+    const long long items = (long long)g.ns * chunks, resident = (long long)per_sm * g.sms;
+    g.grid = (int)(items < resident ? items : resident);
+    CU(cudaFuncSetAttribute(mpd_dev::advect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    return 0;
+}
+
 int launch_step() {
-    mpd_dev::Problem p{g.ns, g.nx, g.nz, g.f, g.u, g.w, g.rho, g.rhow, g.adz, g.flux};
-    mpd_dev::advect_kernel<<<g.grid, g.block, g.smem, g.stream>>>(p);
+    // f -> f1, then the two swap roles: a level chunk's halo must read the other chunks' input
+    mpd_dev::Problem p{g.ns, g.nx, g.nz, g.f, g.f1, g.u, g.w, g.rho, g.rhow, g.adz, g.flux};
+    mpd_dev::advect_kernel<<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax);
     ++g_launches;
     CU(cudaGetLastError());
+    double *t = g.f; g.f = g.f1; g.f1 = t;
     return 0;
 }
 
@@ -72,12 +113,28 @@ const char *mpdata_last_error(void) { return g_failed ? g_err : nullptr; }
 long long mpdata_launch_count(void) { return g_launches; }
 long long mpdata_slice_smem_bytes(int nx, int nz) {
     if (nx < 1 || nz < 3) return -1;
-    return (long long)(mpd_dev::slice_doubles(nx, nz) * sizeof(double));
+    return (long long)(mpd_dev::item_doubles(nx, nz - 1) * sizeof(double));
 }
 
 int mpdata_set_block(int threads) {
-    if (threads < 32 || threads > 1024 || threads % 32) return fail(2, "mpdata_set_block: %d is not a multiple of 32 in 32..1024", threads);
+    if (threads != 0 && (threads < 32 || threads > 1024 || threads % 32))
+        return fail(2, "mpdata_set_block: %d is not 0 (automatic) or a multiple of 32 in 32..1024", threads);
     g.block = threads;
+    return g.ready ? plan_launch() : 0;
+}
+
+int mpdata_set_chunks(int chunks) {
+    if (chunks < 0) return fail(2, "mpdata_set_chunks: %d is negative (0 = automatic)", chunks);
+    g.chunks = chunks;
+    return g.ready ? plan_launch() : 0;
+}
+
+int mpdata_get_launch(int *grid, int *block, int *chunks, long long *smem_bytes) {
+    if (!g.ready) return fail(5, "mpdata_get_launch before mpdata_init");
+    if (grid) *grid = g.grid;
+    if (block) *block = g.use_block;
+    if (chunks) *chunks = g.use_chunks;
+    if (smem_bytes) *smem_bytes = (long long)g.smem;
     return 0;
 }
 
@@ -93,10 +150,10 @@ int mpdata_init(int nslices, int nx, int nz) {
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, dev));
     if (prop.major != 10) return fail(1, "mpdata_init: device %d is sm_%d%d, this library is built for sm_100a only", dev, prop.major, prop.minor);
-    const size_t smem = mpd_dev::slice_doubles(nx, nz) * sizeof(double);
-    if (smem > (size_t)prop.sharedMemPerBlockOptin)
-        return fail(3, "mpdata_init: one slice needs %zu B of shared memory (nx=%d nz=%d), the SM has %zu", smem, nx, nz,
-                    (size_t)prop.sharedMemPerBlockOptin);
+    if (mpd_dev::item_doubles(nx, nz - 1 < 2 * mpd_dev::kHalo + 1 ? nz - 1 : 2 * mpd_dev::kHalo + 1) * sizeof(double) >
+        (size_t)prop.sharedMemPerBlockOptin)
+        return fail(3, "mpdata_init: even one level of a slice with its halo does not fit shared memory (nx=%d): %zu B, the SM has %zu",
+                    nx, mpd_dev::item_doubles(nx, 2 * mpd_dev::kHalo + 1) * sizeof(double), (size_t)prop.sharedMemPerBlockOptin);
     release();
     g.ns = nslices; g.nx = nx; g.nz = nz;
     const size_t nzm = nz - 1;
@@ -105,15 +162,13 @@ int mpdata_init(int nslices, int nx, int nz) {
     g.nw = (size_t)nslices * (nx + 4) * nz;
     g.n2m = (size_t)nslices * nzm;
     g.n2 = (size_t)nslices * nz;
-    g.smem = smem;
     g.sms = prop.multiProcessorCount;
-    // one CTA per slice; beyond (resident CTAs per SM x SMs) slices a CTA walks several
-    const int per_sm = (int)(prop.sharedMemPerMultiprocessor / (smem + 1024)) > 0 ? (int)(prop.sharedMemPerMultiprocessor / (smem + 1024)) : 1;
-    const long long resident = (long long)per_sm * g.sms;
-    g.grid = (int)(nslices < resident ? nslices : resident);
-    CU(cudaFuncSetAttribute(mpd_dev::advect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    g.smem_optin = (int)prop.sharedMemPerBlockOptin;
+    g.smem_sm = (int)prop.sharedMemPerMultiprocessor;
+    if (int rc = plan_launch()) return rc;
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     CU(cudaMalloc(&g.f, g.nf * 8));
+    CU(cudaMalloc(&g.f1, g.nf * 8));
     CU(cudaMalloc(&g.f0, g.nf * 8));
     CU(cudaMalloc(&g.u, g.nu * 8));
     CU(cudaMalloc(&g.w, g.nw * 8));

@@ -55,6 +55,8 @@ def lib():
     L.mpdata_finalize.argtypes, L.mpdata_finalize.restype = [], i32
     L.mpdata_time_steps.argtypes, L.mpdata_time_steps.restype = [i32, i32, C.POINTER(C.c_float)], i32
     L.mpdata_set_block.argtypes, L.mpdata_set_block.restype = [i32], i32
+    L.mpdata_set_chunks.argtypes, L.mpdata_set_chunks.restype = [i32], i32
+    L.mpdata_get_launch.argtypes, L.mpdata_get_launch.restype = [C.POINTER(i32)] * 3 + [C.POINTER(C.c_longlong)], i32
     L.mpdata_slice_smem_bytes.argtypes, L.mpdata_slice_smem_bytes.restype = [i32, i32], C.c_longlong
     L.mpdata_launch_count.argtypes, L.mpdata_launch_count.restype = [], C.c_longlong
     L.mpdata_last_error.argtypes, L.mpdata_last_error.restype = [], C.c_char_p
@@ -127,11 +129,21 @@ class TestAdvect:
         return rel(self.f, self.f_save), rel(self.flux, self.flux_save)
 
 
-def time_steps(prob, iters=50, flush_l2=False, block=None):
-    """Device-resident timing of one step at prob's sizes: mean kernel time in ms (CUDA events)."""
+def launch_shape():
+    """(grid, block, chunks, shared-memory bytes) the library uses for the sizes of the last mpdata_init."""
+    g, b, c, s = C.c_int(), C.c_int(), C.c_int(), C.c_longlong()
+    _check(lib().mpdata_get_launch(C.byref(g), C.byref(b), C.byref(c), C.byref(s)))
+    return g.value, b.value, c.value, s.value
+
+
+def time_steps(prob, iters=50, flush_l2=False, block=None, chunks=None):
+    """Device-resident timing of one step at prob's sizes: mean kernel time in ms (CUDA events).
+    block / chunks: None leaves the library's setting, 0 = automatic."""
     L = lib()
-    if block:
+    if block is not None:
         _check(L.mpdata_set_block(block))
+    if chunks is not None:
+        _check(L.mpdata_set_chunks(chunks))
     _check(L.mpdata_init(prob.nslices, prob.nx, prob.nz))
     f, u, w, rho, rhow, adz, flux = prob.arrays()
     _check(L.mpdata_upload(*[a.ctypes.data for a in (f, u, w, rho, rhow, adz, flux)]))

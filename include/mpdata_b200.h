@@ -16,8 +16,8 @@
  * flux(:, nz) is never written by the reference (A:477-642) and is not written here.
  *
  * Every function returns 0 on success; nonzero = failure, message from mpdata_last_error().
- * Failures: no sm_100 device (1), bad sizes (2; nz >= 3, nx >= 1, nslices >= 1), one slice's seven
- * planes do not fit the 227 KB of shared memory of an SM (3), CUDA runtime error (4), call order (5).
+ * Failures: no sm_100 device (1), bad sizes (2; nz >= 3, nx >= 1, nslices >= 1), seven levels of a slice's
+ * seven planes do not fit the 227 KB of shared memory of an SM (3; nx beyond ~570), CUDA runtime error (4), call order (5).
  * There is NO CPU fallback.  One calling thread; not re-entrant.
  */
 #ifndef MPDATA_B200_H
@@ -48,9 +48,15 @@ int mpdata_finalize(void);
  * timed part), CUDA events around each launch on the library stream; flush_l2 != 0 writes a
  * buffer larger than L2 before each step.  *ms_per_step = mean kernel time. */
 int mpdata_time_steps(int iters, int flush_l2, float *ms_per_step);
-/* threads per CTA (multiple of 32, 32..1024; default 1024) -- results do not depend on it */
+/* threads per CTA (multiple of 32, 32..1024; 0 = automatic, the default) -- results do not depend on it */
 int mpdata_set_block(int threads);
-/* bytes of shared memory one slice needs at these sizes */
+/* level ranges a slice is split into (each CTA recomputes a halo of 3 levels either side); 0 = automatic, the
+ * default: floor(SMs / nslices) while there are fewer slices than SMs, 1 otherwise, more when a whole slice does not
+ * fit shared memory -- results do not depend on it */
+int mpdata_set_chunks(int chunks);
+/* the launch shape in use after mpdata_init (any pointer may be NULL) */
+int mpdata_get_launch(int *grid, int *block, int *chunks, long long *smem_bytes);
+/* bytes of shared memory a whole slice (chunks = 1) needs at these sizes */
 long long mpdata_slice_smem_bytes(int nx, int nz);
 /* kernels launched by this library since it was loaded */
 long long mpdata_launch_count(void);

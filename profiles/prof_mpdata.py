@@ -26,7 +26,6 @@ def main():
     ap.add_argument("--slices", default="48,1184,9472")
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--flush", action="store_true")
-    ap.add_argument("--block", type=int, default=1024)
     args = ap.parse_args()
     import __graft_entry__ as ge
 
@@ -39,7 +38,7 @@ def main():
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
     except Exception:
         pass
-    out = {"hbm_peak_GBs": peak, "block": args.block, "flush_l2": args.flush, "runs": []}
+    out = {"hbm_peak_GBs": peak, "flush_l2": args.flush, "runs": []}
     nx, nz = mpdata.NX, mpdata.NZ
     for ns in [int(s) for s in args.slices.split(",")]:
         P = mpdata.TestAdvect(ns, nx, nz).init(seed=100)
@@ -47,14 +46,17 @@ def main():
         t0 = time.perf_counter()
         mpo.advect_scalar2D_cpu(ns, nx, nz, f, P.u, P.w, P.rho, P.rhow, P.adz, fl, omp_block=8)
         cpu_omp = time.perf_counter() - t0
-        by_block = {str(b): mpdata.time_steps(P, iters=max(5, args.iters // 5), flush_l2=args.flush, block=b) for b in (256, 512)}
-        ms = mpdata.time_steps(P, iters=args.iters, flush_l2=args.flush, block=args.block)
-        by_block[str(args.block)] = ms
+        # launch-shape A/B (results do not depend on it): (chunks, threads per CTA), 0 = the library's choice
+        variants = {"chunks1_b1024": (1, 1024), "chunks1_b512": (1, 512), "chunks2": (2, 0), "chunks3": (3, 0), "chunks4": (4, 0)}
+        by_shape = {name: mpdata.time_steps(P, iters=max(5, args.iters // 5), flush_l2=args.flush, block=b_, chunks=c_)
+                    for name, (c_, b_) in variants.items()}
+        ms = mpdata.time_steps(P, iters=args.iters, flush_l2=args.flush, block=0, chunks=0)
+        shape = dict(zip(("grid", "block", "chunks", "smem_bytes"), mpdata.launch_shape()))
         fo, flo = np.empty_like(P.f), P.flux.copy(order="F")
         assert mpdata.lib().mpdata_download(fo.ctypes.data, flo.ctypes.data) == 0
         pts = ns * nx * (nz - 1)
         b = mpdata.algorithmic_bytes(ns, nx, nz)
-        run = {"nslices": ns, "nx": nx, "nz": nz, "points": pts, "algorithmic_bytes": b, "ms_per_step": ms, "ms_per_step_by_block": by_block,
+        run = {"nslices": ns, "nx": nx, "nz": nz, "points": pts, "algorithmic_bytes": b, "ms_per_step": ms, "launch": shape, "ms_per_step_by_shape": by_shape,
                "points_per_s": pts / (ms * 1e-3), "alg_GBs": b / (ms * 1e-3) / 1e9, "frac_of_hbm": b / (ms * 1e-3) / 1e9 / peak,
                "bitwise_equal_to_oracle": bool(np.array_equal(fo, f) and np.array_equal(flo, fl)),
                "cpu_omp": {"s": cpu_omp, "points_per_s": pts / cpu_omp, "cores": os.cpu_count(), "kind": "port",

@@ -31,13 +31,17 @@ alignas(16) unsigned char smem_raw[227 * 1024];  // the block-scope `extern ... 
 }
 #include "../../codesign-kernels_b200/csrc/mpdata_kernels.cuh"
 
-// One step exactly as mpdata_b200.cu's launch_step issues it (grid CTAs of `block` threads), on
+// One step exactly as mpdata_b200.cu's launch_step issues it (grid CTAs of `block` threads, `chunks`
+// level ranges per slice), on
 // host pointers.  Returns 0, 1 on bad arguments, 3 if a slice does not fit the shared memory.
-extern "C" int mpdata_emul_step(int grid, int block, int ns, int nx, int nz, double *f, const double *u, const double *w,
+extern "C" int mpdata_emul_step(int grid, int block, int chunks, int ns, int nx, int nz, double *f, const double *u, const double *w,
                                 const double *rho, const double *rhow, const double *adz, double *flux) {
-    if (grid < 1 || block < 1 || block > 1024 || ns < 1 || nx < 1 || nz < 3) return 1;
-    if (mpd_dev::slice_doubles(nx, nz) * sizeof(double) > sizeof mpd_dev::smem_raw) return 3;
-    mpd_dev::Problem p{ns, nx, nz, f, u, w, rho, rhow, adz, flux};
+    if (grid < 1 || block < 1 || block > 1024 || ns < 1 || nx < 1 || nz < 3 || chunks < 1 || chunks > nz - 1) return 1;
+    const int nlmax = mpd_dev::max_local_levels(nz - 1, chunks);
+    if (mpd_dev::item_doubles(nx, nlmax) * sizeof(double) > sizeof mpd_dev::smem_raw) return 3;
+    for (size_t j = 0; j < sizeof mpd_dev::smem_raw; ++j) mpd_dev::smem_raw[j] = 0xa5;  // shared memory starts uninitialised
+    const std::vector<double> fin(f, f + (size_t)ns * (nx + 6) * (nz - 1));  // the library ping-pongs two device buffers
+    mpd_dev::Problem p{ns, nx, nz, fin.data(), f, u, w, rho, rhow, adz, flux};
     blockDim.x = (unsigned)block;
     gridDim.x = (unsigned)grid;
     std::barrier<> bar((std::ptrdiff_t)block);
@@ -48,7 +52,7 @@ extern "C" int mpdata_emul_step(int grid, int block, int ns, int nx, int nz, dou
             threadIdx.x = (unsigned)t;
             for (int b = 0; b < grid; ++b) {
                 blockIdx.x = (unsigned)b;
-                mpd_dev::advect_kernel(p);
+                mpd_dev::advect_kernel(p, chunks, nlmax);
                 bar.arrive_and_wait();  // CTAs share the one shared-memory buffer: run them in turn
             }
         });

@@ -43,7 +43,7 @@ def mpo():
 def emul():
     subprocess.run(["make", "-C", os.path.join(ROOT, "tests", "driver"), "libmpdata_emul.so"], check=True, stdout=subprocess.DEVNULL)
     E = C.CDLL(os.path.join(ROOT, "tests", "driver", "libmpdata_emul.so"))
-    E.mpdata_emul_step.argtypes = [C.c_int] * 5 + [C.c_void_p] * 7
+    E.mpdata_emul_step.argtypes = [C.c_int] * 6 + [C.c_void_p] * 7
     E.mpdata_emul_step.restype = C.c_int
     return E
 
@@ -198,17 +198,25 @@ def test_oracle_omp_blocks_equal_serial(mpdata, mpo):
     assert mpo.relative_l1(f2, f) == 0.0
 
 
-@pytest.mark.parametrize("ns,nx,nz,signed", CASES)
+EMUL_CASES = [(6, 32, 58, False), (6, 32, 58, True)] + CASES[2:]  # the emulation runs a host thread per CUDA thread: few slices
+
+
+@pytest.mark.parametrize("ns,nx,nz,signed", EMUL_CASES)
 @pytest.mark.parametrize("block,grid", [(64, 1000), (96, 2), (32, 1)])
 def test_device_source_on_host_bit_identical_to_oracle(mpdata, mpo, emul, ns, nx, nz, signed, block, grid):
+    """Every chunk count (level ranges per slice, each recomputing a halo of 3 levels), down to one
+    owned level per CTA, gives the oracle's bits."""
     P = mpdata.TestAdvect(ns, nx, nz).init(seed=11, signed_velocity=signed)
     f, fl = _run_oracle(mpo, P)
-    fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
-    grid = min(grid, ns)
-    rc = emul.mpdata_emul_step(grid, block, ns, nx, nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)])
-    assert rc == 0
-    assert np.array_equal(fe, f)
-    assert np.array_equal(fle, fl)
+    for chunks in sorted({1, 2, 3, 4, 7, nz - 1}):
+        if chunks > nz - 1:
+            continue
+        fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
+        rc = emul.mpdata_emul_step(min(grid, ns * chunks), block, chunks, ns, nx, nz,
+                                   *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)])
+        assert rc == 0
+        assert np.array_equal(fe, f), chunks
+        assert np.array_equal(fle, fl), chunks
 
 
 def test_device_source_on_host_full_block(mpdata, mpo, emul):
@@ -216,21 +224,26 @@ def test_device_source_on_host_full_block(mpdata, mpo, emul):
     P = mpdata.TestAdvect().init(seed=100)
     f, fl = _run_oracle(mpo, P)
     fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
-    assert emul.mpdata_emul_step(5, 1024, P.nslices, P.nx, P.nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)]) == 0
+    assert emul.mpdata_emul_step(5, 1024, 1, P.nslices, P.nx, P.nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)]) == 0
+    assert np.array_equal(fe, f) and np.array_equal(fle, fl)
+    # the shape the library picks at these sizes on a 148-SM part: 3 chunks, 512 threads, 144 CTAs
+    fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
+    assert emul.mpdata_emul_step(144, 512, 3, P.nslices, P.nx, P.nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)]) == 0
     assert np.array_equal(fe, f) and np.array_equal(fle, fl)
 
 
 def test_abi_exports_and_no_fallback(mpdata):
     L = mpdata.lib()
     names = mpdata.declared_symbols()
-    assert "mpdata_advect_scalar2D" in names and len(names) == 11
+    assert "mpdata_advect_scalar2D" in names and len(names) == 13
     for n in names:
         assert hasattr(L, n), n
     # shared-memory budget at the reference sizes: one slice = 7 planes + columns
-    assert L.mpdata_slice_smem_bytes(32, 58) == 8 * (38 * 57 + 2 * 37 * 57 + 2 * 36 * 58 + 2 * 34 * 57 + 6 * 58) == 118272
+    assert L.mpdata_slice_smem_bytes(32, 58) == 8 * (38 * 57 + 2 * 37 * 57 + 36 * 57 + 36 * 58 + 2 * 34 * 57 + 6 * 57) == 117936
     assert L.mpdata_slice_smem_bytes(32, 2) == -1
     assert L.mpdata_set_block(100) != 0 and b"multiple of 32" in L.mpdata_last_error()
-    assert L.mpdata_set_block(1024) == 0
+    assert L.mpdata_set_block(0) == 0 and L.mpdata_set_chunks(0) == 0
+    assert L.mpdata_set_chunks(-1) == 2
     # no CPU fallback: the product source never mentions the oracle, and without a device init fails
     src = open(os.path.join(ROOT, "codesign-kernels_b200", "mpdata.py")).read() + open(
         os.path.join(ROOT, "codesign-kernels_b200", "csrc", "mpdata_b200.cu")
@@ -250,7 +263,7 @@ def test_abi_exports_and_no_fallback(mpdata):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("ns,nx,nz,signed", CASES + [(1000, 32, 58, True), (300, 60, 40, True)])
+@pytest.mark.parametrize("ns,nx,nz,signed", CASES + [(1000, 32, 58, True), (300, 60, 40, True), (200, 24, 400, True)])
 def test_gpu_bit_identical_to_oracle(mpdata, mpo, ns, nx, nz, signed):
     P = mpdata.TestAdvect(ns, nx, nz).init(seed=100, signed_velocity=signed)
     f, fl = _run_oracle(mpo, P)
@@ -274,8 +287,41 @@ def test_gpu_result_independent_of_block_size(mpdata, mpo, block):
         assert L.mpdata_set_block(block) == 0
         P.advect_scalar2D()
     finally:
-        L.mpdata_set_block(1024)
+        L.mpdata_set_block(0)
     assert np.array_equal(P.f, f) and np.array_equal(P.flux, fl)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunks", [1, 2, 3, 5, 57])
+def test_gpu_result_independent_of_chunk_count(mpdata, mpo, chunks):
+    L = mpdata.lib()
+    P = mpdata.TestAdvect().init(seed=6, signed_velocity=True)
+    f, fl = _run_oracle(mpo, P)
+    try:
+        assert L.mpdata_set_chunks(chunks) == 0
+        P.advect_scalar2D()
+        assert mpdata.launch_shape()[2] == chunks
+    finally:
+        L.mpdata_set_chunks(0)
+    assert np.array_equal(P.f, f) and np.array_equal(P.flux, fl)
+
+
+@pytest.mark.gpu
+def test_gpu_automatic_launch_shape(mpdata):
+    """Fewer slices than SMs: the levels are split so that slices x chunks fills the SMs once."""
+    import torch
+
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    L = mpdata.lib()
+    assert L.mpdata_set_chunks(0) == 0 and L.mpdata_set_block(0) == 0
+    assert L.mpdata_init(48, 32, 58) == 0
+    grid, block, chunks, smem = mpdata.launch_shape()
+    assert chunks == max(1, min(sms // 48, 7)) and grid == 48 * chunks and block in (512, 1024)
+    assert L.mpdata_init(4 * sms, 32, 58) == 0
+    assert mpdata.launch_shape()[2] == 1 and mpdata.launch_shape()[3] == 117936
+    # a slice too tall for shared memory is split further instead of being refused
+    assert L.mpdata_init(4 * sms, 32, 400) == 0
+    assert mpdata.launch_shape()[2] > 1 and mpdata.launch_shape()[3] <= 227 * 1024
 
 
 @pytest.mark.gpu
@@ -296,8 +342,8 @@ def test_gpu_life_cycle_and_errors(mpdata, mpo):
     fo, flo = np.empty_like(P.f), P.flux.copy(order="F")
     assert L.mpdata_download(ptr(fo), ptr(flo)) == 0
     assert np.array_equal(fo, f) and np.array_equal(flo, fl)
-    # a slice that cannot fit an SM's shared memory is refused, not silently run elsewhere
-    assert L.mpdata_init(4, 256, 128) == 3 and b"shared memory" in L.mpdata_last_error()
+    # a plane so wide that seven levels of it cannot fit an SM's shared memory is refused, not silently run elsewhere
+    assert L.mpdata_init(4, 4000, 128) == 3 and b"shared memory" in L.mpdata_last_error()
     assert L.mpdata_init(4, 32, 2) == 2
     ms = mpdata.time_steps(mpdata.TestAdvect().init(), iters=5)
     assert 0.0 < ms < 5.0
