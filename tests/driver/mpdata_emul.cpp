@@ -39,7 +39,7 @@ extern "C" int mpdata_emul_step(int grid, int block, int chunks, int ns, int nx,
     if (grid < 1 || block < 1 || block > 1024 || ns < 1 || nx < 1 || nz < 3 || chunks < 1 || chunks > nz - 1) return 1;
     const int nlmax = mpd_dev::max_local_levels(nz - 1, chunks);
     if (mpd_dev::item_doubles(nx, nlmax) * sizeof(double) > sizeof mpd_dev::smem_raw) return 3;
-    for (size_t j = 0; j < sizeof mpd_dev::smem_raw; ++j) mpd_dev::smem_raw[j] = 0xa5;  // shared memory starts uninitialised
+    for (size_t j = 0; j < sizeof mpd_dev::smem_raw; ++j) mpd_dev::smem_raw[j] = 0xff;  // shared memory starts uninitialised: all-ones bytes = NaN, which would poison any output it reached
     const std::vector<double> fin(f, f + (size_t)ns * (nx + 6) * (nz - 1));  // the library ping-pongs two device buffers
     mpd_dev::Problem p{ns, nx, nz, fin.data(), f, u, w, rho, rhow, adz, flux};
     blockDim.x = (unsigned)block;
