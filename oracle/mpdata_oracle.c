@@ -30,6 +30,10 @@
 #define MN(sl, i, k) mn[(sl) + ns * (size_t)((i) + MXW * ((k)-1))]
 #define S2(a, sl, k) a[(sl) + ns * (size_t)((k)-1)]
 
+/* Timing build only (-fopenmp): every level loop of the step is independent across k (the reference's OpenACC forms
+ * collapse the same loops, A:112-227), so threads take levels; no reduction crosses levels, the bits do not change. */
+#define OMP_K _Pragma("omp parallel for schedule(static) private(i, sl, kb, kc, ib, ic)")
+
 /* Fortran MAX/MIN as compare-select (what gfortran -O3 emits; libm fmax/fmin are calls and 2x slower) */
 static inline double dmax(double a, double b) { return a > b ? a : b; }
 static inline double dmin(double a, double b) { return a < b ? a : b; }
@@ -61,6 +65,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
     for (i = -1; i <= nxp2; ++i) /* A:511 */
         for (sl = 0; sl < ns; ++sl) WWW(sl, i, nz) = 0.0;
 
+    OMP_K
     for (k = 1; k <= nzm; ++k) { /* A:513-526 */
         kc = imin(nzm, k + 1);
         kb = imax(1, k - 1);
@@ -73,6 +78,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
             }
     }
 
+    OMP_K
     for (k = 1; k <= nzm; ++k) { /* A:528-548 */
         kb = imax(1, k - 1);
         for (i = -1; i <= nxp3; ++i)
@@ -86,6 +92,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
             for (sl = 0; sl < ns; ++sl) S2(flux, sl, k) = S2(flux, sl, k) + WWW(sl, i, k);
     }
 
+    OMP_K
     for (k = 1; k <= nzm; ++k) { /* A:550-560 */
         for (sl = 0; sl < ns; ++sl) {
             S2(irho, sl, k) = 1.0 / S2(rho, sl, k);
@@ -96,6 +103,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
                 F(sl, i, k) = F(sl, i, k) - (UUU(sl, i + 1, k) - UUU(sl, i, k) + (WWW(sl, i, k + 1) - WWW(sl, i, k)) * S2(iadz, sl, k)) * S2(irho, sl, k);
     }
 
+    OMP_K
     for (k = 1; k <= nzm; ++k) { /* A:561-585 */
         kc = imin(nzm, k + 1);
         kb = imax(1, k - 1);
@@ -120,6 +128,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
     for (i = -1; i <= nxp2; ++i) /* A:586 */
         for (sl = 0; sl < ns; ++sl) WWW(sl, i, 1) = 0.0;
 
+    OMP_K
     for (k = 1; k <= nzm; ++k) { /* A:589-600 */
         kc = imin(nzm, k + 1);
         kb = imax(1, k - 1);
@@ -131,6 +140,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
                 MN(sl, i, k) = dmin(min5(F(sl, ib, k), F(sl, ic, k), F(sl, i, kb), F(sl, i, kc), F(sl, i, k)), MN(sl, i, k));
             }
     }
+    OMP_K
     for (k = 1; k <= nzm; ++k) { /* A:601-612 */
         kc = imin(nzm, k + 1);
         for (i = 0; i <= nxp1; ++i)
@@ -142,6 +152,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
                                (pp(UUU(sl, ic, k)) + pn(UUU(sl, i, k)) + S2(iadz, sl, k) * (pp(WWW(sl, i, kc)) + pn(WWW(sl, i, k))) + eps);
             }
     }
+    OMP_K
     for (k = 1; k <= nzm; ++k) { /* A:613-627 */
         kb = imax(1, k - 1);
         for (i = 1; i <= nxp1; ++i)
@@ -158,6 +169,7 @@ int mpdo_advect_scalar2D_cpu(int ns, int nx, int nz, double *f, const double *u,
             }
     }
 
+    OMP_K
     for (k = 1; k <= nzm; ++k) /* A:630-637 */
         for (i = 1; i <= nx; ++i)
             for (sl = 0; sl < ns; ++sl)

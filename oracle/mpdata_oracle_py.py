@@ -28,14 +28,17 @@ def _load(name):
     return L
 
 
-def advect_scalar2D_cpu(nslices, nx, nz, f, u, w, rho, rhow, adz, flux, omp_block=0):
+def advect_scalar2D_cpu(nslices, nx, nz, f, u, w, rho, rhow, adz, flux, omp_block=0, omp=False):
     """In place on f and flux (Fortran-ordered float64 arrays of the reference's shapes).
-    omp_block > 0 uses the timing build: blocks of that many slices on OpenMP threads."""
+    omp=True uses the timing build (-O3 -fopenmp: threads take levels inside every loop nest, same bits);
+    omp_block > 0 uses the timing build on blocks of that many slices gathered into private copies."""
     arrs = (f, u, w, rho, rhow, adz, flux)
     for a in arrs:
         assert a.flags.f_contiguous and a.dtype == np.float64
     ptrs = [a.ctypes.data for a in arrs]
-    if omp_block:
+    if omp:
+        rc = _load("libmpdata_oracle_omp.so").mpdo_advect_scalar2D_cpu(nslices, nx, nz, *ptrs)
+    elif omp_block:
         rc = _load("libmpdata_oracle_omp.so").mpdo_advect_scalar2D_cpu_blocks(nslices, nx, nz, *ptrs, omp_block)
     else:
         rc = _load("libmpdata_oracle.so").mpdo_advect_scalar2D_cpu(nslices, nx, nz, *ptrs)

@@ -197,6 +197,9 @@ def test_oracle_omp_blocks_equal_serial(mpdata, mpo):
     mpo.advect_scalar2D_cpu(48, 32, 58, f2, P.u, P.w, P.rho, P.rhow, P.adz, fl2, omp_block=5)
     assert np.array_equal(f, f2) and np.array_equal(fl, fl2)
     assert mpo.relative_l1(f2, f) == 0.0
+    f3, fl3 = P.f.copy(order="F"), P.flux.copy(order="F")
+    mpo.advect_scalar2D_cpu(48, 32, 58, f3, P.u, P.w, P.rho, P.rhow, P.adz, fl3, omp=True)  # threads over levels
+    assert np.array_equal(f, f3) and np.array_equal(fl, fl3)
 
 
 EMUL_CASES = [(6, 32, 58, False), (6, 32, 58, True)] + CASES[2:]  # the emulation runs a host thread per CUDA thread: few slices
