@@ -510,3 +510,37 @@ def test_gpu_matches_committed_fixture(mpdata):
     P = _lcg_problem(mpdata)
     P.advect_scalar2D()
     assert _digest(P.f, P.flux) == (pin["f_sha256"], pin["flux_sha256"])
+
+
+# ------------------------------------------------------------------- C++ driver = the reference's `program test_advect`
+
+
+def _build_driver():
+    subprocess.run(["make", "-C", os.path.join(ROOT, "tests", "driver"), "mpdata_driver"], check=True, stdout=subprocess.DEVNULL)
+    return os.path.join(ROOT, "tests", "driver", "mpdata_driver")
+
+
+def test_driver_builds_and_refuses_to_run_without_a_gpu(mpdata):
+    import torch
+
+    exe = _build_driver()
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by test_gpu_driver_prints_the_reference_lines")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1 and "no CPU fallback" in r.stderr
+    assert "CPU Timing:" in r.stdout and "Relative L1" not in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sizes", [[], ["20", "16", "12"], ["300", "32", "58"]])
+def test_gpu_driver_prints_the_reference_lines(mpdata, sizes):
+    """program test_advect (A:2-66) through the C ABI: CPU leg (oracle), the B200 call, then the reference's
+    two acceptance lines -- both exactly zero (the reference's own GPU build printed 2.2e-16 / 8.2e-17)."""
+    import re
+
+    r = subprocess.run([_build_driver()] + sizes, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    vals = dict(re.findall(r"^ (CPU Timing|B200 Timing|Relative L1 Error - f\s*|Relative L1 Error - flux\s*):\s+(\S+)$", r.stdout, flags=re.M))
+    vals = {k.strip(): float(v) for k, v in vals.items()}
+    assert vals["Relative L1 Error - f"] == 0.0 and vals["Relative L1 Error - flux"] == 0.0
+    assert vals["CPU Timing"] > 0.0 and 0.0 < vals["B200 Timing"] < 1e-2
