@@ -334,3 +334,42 @@ def test_gpu_rejects_bad_connectivity(nested):
     nl = nested.NestedLoops()
     with pytest.raises(nested.CkeError, match="outside 1.."):
         nl.cke_init(prob)
+
+
+# ---- oracle-free properties (hold at any size): the flux is linear in the tracer, and scaling by a power of two is exact
+
+
+def _linearity_holds(run, prob):
+    """run(prob) -> highOrderFlx.  flux(4 * tracer) == 4 * flux(tracer) bit for bit (every product and sum
+    scales exactly by a power of two), flux(0) == 0, and reversing the sign of normalThicknessFlux with the
+    3rd-order coefficients zeroed reverses the sign of the flux exactly."""
+    import copy
+
+    base = run(prob)
+    p4 = copy.copy(prob)
+    p4.tracerCur = np.asfortranarray(4.0 * prob.tracerCur)
+    assert np.array_equal(run(p4), 4.0 * base)
+    p0 = copy.copy(prob)
+    p0.tracerCur = np.asfortranarray(0.0 * prob.tracerCur)
+    assert not np.any(run(p0))
+    pm = copy.copy(prob)
+    pm.advCoefs3rd = np.asfortranarray(0.0 * prob.advCoefs3rd)
+    plus = run(pm)
+    pm2 = copy.copy(pm)
+    pm2.normalThicknessFlux = np.asfortranarray(-pm.normalThicknessFlux)
+    assert np.array_equal(run(pm2), -plus)
+    assert np.any(base != 0.0)
+
+
+def test_emulated_device_source_is_linear_in_the_tracer(nested, emul):
+    prob = make(nested, "gpu_target_pack8", ragged=True)
+    _linearity_holds(lambda p: emul(p, 1, 4, 64, 14, unroll=5)[0], prob)
+    _linearity_holds(lambda p: emul(p, 2, 4, 64, 14, unroll=5)[0], prob)
+
+
+@pytest.mark.gpu
+def test_gpu_flux_is_linear_in_the_tracer_at_the_namelist_sizes(nested):
+    """No oracle in the loop: nested.nml sizes, both implementations."""
+    prob = nested.NestedProblem(packn=8, seed=21)
+    _linearity_holds(lambda p: _run_gpu(nested, p, 1)[0], prob)
+    _linearity_holds(lambda p: _run_gpu(nested, p, 2)[0], prob)
