@@ -373,3 +373,38 @@ def test_gpu_flux_is_linear_in_the_tracer_at_the_namelist_sizes(nested):
     prob = nested.NestedProblem(packn=8, seed=21)
     _linearity_holds(lambda p: _run_gpu(nested, p, 1)[0], prob)
     _linearity_holds(lambda p: _run_gpu(nested, p, 2)[0], prob)
+
+
+# ---- race check of the staged kernel: host threads + barrier under ThreadSanitizer
+
+
+def _tsan_run(tmp_path, emul_source=None, tag="real"):
+    drv = os.path.join(ROOT, "tests", "driver")
+    exe = str(tmp_path / f"cke_tsan_{tag}")
+    cmd = ["/usr/bin/g++", "-O1", "-g", "-fsanitize=thread", "-ffp-contract=off", "-std=c++20", "-pthread", "-I" + drv, "-o", exe,
+           os.path.join(drv, "cke_tsan.cpp")]
+    if emul_source:
+        cmd.insert(1, f'-DCKE_EMUL_SOURCE="{emul_source}"')
+    b = subprocess.run(cmd, capture_output=True, text=True)
+    if b.returncode != 0:
+        pytest.skip("ThreadSanitizer build not available here: " + b.stderr[-200:])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600, env=dict(os.environ, TSAN_OPTIONS="halt_on_error=0 exitcode=0"))
+    return r.returncode, r.stdout + r.stderr
+
+
+def test_device_source_has_no_shared_memory_race_under_tsan(tmp_path):
+    """The kernel as shipped is clean; the same kernel without the barrier between staging the edge records and
+    using them is reported -- so the check would see a missing __syncthreads."""
+    rc, out = _tsan_run(tmp_path)
+    assert rc == 0 and out.count(" rc 0 ") == 4, out[-500:]
+    assert "ThreadSanitizer" not in out, out[-800:]
+    src = open(os.path.join(ROOT, "codesign-kernels_b200", "csrc", "cke_kernels.cuh")).read()
+    at = src.index("// ---- phase B")
+    cut = src.rfind("__syncthreads();", 0, at)
+    (tmp_path / "cke_kernels_nobarrier.cuh").write_text(src[:cut] + "/* barrier removed */" + src[cut + len("__syncthreads();"):])
+    emu = open(os.path.join(ROOT, "tests", "driver", "cke_emul.cpp")).read()
+    inc = '#include "../../codesign-kernels_b200/csrc/cke_kernels.cuh"'
+    assert inc in emu
+    (tmp_path / "cke_emul_nobarrier.cpp").write_text(emu.replace(inc, f'#include "{tmp_path}/cke_kernels_nobarrier.cuh"'))
+    rc, out = _tsan_run(tmp_path, str(tmp_path / "cke_emul_nobarrier.cpp"), tag="nobarrier")
+    assert "ThreadSanitizer: data race" in out

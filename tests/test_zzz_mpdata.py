@@ -544,3 +544,40 @@ def test_gpu_driver_prints_the_reference_lines(mpdata, sizes):
     vals = {k.strip(): float(v) for k, v in vals.items()}
     assert vals["Relative L1 Error - f"] == 0.0 and vals["Relative L1 Error - flux"] == 0.0
     assert vals["CPU Timing"] > 0.0 and 0.0 < vals["B200 Timing"] < 1e-2
+
+
+# ------------------------------------------------------------------- race check of the barrier-phased kernel
+
+
+def _tsan_run(tmp_path, emul_source=None, tag="real"):
+    drv = os.path.join(ROOT, "tests", "driver")
+    exe = str(tmp_path / f"mpdata_tsan_{tag}")
+    cmd = ["/usr/bin/g++", "-O1", "-g", "-fsanitize=thread", "-ffp-contract=off", "-std=c++20", "-pthread", "-I" + drv, "-o", exe,
+           os.path.join(drv, "mpdata_tsan.cpp")]
+    if emul_source:
+        cmd.insert(1, f'-DMPDATA_EMUL_SOURCE="{emul_source}"')
+    b = subprocess.run(cmd, capture_output=True, text=True)
+    if b.returncode != 0:
+        pytest.skip("ThreadSanitizer build not available here: " + b.stderr[-200:])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600, env=dict(os.environ, TSAN_OPTIONS="halt_on_error=0 exitcode=0"))
+    return r.returncode, r.stdout + r.stderr
+
+
+def test_device_source_has_no_race_between_phases_under_tsan(tmp_path):
+    """CUDA threads as host threads, __syncthreads as a barrier, ThreadSanitizer watching shared memory: the kernel
+    as shipped is clean (chunks 1 and 3), and the same kernel with ONE barrier removed is reported -- so the check
+    would see a missing __syncthreads."""
+    rc, out = _tsan_run(tmp_path)
+    assert rc == 0 and "chunks 1 rc 0" in out and "chunks 3 rc 0" in out
+    assert "ThreadSanitizer" not in out, out[-800:]
+    # negative control
+    src = open(os.path.join(ROOT, "codesign-kernels_b200", "csrc", "mpdata_kernels.cuh")).read()
+    at = src.index("        // ---- P3: antidiffusive fluxes")
+    cut = src.rfind("__syncthreads();", 0, at)
+    (tmp_path / "mpdata_kernels_nobarrier.cuh").write_text(src[:cut] + "/* barrier removed */" + src[cut + len("__syncthreads();"):])
+    emu = open(os.path.join(ROOT, "tests", "driver", "mpdata_emul.cpp")).read()
+    inc = '#include "../../codesign-kernels_b200/csrc/mpdata_kernels.cuh"'
+    assert inc in emu
+    (tmp_path / "mpdata_emul_nobarrier.cpp").write_text(emu.replace(inc, f'#include "{tmp_path}/mpdata_kernels_nobarrier.cuh"'))
+    rc, out = _tsan_run(tmp_path, str(tmp_path / "mpdata_emul_nobarrier.cpp"), tag="nobarrier")
+    assert "ThreadSanitizer: data race" in out
