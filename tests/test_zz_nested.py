@@ -1,11 +1,12 @@
 """nested_loops mini-app: the MPAS-Ocean high-order flux loop behind the reference's
 own C interface (nested_loops/cke.hpp:7-23).
 
-PARITY UNPINNED: the reference holds no outputs for this kernel (inputs come from the compiler's
-random_number).  What it holds is its acceptance test -- every loop form within errTol = 1e-10 of
-the original CPU form (nested_vars.F90:33, nested.F90:267-279) -- reproduced here for the oracle's
-forms, for the host emulation of the device source, and (GPU) for the CUDA path, which is also
-required to be BIT-IDENTICAL to the oracle's cke_impl1 / cke_impl2 restatements.
+PARITY PINNED ON THE REFERENCE COMPILED HERE: oracle/_ref/libnested_yakl_ref.so is the reference's
+own C++ (nested_loops/nested_yakl_c.cpp:142-306 on the vendored YAKL headers, host back end) built by
+`make -C oracle ref` from the sources where they lie.  oracle/cke_oracle.c is checked against it bit
+for bit (and with the reference's own criterion, errTol = 1e-10, nested.F90:267-279), and the -m gpu
+tests compare the CUDA path with it directly.  The reference holds no stored outputs (inputs come from
+the compiler's random_number), so "the reference run here on the same inputs" is the pin.
 
 This file sorts last on purpose: the -m gpu tests here are the newest in the suite.
 """
@@ -35,6 +36,16 @@ def cko():
 
     subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, stdout=subprocess.DEVNULL)
     return cke_oracle_py
+
+
+@pytest.fixture(scope="module")
+def yref():
+    """The reference's own C++ (oracle/_ref).  Built here from /root/reference; on the GPU box the prebuilt .so travels."""
+    import ref_yakl_py
+
+    if not ref_yakl_py.available():
+        pytest.skip("oracle/_ref/libnested_yakl_ref.so absent and /root/reference not present to build it")
+    return ref_yakl_py
 
 
 def numpy_reference(prob):
@@ -102,6 +113,55 @@ def test_oracle_forms_agree_like_the_reference_check(nested, cko, name, ragged):
         assert bad == 0, (label, bad, worst)
         # with 0/1 masks and tracers that vanish outside the level range the forms are equal bit for bit
         assert np.array_equal(flx[: prob.nVertLevels], ref[: prob.nVertLevels]), label
+
+
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("ragged", [False, True])
+def test_oracle_is_pinned_on_the_reference_compiled_here(nested, cko, yref, name, ragged):
+    """oracle/cke_oracle.c against the reference's own yakl_original_loop / yakl_gpu_optimized
+    (nested_yakl_c.cpp:184-243, 260-306) on the same inputs: bit for bit on the nVertLevels rows the
+    reference writes (it leaves the F90_PACK_SIZE padding rows of highOrderFlx unset), and zero
+    failures of the reference's own errTol test."""
+    prob = make(nested, name, ragged)
+    nv = prob.nVertLevels
+    r = yref.RefProblem(prob)
+    ref_orig, ref_opt = r.original_loop(), r.gpu_optimized()
+    assert np.array_equal(cko.original_cpu(prob)[:nv], ref_orig[:nv])
+    assert np.array_equal(cko.gpu_optimized(prob)[:nv], ref_opt[:nv])
+    assert np.array_equal(cko.impl2(prob)[:nv], ref_orig[:nv])  # cke_impl2 = the level-range form
+    assert np.array_equal(cko.impl1(prob)[0][:nv], ref_opt[:nv])  # cke_impl1 = the cellMask form (0/1 masks)
+    bad, worst = cko.check(ref_opt, ref_orig, prob, nested.ERR_TOL)
+    assert bad == 0, worst
+
+
+def test_oracle_vs_reference_with_general_masks(nested, cko, yref):
+    """Non-0/1 cellMask and tracers that do not vanish outside the level range: the two reference forms differ from
+    each other, and each oracle form still follows its own reference form bit for bit."""
+    prob = make(nested, "gpu_target_pack8", ragged=True)
+    rng = np.random.default_rng(5)
+    prob.cellMask = np.asfortranarray(rng.random(prob.cellMask.shape))
+    prob.tracerCur = np.asfortranarray(15.0 * rng.random(prob.tracerCur.shape))
+    nv = prob.nVertLevels
+    r = yref.RefProblem(prob)
+    ref_orig, ref_opt = r.original_loop(), r.gpu_optimized()
+    assert not np.array_equal(ref_orig[:nv], ref_opt[:nv])
+    assert np.array_equal(cko.original_cpu(prob)[:nv], ref_orig[:nv])
+    assert np.array_equal(cko.gpu_optimized(prob)[:nv], ref_opt[:nv])
+    # (cke_impl2 multiplies by cellMask inside the level range, cke_impl2.cpp:58-59, so with a fractional mask it is
+    # neither of the two YAKL forms; it is pinned on them through the 0/1-mask cases above.)
+
+
+def test_oracle_vs_reference_at_the_namelist_sizes(nested, cko, yref):
+    """nested.nml:1-7 as shipped, both paddings (F90_PACK_SIZE 1 and 8)."""
+    for packn in (1, 8):
+        prob = nested.NestedProblem(packn=packn, seed=11)
+        nv = prob.nVertLevels
+        r = yref.RefProblem(prob)
+        ref_orig, ref_opt = r.original_loop(), r.gpu_optimized()
+        assert np.array_equal(cko.original_cpu(prob)[:nv], ref_orig[:nv])
+        assert np.array_equal(cko.gpu_optimized(prob)[:nv], ref_opt[:nv])
+        bad, worst = cko.check(ref_opt, ref_orig, prob, nested.ERR_TOL)
+        assert bad == 0 and worst == 0.0
 
 
 def test_oracle_known_answer_by_hand(nested, cko):
@@ -325,6 +385,37 @@ def test_gpu_general_masks_follow_each_form(nested, cko):
     assert np.array_equal(out, w) and np.array_equal(tracer, tr)
     out2, _, _, _ = _run_gpu(nested, prob, 2)
     assert np.array_equal(out2, cko.impl2(prob))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("ragged", [False, True])
+def test_gpu_bit_identical_to_the_reference_compiled_here(nested, yref, name, ragged):
+    """The CUDA path against oracle/_ref directly (no restatement in the loop): cke_impl1 == the reference's
+    yakl_gpu_optimized and cke_impl2 == its yakl_original_loop, bit for bit on the rows the reference writes."""
+    prob = make(nested, name, ragged)
+    nv = prob.nVertLevels
+    r = yref.RefProblem(prob)
+    out1, _, _, _ = _run_gpu(nested, prob, 1)
+    assert np.array_equal(out1[:nv], r.gpu_optimized()[:nv])
+    out2, _, _, _ = _run_gpu(nested, prob, 2)
+    assert np.array_equal(out2[:nv], r.original_loop()[:nv])
+
+
+@pytest.mark.gpu
+def test_gpu_namelist_problem_against_the_reference_compiled_here(nested, yref):
+    """nested.nml:1-7 as shipped at the GPU target's padding; errTol test of nested.F90:267-279 against the
+    reference's own original loop, and in fact bit-identical."""
+    prob = nested.NestedProblem(packn=8, seed=11)
+    nv = prob.nVertLevels
+    r = yref.RefProblem(prob)
+    ref_orig = r.original_loop()
+    out1, _, _, _ = _run_gpu(nested, prob, 1, iters=3)
+    out2, _, _, _ = _run_gpu(nested, prob, 2, iters=3)
+    for out in (out1, out2):
+        rel = np.abs(out[:nv] - ref_orig[:nv]) / np.maximum(np.abs(ref_orig[:nv]), 1e-300)
+        assert (rel <= nested.ERR_TOL).all()
+        assert np.array_equal(out[:nv], ref_orig[:nv])
 
 
 @pytest.mark.gpu
