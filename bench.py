@@ -106,72 +106,171 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_baseline(ne, nlev, qsize, reps, want_serial=False):
-    """The oracle (C port of F90:100-202 + DSS) with OpenMP over elements on all host cores."""
-    import numpy as np
+def _host_threads():
+    """Threads the CPU legs may use: the cores this process may run on.  torchrun exports OMP_NUM_THREADS=1 to its
+    workers; the CPU arm must not inherit that (round 1's N>1 reference lines ran on one core)."""
+    forced = os.environ.get("BWK_CPU_THREADS")
+    n = int(forced) if forced else len(os.sched_getaffinity(0))
+    os.environ["OMP_NUM_THREADS"] = str(n)  # before libbwk_oracle_omp.so (libgomp) is loaded
+    return n
 
+
+def _oracle():
+    _host_threads()
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_py as orc
 
     orc.build()
-    n = 6 * ne * ne
-    dvv, elem, q0 = orc.initialize_data(n, nlev, qsize)
-    dss = orc.Dss(n, orc.cubed_sphere_gdof(ne))
-    rs = dss.rspheremp(elem)
+    return orc
+
+
+class CpuProblem:
+    """One cubed sphere on the host for the CPU oracle (C port of F90:100-202 + DSS, OpenMP over elements)."""
+
+    def __init__(self, orc, ne, nlev, qsize):
+        self.orc, self.ne, self.nlev, self.qsize = orc, ne, nlev, qsize
+        self.n = 6 * ne * ne
+        self.dvv, self.elem, self.q = orc.initialize_data_parallel(self.n, nlev, qsize)
+        self.dss = orc.Dss(self.n, orc.cubed_sphere_gdof(ne))
+        self.rs = self.dss.rspheremp(self.elem)
+        self.updates = 16.0 * nlev * qsize * self.n
+
+    def reinit(self):
+        self.orc.initialize_data_parallel(self.n, self.nlev, self.qsize, qtens=self.q)
+
+    def step_full(self):
+        t = time.perf_counter()
+        self.dss.biharmonic_full(self.elem, self.rs, self.q, self.dvv, omp=True)
+        return time.perf_counter() - t
+
+    def step_laplace(self, omp=True):
+        t = time.perf_counter()
+        self.orc.biharmonic_wk_scalar_cpu(self.elem, self.q, self.dvv, omp=omp)
+        return time.perf_counter() - t
+
+    def label(self):
+        return f"ne{self.ne}np4 L{self.nlev} q{self.qsize} ({self.n} elements)"
+
+
+def _host_mem_available_gb():
+    try:
+        import psutil
+
+        return psutil.virtual_memory().available / 2**30
+    except Exception:
+        return 0.0
+
+
+def cpu_baseline(ne_small, nlev, qsize, reps, want_serial=False, ne_full=None, full_budget_s=25.0):
+    """The oracle with OpenMP over elements on all host cores: a small sphere (ne_small) timed `reps` times and, when
+    host memory and the time budget allow, ONE step of the headline sphere itself (ne_full)."""
+    orc = _oracle()
     cores = orc.lib(omp=True).bwko_omp_max_threads()
+    pr = CpuProblem(orc, ne_small, nlev, qsize)
     times, lap_times = [], []
     for _ in range(reps):
-        q = q0.copy(order="F")
-        t = time.perf_counter()
-        dss.biharmonic_full(elem, rs, q, dvv, omp=True)
-        times.append(time.perf_counter() - t)
-        q = q0.copy(order="F")
-        t = time.perf_counter()
-        orc.biharmonic_wk_scalar_cpu(elem, q, dvv, omp=True)
-        lap_times.append(time.perf_counter() - t)
-    updates = 16.0 * nlev * qsize * n
+        pr.reinit()
+        times.append(pr.step_full())
+        pr.reinit()
+        lap_times.append(pr.step_laplace())
     out = {
-        "value": updates / min(times), "unit": UNIT, "cores": cores, "kind": "port",
-        "sample": f"ne{ne}np4 L{nlev} q{qsize} ({n} elements), full biharmonic, OpenMP over elements, best of {reps}",
+        "value": pr.updates / min(times), "unit": UNIT, "cores": cores, "kind": "port",
+        "sample": f"{pr.label()}, full biharmonic, OpenMP over elements, best of {reps}",
         "times_s": [round(t, 4) for t in times],
-        "laplace_only_value": updates / min(lap_times),
+        "laplace_only_value": pr.updates / min(lap_times),
     }
     if want_serial:
-        q = q0.copy(order="F")
-        t = time.perf_counter()
-        orc.biharmonic_wk_scalar_cpu(elem, q, dvv)
-        out["laplace_only_serial_value"] = updates / (time.perf_counter() - t)
+        pr.reinit()
+        out["laplace_only_serial_value"] = pr.updates / pr.step_laplace(omp=False)
         out["serial_note"] = "1 core, no OpenMP: the reference's own CPU path is serial (no !$omp in atmosphere/)"
+    small_rate = out["value"]
+    del pr
+    if ne_full and ne_full != ne_small:
+        need_gb = 128.0 * nlev * qsize * 6 * ne_full * ne_full / 2**30 * 1.15 + 2
+        predicted = 16.0 * nlev * qsize * 6 * ne_full * ne_full / small_rate
+        if _host_mem_available_gb() > need_gb and predicted < full_budget_s:
+            pf = CpuProblem(orc, ne_full, nlev, qsize)
+            t = pf.step_full()
+            out["small_sample_value"] = small_rate
+            out["small_sample"] = out["sample"]
+            out["value"] = pf.updates / t
+            out["sample"] = f"{pf.label()} = the headline workload itself, full biharmonic, OpenMP over elements, 1 step of {t:.2f} s"
+            del pf
+        else:
+            out["full_config_skipped"] = f"ne{ne_full} needs {need_gb:.0f} GB of host memory and ~{predicted:.0f} s per step"
     return out
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU implementation of the path (C oracle port; the
-    Fortran original cannot be compiled here) on a bounded sample, all host threads."""
+    """--impl reference: the reference's CPU implementation of the path (C oracle port; the Fortran original cannot be
+    compiled here) with all the host threads it can use, on rank 0 only.  Each step is one pass over the HEADLINE sphere
+    (ne120 L72 q40, 32 GB on the host) when host memory allows and the K+W steps fit a few minutes; otherwise over the
+    largest smaller sphere of the same L/q that does (the rate of this streaming loop does not depend on ne; said in
+    `cpu_baseline.sample`)."""
     if rank != 0:
         return
-    ne_s = args.cpu_ne
+    orc = _oracle()
+    cores = orc.lib(omp=True).bwko_omp_max_threads()
+    nsteps = args.warmup + args.steps
+    # probe: one step of the small sphere -> rate -> the largest sphere whose K+W steps (plus re-initialisation) fit the budget
+    probe = CpuProblem(orc, args.cpu_ne, args.nlev, args.qsize)
+    probe.step_full()
+    probe.reinit()
+    rate = probe.updates / probe.step_full()
+    del probe
+    budget_s = float(os.environ.get("BWK_REF_BUDGET_S", "200"))
+    mem = _host_mem_available_gb()
+    ne_s, why = args.cpu_ne, ""
+    for ne_c in sorted({args.ne, 90, 60, args.cpu_ne}, reverse=True):
+        if ne_c > args.ne:
+            continue
+        upd = 16.0 * args.nlev * args.qsize * 6 * ne_c * ne_c
+        need_gb = 8.0 * upd / 2**30 * 1.15 + 2
+        t_step = upd / rate
+        if mem > need_gb and nsteps * t_step * 1.25 < budget_s:
+            ne_s = ne_c
+            break
+        why += f"ne{ne_c}: {need_gb:.0f} GB, {nsteps} x {t_step:.1f} s; "
+    pr = CpuProblem(orc, ne_s, args.nlev, args.qsize)
     times = []
-    res = None
-    for i in range(args.warmup + args.steps):
-        res = cpu_baseline(ne_s, args.nlev, args.qsize, 1)
+    for i in range(nsteps):
+        pr.reinit()  # untimed, as the GPU arm re-generates its inputs before every step
+        dt = pr.step_full()
         if i >= args.warmup:
-            times.append(res["times_s"][0])
-    n = 6 * ne_s * ne_s
-    updates = 16.0 * args.nlev * args.qsize * n
+            times.append(dt)
     tot = sum(times)
-    value = updates * len(times) / tot
+    value = pr.updates * len(times) / tot
+    same = ne_s == args.ne
+    sample = (f"{pr.label()}{' = the headline workload itself' if same else ' (smaller sphere, same L/q: ' + why + 'over the budget)'}, "
+              f"full biharmonic, OpenMP over elements on {cores} threads, {len(times)} timed steps")
+    nglob = 6 * args.ne * args.ne
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * tot / len(times), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic (reference LCG, F90:77-91)",
-        "config": {"workload": f"ne{args.ne}np4 L{args.nlev} q{args.qsize}, {6 * args.ne * args.ne} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
-                   "sample": res["sample"]},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": res["cores"], "kind": "port", "sample": res["sample"]},
+        "config": workload_config(args.ne, args.nlev, args.qsize, nglob, world, args.variant),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "same_config": same,
+                         "probe_rate_small_sphere": rate, "probe_sample": f"ne{args.cpu_ne}np4 L{args.nlev} q{args.qsize}"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def workload_config(ne, nlev, qsize, nglob, world, variant):
+    """`config` of the JSON line, identical for both arms"""
+    return {"workload": f"ne{ne}np4 L{nlev} q{qsize}, {nglob} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
+            "partition": f"contiguous element blocks over {world} rank(s)",
+            "l2": "working set >> L2 (no flush needed); inputs re-generated before every step", "variant": variant}
+
+
+def expected_checksum(ne, nlev, qsize):
+    """bit checksum of the full biharmonic of the LCG inputs recorded from a 1-GPU run (profiles/expected_checksums.json)"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "expected_checksums.json")) as f:
+            return json.load(f).get(f"ne{ne}_L{nlev}_q{qsize}_full")
+    except Exception:
+        return None
 
 
 def main():
@@ -191,6 +290,7 @@ def main():
     ap.add_argument("--no-dp3d", action="store_true", help="skip the biharmonic_wk_dp3d (SURVEY 8(f)3) timing")
     ap.add_argument("--no-mini", action="store_true", help="skip the two mini-app timings (nested_loops, mmf-mpdata-tracer; SURVEY 8(f)4)")
     ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--pcie", action="store_true", help="also at N=1: time plain pinned H2D/D2H copies next to the e2e call")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -274,6 +374,21 @@ def main():
     tot_ms, launches, wall = timed_steps(ku.run_biharmonic_device, args.warmup, args.steps)
     ms_per_step = tot_ms / args.steps
     value = updates_global / (ms_per_step * 1e-3)
+
+    # ---- checksum of the last timed step's result: the bit checksum does not depend on the partition (per-rank values
+    #      add up mod 2^64), so the lines of N = 1, 2, 4, 8 prove "N ranks == 1 rank bit for bit" by themselves
+    ck_local = (ku.checksum_bits(first),) + tuple(ku.checksum())
+    if world > 1:
+        ck_all = [None] * world
+        dist.all_gather_object(ck_all, ck_local)
+    else:
+        ck_all = [ck_local]
+    bits = sum(c[0] for c in ck_all) % (1 << 64)
+    want = expected_checksum(ne, nlev, qsize)
+    checksum = {"bits": f"{bits:016x}", "sum": sum(c[1] for c in ck_all), "sumsq": sum(c[2] for c in ck_all),
+                "expected_bits": want, "match": (f"{bits:016x}" == want) if want else None,
+                "note": "bits = sum over values of mix64(bits)*(2*global_index+1) mod 2^64 of the last timed step's qtens (partition-independent); "
+                        "sum/sumsq are floating-point sums in rank order (last bits may depend on N); expected = 1-GPU run recorded in profiles/expected_checksums.json"}
 
     # ---- reference-pinned single Laplacian on the same data
     lap_ms, lap_launches, _ = timed_steps(lambda: ku.run_device(1, count), 1, args.steps)
@@ -390,9 +505,40 @@ def main():
                 if i >= 1:
                     tot += max_over_ranks(dt)
             bytes_q = 8.0 * es * count
+            pcie = None
+            if world > 1 or args.pcie:
+                # what the host side of this box gives every rank when all ranks copy at once: the
+                # e2e call cannot go faster than min(h2d, d2h) together
+                nb = min(int(bytes_q), 4 << 30)
+                hbuf = torch.from_numpy(hq.reshape(-1, order="F")[: nb // 8])
+                dbuf = torch.empty(nb // 8, dtype=torch.float64, device="cuda")
+                dbuf2 = torch.empty(nb // 8, dtype=torch.float64, device="cuda")
+                s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+                def timed_copy(up, down):
+                    barrier()
+                    t0 = time.perf_counter()
+                    if up:
+                        with torch.cuda.stream(s1):
+                            dbuf.copy_(hbuf, non_blocking=True)
+                    if down:
+                        with torch.cuda.stream(s2):
+                            hbuf2.copy_(dbuf2, non_blocking=True)
+                    torch.cuda.synchronize()
+                    return max_over_ranks(time.perf_counter() - t0)
+
+                hbuf2 = torch.from_numpy(hq.reshape(-1, order="F")[nb // 8: 2 * (nb // 8)]) if 2 * nb <= bytes_q else torch.empty(nb // 8, dtype=torch.float64).pin_memory()
+                timed_copy(True, True)
+                pcie = {"bytes_per_copy": nb, "ranks_concurrent": world,
+                        "h2d_alone_GBps_per_rank": nb / timed_copy(True, False) / 1e9,
+                        "d2h_alone_GBps_per_rank": nb / timed_copy(False, True) / 1e9,
+                        "both_GBps_per_rank_per_direction": nb / timed_copy(True, True) / 1e9,
+                        "note": "all ranks copy at the same time from/to pinned host memory (cudaMemcpyAsync through torch); slowest rank"}
+                del dbuf, dbuf2
             e2e = {"value": updates_global * nst / tot, "unit": UNIT, "h2d_bytes_per_step": bytes_q + 1152.0 * count + 128,
                    "d2h_bytes_per_step": bytes_q, "ms_per_step": 1e3 * tot / nst, "steps": nst,
-                   "api": "bwk_biharmonic_wk_scalar_full(elem, qtens, deriv) with pinned host arrays, host wall clock"}
+                   "api": "bwk_biharmonic_wk_scalar_full(elem, qtens, deriv) with pinned host arrays, host wall clock",
+                   "GBps_per_rank_per_direction": bytes_q / (tot / nst) / 1e9, "pcie": pcie}
         except Exception as ex:  # e.g. not enough pinned host memory
             e2e = {"value": None, "unit": UNIT, "error": str(ex)[:200]}
 
@@ -401,7 +547,7 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_baseline(args.cpu_ne, nlev, qsize, 3, want_serial=True)
+        cpu = cpu_baseline(args.cpu_ne, nlev, qsize, 3, want_serial=True, ne_full=ne)
 
     # ---- biharmonic_wk_dp3d: T, v, dp3d of every level, its own context (qsize = 4), device resident
     dp3d = None
@@ -454,9 +600,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (reference LCG F90:77-91, generated on the device; cubed-sphere connectivity SURVEY App. D)",
-            "config": {"workload": f"ne{ne}np4 L{nlev} q{qsize}, {nglob} elements, full biharmonic (Laplace -> DSS -> rspheremp -> Laplace)",
-                       "partition": f"contiguous element blocks over {world} rank(s)", "l2": "working set >> L2 (no flush needed); inputs re-generated before every step",
-                       "variant": args.variant},
+            "config": workload_config(ne, nlev, qsize, nglob, world, args.variant), "checksum": checksum,
             "laplace_only": lap, "advance_hypervis_scalar": hv, "biharmonic_wk_dp3d": dp3d, "mini_apps": mini, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)

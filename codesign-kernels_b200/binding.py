@@ -71,6 +71,7 @@ def lib():
         "bwk_save_qtens": [],
         "bwk_compute_l2norm": [dp],
         "bwk_checksum": [dp, dp],
+        "bwk_checksum_bits": [i64, C.POINTER(C.c_uint64)],
         "bwk_periodicity_defect": [i64, dp],
         "bwk_download_elements": [i64, i64, p],
         "bwk_upload_elements": [i64, i64, p],
@@ -381,6 +382,12 @@ class KernelUtils:
         a, b = C.c_double(), C.c_double()
         _ck(lib().bwk_checksum(C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def checksum_bits(self, elem_first_global=0):
+        """partition-independent checksum of the field's bits (per-rank values add up mod 2^64)"""
+        h = C.c_uint64()
+        _ck(lib().bwk_checksum_bits(elem_first_global, C.byref(h)))
+        return h.value
 
     def periodicity_defect(self, period_elems):
         v = C.c_double()

@@ -1024,6 +1024,22 @@ int bwk_checksum(double *sum, double *sumsq)
     return 0;
 }
 
+int bwk_checksum_bits(int64_t elem_first_global, uint64_t *hash)
+{
+    if (need_init()) return 1;
+    if (elem_first_global < 0 || !hash) return fail("bad arguments");
+    static_assert(sizeof(unsigned long long) == sizeof(double), "partials buffer is reused");
+    unsigned long long *dp = reinterpret_cast<unsigned long long *>(g.d_partials), *hp = reinterpret_cast<unsigned long long *>(g.h_partials);
+    CK(launch_bits_checksum(g.d_q, (int64_t)g.q_doubles, (uint64_t)elem_first_global * 16ull * (uint64_t)g.kq, dp, NPARTIAL_BLOCKS, g.s_main));
+    g.launches++;
+    CK(cudaMemcpyAsync(hp, dp, sizeof(unsigned long long) * NPARTIAL_BLOCKS, cudaMemcpyDeviceToHost, g.s_main));
+    CK(cudaStreamSynchronize(g.s_main));
+    unsigned long long a = 0;
+    for (int i = 0; i < NPARTIAL_BLOCKS; ++i) a += hp[i];
+    *hash = a;
+    return 0;
+}
+
 int bwk_periodicity_defect(int64_t period_elems, double *max_abs_diff)
 {
     if (need_init()) return 1;

@@ -1606,6 +1606,36 @@ __global__ void period_defect_kernel(const double *__restrict__ q, int64_t n, in
     block_reduce_store<1>(acc, partials, true);
 }
 
+// Partition-independent checksum of the BITS of the field: sum over values of mix64(bits) * (2*global_index + 1) mod 2^64.
+// Integer addition is associative and commutative, so the per-rank sums of any contiguous partition add up to the 1-rank
+// value exactly: equal checksums <=> (up to 2^-64) bit-identical fields in identical global positions.
+__global__ void bits_checksum_kernel(const double *__restrict__ q, int64_t n, uint64_t index0, unsigned long long *partials)
+{
+    unsigned long long acc = 0;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+        uint64_t x = (uint64_t)__double_as_longlong(q[t]);
+        x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+        x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+        x ^= x >> 31;
+        acc += x * (2ull * (index0 + (uint64_t)t) + 1ull);
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    __shared__ unsigned long long sh[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) sh[warp] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long a = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) a += sh[w];
+        partials[blockIdx.x] = a;
+    }
+}
+cudaError_t launch_bits_checksum(const double *q, int64_t n, uint64_t index0, unsigned long long *partials, int nblocks, cudaStream_t st)
+{
+    bits_checksum_kernel<<<nblocks, 256, 0, st>>>(q, n, index0, partials);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_l2_partials(const double *q, const double *qs, int64_t n, double *partials, int nblocks, cudaStream_t st)
 {
     l2_partials_kernel<<<nblocks, 256, 0, st>>>(q, qs, n, partials);

@@ -88,6 +88,8 @@ cudaError_t launch_init_data(const double *table, int64_t nelemd_global, int64_t
                              int seed_mode, double *elem, double *qtens, cudaStream_t st);
 cudaError_t launch_l2_partials(const double *q, const double *qs, int64_t n, double *partials /*[2*nblocks]*/, int nblocks, cudaStream_t st);
 cudaError_t launch_sum_partials(const double *q, int64_t n, double *partials /*[2*nblocks]*/, int nblocks, cudaStream_t st);
+// bit checksum: partials[b] = sum over the block's values of mix64(bits) * (2*(index0 + t) + 1) mod 2^64
+cudaError_t launch_bits_checksum(const double *q, int64_t n, uint64_t index0, unsigned long long *partials /*[nblocks]*/, int nblocks, cudaStream_t st);
 cudaError_t launch_period_defect(const double *q, int64_t n, int64_t period, double *partials /*[nblocks]*/, int nblocks, cudaStream_t st);
 
 } // namespace bwk

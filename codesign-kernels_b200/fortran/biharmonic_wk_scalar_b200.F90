@@ -75,10 +75,19 @@ module biharmonic_wk_scalar_b200
 
 contains
 
-  !! once, after allocate_data(): the analogue of `!$acc enter data pcreate(...)` (F90:553)
-  subroutine b200_init()
+  !! once, after allocate_data(): the analogue of `!$acc enter data pcreate(...)` (F90:553).
+  !! Without arguments the context takes kernel_utils' compile-time nlev and qsize (F90:11-13), which is what
+  !! biharmonic_wk_scalar and advance_hypervis_scalar need.  biharmonic_wk_dp3d works on four fields per level
+  !! (T, v(1), v(2), dp3d) and needs its own context: call b200_finalize(), then b200_init(qsize_ctx=4).
+  subroutine b200_init(nlev_ctx, qsize_ctx)
     implicit none
-    if (bwk_init(int(nelemd,c_int), int(nlev,c_int), int(qsize,c_int)) /= 0) error stop "bwk_init failed"
+    integer, intent(in), optional :: nlev_ctx, qsize_ctx
+    integer :: nl, nq
+    nl = nlev
+    nq = qsize
+    if (present(nlev_ctx)) nl = nlev_ctx
+    if (present(qsize_ctx)) nq = qsize_ctx
+    if (bwk_init(int(nelemd,c_int), int(nl,c_int), int(nq,c_int)) /= 0) error stop "bwk_init failed"
   end subroutine b200_init
 
   subroutine b200_finalize()
@@ -119,7 +128,8 @@ contains
 
   !! Upstream HOMME biharmonic_wk_dp3d (viscosity_mod), kernel-extraction style: the state the upstream routine reads through
   !! elem(ie)%state is passed in the output arrays (ttens = T, dptens = dp3d, vtens = v on entry, as qtens is the input
-  !! of biharmonic_wk_scalar), elem(ie)%vec_sphere2cart as a plain array.  Needs b200_init(nelemd, nlev, 4) and a topology.
+  !! of biharmonic_wk_scalar), elem(ie)%vec_sphere2cart as a plain array.  Needs a context made with b200_init(qsize_ctx=4)
+  !! (the library rejects any other qsize for this call) and a topology.
   !!   dptens, ttens (np,np,nlev,nelemd) ; vtens (np,np,2,nlev,nelemd) ; vec_sphere2cart (np,np,3,2,nelemd)
   !!   var_coef1 = .false.: no tensorVisc in the first application (hypervis_scaling > 0 upstream)
   subroutine biharmonic_wk_dp3d(elem,vec_sphere2cart,dptens,ttens,vtens,deriv,var_coef1,undamprrcart)

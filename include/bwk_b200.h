@@ -111,6 +111,11 @@ int bwk_save_qtens(void);
 int bwk_compute_l2norm(double *l2);
 /* sum and sum of squares of the device qtens (checksums for size-independent tests) */
 int bwk_checksum(double *sum, double *sumsq);
+/* checksum of the BITS of the device qtens that does not depend on how the elements are split over ranks:
+ * sum over values of mix64(bits) * (2*global_index + 1) mod 2^64, global_index counted from global element
+ * `elem_first_global`.  The per-rank values of any contiguous partition add up (mod 2^64) to the 1-rank value,
+ * so equal sums prove "N ranks == 1 rank bit for bit" (bench.py prints it for every N). */
+int bwk_checksum_bits(int64_t elem_first_global, uint64_t *hash);
 /* max_i |q_i - q_{i mod period}| over the device qtens, period in elements (LCG inputs
  * repeat every 8192 elements, so must the reference-pinned output) */
 int bwk_periodicity_defect(int64_t period_elems, double *max_abs_diff);

@@ -86,6 +86,35 @@ def initialize_subset(nelemd_total, nlev, qsize, first, count):
     return dvv, elem, qtens
 
 
+def initialize_data_parallel(nelemd, nlev, qsize, threads=None, qtens=None):
+    """initialize_data (F90:48-58) through the closed form of the LCG (bwko_initialize_subset), element blocks filled by
+    host threads (ctypes drops the GIL): the 32 GB ne120 field in seconds instead of a minute.  Same values as
+    initialize_data (tests/test_oracle_kat.py)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    threads = threads or max(1, len(os.sched_getaffinity(0)))
+    dvv = np.empty(16)
+    elem = np.empty((nelemd, 144))
+    if qtens is None:
+        qtens = np.empty((4, 4, nlev, qsize, nelemd), order="F")
+    es = 16 * nlev * qsize
+    flat = qtens.reshape(-1, order="F")  # a view: qtens is Fortran-contiguous
+    assert flat.base is not None and flat.ctypes.data == qtens.ctypes.data
+    step = max(1, -(-nelemd // (threads * 4)))
+    L = lib()
+
+    def fill(f):
+        c = min(step, nelemd - f)
+        d = np.empty(16)
+        L.bwko_initialize_subset(nelemd, nlev, qsize, f, c, _p(d), C.c_void_p(elem.ctypes.data + 8 * 144 * f), C.c_void_p(flat.ctypes.data + 8 * es * f))
+        return d
+
+    with ThreadPoolExecutor(threads) as ex:
+        ds = list(ex.map(fill, range(0, nelemd, step)))
+    dvv[:] = ds[0]
+    return dvv, elem, qtens
+
+
 def _dims(qtens):
     return qtens.shape[2], qtens.shape[3], qtens.shape[4]
 

@@ -97,6 +97,7 @@ def main():
             ku.run_biharmonic_device()
             ku.sync()
         np.save(os.path.join(outdir, f"dev_{rank}.npy"), ku.download_elements(0, count))
+        np.save(os.path.join(outdir, f"bits_{rank}.npy"), np.array([ku.checksum_bits(first)], dtype=np.uint64))
         # advance_hypervis_scalar across ranks: two DSS exchanges per subcycle, halo buffers reused
         dp, dpd, coef = hypervis_inputs(n, nlev)
         ku.initialize_data_device(n, first)

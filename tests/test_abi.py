@@ -74,6 +74,10 @@ def test_fortran_wrapper_matches_reference_signature():
     assert subs["biharmonic_wk_scalar_cpusig"]["args"] == ["elem", "qtens", "deriv", "nets", "nete"]
     assert subs["advance_hypervis_scalar"]["args"] == ["elem", "qdp", "dp", "dpdiss", "deriv", "dt2", "nu_q", "hypervis_subcycle_q", "limiter"]
     assert subs["biharmonic_wk_dp3d"]["args"] == ["elem", "vec_sphere2cart", "dptens", "ttens", "vtens", "deriv", "var_coef1", "undamprrcart"]
+    # the dp3d entry needs a context with qsize = 4 while kernel_utils' qsize is a compile-time 40: b200_init takes the
+    # context's nlev / qsize as optional arguments
+    assert subs["b200_init"]["args"] == ["nlev_ctx", "qsize_ctx"]
+    assert all("optional" in subs["b200_init"]["vars"][a].get("attrspec", []) for a in ("nlev_ctx", "qsize_ctx"))
     text = open(path).read()
     for sym in re.findall(r'bind\(c,\s*name="(bwk_[a-z0-9_]+)"\)', text, flags=re.I):
         assert sym in open(os.path.join(ROOT, "include", "bwk_b200.h")).read(), sym

@@ -8,6 +8,8 @@ import sys
 import numpy as np
 import pytest
 
+from patch_oracle import patch_oracle_full as _patch_oracle_full
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WORKER = os.path.join(ROOT, "tests", "mg_worker.py")
 
@@ -46,7 +48,11 @@ def test_multi_gpu_matches_single_gpu_bitwise(bwk, oracle, tmp_path, ne, nlev, q
         ku.set_topology_cubed_sphere(ne)
         ku.run_biharmonic_device()
         single = ku.download_elements(0, n)
+        single_bits = ku.checksum_bits(0)
     assert np.array_equal(multi, single)
+    # the partition-independent bit checksum bench.py prints for every N: the per-rank values add up (mod 2^64) to the 1-rank value
+    with np.errstate(over="ignore"):
+        assert int(np.sum([np.load(tmp_path / f"bits_{r}.npy")[0] for r in range(world)], dtype=np.uint64)) == single_bits
     # advance_hypervis_scalar: N ranks == 1 rank bit for bit
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from mg_worker import hypervis_inputs
@@ -90,35 +96,6 @@ def test_dp3d_multi_gpu_matches_single_gpu_bitwise(bwk, tmp_path):
         ku.run_biharmonic_dp3d_device(True, True)
         single = ku.download_elements(0, n)
     assert np.array_equal(multi, single)
-
-
-def _patch_oracle_full(oracle, ne, nlev, qsize, gd, e):
-    """Full biharmonic of ONE element e of a big cubed sphere from the oracle's pieces: the CPU-order Laplacian
-    (F90:109-200) of e and of every element sharing a node with it, the DSS sum over coincident points in ascending
-    global point order, rspheremp from the same sums of spheremp, then the Laplacian of e again."""
-    n = 6 * ne * ne
-    keys = gd[e]
-    nbrs = np.unique(np.nonzero(np.isin(gd, keys))[0])
-    lap, sph = {}, {}
-    for m in nbrs:
-        dvv, elem, q = oracle.initialize_subset(n, nlev, qsize, int(m), 1)
-        sph[int(m)] = elem[0, 64:80].copy()
-        lap[int(m)] = oracle.biharmonic_wk_scalar_cpu(elem, q, dvv).reshape(16, nlev * qsize, order="F")
-        if m == e:
-            dvv_e, elem_e = dvv, elem
-    out = np.empty((16, nlev * qsize))
-    for pt in range(16):
-        members = [(int(m), int(t)) for m in nbrs for t in np.nonzero(gd[m] == keys[pt])[0]]
-        members.sort()
-        s = None
-        w = None
-        for m, t in members:
-            s = lap[m][t].copy() if s is None else s + lap[m][t]
-            w = sph[m][t] if w is None else w + sph[m][t]
-        out[pt] = s  # the oracle scales by rspheremp inside its second sweep (element_sweep2)
-        out[pt] *= 1.0 / w
-    q2 = np.asfortranarray(out.reshape((4, 4, nlev, qsize, 1), order="F"))
-    return oracle.biharmonic_wk_scalar_cpu(elem_e, q2, dvv_e)
 
 
 @pytest.mark.gpu

@@ -136,6 +136,36 @@ def test_linearity_and_idempotent_reinit(bwk, oracle):
         assert np.array_equal(ku.qtens, a)
 
 
+def test_checksum_bits_is_position_aware_and_partition_independent(bwk):
+    """bwk_checksum_bits == the same formula in numpy; two half-size contexts holding the two halves of the field add up
+    (mod 2^64) to the whole; swapping two values changes it."""
+    def ref(q, index0):
+        x = q.ravel(order="F").view(np.uint64).copy()
+        with np.errstate(over="ignore"):
+            x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            x = x ^ (x >> np.uint64(31))
+            w = np.uint64(2) * (np.uint64(index0) + np.arange(x.size, dtype=np.uint64)) + np.uint64(1)
+            return int(np.sum(x * w, dtype=np.uint64))
+    n, nlev, qsize = 10, 7, 3
+    with bwk.KernelUtils(n, nlev, qsize).allocate_data() as ku:
+        ku.initialize_data()
+        ku.update_device()
+        whole = ku.checksum_bits(0)
+        assert whole == ref(ku.qtens, 0)
+        q = ku.qtens.copy(order="F")
+        ku.qtens[0, 0, 0, 0, 0], ku.qtens[1, 0, 0, 0, 0] = q[1, 0, 0, 0, 0], q[0, 0, 0, 0, 0]
+        ku.update_device(elem=False, deriv=False)
+        assert ku.checksum_bits(0) != whole
+    parts = []
+    for first, cnt in ((0, 4), (4, 6)):
+        with bwk.KernelUtils(cnt, nlev, qsize).allocate_data() as ku:
+            ku.qtens[...] = q[..., first:first + cnt]
+            ku.update_device(elem=False, deriv=False)
+            parts.append(ku.checksum_bits(first))
+    assert (parts[0] + parts[1]) % (1 << 64) == whole
+
+
 def test_high_entropy_inputs(bwk, oracle):
     """Robustness run: splitmix64 values instead of the 17-bit LCG lattice.
     All operands stay positive, so the same tolerances hold."""
@@ -191,6 +221,68 @@ def test_ne120_q40_full_size_properties(bwk, oracle):
             _check(oracle, ku.download_elements(first, 4), ref)
         s, ss = ku.checksum()
         assert s < 0 and ss > 0 and np.isfinite(s) and np.isfinite(ss)
+
+
+def test_ne30_q40_whole_array_against_the_oracle(bwk, oracle):
+    """BASELINE config 3 verbatim: ne30np4 nlev=72 qsize=40 (5,400 elements, 1.99 GB), "GPU result compared against the
+    reference CPU output" on the WHOLE array -- the single Laplacian the reference computes (F90:186-200) and the full
+    biharmonic.  The CPU side is the oracle's OpenMP build (bit-identical to the parity build,
+    tests/test_oracle_kat.py::test_omp_*)."""
+    ne, nlev, qsize = 30, 72, 40
+    n = 6 * ne * ne
+    dvv, elem, q = oracle.initialize_data(n, nlev, qsize)
+    with bwk.KernelUtils(n, nlev, qsize).allocate_data(host_arrays=False) as ku:
+        ku.initialize_data_device()
+        ku.set_topology_cubed_sphere(ne)
+        assert np.array_equal(ku.download_elements(0, n), q)  # device generator == sequential host generator, whole array
+        ku.run_device()
+        got = ku.download_elements(0, n)
+        ref = oracle.biharmonic_wk_scalar_cpu(elem, q.copy(order="F"), dvv, omp=True)
+        l2, mr = _check(oracle, got, ref)
+        print(f"ne30 q40 single Laplacian, whole array: L2 {l2:.3e} maxrel {mr:.3e}")
+        ku.initialize_data_device()
+        ku.run_biharmonic_device()
+        got = ku.download_elements(0, n)
+        dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
+        ref = dss.biharmonic_full(elem, dss.rspheremp(elem), q, dvv, omp=True)
+        mr = oracle.max_rel(got, ref)
+        print(f"ne30 q40 full biharmonic, whole array: maxrel {mr:.3e}")
+        assert mr <= REL_TOL, mr
+
+
+def test_ne120_q40_full_biharmonic_headline_config(bwk, oracle):
+    """The configuration bench.py times (BASELINE config 4 on one GPU: ne120np4 L72 q40, full biharmonic, 63.7 GB with
+    the sweep-1 buffer).  Elements at cube corners, on face edges, next to the 8,192-element period boundary of the
+    LCG inputs and in face interiors are compared with the patch oracle (bit-identical to the whole-sphere oracle,
+    tests/test_plan.py::test_patch_oracle_equals_full_oracle); face-interior elements 8,192 apart see identical inputs
+    in identical positions and must agree bit for bit; two runs give the same checksum."""
+    from patch_oracle import patch_oracle_full
+
+    ne, nlev, qsize = 120, 72, 40
+    n, f = 6 * ne * ne, ne * ne
+    gd = oracle.cubed_sphere_gdof(ne).reshape(n, 16)
+    with bwk.KernelUtils(n, nlev, qsize).allocate_data(host_arrays=False) as ku:
+        ku.initialize_data_device()
+        ku.set_topology_cubed_sphere(ne)
+        ku.run_biharmonic_device()
+        ku.sync()
+        picks = [0, ne - 1, f - 1, n - 1,  # cube corners (3 elements share the vertex)
+                 60, 60 * ne, 2 * f + 119 * ne + 17, 5 * f + 33 * ne + ne - 1,  # face edges
+                 8191, 8192, 3 * f + 60 * ne + 60, 4 * f + 7 * ne + 101]  # period boundary, interiors
+        worst = 0.0
+        for e in picks:
+            ref = patch_oracle_full(oracle, ne, nlev, qsize, gd, e)
+            mr = oracle.max_rel(ku.download_elements(e, 1), ref)
+            worst = max(worst, mr)
+            assert mr <= REL_TOL, (e, mr)
+        print(f"ne120 q40 full biharmonic vs patch oracle at {len(picks)} elements: worst maxrel {worst:.3e}")
+        for e in (5 * ne + 7, 2 * f + 9 * ne + 3, 5 * f + 40 * ne + 50):
+            assert np.array_equal(ku.download_elements(e, 1), ku.download_elements(e + 8192, 1)), e
+        c1 = ku.checksum()
+        ku.initialize_data_device()
+        ku.run_biharmonic_device()
+        ku.sync()
+        assert ku.checksum() == c1 and np.isfinite(c1[0]) and c1[1] > 0
 
 
 # ------------------------------------------------------------------ full biharmonic (parity unpinned)

@@ -94,3 +94,22 @@ def test_lcg_period_makes_elements_repeat_every_8192(oracle):
     # qtens offset 8192 elements * 16*nlev*qsize doubles is a multiple of the LCG period only when
     # 16*nlev*qsize*8192 % 131072 == 0, i.e. always (8192*16 = 131072)
     assert np.array_equal(q0, q1)
+
+
+def test_omp_full_biharmonic_is_bit_identical(oracle):
+    """the timing build (-O3 -fopenmp) of Laplace -> DSS -> rspheremp -> Laplace gives the parity build's bits, so the
+    whole-array ne30 q40 GPU test (BASELINE config 3) may use it"""
+    ne, nlev, qsize = 3, 5, 2
+    n = 6 * ne * ne
+    dvv, elem, q = oracle.initialize_data(n, nlev, qsize)
+    dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
+    rs = dss.rspheremp(elem)
+    a = dss.biharmonic_full(elem, rs, q.copy(order="F"), dvv)
+    b = dss.biharmonic_full(elem, rs, q.copy(order="F"), dvv, omp=True)
+    assert np.array_equal(a, b)
+
+
+def test_parallel_closed_form_initialize_data_equals_the_sequential_one(oracle):
+    dvv, elem, q = oracle.initialize_data(37, 5, 3)
+    dvv2, elem2, q2 = oracle.initialize_data_parallel(37, 5, 3, threads=3)
+    assert np.array_equal(dvv, dvv2) and np.array_equal(elem, elem2) and np.array_equal(q, q2)

@@ -131,3 +131,19 @@ def test_strips_tile_the_elements_and_are_west_east_chains(bwk, ne, nranks):
             for a, k in zip(ff, cc):
                 covered[a : a + k] += 1
         assert np.all(covered == 1)
+
+
+@pytest.mark.parametrize("ne,nlev,qsize", [(2, 3, 2), (4, 5, 1)])
+def test_patch_oracle_equals_full_oracle(oracle, ne, nlev, qsize):
+    """tests/patch_oracle.py (used to check BASELINE's 32 GB / 258 GB configurations element by element) gives the bits of
+    the whole-sphere oracle, at face-interior elements, face edges and cube corners."""
+    from patch_oracle import patch_oracle_full
+
+    n = 6 * ne * ne
+    dvv, elem, q = oracle.initialize_data(n, nlev, qsize)
+    dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
+    ref = dss.biharmonic_full(elem, dss.rspheremp(elem), q, dvv)
+    gd = oracle.cubed_sphere_gdof(ne).reshape(n, 16)
+    for e in sorted({0, ne - 1, ne * ne - 1, ne * ne, n - 1, n // 2, 2 * ne * ne + ne + 1}):
+        got = patch_oracle_full(oracle, ne, nlev, qsize, gd, e)
+        assert np.array_equal(got[..., 0], ref[..., e]), e
