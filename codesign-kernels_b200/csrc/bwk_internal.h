@@ -58,7 +58,9 @@ struct StripReg {
     int32_t diag_src[4];      // SW, NW of the first member, SE, NE of the last: local element / halo slot, -1 = none
     uint8_t diag_kind[4];     // SRC_TMPCOL (local slab, diag_pt = point 0..15) or SRC_HALO (diag_pt = position in the row)
     uint8_t diag_pt[4];
-    uint8_t pad1[12];
+    int32_t first;            // first local element of the strip (the persistent sweep reads the strip from this record alone)
+    int32_t count;            // members (1..STRIP_MAX)
+    uint8_t pad1[4];
 };
 static_assert(sizeof(StripReg) == 128, "StripReg must be 128 bytes");
 constexpr int ROW_IN_HALO = 255;

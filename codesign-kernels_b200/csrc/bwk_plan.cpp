@@ -400,6 +400,8 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
             while (n < STRIP_MAX && i + n < list.size() && linked(list[i + n - 1], list[i + n])) ++n;
             out->push_back(list[i] * 8 + (n - 1));
             reg->push_back(regular_strip(list[i], n));
+            reg->back().first = list[i];
+            reg->back().count = n;
             i += (size_t)n;
         }
     };
