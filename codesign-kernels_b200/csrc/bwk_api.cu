@@ -108,6 +108,8 @@ struct Ctx {
     int32_t *d_send_elem = nullptr, *d_send_row = nullptr;
     int32_t *d_strips_all = nullptr, *d_strips_dep = nullptr, *d_strips_indep = nullptr;
     StripReg *d_reg_all = nullptr, *d_reg_dep = nullptr, *d_reg_indep = nullptr;
+    int *d_work = nullptr;            // item counter of the persistent strip sweep
+    int64_t nfast[3] = {0, 0, 0};     // leading strips of the all / dependent / independent lists the persistent sweep takes (full, regular)
     std::vector<int64_t> send_offset; // per peer, rows
     bool have_metric = false, have_topology = false, have_rsph = false, rsph_user = false;
     SweepParams sp{};
@@ -266,6 +268,42 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
     return 0;
 }
 
+// strip sweep over one of the plan's three lists (0 all, 1 dependent, 2 independent): the full regular strips through the
+// persistent kernel (units of BWK_PERSIST_T tiles, default 4), the others through sweep2_strip_kernel behind it
+int sweep2_list(int which, cudaStream_t st, int mode = MODE_SWEEP2, const CUtensorMap *out = nullptr)
+{
+    int32_t *const ds[3] = {g.d_strips_all, g.d_strips_dep, g.d_strips_indep};
+    StripReg *const dr[3] = {g.d_reg_all, g.d_reg_dep, g.d_reg_indep};
+    const size_t sizes[3] = {g.plan.strips_all.size(), g.plan.strips_dependent.size(), g.plan.strips_independent.size()};
+    const int64_t n = (int64_t)sizes[which];
+    int64_t nf = g.nfast[which];
+    static const int persist = std::getenv("BWK_PERSIST") ? std::atoi(std::getenv("BWK_PERSIST")) : 1; // A/B knob: 0 = round-1 form
+    static const int tpu = std::getenv("BWK_PERSIST_T") ? std::max(3, std::atoi(std::getenv("BWK_PERSIST_T"))) : 4;
+    const int ntiles = (g.kq + TILE_SLABS - 1) / TILE_SLABS;
+    if (!persist || ntiles < 3 || (mode != MODE_SWEEP2 && mode != MODE_DSS)) nf = 0;
+    if (nf > 0) {
+        SweepParams p = g.sp;
+        if (out) p.map_out = *out;
+        if (g.src_is_w) {
+            p.tmp = g.d_w;
+            p.map_tmp = g.map_w;
+            p.map_rows = g.map_w_rows;
+            p.map_pt = g.map_w_pt;
+        }
+        p.strip_reg = dr[which];
+        p.strip_count = (int)nf;
+        p.work_counter = g.d_work;
+        static const int nbr_ahead = std::getenv("BWK_NBR_AHEAD") ? std::atoi(std::getenv("BWK_NBR_AHEAD")) : 2; // tuning knob
+        p.nbr_ahead = nbr_ahead == 1 ? 1 : 2;
+        CK(cudaMemsetAsync(g.d_work, 0, sizeof(int), st));
+        p.units = std::max(1, ntiles / tpu);
+        p.tiles_per_unit = ntiles / p.units;
+        CK(launch_sweep2_persist(mode, p, st));
+        g.launches++;
+    }
+    return sweep2(ds[which] + nf, dr[which] + nf, n - nf, st, mode, out);
+}
+
 int laplace_range(int first0, int count, cudaStream_t st)
 {
     if (!g.have_metric) return fail("no element metric on the device: call bwk_upload(elem, ..., deriv) first");
@@ -395,10 +433,31 @@ int install_plan(Plan &&pl)
     CK(cudaMalloc(&g.d_dss, sizeof(ElemDss) * (size_t)g.nelem));
     CK(cudaMemcpy(g.d_dss, P.dss.data(), sizeof(ElemDss) * (size_t)g.nelem, cudaMemcpyHostToDevice));
     if (upload_list(P.boundary_list, &g.d_boundary) || upload_list(P.interior_list, &g.d_interior) || upload_list(P.dependent_list, &g.d_dependent) ||
-        upload_list(P.independent_list, &g.d_independent) || upload_list(P.strips_all, &g.d_strips_all) ||
-        upload_list(P.strips_dependent, &g.d_strips_dep) || upload_list(P.strips_independent, &g.d_strips_indep) ||
-        upload_regs(P.reg_all, &g.d_reg_all) || upload_regs(P.reg_dependent, &g.d_reg_dep) || upload_regs(P.reg_independent, &g.d_reg_indep))
+        upload_list(P.independent_list, &g.d_independent))
         return 1;
+    {
+        // device strip lists: the full regular strips first (the persistent sweep takes those), the others behind them
+        // (face-edge strips with reversed rows, short strips at row ends: sweep2_strip_kernel); both parts keep element order
+        const std::vector<int32_t> *S[3] = {&P.strips_all, &P.strips_dependent, &P.strips_independent};
+        const std::vector<StripReg> *R[3] = {&P.reg_all, &P.reg_dependent, &P.reg_independent};
+        int32_t **ds[3] = {&g.d_strips_all, &g.d_strips_dep, &g.d_strips_indep};
+        StripReg **dr[3] = {&g.d_reg_all, &g.d_reg_dep, &g.d_reg_indep};
+        for (int w = 0; w < 3; ++w) {
+            std::vector<int32_t> hs;
+            std::vector<StripReg> hr;
+            hs.reserve(S[w]->size());
+            hr.reserve(S[w]->size());
+            for (int pass = 0; pass < 2; ++pass) // pass 0 collects the fast strips, pass 1 the rest
+                for (size_t i = 0; i < S[w]->size(); ++i) {
+                    const bool fast = (*R[w])[i].regular && strip_count((*S[w])[i]) == STRIP_MAX;
+                    if (fast == (pass == 0)) { hs.push_back((*S[w])[i]); hr.push_back((*R[w])[i]); }
+                }
+            int64_t nf = 0;
+            while (nf < (int64_t)hr.size() && hr[(size_t)nf].regular && strip_count(hs[(size_t)nf]) == STRIP_MAX) ++nf;
+            g.nfast[w] = nf;
+            if (upload_list(hs, ds[w]) || upload_regs(hr, dr[w])) return 1;
+        }
+    }
     // halo (receive) buffer and send buffer, rows of [KQ][4] doubles
     const int64_t nrecv = P.recv_offset.back();
     free_dev(g.d_halo);
@@ -484,7 +543,7 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
     const Plan &P = g.plan;
     if (P.nranks == 1) {
         if (produce(0, g.nelem, (const int32_t *)nullptr)) return 1;
-        return sweep2(g.d_strips_all, g.d_reg_all, (int64_t)P.strips_all.size(), g.s_main, consume_mode, out);
+        return sweep2_list(0, g.s_main, consume_mode, out);
     }
     static const bool trace = std::getenv("BWK_TRACE") != nullptr; // debugging aid: serialised phases with their durations on stderr
     if (trace) {
@@ -500,8 +559,8 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
         if (lap("produce(boundary)", g.s_main, [&] { return produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary); })) return 1;
         if (g.comm && lap("pack + ncclSend/Recv", g.s_comm, [&] { return exchange_halo(); })) return 1;
         if (lap("produce(interior)", g.s_main, [&] { return produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior); })) return 1;
-        if (lap("consume(independent strips)", g.s_main, [&] { return sweep2(g.d_strips_indep, g.d_reg_indep, (int64_t)P.strips_independent.size(), g.s_main, consume_mode, out); })) return 1;
-        if (lap("consume(dependent strips)", g.s_main, [&] { return sweep2(g.d_strips_dep, g.d_reg_dep, (int64_t)P.strips_dependent.size(), g.s_main, consume_mode, out); })) return 1;
+        if (lap("consume(independent strips)", g.s_main, [&] { return sweep2_list(2, g.s_main, consume_mode, out); })) return 1;
+        if (lap("consume(dependent strips)", g.s_main, [&] { return sweep2_list(1, g.s_main, consume_mode, out); })) return 1;
         std::fprintf(stderr, "[bwk trace rank %d] boundary %zu interior %zu elements; independent %zu dependent %zu strips\n", P.rank,
                      P.boundary_list.size(), P.interior_list.size(), P.strips_independent.size(), P.strips_dependent.size());
         return 0;
@@ -512,9 +571,9 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
     if (exchange_halo()) return 1;
     CK(cudaEventRecord(g.ev_halo, g.s_comm));
     if (produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior)) return 1;
-    if (sweep2(g.d_strips_indep, g.d_reg_indep, (int64_t)P.strips_independent.size(), g.s_main, consume_mode, out)) return 1;
+    if (sweep2_list(2, g.s_main, consume_mode, out)) return 1;
     CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
-    if (sweep2(g.d_strips_dep, g.d_reg_dep, (int64_t)P.strips_dependent.size(), g.s_main, consume_mode, out)) return 1;
+    if (sweep2_list(1, g.s_main, consume_mode, out)) return 1;
     // the next pass's exchange overwrites the halo buffer: it must not start before these strips have read it
     CK(cudaEventRecord(g.ev_misc, g.s_main));
     CK(cudaStreamWaitEvent(g.s_comm, g.ev_misc, 0));
@@ -747,6 +806,7 @@ int bwk_init(int nelemd, int nlev, int qsize)
     CK(cudaMalloc(&g.d_elem, sizeof(double) * ELEM_DOUBLES * nelemd));
     CK(cudaMalloc(&g.d_metric, sizeof(double) * METRIC_DOUBLES * nelemd));
     CK(cudaMalloc(&g.d_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS));
+    CK(cudaMalloc(&g.d_work, sizeof(int)));
     CK(cudaMallocHost(&g.h_partials, sizeof(double) * 2 * NPARTIAL_BLOCKS));
     if (make_slab_map(&g.sp.map_q, g.d_q, g.kq, nelemd)) return 1;
     // until a topology is installed map_tmp aliases map_q (never dereferenced by MODE_LAPLACE)
@@ -769,6 +829,7 @@ int bwk_finalize(void)
             for (int e = 0; e < 2; ++e)
                 if (kv.second.ev[c][e]) cudaEventDestroy(kv.second.ev[c][e]);
     g_tune.clear();
+    free_dev(g.d_work);
     free_dev(g.d_w); free_dev(g.d_ratio); free_dev(g.d_v2c); free_dev(g.d_metric_plain);
     free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
     free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);
@@ -1242,7 +1303,7 @@ int bwk_run_biharmonic_phase(int phase)
     if (g.plan.nranks != 1) return fail("bwk_run_biharmonic_phase is a single-rank profiling hook");
     if (compute_rspheremp()) return 1;
     if (phase == 1) return sweep(MODE_SWEEP1, 0, g.nelem, nullptr, g.s_main);
-    if (phase == 2) return sweep2(g.d_strips_all, g.d_reg_all, (int64_t)g.plan.strips_all.size(), g.s_main);
+    if (phase == 2) return sweep2_list(0, g.s_main);
     return fail("phase must be 1 or 2");
 }
 

@@ -25,6 +25,7 @@
 #include "bwk_kernels.h"
 
 #include <algorithm>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 
@@ -1050,6 +1051,381 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) sweep2_strip_kernel(const __
     else sweep2_generic<STAGES, WARPS, KIND>(p, stages, bars, metric_all, extra, first, cnt);
 }
 
+// ------------------------------------------------------------------------------------------
+// Persistent form of the regular strip sweep (round 2).  Same per-tile protocol as sweep2_regular, but
+//   * the grid is one wave (3 CTAs per SM) and a CTA walks work items i = blockIdx.x, + gridDim.x, ...;
+//     item i = (unit i / nstrips, strip i % nstrips), a unit is only 3-5 tiles of the (k,q) axis.  All CTAs do the same
+//     work per item, so the CTAs holding a strip and its S/N neighbour strips (30 items apart at ne120) stay within a few
+//     tiles of each other for the whole launch: the neighbours' rows are read while the lines are still in L2
+//     (short units gave 1.11x DRAM reads against 1.23-1.29x at 15 tiles in round 1, but paid 2.7 us of pipeline
+//     fill/drain per CTA -- here the pipeline never drains);
+//   * the TMA ring, the S/N row buffers, the strip-end boxes and every mbarrier run CONTINUOUSLY across items: lane 0
+//     looks 1 (strip ends) and 2 (tile, rows) tiles ahead, into the next item when the current one runs out.  Items are
+//     described by a small per-warp record (PDesc, EndTma) decoded from the strip's StripReg into one of two slots one
+//     tile before the look-ahead first needs it; the folded metric is double buffered the same way (cp.async);
+//   * only full regular strips (4 members) are taken, so every barrier's arrival count is a constant of the warp; the
+//     host sends the other strips (face-edge strips with reversed rows, short strips at row ends) to sweep2_strip_kernel.
+// Shared memory is carved to the byte: 76,640 B per CTA, three CTAs per SM.
+// ------------------------------------------------------------------------------------------
+struct PDesc {             // one work item as one warp sees it (64 bytes)
+    int32_t le;            // the warp's element
+    int32_t tile0, ntile;  // first tile of the item's unit, tiles in it (>= 3)
+    int32_t elemS, elemN;  // sources of the S / N neighbour rows (local element or halo slot)
+    uint32_t sel;          // c0S | c0N << 8 | S row in halo << 16 | N row in halo << 17 | all_std << 18
+    uint32_t cn_pack, cperm_pack;
+    uint32_t end_bytes;    // bytes of the strip-end boxes of one tile (end warps)
+    int32_t pad[7];
+};
+static_assert(sizeof(PDesc) == 64 && sizeof(EndTma) == 16, "descriptor sizes are part of the shared-memory budget");
+static_assert(offsetof(StripReg, s_src) == 4 && offsetof(StripReg, n_src) == 20 && offsetof(StripReg, s_c0) == 36 && offsetof(StripReg, n_c0) == 40 &&
+              offsetof(StripReg, corner_n) == 44 && offsetof(StripReg, corner_perm) == 60 && offsetof(StripReg, end_src) == 76 &&
+              offsetof(StripReg, end_kind) == 84 && offsetof(StripReg, end_row) == 86 && offsetof(StripReg, end_rev) == 88 &&
+              offsetof(StripReg, all_std) == 90 && offsetof(StripReg, diag_src) == 92 && offsetof(StripReg, diag_kind) == 108 &&
+              offsetof(StripReg, diag_pt) == 112 && offsetof(StripReg, first) == 116, "the persistent sweep decodes StripReg by 32-bit word");
+
+template <int STAGES, int WARPS>
+constexpr int persist_smem_bytes()
+{
+    return WARPS * STAGES * TILE_BYTES + STRIP_EXTRA_BYTES + 2 * WARPS * METRIC_DOUBLES * 8 + 2 * WARPS * (int)sizeof(PDesc) + 12 * (int)sizeof(EndTma) +
+           WARPS * (STAGES + 2) * 8 + 2 * 8 + 16; // + the work queue's two mbarriers and four ints
+}
+
+template <int STAGES, int WARPS, int KIND>
+__global__ void __launch_bounds__(WARPS * 32, 3) sweep2_persist_kernel(const __grid_constant__ SweepParams p)
+{
+    static_assert(WARPS == STRIP_MAX && KIND != SK_POST, "full strips, DSS or DSS + Laplacian");
+    constexpr int SB = TILE_BYTES;
+    extern __shared__ __align__(1024) unsigned char psm[];
+    unsigned char *stages = psm;                                   // [warp][stage][4 KB], SWIZZLE_128B (needs the 1024-byte base)
+    unsigned char *rowbuf = stages + WARPS * STAGES * SB;          // [set 2][warp][S,N][32][32 B]
+    unsigned char *endbuf = rowbuf + ROWBUF_BYTES;                 // [W,E][column 2048 | diagonal 512 | diagonal 512]
+    double *metric_all = reinterpret_cast<double *>(endbuf + ENDBUF_BYTES);           // [slot 2][warp][64]
+    PDesc *desc_all = reinterpret_cast<PDesc *>(metric_all + 2 * WARPS * METRIC_DOUBLES); // [slot 2][warp]
+    EndTma *ends_all = reinterpret_cast<EndTma *>(desc_all + 2 * WARPS);              // [slot 2][W,E][column, S diag, N diag]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(ends_all + 12);                      // full [warp][stage]
+    uint64_t *cbars = bars + WARPS * STAGES;                                           // cons [warp][2]
+    uint64_t *ibars = cbars + WARPS * 2;                                               // "item id published" [2]
+    volatile int *wq = reinterpret_cast<volatile int *>(ibars + 2);                    // [0,1] published ids, [2,3] the CTA's first two items
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool w_end = warp == 0, e_end = warp == WARPS - 1, is_end = w_end || e_end;
+    const int side = e_end ? 1 : 0;
+    const int ntiles_all = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
+    const int ubase = ntiles_all / p.units, urem = ntiles_all % p.units; // unit u: tiles [u*ubase + min(u,urem), + ubase + (u < urem))
+    const int nstrips = p.strip_count;
+    const int nitems = nstrips * p.units;
+    // Work items come from a global counter (dynamic): the items in flight are then always the ~444 most recently
+    // fetched ones, i.e. a compact band of neighbouring strips of one unit whose shared lines are in L2.  (A static
+    // round-robin assignment lets the CTAs drift apart over their ~1000 items: measured 4.1x DRAM reads, 26 ms.)
+    if (threadIdx.x == 0) {
+        if ((smem_u32(psm) & 1023u) != 0) __trap(); // the budget has no alignment slack
+        wq[2] = atomicAdd(p.work_counter, 1);
+        wq[3] = atomicAdd(p.work_counter, 1);
+        mbar_init(smem_u32(&ibars[0]), 1);
+        mbar_init(smem_u32(&ibars[1]), 1);
+    }
+    __syncthreads();
+    int it = wq[2], nxt = wq[3];
+    if (it >= nitems) return;
+
+    const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
+    const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
+    const uint32_t cbar0 = smem_u32(&cbars[warp * 2]);
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + s * 8, is_end ? 3u : 2u); // tile + S/N rows (+ strip-end boxes)
+        mbar_init(cbar0, is_end ? 32u : 64u);                                       // every lane of every mate
+        mbar_init(cbar0 + 8, is_end ? 32u : 64u);
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+
+    // whole warp: decode item `item` (its StripReg word `raw` per lane) into descriptor slot sl
+    auto decode = [&](int sl, int item, uint32_t raw) {
+        auto W = [&](int i) { return __shfl_sync(0xffffffffu, raw, i); };
+        const uint32_t first = W(29), sS = W(1 + warp), sN = W(5 + warp);
+        const uint32_t c0S = (W(9) >> (8 * warp)) & 255u, c0N = (W(10) >> (8 * warp)) & 255u;
+        const uint32_t cn = W(11 + warp), cp = W(15 + warp);
+        const uint32_t w21 = W(21), w22 = W(22), w27 = W(27), w28 = W(28);
+        const uint32_t esrc = W(19 + side), dsrc0 = W(23 + 2 * side), dsrc1 = W(24 + 2 * side);
+        if (lane == 0) {
+            const int u = item / nstrips;
+            PDesc &D = desc_all[sl * WARPS + warp];
+            D.le = (int32_t)first + warp;
+            D.tile0 = u * ubase + min(u, urem);
+            D.ntile = ubase + (u < urem ? 1 : 0);
+            D.elemS = (int32_t)sS;
+            D.elemN = (int32_t)sN;
+            const uint32_t hS = c0S == (uint32_t)ROW_IN_HALO, hN = c0N == (uint32_t)ROW_IN_HALO;
+            D.sel = (hS ? 0u : c0S) | ((hN ? 0u : c0N) << 8) | (hS << 16) | (hN << 17) | ((((w22 >> 16) & 255u) ? 1u : 0u) << 18);
+            D.cn_pack = cn;
+            D.cperm_pack = cp;
+            uint32_t eb = 0;
+            if (is_end) {
+                EndTma *E = ends_all + (sl * 2 + side) * 3;
+                const int kind = (w21 >> (8 * side)) & 255, row = (w21 >> (16 + 8 * side)) & 255;
+                EndTma e{ET_NONE, 0, 0, 0, 0, 0, 0};
+                if (kind == SRC_TMPCOL) e = {ET_COL, (uint8_t)(row ? 1 : 0), 0, 0, row ? 2 : 0, 0, 0};
+                else if (kind == SRC_TMP) e = {ET_ROW, 0, 0, 0, 4 * row, 0, 0};
+                else e = {ET_HALOROW, 0, 0, 0, 0, 0, 0};
+                e.rev = (uint8_t)((w22 >> (8 * side)) & 255u);
+                e.src = (int32_t)esrc;
+                E[0] = e;
+                eb += end_box_bytes(e.kind);
+#pragma unroll
+                for (int which = 1; which < 3; ++which) {
+                    const int d = side * 2 + (which - 1);
+                    const int32_t ds = (int32_t)(which == 1 ? dsrc0 : dsrc1);
+                    EndTma f{ET_NONE, 0, 0, 0, 0, 0, 0};
+                    if (ds >= 0) {
+                        const int pt = (w28 >> (8 * d)) & 255, dk = (w27 >> (8 * d)) & 255;
+                        if (dk == SRC_HALO) f = {ET_HALOPT, (uint8_t)(pt & 1), 0, 0, pt & 2, 0, 0};
+                        else f = {ET_PT, (uint8_t)(pt & 1), 0, 0, pt & 2, pt >> 2, 0};
+                        f.src = ds;
+                    }
+                    E[which] = f;
+                    eb += end_box_bytes(f.kind);
+                }
+            }
+            D.end_bytes = eb;
+        }
+        __syncwarp();
+    };
+    auto load_raw = [&](int item) { return __ldg(reinterpret_cast<const uint32_t *>(p.strip_reg + (item % nstrips)) + lane); };
+    auto load_metric = [&](int sl) { // this warp's folded metric (512 B) of the item in slot sl, asynchronously
+        const int le = desc_all[sl * WARPS + warp].le;
+        cp_async16(smem_u32(metric_all + (sl * WARPS + warp) * METRIC_DOUBLES) + lane * 16, p.metric + (size_t)le * METRIC_DOUBLES + lane * 2, 16u);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    // ---- lane 0's three producers; (sl, n) = descriptor slot and tile inside that item, s = ring stage / barrier of that tile
+    auto issue_tile = [&](int sl, int n, int s) {
+        const PDesc &D = desc_all[sl * WARPS + warp];
+        const uint32_t bar = bar0 + s * 8;
+        mbar_expect_tx(bar, (uint32_t)TILE_BYTES);
+        tma_load_3d(stage0 + s * SB, &p.map_tmp, 0, (D.tile0 + n) * TILE_SLABS, D.le, bar);
+    };
+    auto issue_nbr = [&](int sl, int n, int s, int q) {
+        const PDesc &D = desc_all[sl * WARPS + warp];
+        const int kq0 = (D.tile0 + n) * TILE_SLABS;
+        const uint32_t bar = bar0 + s * 8;
+        const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((q * STRIP_MAX + warp) * 2048);
+        const uint32_t sel = D.sel;
+        mbar_expect_tx(bar, 2048u);
+        tma_load_3d(rb, (sel >> 16) & 1u ? &p.map_halo : &p.map_rows, (int)(sel & 255u), kq0, D.elemS, bar);
+        tma_load_3d(rb + 1024, (sel >> 17) & 1u ? &p.map_halo : &p.map_rows, (int)((sel >> 8) & 255u), kq0, D.elemN, bar);
+    };
+    auto issue_end = [&](int sl, int n, int s) {
+        const PDesc &D = desc_all[sl * WARPS + warp];
+        const int kq0 = (D.tile0 + n) * TILE_SLABS;
+        const uint32_t bar = bar0 + s * 8;
+        mbar_expect_tx(bar, D.end_bytes);
+#pragma unroll
+        for (int which = 0; which < 3; ++which) {
+            const EndTma e = ends_all[(sl * 2 + side) * 3 + which];
+            const uint32_t dst = smem_u32(endbuf) + (uint32_t)(side * END_SIDE_BYTES + (which ? 1536 + 512 * which : 0));
+            switch (e.kind) {
+            case ET_COL:
+#pragma unroll
+                for (int j = 0; j < 4; ++j) tma_load_4d(dst + j * 512, &p.map_pt, e.c0, j, kq0, e.src, bar);
+                break;
+            case ET_ROW: tma_load_3d(dst, &p.map_rows, e.c0, kq0, e.src, bar); break;
+            case ET_HALOROW: tma_load_3d(dst, &p.map_halo, 0, kq0, e.src, bar); break;
+            case ET_PT: tma_load_4d(dst, &p.map_pt, e.c0, e.c1, kq0, e.src, bar); break;
+            case ET_HALOPT: tma_load_3d(dst, &p.map_halo_pt, e.c0, kq0, e.src, bar); break;
+            default: break;
+            }
+        }
+    };
+
+    decode(0, it, load_raw(it));
+    load_metric(0);
+    __syncthreads(); // the only CTA-wide barrier: every warp's mbarriers are initialised before a mate touches them
+    if (lane == 0) { // fill the pipeline: tiles 0..2, rows 0..1, strip-end boxes 0 of the first item (every unit has >= 3 tiles)
+#pragma unroll
+        for (int n = 0; n < STAGES; ++n) issue_tile(0, n, n);
+        issue_nbr(0, 0, 0, 0);
+        if (p.nbr_ahead == 2) issue_nbr(0, 1, 1, 1);
+        if (is_end) issue_end(0, 0, 0);
+    }
+
+    const int sw = lane & 7;         // SWIZZLE_128B
+    const int swz = (lane >> 2) & 1; // SWIZZLE_32B
+    const uint64_t pol_out = l2_policy_evict_first();
+    int sl = 0, s = 0;
+    uint32_t parity = 0, g = 0; // g: tiles this warp has done (rowbuf set g & 1, cons parity (g >> 1) & 1)
+
+    uint32_t kitem = 0; // items this CTA has started
+    while (true) {
+        const bool has_next = nxt < nitems;
+        uint32_t raw = 0;
+        int pend = 0;
+        if (has_next) {
+            raw = load_raw(nxt); // consumed one tile before the look-ahead crosses into the next item
+            if (threadIdx.x == 0) pend = atomicAdd(p.work_counter, 1); // the id of the item after the next; published below
+        }
+        const PDesc &D = desc_all[sl * WARPS + warp];
+        const int ntile = D.ntile, tile0 = D.tile0, le = D.le;
+        const uint32_t cn_pack = D.cn_pack, cperm_pack = D.cperm_pack;
+        const bool std_corners = (D.sel >> 18) & 1u;
+        const SmemMetric M{metric_all + (sl * WARPS + warp) * METRIC_DOUBLES};
+        const EndTma *endtma = ends_all + sl * 6;
+
+        auto read_end = [&](int sd, double (&col)[4], double &d0, double &d1) {
+            const unsigned char *eb = endbuf + sd * END_SIDE_BYTES;
+            const EndTma c = endtma[3 * sd];
+            const int rm = c.rev ? 3 : 0;
+            if (c.kind == ET_COL) {
+                const unsigned char *b = eb + lane * 16 + c.hi * 8;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + ((t ^ rm) << 9));
+            } else {
+                const unsigned char *b = eb + lane * 32;
+                const int x = ((lane >> 2) & 1) ^ (rm >> 1), y = rm & 1;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + (((t >> 1) ^ x) << 4) + (((t & 1) ^ y) << 3));
+            }
+            d0 = *reinterpret_cast<const double *>(eb + 2048 + lane * 16 + endtma[3 * sd + 1].hi * 8);
+            d1 = *reinterpret_cast<const double *>(eb + 2560 + lane * 16 + endtma[3 * sd + 2].hi * 8);
+        };
+
+        for (int n = 0; n < ntile; ++n) {
+            if (n == ntile - 2 && has_next) { // the look-ahead reaches the next item at the end of this iteration
+                decode(sl ^ 1, nxt, raw);
+                load_metric(sl ^ 1);
+                if (threadIdx.x == 0) { // publish the id fetched at the top of this item (slot kitem & 1, read at the top of the next item)
+                    wq[kitem & 1u] = pend;
+                    mbar_arrive(smem_u32(&ibars[kitem & 1u]));
+                }
+            }
+            const int q = (int)(g & 1u);
+            const uint32_t qparity = (g >> 1) & 1u;
+            const int kq0 = (tile0 + n) * TILE_SLABS;
+            unsigned char *row = stages + ((size_t)warp * STAGES + s) * SB + lane * 128;
+            const unsigned char *rb = rowbuf + (size_t)((q * STRIP_MAX + warp) * 2048) + lane * 32;
+            double v[16], nb[4][4], dg[4];
+
+            mbar_wait(bar0 + s * 8, parity);
+            if (n == 0) { // this item's metric: staged by this warp's own cp.async one or two tiles ago
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                __syncwarp();
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+                v[2 * c] = t.x;
+                v[2 * c + 1] = t.y;
+            }
+            {
+                const double2 a = *reinterpret_cast<const double2 *>(rb + (swz << 4)), b = *reinterpret_cast<const double2 *>(rb + ((1 ^ swz) << 4));
+                nb[EDGE_S][0] = a.x; nb[EDGE_S][1] = a.y; nb[EDGE_S][2] = b.x; nb[EDGE_S][3] = b.y;
+                const double2 c = *reinterpret_cast<const double2 *>(rb + 1024 + (swz << 4)), d = *reinterpret_cast<const double2 *>(rb + 1024 + ((1 ^ swz) << 4));
+                nb[EDGE_N][0] = c.x; nb[EDGE_N][1] = c.y; nb[EDGE_N][2] = d.x; nb[EDGE_N][3] = d.y;
+            }
+            if (w_end) {
+                read_end(0, nb[EDGE_W], dg[0], dg[2]);
+            } else {
+                mbar_wait(bar0 - STAGES * 8 + s * 8, parity);
+                const unsigned char *mrow = row - STAGES * SB;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_W][t] = *reinterpret_cast<const double *>(mrow + (((2 * t + 1) ^ sw) << 4) + 8);
+                dg[0] = *reinterpret_cast<const double *>(rb - 2048 + ((1 ^ swz) << 4) + 8);
+                dg[2] = *reinterpret_cast<const double *>(rb - 2048 + 1024 + ((1 ^ swz) << 4) + 8);
+            }
+            if (e_end) {
+                read_end(1, nb[EDGE_E], dg[1], dg[3]);
+            } else {
+                mbar_wait(bar0 + STAGES * 8 + s * 8, parity);
+                const unsigned char *mrow = row + STAGES * SB;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) nb[EDGE_E][t] = *reinterpret_cast<const double *>(mrow + (((2 * t) ^ sw) << 4));
+                dg[1] = *reinterpret_cast<const double *>(rb + 2048 + (swz << 4));
+                dg[3] = *reinterpret_cast<const double *>(rb + 2048 + 1024 + (swz << 4));
+            }
+
+            // ---- DSS (edgeVunpack), corners in ascending global point order
+            v[1] += nb[EDGE_S][1]; v[2] += nb[EDGE_S][2];
+            v[13] += nb[EDGE_N][1]; v[14] += nb[EDGE_N][2];
+            v[4] += nb[EDGE_W][1]; v[8] += nb[EDGE_W][2];
+            v[7] += nb[EDGE_E][1]; v[11] += nb[EDGE_E][2];
+            if (std_corners) {
+                v[0] = ((dg[0] + nb[EDGE_S][0]) + nb[EDGE_W][0]) + v[0];
+                v[3] = ((nb[EDGE_S][3] + dg[1]) + v[3]) + nb[EDGE_E][0];
+                v[12] = ((nb[EDGE_W][3] + v[12]) + dg[2]) + nb[EDGE_N][0];
+                v[15] = ((v[15] + nb[EDGE_E][3]) + nb[EDGE_N][3]) + dg[3];
+            } else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int pt = c == 0 ? 0 : (c == 1 ? 3 : (c == 2 ? 12 : 15));
+                    const double cv0 = v[pt];
+                    const double cv1 = nb[c < 2 ? EDGE_S : EDGE_N][(c & 1) ? 3 : 0];
+                    const double cv2 = nb[(c & 1) ? EDGE_E : EDGE_W][c < 2 ? 0 : 3];
+                    const double cv3 = dg[c];
+                    const int perm = (cperm_pack >> (8 * c)) & 255, cn = (cn_pack >> (8 * c)) & 255;
+                    auto pick = [&](int k) {
+                        const int w = (perm >> (2 * k)) & 3;
+                        return w == 0 ? cv0 : (w == 1 ? cv1 : (w == 2 ? cv2 : cv3));
+                    };
+                    double sum = pick(0);
+                    if (cn > 1) sum = sum + pick(1);
+                    if (cn > 2) sum = sum + pick(2);
+                    if (cn > 3) sum = sum + pick(3);
+                    v[pt] = sum;
+                }
+            }
+            // the mates' values have been consumed: tell them (the operands tie the arrival to the sums)
+            if (!w_end) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 - 16 + q * 8), "d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]) : "memory");
+            if (!e_end) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cbar0 + 16 + q * 8), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
+            const int s1 = s + 1 == STAGES ? 0 : s + 1, s2 = s == 0 ? STAGES - 1 : s - 1; // stages of tiles g+1 and g+2 (= g-1)
+            if (is_end) { // endbuf consumed by every lane: the next tile's boxes travel while this tile's Laplacian runs
+                asm volatile("" ::"d"(v[0]), "d"(v[12]), "d"(v[4]), "d"(v[8]), "d"(v[3]), "d"(v[15]), "d"(v[7]), "d"(v[11]) : "memory");
+                __syncwarp();
+                if (lane == 0) {
+                    if (n + 1 < ntile) issue_end(sl, n + 1, s1);
+                    else if (has_next) issue_end(sl ^ 1, 0, s1);
+                }
+            }
+
+            if (KIND != SK_DSS) laplace_slab(v, M);
+            mbar_wait(cbar0 + q * 8, qparity); // both mates have read this tile's columns and this rowbuf set
+#pragma unroll
+            for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
+            fence_proxy_async();
+            __syncwarp();
+
+            if (lane == 0) {
+                tma_store_3d_hint(&p.map_out, 0, kq0, le, stage0 + s * SB, pol_out);
+                bulk_commit();
+                // tile g+2: into the stage tile g-1 used (once its store has read it) and into rowbuf set q
+                int sl2 = sl, n2 = n + 2;
+                bool have2 = true;
+                if (n2 >= ntile) { sl2 = sl ^ 1; n2 -= ntile; have2 = has_next; }
+                if (have2) {
+                    if (g >= 1) {
+                        bulk_wait_read<1>();
+                        issue_tile(sl2, n2, s2);
+                    }
+                    if (p.nbr_ahead == 2) issue_nbr(sl2, n2, s2, q);
+                }
+                if (p.nbr_ahead != 2) { // rows one tile ahead: the owner of those lines has usually asked for them by then
+                    if (n + 1 < ntile) issue_nbr(sl, n + 1, s1, q ^ 1);
+                    else if (has_next) issue_nbr(sl ^ 1, 0, s1, q ^ 1);
+                }
+            }
+            s = s1;
+            if (s == 0) parity ^= 1u;
+            ++g;
+        }
+        if (!has_next) break;
+        it = nxt;
+        mbar_wait(smem_u32(&ibars[kitem & 1u]), (kitem >> 1) & 1u);
+        nxt = wq[kitem & 1u];
+        ++kitem;
+        sl ^= 1;
+    }
+    if (lane == 0) bulk_wait_read<0>();
+}
+
 // kernel configurations: (STAGES, WARPS, MINB)
 #define BWK_CFG_LAPLACE 3, 4, 3
 #define BWK_CFG_SWEEP1 3, 4, 3
@@ -1118,6 +1494,40 @@ static cudaError_t launch_strip_t(const SweepParams &p, cudaStream_t st)
     dim3 grid((unsigned)p.strip_count, (unsigned)p.units);
     sweep2_strip_kernel<STAGES, WARPS, MINB, KIND><<<grid, WARPS * 32, smem, st>>>(p);
     return cudaGetLastError();
+}
+
+template <int STAGES, int WARPS, int KIND>
+static cudaError_t launch_persist_t(const SweepParams &p, cudaStream_t st)
+{
+    constexpr int smem = persist_smem_bytes<STAGES, WARPS>();
+    static_assert(3 * (smem + 1024) <= 228 * 1024, "three CTAs per SM");
+    static int ctas = 0;
+    if (!ctas) {
+        cudaError_t e = cudaFuncSetAttribute(sweep2_persist_kernel<STAGES, WARPS, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sweep2_persist_kernel<STAGES, WARPS, KIND>, WARPS * 32, smem);
+        if (e != cudaSuccess) return e;
+        ctas = sms * (per_sm > 0 ? per_sm : 1);
+    }
+    if (p.strip_count <= 0 || p.units <= 0) return cudaSuccess;
+    const long long nitems = (long long)p.strip_count * p.units;
+    const int grid = (int)(nitems < ctas ? nitems : ctas);
+    sweep2_persist_kernel<STAGES, WARPS, KIND><<<grid, WARPS * 32, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+// persistent strip sweep over a list of FULL REGULAR strips (p.strip_reg / p.strip_count); p.units = number of units of the
+// (k,q) axis, each of at least 3 tiles.  mode: MODE_SWEEP2 or MODE_DSS
+cudaError_t launch_sweep2_persist(int mode, const SweepParams &p, cudaStream_t st)
+{
+    const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
+    if (p.units < 1 || ntiles / p.units < 3) return cudaErrorInvalidValue;
+    if (mode == MODE_SWEEP2) return launch_persist_t<3, 4, SK_LAP>(p, st);
+    if (mode == MODE_DSS) return launch_persist_t<3, 4, SK_DSS>(p, st);
+    return cudaErrorInvalidValue;
 }
 
 bool sweep1_pre_fits(int nlev) { return sweep_smem_bytes<3, 4>() + nlev * 128 <= 227 * 1024; }

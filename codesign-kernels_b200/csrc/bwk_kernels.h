@@ -44,6 +44,8 @@ struct SweepParams {
     const int32_t *strips;  // MODE_SWEEP2: work units, first*8 + (count-1) (bwk_internal.h); grid x = strip_count
     const StripReg *strip_reg; // MODE_SWEEP2: one per strip, same order
     int strip_count;
+    int *work_counter;      // persistent strip sweep: global item counter, zero at launch
+    int nbr_ahead;          // persistent strip sweep: the S/N rows are requested this many tiles ahead (1 or 2)
     int elem_first;         // 0-based first local element (when elem_list == nullptr)
     int elem_count;         // grid x (MODE_LAPLACE / MODE_SWEEP1)
     int kq;                 // nlev*qsize
@@ -61,6 +63,8 @@ void set_sweep2_tiles_per_unit(int tpu); // tuning knob (BWK_SWEEP2_TPU): > 0 fo
 int sweep2_tiles_per_unit_forced();
 
 cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st);
+// persistent strip sweep (MODE_SWEEP2 / MODE_DSS) over full regular strips only: p.strip_reg / p.strip_count, p.units units of >= 3 tiles
+cudaError_t launch_sweep2_persist(int mode, const SweepParams &p, cudaStream_t st);
 // MODE_SWEEP1_PRE needs nlev*128 more bytes of shared memory per CTA than the other element-local sweeps; false if that does not fit
 bool sweep1_pre_fits(int nlev);
 // advance_hypervis_scalar, pointwise part: out = limiter2d_zero(qdp*spheremp - coef*qtens) * rspheremp over the slabs of
