@@ -90,6 +90,11 @@ struct NcclApi {
 constexpr int NPARTIAL_BLOCKS = 148 * 8;
 constexpr int NEVENTS = 64;
 
+// the warp-strip sweep's views of a field laid out like qtens (8-slab boxes, see bwk_kernels.h)
+struct Field4Maps {
+    CUtensorMap slab4, rows4, rows1, col, pt8;
+};
+
 struct Ctx {
     bool inited = false;
     int nelem = 0, nlev = 0, qsize = 0, kq = 0;
@@ -98,6 +103,7 @@ struct Ctx {
     double *d_q = nullptr, *d_tmp = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
     double *d_w = nullptr, *d_ratio = nullptr; // advance_hypervis_scalar: biharmonic work buffer, dpdiss/dp [nelem][nlev][16]
     CUtensorMap map_w, map_w_rows, map_w_pt; // the work buffer seen as slabs / edge rows / i-pairs (strip sweeps reading it)
+    Field4Maps f4_tmp, f4_w, f4_q;           // warp-strip sweep: 8-slab views of tmp, the work buffer and qtens
     bool src_is_w = false;                  // strip sweeps and the halo pack read the work buffer instead of tmp
     double *d_v2c = nullptr, *d_metric_plain = nullptr; // biharmonic_wk_dp3d: vec_sphere2cart [nelem][96]; folded metric without tensorVisc
     bool have_v2c = false, have_metric_plain = false;
@@ -176,6 +182,22 @@ int make_slab_map(CUtensorMap *m, double *base, int kq, int64_t nelem)
     return make_map(m, base, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+int make_field4_maps(Field4Maps *m, double *base, int kq, int64_t nelem)
+{
+    const uint64_t n = (uint64_t)std::max<int64_t>(nelem, 1);
+    const uint32_t e4 = (uint32_t)std::min<uint64_t>(4, n);
+    const uint64_t dims[3] = {16, (uint64_t)kq, n}, str[2] = {128, (uint64_t)kq * 128};
+    const uint32_t b_slab4[3] = {16, 8, e4}, b_rows4[3] = {4, 8, e4}, b_rows1[3] = {4, 8, 1};
+    if (make_map(&m->slab4, base, 3, dims, str, b_slab4, CU_TENSOR_MAP_SWIZZLE_128B)) return 1;
+    if (make_map(&m->rows4, base, 3, dims, str, b_rows4, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+    if (make_map(&m->rows1, base, 3, dims, str, b_rows1, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+    const uint64_t cdims[4] = {4, 4, (uint64_t)kq, n}, cstr[3] = {32, 128, (uint64_t)kq * 128};
+    const uint32_t b_col[4] = {2, 4, 8, 1}, b_pt[4] = {2, 1, 8, 1};
+    if (make_map(&m->col, base, 4, cdims, cstr, b_col, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+    if (make_map(&m->pt8, base, 4, cdims, cstr, b_pt, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+    return 0;
+}
+
 int need_init()
 {
     if (!g.inited) return fail("bwk_init has not been called");
@@ -219,7 +241,8 @@ constexpr int TUNE_CAND[2] = {15, 9};
 std::map<uint64_t, StripTune> g_tune;
 
 // launch sweep 2 (or the DSS-only sweep) over `count` strips of a device strip list
-int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaStream_t st, int mode = MODE_SWEEP2, const CUtensorMap *out = nullptr)
+int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaStream_t st, int mode = MODE_SWEEP2, const CUtensorMap *out = nullptr,
+           bool wstrip = false)
 {
     if (count <= 0) return 0;
     SweepParams p = g.sp;
@@ -230,10 +253,20 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
         p.map_rows = g.map_w_rows;
         p.map_pt = g.map_w_pt;
     }
+    if (wstrip) { // the same choices for the warp-strip sweep's 8-slab views
+        const Field4Maps &src = g.src_is_w ? g.f4_w : g.f4_tmp;
+        p.map4_tmp = src.slab4;
+        p.map4_rows = src.rows4;
+        p.map1_rows = src.rows1;
+        p.map_col = src.col;
+        p.map_pt8 = src.pt8;
+        p.map4_out = out == &g.map_w ? g.f4_w.slab4 : g.f4_q.slab4;
+        p.map4_q = g.f4_q.slab4;
+    }
     int hint = 0, timed = -1;
     StripTune *t = nullptr;
     if (sweep2_tiles_per_unit_forced() == 0 && count * ((g.kq + TILE_SLABS - 1) / TILE_SLABS) >= 148 * 64 && g_tune.size() < 4096) {
-        t = &g_tune[((uint64_t)mode << 56) ^ ((uint64_t)count << 20) ^ (uint64_t)g.kq];
+        t = &g_tune[((uint64_t)mode << 56) ^ ((uint64_t)wstrip << 55) ^ ((uint64_t)count << 20) ^ (uint64_t)g.kq];
         if (t->best >= 0) hint = TUNE_CAND[t->best];
         else if (t->calls <= 1) { hint = TUNE_CAND[0]; timed = t->calls == 1 ? 0 : -1; }
         else if (t->calls == 2) { hint = TUNE_CAND[1]; timed = 1; }
@@ -262,7 +295,7 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
         CK(cudaEventCreate(&t->ev[timed][1]));
         CK(cudaEventRecord(t->ev[timed][0], st));
     }
-    CK(launch_sweep(mode, p, st));
+    CK(wstrip ? launch_sweep2_wstrip(mode, p, st) : launch_sweep(mode, p, st));
     if (timed >= 0) CK(cudaEventRecord(t->ev[timed][1], st));
     g.launches++;
     return 0;
@@ -277,10 +310,16 @@ int sweep2_list(int which, cudaStream_t st, int mode = MODE_SWEEP2, const CUtens
     const size_t sizes[3] = {g.plan.strips_all.size(), g.plan.strips_dependent.size(), g.plan.strips_independent.size()};
     const int64_t n = (int64_t)sizes[which];
     int64_t nf = g.nfast[which];
-    static const int persist = std::getenv("BWK_PERSIST") ? std::atoi(std::getenv("BWK_PERSIST")) : 1; // A/B knob: 0 = round-1 form
+    // A/B knob BWK_STRIP_FORM: 2 (default) = warp-strip sweep for the fast strips, 1 = persistent one-warp-per-member sweep,
+    // 0 = everything through sweep2_strip_kernel (the round-1 form)
+    static const int form = std::getenv("BWK_STRIP_FORM") ? std::atoi(std::getenv("BWK_STRIP_FORM")) : 2;
     static const int tpu = std::getenv("BWK_PERSIST_T") ? std::max(3, std::atoi(std::getenv("BWK_PERSIST_T"))) : 4;
     const int ntiles = (g.kq + TILE_SLABS - 1) / TILE_SLABS;
-    if (!persist || ntiles < 3 || (mode != MODE_SWEEP2 && mode != MODE_DSS)) nf = 0;
+    if (form == 2 && nf > 0) {
+        if (sweep2(ds[which], dr[which], nf, st, mode, out, true)) return 1;
+        return sweep2(ds[which] + nf, dr[which] + nf, n - nf, st, mode, out);
+    }
+    if (form != 1 || ntiles < 3 || (mode != MODE_SWEEP2 && mode != MODE_DSS)) nf = 0;
     if (nf > 0) {
         SweepParams p = g.sp;
         if (out) p.map_out = *out;
@@ -447,13 +486,20 @@ int install_plan(Plan &&pl)
             std::vector<StripReg> hr;
             hs.reserve(S[w]->size());
             hr.reserve(S[w]->size());
+            // fast = full regular strip whose members' S (and N) neighbours are consecutive elements (or consecutive halo
+            // slots) facing with the same row: one {4, 8 slabs, 4 elements} TMA box fetches the four members' rows
+            auto is_fast = [](const StripReg &r, int32_t strip) {
+                if (!r.regular || strip_count(strip) != STRIP_MAX) return false;
+                for (int m = 1; m < STRIP_MAX; ++m)
+                    if (r.s_src[m] != r.s_src[0] + m || r.s_c0[m] != r.s_c0[0] || r.n_src[m] != r.n_src[0] + m || r.n_c0[m] != r.n_c0[0]) return false;
+                return true;
+            };
+            int64_t nf = 0;
             for (int pass = 0; pass < 2; ++pass) // pass 0 collects the fast strips, pass 1 the rest
                 for (size_t i = 0; i < S[w]->size(); ++i) {
-                    const bool fast = (*R[w])[i].regular && strip_count((*S[w])[i]) == STRIP_MAX;
-                    if (fast == (pass == 0)) { hs.push_back((*S[w])[i]); hr.push_back((*R[w])[i]); }
+                    const bool fast = is_fast((*R[w])[i], (*S[w])[i]);
+                    if (fast == (pass == 0)) { hs.push_back((*S[w])[i]); hr.push_back((*R[w])[i]); nf += pass == 0; }
                 }
-            int64_t nf = 0;
-            while (nf < (int64_t)hr.size() && hr[(size_t)nf].regular && strip_count(hs[(size_t)nf]) == STRIP_MAX) ++nf;
             g.nfast[w] = nf;
             if (upload_list(hs, ds[w]) || upload_regs(hr, dr[w])) return 1;
         }
@@ -497,6 +543,18 @@ int install_plan(Plan &&pl)
             if (make_map(&g.sp.map_halo, g.d_halo, 3, hdims, hstr, box, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
             if (make_map(&g.sp.map_halo_pt, g.d_halo, 3, hdims, hstr, hpbox, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
         }
+    }
+    // warp-strip sweep: 8-slab views of tmp and qtens, and of the received rows
+    if (make_field4_maps(&g.f4_tmp, g.d_tmp, g.kq, g.nelem) || make_field4_maps(&g.f4_q, g.d_q, g.kq, g.nelem)) return 1;
+    g.sp.map4_halo = g.f4_tmp.rows4; // (never dereferenced without a halo)
+    g.sp.map1_halo = g.f4_tmp.rows1;
+    g.sp.map_halo_pt8 = g.f4_tmp.rows1;
+    if (nrecv > 0) {
+        const uint64_t hdims[3] = {4, (uint64_t)g.kq, (uint64_t)nrecv}, hstr[2] = {32, (uint64_t)g.kq * 32};
+        const uint32_t b4[3] = {4, 8, (uint32_t)std::min<int64_t>(4, nrecv)}, b1[3] = {4, 8, 1}, bp[3] = {2, 8, 1};
+        if (make_map(&g.sp.map4_halo, g.d_halo, 3, hdims, hstr, b4, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+        if (make_map(&g.sp.map1_halo, g.d_halo, 3, hdims, hstr, b1, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+        if (make_map(&g.sp.map_halo_pt8, g.d_halo, 3, hdims, hstr, bp, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
     }
     g.sp.tmp = g.d_tmp;
     g.sp.halo = g.d_halo;
@@ -603,6 +661,7 @@ int hypervis_device(double dt2, double nu_q, int subcycles, int limiter)
         const uint64_t cdims[4] = {4, 4, (uint64_t)g.kq, (uint64_t)g.nelem}, cstr[3] = {32, 128, (uint64_t)g.kq * 128};
         const uint32_t pbox[4] = {2, 1, TILE_SLABS, 1};
         if (make_map(&g.map_w_pt, g.d_w, 4, cdims, cstr, pbox, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+        if (make_field4_maps(&g.f4_w, g.d_w, g.kq, g.nelem)) return 1;
     }
     g.sp.prescale = g.d_ratio;
     g.sp.nlev = g.nlev;

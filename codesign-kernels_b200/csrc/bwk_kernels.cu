@@ -1426,6 +1426,292 @@ __global__ void __launch_bounds__(WARPS * 32, 3) sweep2_persist_kernel(const __g
     if (lane == 0) bulk_wait_read<0>();
 }
 
+// ------------------------------------------------------------------------------------------
+// Warp-strip form of the regular strip sweep (round 2): ONE WARP owns all four members of a strip.
+// Lane l = (member l >> 3, slab l & 7): a warp's tile is 8 consecutive (k,q) slabs of 4 consecutive elements, one
+// 4 KB TMA box {16, 8 slabs, 4 elements}; row r of the staged tile is lane r's slab, so the swizzled 128-byte reads are
+// those of the element-local sweeps.  The W/E edge exchange between strip mates and the diagonal corner values are
+// warp shuffles by 8 lanes -- no shared-memory column reads, no mate / cons mbarriers, no in-place hazard: the four
+// warps of a CTA are completely independent pipelines that only share the strip's staged metric.  (In the one-warp-
+// per-member form the largest stalls were the waits on the mates' barriers: 16 % of the samples.)
+//   * S/N neighbour rows of the four members: one {4, 8, 4} box each (the neighbours of consecutive members of a
+//     face-interior strip are consecutive elements; the host sends every other strip to sweep2_strip_kernel);
+//   * strip ends: the outside neighbour's facing column as ONE unswizzled {2 (i pair), 4 (j), 8 slabs} box, the two
+//     diagonal values as {2,1,8} boxes, read by the eight lanes of the end member only;
+//   * a CTA = 4 warps on the same strip, warp w takes slabs [8w, 8w+8) of every 32-slab tile of the unit, so the
+//     CTA still streams 4 KB contiguous per element and tile.
+// ------------------------------------------------------------------------------------------
+constexpr int WS_SLABS = 8;                                   // slabs of one member in a warp tile
+constexpr int WS_ROWBUF_BYTES = 2 * 4 * 2 * 1024;             // [set][warp][S,N][4 members x 8 slabs x 32 B]
+constexpr int WS_END_SIDE = 512 + 2 * 128;                    // facing column (or row) + two diagonals, 8 slabs
+constexpr int WS_ENDBUF_BYTES = 4 * 2 * WS_END_SIDE;          // [warp][W,E]
+constexpr int WS_METRIC_STRIDE = METRIC_DOUBLES + 2;          // doubles; +16 B per member: the four members' reads hit different banks
+template <int STAGES>
+constexpr int wstrip_smem_bytes()
+{
+    return 1024 + 4 * STAGES * TILE_BYTES + WS_ROWBUF_BYTES + WS_ENDBUF_BYTES + 4 * (STAGES + 1) * 8 + 4 * WS_METRIC_STRIDE * 8 + 6 * 16 + 4 * 34 * 8 + 64;
+}
+__device__ __forceinline__ uint32_t ws_end_box_bytes(int kind)
+{
+    return kind == ET_COL ? 512u : (kind == ET_ROW || kind == ET_HALOROW) ? 256u : kind == ET_NONE ? 0u : 128u;
+}
+__device__ __forceinline__ double shfl_up8(double x) { return __shfl_up_sync(0xffffffffu, x, 8); }
+__device__ __forceinline__ double shfl_down8(double x) { return __shfl_down_sync(0xffffffffu, x, 8); }
+
+template <int STAGES, int KIND>
+__global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_constant__ SweepParams p)
+{
+    constexpr int SB = TILE_BYTES, WARPS = 4;
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    unsigned char *stages = smem;                                               // [warp][stage][4 members x 8 slabs x 128 B], SWIZZLE_128B
+    unsigned char *rowbuf = stages + WARPS * STAGES * SB;                       // [set][warp][S,N][32 x 32 B], SWIZZLE_32B
+    unsigned char *endbuf = rowbuf + WS_ROWBUF_BYTES;                           // [warp][W,E][column 512 | diagonal 128 | diagonal 128]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(endbuf + WS_ENDBUF_BYTES);    // full [warp][stage], qdp_full [warp]
+    double *metric_s = reinterpret_cast<double *>(bars + WARPS * (STAGES + 1)); // [member][WS_METRIC_STRIDE]
+    EndTma *endtma = reinterpret_cast<EndTma *>(metric_s + 4 * WS_METRIC_STRIDE); // [W column, SW, NW, E column, SE, NE]
+    double *hv_s = reinterpret_cast<double *>(endtma + 6);                      // SK_POST: [member][spheremp 16 | rspheremp 16 | pad 2]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int member = lane >> 3, j = lane & 7;
+    const StripReg &rg = p.strip_reg[blockIdx.x];
+    const int first = rg.first;
+    const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
+    const int t0 = blockIdx.y * p.tiles_per_unit;
+    const int t1 = min(t0 + p.tiles_per_unit, ntiles);
+    int my_n = t1 - t0; // this warp's tiles: slabs [(t0 + n) * 32 + 8 warp, + 8) of the four members
+    if (my_n > 0 && (t1 - 1) * TILE_SLABS + warp * WS_SLABS >= p.kq) --my_n;
+    const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
+    const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
+    const uint32_t qbar = smem_u32(&bars[WARPS * STAGES + warp]);
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + s * 8, 3u); // tile + S/N rows + strip-end boxes
+        mbar_init(qbar, 1u);
+        fence_barrier_init();
+        fence_proxy_async();
+        const int pre = my_n < STAGES ? my_n : STAGES;
+        for (int n = 0; n < pre; ++n) {
+            mbar_expect_tx(bar0 + n * 8, (uint32_t)TILE_BYTES);
+            tma_load_3d(stage0 + n * SB, &p.map4_tmp, 0, (t0 + n) * TILE_SLABS + warp * WS_SLABS, first, bar0 + n * 8);
+        }
+    }
+    { // the four members' folded metric (thread t: 16 bytes), shared by the four warps
+        const int m = threadIdx.x >> 5, c = (threadIdx.x & 31) * 2;
+        *reinterpret_cast<double2 *>(metric_s + m * WS_METRIC_STRIDE + c) = __ldg(reinterpret_cast<const double2 *>(p.metric + (size_t)(first + m) * METRIC_DOUBLES + c));
+        if (KIND == SK_POST) {
+            const int l = threadIdx.x & 31;
+            hv_s[m * 34 + l] = l < 16 ? p.elem[(size_t)(first + m) * ELEM_DOUBLES + 64 + l] : p.rsph[(size_t)(first + m) * 16 + l - 16];
+        }
+    }
+    if (threadIdx.x < 6) {
+        const int k = threadIdx.x, side = k / 3, which = k % 3;
+        EndTma e{ET_NONE, 0, 0, 0, 0, 0, 0};
+        if (which == 0) {
+            const int kind = rg.end_kind[side], row = rg.end_row[side];
+            if (kind == SRC_TMPCOL) e = {ET_COL, (uint8_t)(row ? 1 : 0), 0, 0, row ? 2 : 0, 0, 0};
+            else if (kind == SRC_TMP) e = {ET_ROW, 0, 0, 0, 4 * row, 0, 0};
+            else e = {ET_HALOROW, 0, 0, 0, 0, 0, 0};
+            e.rev = rg.end_rev[side];
+            e.src = rg.end_src[side];
+        } else {
+            const int d = side * 2 + (which - 1);
+            if (rg.diag_src[d] >= 0) {
+                const int pt = rg.diag_pt[d];
+                if (rg.diag_kind[d] == SRC_HALO) e = {ET_HALOPT, (uint8_t)(pt & 1), 0, 0, pt & 2, 0, 0};
+                else e = {ET_PT, (uint8_t)(pt & 1), 0, 0, pt & 2, pt >> 2, 0};
+                e.src = rg.diag_src[d];
+            }
+        }
+        endtma[k] = e;
+    }
+    __syncthreads(); // the only CTA-wide barrier
+    if (my_n <= 0) return;
+
+    const int swz = (lane >> 2) & 1, sw = lane & 7;
+    const int elemS = rg.s_src[0], elemN = rg.n_src[0];
+    const int rawS = rg.s_c0[0], rawN = rg.n_c0[0];
+    const CUtensorMap *mapS = rawS == ROW_IN_HALO ? &p.map4_halo : &p.map4_rows, *mapN = rawN == ROW_IN_HALO ? &p.map4_halo : &p.map4_rows;
+    const int c0S = rawS == ROW_IN_HALO ? 0 : rawS, c0N = rawN == ROW_IN_HALO ? 0 : rawN;
+    const bool std_corners = rg.all_std != 0;
+    uint32_t cn_pack = 0, cperm_pack = 0; // this lane's member: four corner counts / summation orders
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        cn_pack |= (uint32_t)rg.corner_n[member][c] << (8 * c);
+        cperm_pack |= (uint32_t)rg.corner_perm[member][c] << (8 * c);
+    }
+    const uint64_t pol_out = l2_policy_evict_first();
+    unsigned char *endbuf_w = endbuf + warp * 2 * WS_END_SIDE;
+    uint32_t end_bytes = 0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) end_bytes += ws_end_box_bytes(endtma[k].kind);
+
+    auto kq_of = [&](int n) { return (t0 + n) * TILE_SLABS + warp * WS_SLABS; };
+    auto issue_tile = [&](int n, int s) {
+        mbar_expect_tx(bar0 + s * 8, (uint32_t)TILE_BYTES);
+        tma_load_3d(stage0 + s * SB, &p.map4_tmp, 0, kq_of(n), first, bar0 + s * 8);
+    };
+    auto issue_nbr = [&](int n) {
+        const uint32_t nbar = bar0 + (n % STAGES) * 8;
+        const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((((n & 1) * WARPS) + warp) * 2048);
+        mbar_expect_tx(nbar, 2048u);
+        tma_load_3d(rb, mapS, c0S, kq_of(n), elemS, nbar);
+        tma_load_3d(rb + 1024, mapN, c0N, kq_of(n), elemN, nbar);
+    };
+    auto issue_end = [&](int n) {
+        const int kq0 = kq_of(n);
+        const uint32_t ebar = bar0 + (n % STAGES) * 8;
+        mbar_expect_tx(ebar, end_bytes);
+#pragma unroll
+        for (int side = 0; side < 2; ++side) {
+#pragma unroll
+            for (int which = 0; which < 3; ++which) {
+                const EndTma e = endtma[3 * side + which];
+                const uint32_t dst = smem_u32(endbuf_w) + (uint32_t)(side * WS_END_SIDE + (which ? 384 + 128 * which : 0));
+                switch (e.kind) {
+                case ET_COL: tma_load_4d(dst, &p.map_col, e.c0, 0, kq0, e.src, ebar); break;
+                case ET_ROW: tma_load_3d(dst, &p.map1_rows, e.c0, kq0, e.src, ebar); break;
+                case ET_HALOROW: tma_load_3d(dst, &p.map1_halo, 0, kq0, e.src, ebar); break;
+                case ET_PT: tma_load_4d(dst, &p.map_pt8, e.c0, e.c1, kq0, e.src, ebar); break;
+                case ET_HALOPT: tma_load_3d(dst, &p.map_halo_pt8, e.c0, kq0, e.src, ebar); break;
+                default: break;
+                }
+            }
+        }
+    };
+    // lanes of an end member: the four values along the facing edge (own orientation) and the two diagonals
+    auto read_end = [&](int side, double (&col)[4], double &d0, double &d1) {
+        const unsigned char *eb = endbuf_w + side * WS_END_SIDE;
+        const EndTma c = endtma[3 * side];
+        const int rm = c.rev ? 3 : 0;
+        if (c.kind == ET_COL) { // [slab][j][i pair]
+            const unsigned char *b = eb + j * 64 + c.hi * 8;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + ((t ^ rm) << 4));
+        } else { // [slab][4 doubles], SWIZZLE_32B
+            const unsigned char *b = eb + j * 32;
+            const int x = ((j >> 2) & 1) ^ (rm >> 1), y = rm & 1;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + (((t >> 1) ^ x) << 4) + (((t & 1) ^ y) << 3));
+        }
+        d0 = *reinterpret_cast<const double *>(eb + 512 + j * 16 + endtma[3 * side + 1].hi * 8);
+        d1 = *reinterpret_cast<const double *>(eb + 640 + j * 16 + endtma[3 * side + 2].hi * 8);
+    };
+
+    if (lane == 0) {
+        issue_nbr(0);
+        if (my_n > 1) issue_nbr(1);
+        issue_end(0);
+    }
+    const SmemMetric M{metric_s + member * WS_METRIC_STRIDE};
+
+    for (int n = 0; n < my_n; ++n) {
+        const int s = n % STAGES, q = n & 1;
+        const int kq0 = kq_of(n);
+        const uint32_t parity = (uint32_t)((n / STAGES) & 1);
+        unsigned char *row = stages + ((size_t)warp * STAGES + s) * SB + lane * 128;
+        const unsigned char *rb = rowbuf + (size_t)((q * WARPS + warp) * 2048) + lane * 32;
+        double v[16], nbS[4], nbN[4], nbW[4], nbE[4], dg[4];
+
+        mbar_wait(bar0 + s * 8, parity);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+            v[2 * c] = t.x;
+            v[2 * c + 1] = t.y;
+        }
+        {
+            const double2 a = *reinterpret_cast<const double2 *>(rb + (swz << 4)), b = *reinterpret_cast<const double2 *>(rb + ((1 ^ swz) << 4));
+            nbS[0] = a.x; nbS[1] = a.y; nbS[2] = b.x; nbS[3] = b.y;
+            const double2 c = *reinterpret_cast<const double2 *>(rb + 1024 + (swz << 4)), d = *reinterpret_cast<const double2 *>(rb + 1024 + ((1 ^ swz) << 4));
+            nbN[0] = c.x; nbN[1] = c.y; nbN[2] = d.x; nbN[3] = d.y;
+        }
+        // ---- W/E mates are 8 lanes away: their facing columns and the facing ends of their S/N neighbour rows by shuffle
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            nbW[t] = shfl_up8(v[3 + 4 * t]);   // west mate's E column (points 3,7,11,15)
+            nbE[t] = shfl_down8(v[4 * t]);     // east mate's W column (points 0,4,8,12)
+        }
+        dg[0] = shfl_up8(nbS[3]);   // SW: east end of the west mate's S row
+        dg[2] = shfl_up8(nbN[3]);   // NW
+        dg[1] = shfl_down8(nbS[0]); // SE: west end of the east mate's S row
+        dg[3] = shfl_down8(nbN[0]); // NE
+        if (member == 0) read_end(0, nbW, dg[0], dg[2]); // strip ends: the outside neighbour, staged by TMA
+        if (member == 3) read_end(1, nbE, dg[1], dg[3]);
+
+        // ---- DSS (edgeVunpack): mid-edge points, then corners in ascending global point order
+        v[1] += nbS[1]; v[2] += nbS[2];
+        v[13] += nbN[1]; v[14] += nbN[2];
+        v[4] += nbW[1]; v[8] += nbW[2];
+        v[7] += nbE[1]; v[11] += nbE[2];
+        if (std_corners) {
+            v[0] = ((dg[0] + nbS[0]) + nbW[0]) + v[0];   // PERM_SW
+            v[3] = ((nbS[3] + dg[1]) + v[3]) + nbE[0];   // PERM_SE
+            v[12] = ((nbW[3] + v[12]) + dg[2]) + nbN[0]; // PERM_NW
+            v[15] = ((v[15] + nbE[3]) + nbN[3]) + dg[3]; // PERM_NE
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int pt = c == 0 ? 0 : (c == 1 ? 3 : (c == 2 ? 12 : 15));
+                const double cv0 = v[pt];
+                const double cv1 = (c < 2 ? nbS : nbN)[(c & 1) ? 3 : 0];
+                const double cv2 = ((c & 1) ? nbE : nbW)[c < 2 ? 0 : 3];
+                const double cv3 = dg[c];
+                const int perm = (cperm_pack >> (8 * c)) & 255, cn = (cn_pack >> (8 * c)) & 255;
+                auto pick = [&](int k) {
+                    const int w = (perm >> (2 * k)) & 3;
+                    return w == 0 ? cv0 : (w == 1 ? cv1 : (w == 2 ? cv2 : cv3));
+                };
+                double sum = pick(0);
+                if (cn > 1) sum = sum + pick(1);
+                if (cn > 2) sum = sum + pick(2);
+                if (cn > 3) sum = sum + pick(3);
+                v[pt] = sum;
+            }
+        }
+        // every lane has its tile row, its S/N rows and (end members) the strip-end values in registers: the strip-end
+        // buffer can take the next tile's boxes and, for SK_POST, the stage can take the slab of Qdp
+        asm volatile("" ::"d"(v[0]), "d"(v[3]), "d"(v[5]), "d"(v[6]), "d"(v[9]), "d"(v[10]), "d"(v[12]), "d"(v[15]) : "memory");
+        __syncwarp();
+        if (lane == 0) {
+            if (n + 1 < my_n) issue_end(n + 1);
+            if (KIND == SK_POST) {
+                mbar_expect_tx(qbar, (uint32_t)TILE_BYTES);
+                tma_load_3d(stage0 + s * SB, &p.map4_q, 0, kq0, first, qbar);
+            }
+        }
+
+        if (KIND != SK_DSS) laplace_slab(v, M);
+
+        if (KIND == SK_POST) {
+            mbar_wait(qbar, (uint32_t)(n & 1));
+            double a[16];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const double2 t = *reinterpret_cast<const double2 *>(row + ((c ^ sw) << 4));
+                a[2 * c] = t.x;
+                a[2 * c + 1] = t.y;
+            }
+            hypervis_update_slab(v, a, hv_s + member * 34, hv_s + member * 34 + 16, p.hv_coef, p.hv_limiter);
+        }
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<double2 *>(row + ((c ^ sw) << 4)) = make_double2(v[2 * c], v[2 * c + 1]);
+        fence_proxy_async();
+        __syncwarp();
+
+        if (lane == 0) {
+            tma_store_3d_hint(&p.map4_out, 0, kq0, first, stage0 + s * SB, pol_out);
+            bulk_commit();
+            if (n >= 1 && n - 1 + STAGES < my_n) { // refill the stage tile n-1 used, once its store has read it
+                bulk_wait_read<1>();
+                issue_tile(n - 1 + STAGES, (n - 1) % STAGES);
+            }
+            if (n + 2 < my_n) issue_nbr(n + 2); // rowbuf set q is free: every lane consumed it before the __syncwarp above
+        }
+    }
+    if (lane == 0) bulk_wait_read<0>();
+}
+
 // kernel configurations: (STAGES, WARPS, MINB)
 #define BWK_CFG_LAPLACE 3, 4, 3
 #define BWK_CFG_SWEEP1 3, 4, 3
@@ -1527,6 +1813,32 @@ cudaError_t launch_sweep2_persist(int mode, const SweepParams &p, cudaStream_t s
     if (p.units < 1 || ntiles / p.units < 3) return cudaErrorInvalidValue;
     if (mode == MODE_SWEEP2) return launch_persist_t<3, 4, SK_LAP>(p, st);
     if (mode == MODE_DSS) return launch_persist_t<3, 4, SK_DSS>(p, st);
+    return cudaErrorInvalidValue;
+}
+
+template <int STAGES, int KIND>
+static cudaError_t launch_wstrip_t(const SweepParams &p, cudaStream_t st)
+{
+    constexpr int smem = wstrip_smem_bytes<STAGES>();
+    static_assert(3 * (smem + 1024) <= 228 * 1024, "three CTAs per SM");
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(sweep2_wstrip_kernel<STAGES, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    if (p.strip_count <= 0 || p.units <= 0) return cudaSuccess;
+    dim3 grid((unsigned)p.strip_count, (unsigned)p.units);
+    sweep2_wstrip_kernel<STAGES, KIND><<<grid, 128, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+// warp-strip sweep over full regular strips whose members' S/N neighbours are consecutive elements (p.strip_reg / p.strip_count)
+cudaError_t launch_sweep2_wstrip(int mode, const SweepParams &p, cudaStream_t st)
+{
+    if (mode == MODE_SWEEP2) return launch_wstrip_t<3, SK_LAP>(p, st);
+    if (mode == MODE_DSS) return launch_wstrip_t<3, SK_DSS>(p, st);
+    if (mode == MODE_SWEEP2_POST) return launch_wstrip_t<3, SK_POST>(p, st);
     return cudaErrorInvalidValue;
 }
 
