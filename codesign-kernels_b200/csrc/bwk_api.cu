@@ -254,6 +254,8 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
         p.map_pt = g.map_w_pt;
     }
     if (wstrip) { // the same choices for the warp-strip sweep's 8-slab views
+        static const int dbg = std::getenv("BWK_DEBUG_FLAGS") ? std::atoi(std::getenv("BWK_DEBUG_FLAGS")) : 0;
+        p.debug_flags = dbg;
         const Field4Maps &src = g.src_is_w ? g.f4_w : g.f4_tmp;
         p.map4_tmp = src.slab4;
         p.map4_rows = src.rows4;

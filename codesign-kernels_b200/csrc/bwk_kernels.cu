@@ -1436,24 +1436,31 @@ __global__ void __launch_bounds__(WARPS * 32, 3) sweep2_persist_kernel(const __g
 // per-member form the largest stalls were the waits on the mates' barriers: 16 % of the samples.)
 //   * S/N neighbour rows of the four members: one {4, 8, 4} box each (the neighbours of consecutive members of a
 //     face-interior strip are consecutive elements; the host sends every other strip to sweep2_strip_kernel);
-//   * strip ends: the outside neighbour's facing column as ONE unswizzled {2 (i pair), 4 (j), 8 slabs} box, the two
-//     diagonal values as {2,1,8} boxes, read by the eight lanes of the end member only;
+//   * strip ends: only the 16 lanes of the two end members need the outside neighbour's facing column and the two
+//     diagonal values (6 doubles per lane and tile).  They fetch them themselves with 8-byte cp.async one tile ahead
+//     into private slots -- every source kind and orientation is folded into one base/stride record per strip end.
+//     (Staging them by TMA, as the one-warp-per-member form does, cost ~150 of 864 instructions per tile here: six
+//     small boxes issued by lane 0 and a kind switch on both sides.);
 //   * a CTA = 4 warps on the same strip, warp w takes slabs [8w, 8w+8) of every 32-slab tile of the unit, so the
 //     CTA still streams 4 KB contiguous per element and tile.
 // ------------------------------------------------------------------------------------------
 constexpr int WS_SLABS = 8;                                   // slabs of one member in a warp tile
 constexpr int WS_ROWBUF_BYTES = 2 * 4 * 2 * 1024;             // [set][warp][S,N][4 members x 8 slabs x 32 B]
-constexpr int WS_END_SIDE = 512 + 2 * 128;                    // facing column (or row) + two diagonals, 8 slabs
-constexpr int WS_ENDBUF_BYTES = 4 * 2 * WS_END_SIDE;          // [warp][W,E]
+constexpr int WS_ENDBUF_BYTES = 4 * 2 * 16 * 48;              // [warp][set][end lane 16][4 edge values, 2 diagonals]
 constexpr int WS_METRIC_STRIDE = METRIC_DOUBLES + 2;          // doubles; +16 B per member: the four members' reads hit different banks
+// Source of one strip end, decoded once per CTA: the outside neighbour's four values along the facing edge in THIS
+// element's orientation are at col + slab * slab_bytes + t * step (a column or a row of a local slab, or a received halo
+// row, either direction), the two diagonal corner values at d0 / d1 + slab * d?_slab_bytes (nullptr = none, cube corner).
+struct WsEnd {
+    const unsigned char *col, *d0, *d1;
+    int32_t step, slab_bytes, d0_slab_bytes, d1_slab_bytes;
+    int32_t pad[2];
+};
+static_assert(sizeof(WsEnd) == 48, "WsEnd layout");
 template <int STAGES>
 constexpr int wstrip_smem_bytes()
 {
-    return 1024 + 4 * STAGES * TILE_BYTES + WS_ROWBUF_BYTES + WS_ENDBUF_BYTES + 4 * (STAGES + 1) * 8 + 4 * WS_METRIC_STRIDE * 8 + 6 * 16 + 4 * 34 * 8 + 64;
-}
-__device__ __forceinline__ uint32_t ws_end_box_bytes(int kind)
-{
-    return kind == ET_COL ? 512u : (kind == ET_ROW || kind == ET_HALOROW) ? 256u : kind == ET_NONE ? 0u : 128u;
+    return 1024 + 4 * STAGES * TILE_BYTES + WS_ROWBUF_BYTES + WS_ENDBUF_BYTES + 4 * (STAGES + 1) * 8 + 4 * WS_METRIC_STRIDE * 8 + 2 * 48 + 4 * 34 * 8 + 64;
 }
 __device__ __forceinline__ double shfl_up8(double x) { return __shfl_up_sync(0xffffffffu, x, 8); }
 __device__ __forceinline__ double shfl_down8(double x) { return __shfl_down_sync(0xffffffffu, x, 8); }
@@ -1466,11 +1473,11 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
     unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     unsigned char *stages = smem;                                               // [warp][stage][4 members x 8 slabs x 128 B], SWIZZLE_128B
     unsigned char *rowbuf = stages + WARPS * STAGES * SB;                       // [set][warp][S,N][32 x 32 B], SWIZZLE_32B
-    unsigned char *endbuf = rowbuf + WS_ROWBUF_BYTES;                           // [warp][W,E][column 512 | diagonal 128 | diagonal 128]
+    unsigned char *endbuf = rowbuf + WS_ROWBUF_BYTES;                           // [warp][set][end lane][48 B]: cp.async slots of the end members
     uint64_t *bars = reinterpret_cast<uint64_t *>(endbuf + WS_ENDBUF_BYTES);    // full [warp][stage], qdp_full [warp]
     double *metric_s = reinterpret_cast<double *>(bars + WARPS * (STAGES + 1)); // [member][WS_METRIC_STRIDE]
-    EndTma *endtma = reinterpret_cast<EndTma *>(metric_s + 4 * WS_METRIC_STRIDE); // [W column, SW, NW, E column, SE, NE]
-    double *hv_s = reinterpret_cast<double *>(endtma + 6);                      // SK_POST: [member][spheremp 16 | rspheremp 16 | pad 2]
+    WsEnd *wsend = reinterpret_cast<WsEnd *>(metric_s + 4 * WS_METRIC_STRIDE);  // [W end, E end]
+    double *hv_s = reinterpret_cast<double *>(wsend + 2);                       // SK_POST: [member][spheremp 16 | rspheremp 16 | pad 2]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int member = lane >> 3, j = lane & 7;
@@ -1486,7 +1493,7 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
     const uint32_t qbar = smem_u32(&bars[WARPS * STAGES + warp]);
     if (lane == 0) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + s * 8, 3u); // tile + S/N rows + strip-end boxes
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + s * 8, 2u); // tile + S/N rows
         mbar_init(qbar, 1u);
         fence_barrier_init();
         fence_proxy_async();
@@ -1504,33 +1511,56 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
             hv_s[m * 34 + l] = l < 16 ? p.elem[(size_t)(first + m) * ELEM_DOUBLES + 64 + l] : p.rsph[(size_t)(first + m) * 16 + l - 16];
         }
     }
-    if (threadIdx.x < 6) {
-        const int k = threadIdx.x, side = k / 3, which = k % 3;
-        EndTma e{ET_NONE, 0, 0, 0, 0, 0, 0};
-        if (which == 0) {
-            const int kind = rg.end_kind[side], row = rg.end_row[side];
-            if (kind == SRC_TMPCOL) e = {ET_COL, (uint8_t)(row ? 1 : 0), 0, 0, row ? 2 : 0, 0, 0};
-            else if (kind == SRC_TMP) e = {ET_ROW, 0, 0, 0, 4 * row, 0, 0};
-            else e = {ET_HALOROW, 0, 0, 0, 0, 0, 0};
-            e.rev = rg.end_rev[side];
-            e.src = rg.end_src[side];
-        } else {
-            const int d = side * 2 + (which - 1);
-            if (rg.diag_src[d] >= 0) {
-                const int pt = rg.diag_pt[d];
-                if (rg.diag_kind[d] == SRC_HALO) e = {ET_HALOPT, (uint8_t)(pt & 1), 0, 0, pt & 2, 0, 0};
-                else e = {ET_PT, (uint8_t)(pt & 1), 0, 0, pt & 2, pt >> 2, 0};
-                e.src = rg.diag_src[d];
-            }
+    if (threadIdx.x < 2) { // the two strip ends: fold source kind, row/column and orientation into base + strides
+        const int side = threadIdx.x;
+        const size_t kq = (size_t)p.kq;
+        const unsigned char *tmp = reinterpret_cast<const unsigned char *>(p.tmp), *halo = reinterpret_cast<const unsigned char *>(p.halo);
+        WsEnd e{nullptr, nullptr, nullptr, 0, 0, 0, 0, {0, 0}};
+        const int kind = rg.end_kind[side], row = rg.end_row[side], rev = rg.end_rev[side];
+        const size_t src = (size_t)rg.end_src[side];
+        if (kind == SRC_TMPCOL) { // the neighbour's i = 1 (row 0) or i = np (row 1) column: points i + 4 t
+            e.col = tmp + src * kq * 128 + ((row ? 3 : 0) + (rev ? 12 : 0)) * 8;
+            e.step = rev ? -32 : 32;
+            e.slab_bytes = 128;
+        } else if (kind == SRC_TMP) { // a natural j-row of the neighbour's slab
+            e.col = tmp + src * kq * 128 + (4 * row + (rev ? 3 : 0)) * 8;
+            e.step = rev ? -8 : 8;
+            e.slab_bytes = 128;
+        } else { // a received halo row
+            e.col = halo + src * kq * 32 + (rev ? 24 : 0);
+            e.step = rev ? -8 : 8;
+            e.slab_bytes = 32;
         }
-        endtma[k] = e;
+#pragma unroll
+        for (int which = 0; which < 2; ++which) {
+            const int d = side * 2 + which;
+            const unsigned char *ptr = nullptr;
+            int sb = 0;
+            if (rg.diag_src[d] >= 0) {
+                const size_t ds = (size_t)rg.diag_src[d];
+                if (rg.diag_kind[d] == SRC_HALO) { ptr = halo + ds * kq * 32 + rg.diag_pt[d] * 8; sb = 32; }
+                else { ptr = tmp + ds * kq * 128 + rg.diag_pt[d] * 8; sb = 128; }
+            }
+            if (which == 0) { e.d0 = ptr; e.d0_slab_bytes = sb; }
+            else { e.d1 = ptr; e.d1_slab_bytes = sb; }
+        }
+        if (p.debug_flags & 2) {
+            e.col = tmp + (size_t)first * kq * 128;
+            e.step = 8;
+            e.slab_bytes = 128;
+            e.d0 = e.d1 = e.col;
+            e.d0_slab_bytes = e.d1_slab_bytes = 128;
+        }
+        wsend[side] = e;
     }
     __syncthreads(); // the only CTA-wide barrier
     if (my_n <= 0) return;
 
     const int swz = (lane >> 2) & 1, sw = lane & 7;
-    const int elemS = rg.s_src[0], elemN = rg.n_src[0];
-    const int rawS = rg.s_c0[0], rawN = rg.n_c0[0];
+    // (p.debug_flags, timing experiments only, results are wrong: 1 = the S/N rows are read from the strip's own slabs,
+    //  2 = the strip-end values are read from the strip's own first slab: no line of another CTA is touched)
+    const int elemS = (p.debug_flags & 1) ? first : rg.s_src[0], elemN = (p.debug_flags & 1) ? first : rg.n_src[0];
+    const int rawS = (p.debug_flags & 1) ? 0 : rg.s_c0[0], rawN = (p.debug_flags & 1) ? 12 : rg.n_c0[0];
     const CUtensorMap *mapS = rawS == ROW_IN_HALO ? &p.map4_halo : &p.map4_rows, *mapN = rawN == ROW_IN_HALO ? &p.map4_halo : &p.map4_rows;
     const int c0S = rawS == ROW_IN_HALO ? 0 : rawS, c0N = rawN == ROW_IN_HALO ? 0 : rawN;
     const bool std_corners = rg.all_std != 0;
@@ -1541,11 +1571,11 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
         cperm_pack |= (uint32_t)rg.corner_perm[member][c] << (8 * c);
     }
     const uint64_t pol_out = l2_policy_evict_first();
-    unsigned char *endbuf_w = endbuf + warp * 2 * WS_END_SIDE;
-    uint32_t end_bytes = 0;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) end_bytes += ws_end_box_bytes(endtma[k].kind);
-
+    // end-member lanes: slot of this lane in the warp's two cp.async sets, and the strip end it serves
+    const bool end_lane = member == 0 || member == 3;
+    const int eside = member == 3 ? 1 : 0;
+    const uint32_t eslot0 = smem_u32(endbuf) + (uint32_t)(warp * 1536 + (eside * 8 + j) * 48);
+    const unsigned char *eslot0_p = endbuf + warp * 1536 + (eside * 8 + j) * 48;
     auto kq_of = [&](int n) { return (t0 + n) * TILE_SLABS + warp * WS_SLABS; };
     auto issue_tile = [&](int n, int s) {
         mbar_expect_tx(bar0 + s * 8, (uint32_t)TILE_BYTES);
@@ -1558,51 +1588,28 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
         tma_load_3d(rb, mapS, c0S, kq_of(n), elemS, nbar);
         tma_load_3d(rb + 1024, mapN, c0N, kq_of(n), elemN, nbar);
     };
-    auto issue_end = [&](int n) {
-        const int kq0 = kq_of(n);
-        const uint32_t ebar = bar0 + (n % STAGES) * 8;
-        mbar_expect_tx(ebar, end_bytes);
+    // end-member lanes: fetch the strip-end values of tile n into set n & 1 (six 8-byte cp.async, one group)
+    auto fetch_end = [&](int n) {
+        if (end_lane) {
+            const WsEnd e = wsend[eside];
+            const int slab = kq_of(n) + j;
+            const uint32_t ok = slab < p.kq ? 8u : 0u; // slabs past a ragged end: zero fill, nothing is read
+            const size_t sl = ok ? (size_t)slab : 0;
+            const uint32_t dst = eslot0 + (uint32_t)((n & 1) * 768);
+            const unsigned char *c = e.col + sl * (size_t)e.slab_bytes;
 #pragma unroll
-        for (int side = 0; side < 2; ++side) {
-#pragma unroll
-            for (int which = 0; which < 3; ++which) {
-                const EndTma e = endtma[3 * side + which];
-                const uint32_t dst = smem_u32(endbuf_w) + (uint32_t)(side * WS_END_SIDE + (which ? 384 + 128 * which : 0));
-                switch (e.kind) {
-                case ET_COL: tma_load_4d(dst, &p.map_col, e.c0, 0, kq0, e.src, ebar); break;
-                case ET_ROW: tma_load_3d(dst, &p.map1_rows, e.c0, kq0, e.src, ebar); break;
-                case ET_HALOROW: tma_load_3d(dst, &p.map1_halo, 0, kq0, e.src, ebar); break;
-                case ET_PT: tma_load_4d(dst, &p.map_pt8, e.c0, e.c1, kq0, e.src, ebar); break;
-                case ET_HALOPT: tma_load_3d(dst, &p.map_halo_pt8, e.c0, kq0, e.src, ebar); break;
-                default: break;
-                }
-            }
+            for (int t = 0; t < 4; ++t) cp_async8(dst + t * 8, c + t * e.step, ok);
+            if (e.d0) cp_async8(dst + 32, e.d0 + sl * (size_t)e.d0_slab_bytes, ok);
+            if (e.d1) cp_async8(dst + 40, e.d1 + sl * (size_t)e.d1_slab_bytes, ok);
         }
-    };
-    // lanes of an end member: the four values along the facing edge (own orientation) and the two diagonals
-    auto read_end = [&](int side, double (&col)[4], double &d0, double &d1) {
-        const unsigned char *eb = endbuf_w + side * WS_END_SIDE;
-        const EndTma c = endtma[3 * side];
-        const int rm = c.rev ? 3 : 0;
-        if (c.kind == ET_COL) { // [slab][j][i pair]
-            const unsigned char *b = eb + j * 64 + c.hi * 8;
-#pragma unroll
-            for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + ((t ^ rm) << 4));
-        } else { // [slab][4 doubles], SWIZZLE_32B
-            const unsigned char *b = eb + j * 32;
-            const int x = ((j >> 2) & 1) ^ (rm >> 1), y = rm & 1;
-#pragma unroll
-            for (int t = 0; t < 4; ++t) col[t] = *reinterpret_cast<const double *>(b + (((t >> 1) ^ x) << 4) + (((t & 1) ^ y) << 3));
-        }
-        d0 = *reinterpret_cast<const double *>(eb + 512 + j * 16 + endtma[3 * side + 1].hi * 8);
-        d1 = *reinterpret_cast<const double *>(eb + 640 + j * 16 + endtma[3 * side + 2].hi * 8);
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
     if (lane == 0) {
         issue_nbr(0);
         if (my_n > 1) issue_nbr(1);
-        issue_end(0);
     }
+    fetch_end(0);
     const SmemMetric M{metric_s + member * WS_METRIC_STRIDE};
 
     for (int n = 0; n < my_n; ++n) {
@@ -1636,8 +1643,15 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
         dg[2] = shfl_up8(nbN[3]);   // NW
         dg[1] = shfl_down8(nbS[0]); // SE: west end of the east mate's S row
         dg[3] = shfl_down8(nbN[0]); // NE
-        if (member == 0) read_end(0, nbW, dg[0], dg[2]); // strip ends: the outside neighbour, staged by TMA
-        if (member == 3) read_end(1, nbE, dg[1], dg[3]);
+        // strip ends: the outside neighbour's values, fetched by this lane's own cp.async one tile ago
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        if (end_lane) {
+            const double2 *es = reinterpret_cast<const double2 *>(eslot0_p + q * 768);
+            const double2 c01 = es[0], c23 = es[1], dd = es[2];
+            if (member == 0) { nbW[0] = c01.x; nbW[1] = c01.y; nbW[2] = c23.x; nbW[3] = c23.y; dg[0] = dd.x; dg[2] = dd.y; }
+            else { nbE[0] = c01.x; nbE[1] = c01.y; nbE[2] = c23.x; nbE[3] = c23.y; dg[1] = dd.x; dg[3] = dd.y; }
+        }
+        if (n + 1 < my_n) fetch_end(n + 1);
 
         // ---- DSS (edgeVunpack): mid-edge points, then corners in ascending global point order
         v[1] += nbS[1]; v[2] += nbS[2];
@@ -1669,13 +1683,10 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
                 v[pt] = sum;
             }
         }
-        // every lane has its tile row, its S/N rows and (end members) the strip-end values in registers: the strip-end
-        // buffer can take the next tile's boxes and, for SK_POST, the stage can take the slab of Qdp
-        asm volatile("" ::"d"(v[0]), "d"(v[3]), "d"(v[5]), "d"(v[6]), "d"(v[9]), "d"(v[10]), "d"(v[12]), "d"(v[15]) : "memory");
-        __syncwarp();
-        if (lane == 0) {
-            if (n + 1 < my_n) issue_end(n + 1);
-            if (KIND == SK_POST) {
+        if (KIND == SK_POST) { // every lane has its tile row in registers: the stage can take the slab of Qdp while the Laplacian runs
+            asm volatile("" ::"d"(v[0]), "d"(v[3]), "d"(v[5]), "d"(v[6]), "d"(v[9]), "d"(v[10]), "d"(v[12]), "d"(v[15]) : "memory");
+            __syncwarp();
+            if (lane == 0) {
                 mbar_expect_tx(qbar, (uint32_t)TILE_BYTES);
                 tma_load_3d(stage0 + s * SB, &p.map4_q, 0, kq0, first, qbar);
             }

@@ -56,6 +56,7 @@ struct SweepParams {
     const StripReg *strip_reg; // MODE_SWEEP2: one per strip, same order
     int strip_count;
     int *work_counter;      // persistent strip sweep: global item counter, zero at launch
+    int debug_flags;        // warp-strip sweep: timing experiments (BWK_DEBUG_FLAGS), 0 in production
     int nbr_ahead;          // persistent strip sweep: the S/N rows are requested this many tiles ahead (1 or 2)
     int elem_first;         // 0-based first local element (when elem_list == nullptr)
     int elem_count;         // grid x (MODE_LAPLACE / MODE_SWEEP1)
