@@ -99,7 +99,7 @@ struct Ctx {
     bool inited = false;
     int nelem = 0, nlev = 0, qsize = 0, kq = 0;
     size_t q_doubles = 0;
-    cudaStream_t s_main = nullptr, s_comm = nullptr, s_h2d = nullptr, s_d2h = nullptr;
+    cudaStream_t s_main = nullptr, s_comm = nullptr, s_dep = nullptr, s_h2d = nullptr, s_d2h = nullptr;
     double *d_q = nullptr, *d_tmp = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
     double *d_w = nullptr, *d_ratio = nullptr; // advance_hypervis_scalar: biharmonic work buffer, dpdiss/dp [nelem][nlev][16]
     CUtensorMap map_w, map_w_rows, map_w_pt; // the work buffer seen as slabs / edge rows / i-pairs (strip sweeps reading it)
@@ -129,7 +129,7 @@ struct Ctx {
     // comm
     ncclComm_t comm = nullptr;
     int rank = 0, nranks = 1;
-    cudaEvent_t ev_b = nullptr, ev_halo = nullptr, ev_misc = nullptr;
+    cudaEvent_t ev_b = nullptr, ev_halo = nullptr, ev_misc = nullptr, ev_start = nullptr, ev_int = nullptr;
     cudaEvent_t events[NEVENTS] = {};
     std::vector<cudaEvent_t> chunk_up, chunk_done;
     // host-buffer pipeline of the full biharmonic (bwk_biharmonic_wk_scalar_full): strips_all re-ordered
@@ -602,7 +602,7 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
 {
     const Plan &P = g.plan;
     if (P.nranks == 1) {
-        if (produce(0, g.nelem, (const int32_t *)nullptr)) return 1;
+        if (produce(0, g.nelem, (const int32_t *)nullptr, g.s_main)) return 1;
         return sweep2_list(0, g.s_main, consume_mode, out);
     }
     static const bool trace = std::getenv("BWK_TRACE") != nullptr; // debugging aid: serialised phases with their durations on stderr
@@ -616,27 +616,53 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
             std::fprintf(stderr, "[bwk trace rank %d] %-28s %9.1f us\n", P.rank, what, us);
             return 0;
         };
-        if (lap("produce(boundary)", g.s_main, [&] { return produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary); })) return 1;
+        if (lap("produce(boundary)", g.s_main, [&] { return produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary, g.s_main); })) return 1;
         if (g.comm && lap("pack + ncclSend/Recv", g.s_comm, [&] { return exchange_halo(); })) return 1;
-        if (lap("produce(interior)", g.s_main, [&] { return produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior); })) return 1;
+        if (lap("produce(interior)", g.s_main, [&] { return produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior, g.s_main); })) return 1;
         if (lap("consume(independent strips)", g.s_main, [&] { return sweep2_list(2, g.s_main, consume_mode, out); })) return 1;
         if (lap("consume(dependent strips)", g.s_main, [&] { return sweep2_list(1, g.s_main, consume_mode, out); })) return 1;
         std::fprintf(stderr, "[bwk trace rank %d] boundary %zu interior %zu elements; independent %zu dependent %zu strips\n", P.rank,
                      P.boundary_list.size(), P.interior_list.size(), P.strips_independent.size(), P.strips_dependent.size());
         return 0;
     }
-    if (produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary)) return 1;
-    CK(cudaEventRecord(g.ev_b, g.s_main));
-    CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
+    static const bool old_sched = std::getenv("BWK_MULTI_SCHED") && std::atoi(std::getenv("BWK_MULTI_SCHED")) == 0; // A/B knob: round-1 schedule
+    if (old_sched) {
+        if (produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary, g.s_main)) return 1;
+        CK(cudaEventRecord(g.ev_b, g.s_main));
+        CK(cudaStreamWaitEvent(g.s_comm, g.ev_b, 0));
+        if (exchange_halo()) return 1;
+        CK(cudaEventRecord(g.ev_halo, g.s_comm));
+        if (produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior, g.s_main)) return 1;
+        if (sweep2_list(2, g.s_main, consume_mode, out)) return 1;
+        CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
+        if (sweep2_list(1, g.s_main, consume_mode, out)) return 1;
+        // the next pass's exchange overwrites the halo buffer: it must not start before these strips have read it
+        CK(cudaEventRecord(g.ev_misc, g.s_main));
+        CK(cudaStreamWaitEvent(g.s_comm, g.ev_misc, 0));
+        return 0;
+    }
+    // Three streams, no kernel waits for a kernel it does not depend on:
+    //   s_comm (highest priority): produce(boundary) -> edge pack -> ncclSend/Recv        -> ev_halo
+    //   s_main:                    produce(interior) -> ev_int -> independent strips (after ev_b: they read boundary elements' tmp)
+    //   s_dep:                     after ev_int and ev_halo: dependent strips, concurrently with the independent ones
+    // The boundary elements' CTAs are dispatched ahead of the interior grid (priority), their tail and the small dependent-strip
+    // launch no longer run on a partly empty GPU (round 1: two serialised small launches per step on s_main).
+    CK(cudaEventRecord(g.ev_start, g.s_main));
+    CK(cudaStreamWaitEvent(g.s_comm, g.ev_start, 0));
+    if (produce(0, (int)P.boundary_list.size(), (const int32_t *)g.d_boundary, g.s_comm)) return 1;
+    CK(cudaEventRecord(g.ev_b, g.s_comm));
     if (exchange_halo()) return 1;
     CK(cudaEventRecord(g.ev_halo, g.s_comm));
-    if (produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior)) return 1;
+    if (produce(0, (int)P.interior_list.size(), (const int32_t *)g.d_interior, g.s_main)) return 1;
+    CK(cudaEventRecord(g.ev_int, g.s_main));
+    CK(cudaStreamWaitEvent(g.s_main, g.ev_b, 0));
     if (sweep2_list(2, g.s_main, consume_mode, out)) return 1;
-    CK(cudaStreamWaitEvent(g.s_main, g.ev_halo, 0));
-    if (sweep2_list(1, g.s_main, consume_mode, out)) return 1;
-    // the next pass's exchange overwrites the halo buffer: it must not start before these strips have read it
-    CK(cudaEventRecord(g.ev_misc, g.s_main));
-    CK(cudaStreamWaitEvent(g.s_comm, g.ev_misc, 0));
+    CK(cudaStreamWaitEvent(g.s_dep, g.ev_int, 0));
+    CK(cudaStreamWaitEvent(g.s_dep, g.ev_halo, 0));
+    if (sweep2_list(1, g.s_dep, consume_mode, out)) return 1;
+    // join; the next pass's exchange overwrites the halo buffer only after ev_start of that pass, i.e. after these strips
+    CK(cudaEventRecord(g.ev_misc, g.s_dep));
+    CK(cudaStreamWaitEvent(g.s_main, g.ev_misc, 0));
     return 0;
 }
 
@@ -645,7 +671,7 @@ int biharmonic_device(int produce_mode = MODE_SWEEP1, const CUtensorMap *out = n
     if (!g.have_metric) return fail("no element metric on the device");
     if (!g.have_topology) return fail("no topology: call bwk_set_topology_* first");
     if (compute_rspheremp()) return 1;
-    return dss_pass([&](int first, int count, const int32_t *list) { return sweep(produce_mode, first, count, list, g.s_main); }, consume_mode, out);
+    return dss_pass([&](int first, int count, const int32_t *list, cudaStream_t st) { return sweep(produce_mode, first, count, list, st); }, consume_mode, out);
 }
 
 // advance_hypervis_scalar on the device-resident Qdp (d_q); see bwk_b200.h
@@ -677,8 +703,8 @@ int hypervis_device(double dt2, double nu_q, int subcycles, int limiter)
             // Qtens = biharmonic(dpdiss * Qdp / dp) -> work buffer (Qdp itself is still needed)
             if (biharmonic_device(MODE_SWEEP1_PRE, &g.map_w)) return 1;
             // Qdp = DSS(limiter(Qdp * spheremp - dt nu_q Qtens)) * rspheremp
-            auto post = [&](int first, int count, const int32_t *list) {
-                CK(launch_hypervis_post(g.d_q, g.d_w, g.d_tmp, g.d_elem, g.d_rsph, list, first, count, g.kq, coef, limiter, g.s_main));
+            auto post = [&](int first, int count, const int32_t *list, cudaStream_t st) {
+                CK(launch_hypervis_post(g.d_q, g.d_w, g.d_tmp, g.d_elem, g.d_rsph, list, first, count, g.kq, coef, limiter, st));
                 g.launches++;
                 return 0;
             };
@@ -691,7 +717,7 @@ int hypervis_device(double dt2, double nu_q, int subcycles, int limiter)
         // pass 2: DSS of the work buffer -> Qdp.  Nothing to produce: the halo exchange starts as soon as pass 1 is done and
         // overlaps the independent strips.
         g.src_is_w = true;
-        const int rc = dss_pass([](int, int, const int32_t *) { return 0; }, MODE_DSS, &g.sp.map_q);
+        const int rc = dss_pass([](int, int, const int32_t *, cudaStream_t) { return 0; }, MODE_DSS, &g.sp.map_q);
         g.src_is_w = false;
         if (rc) return 1;
     }
@@ -718,8 +744,8 @@ int dp3d_device(int var_coef1, int undamp)
         }
         metric1 = g.d_metric_plain;
     }
-    auto produce = [&](int first, int count, const int32_t *list) {
-        CK(launch_dp3d_laplace(true, g.d_q, g.d_tmp, metric1, g.d_v2c, g.d_elem, g.d_rsph, list, first, count, g.nlev, undamp, g.s_main));
+    auto produce = [&](int first, int count, const int32_t *list, cudaStream_t st) {
+        CK(launch_dp3d_laplace(true, g.d_q, g.d_tmp, metric1, g.d_v2c, g.d_elem, g.d_rsph, list, first, count, g.nlev, undamp, st));
         if (count > 0) g.launches++;
         return 0;
     };
@@ -857,11 +883,14 @@ int bwk_init(int nelemd, int nlev, int qsize)
         CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
         CK(cudaStreamCreateWithPriority(&g.s_comm, cudaStreamNonBlocking, prio_hi));
     }
+    CK(cudaStreamCreateWithFlags(&g.s_dep, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&g.ev_b, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&g.ev_halo, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&g.ev_misc, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&g.ev_start, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&g.ev_int, cudaEventDisableTiming));
     for (int i = 0; i < NEVENTS; ++i) CK(cudaEventCreate(&g.events[i]));
     CK(cudaMalloc(&g.d_q, sizeof(double) * g.q_doubles));
     CK(cudaMalloc(&g.d_elem, sizeof(double) * ELEM_DOUBLES * nelemd));
@@ -902,6 +931,9 @@ int bwk_finalize(void)
     if (g.ev_b) cudaEventDestroy(g.ev_b);
     if (g.ev_halo) cudaEventDestroy(g.ev_halo);
     if (g.ev_misc) cudaEventDestroy(g.ev_misc);
+    if (g.ev_start) cudaEventDestroy(g.ev_start);
+    if (g.ev_int) cudaEventDestroy(g.ev_int);
+    if (g.s_dep) cudaStreamDestroy(g.s_dep);
     if (g.s_main) cudaStreamDestroy(g.s_main);
     if (g.s_comm) cudaStreamDestroy(g.s_comm);
     if (g.s_h2d) cudaStreamDestroy(g.s_h2d);
@@ -938,6 +970,7 @@ int bwk_sync(void)
     if (need_init()) return 1;
     CK(cudaStreamSynchronize(g.s_main));
     CK(cudaStreamSynchronize(g.s_comm));
+    CK(cudaStreamSynchronize(g.s_dep));
     CK(cudaStreamSynchronize(g.s_h2d));
     CK(cudaStreamSynchronize(g.s_d2h));
     return 0;

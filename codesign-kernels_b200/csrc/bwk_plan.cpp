@@ -409,8 +409,17 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
         std::vector<int32_t> all((size_t)pl.count);
         for (int64_t le = 0; le < pl.count; ++le) all[(size_t)le] = (int32_t)le;
         make_strips(all, &pl.strips_all, &pl.reg_all);
-        make_strips(pl.dependent_list, &pl.strips_dependent, &pl.reg_dependent);
-        make_strips(pl.independent_list, &pl.strips_independent, &pl.reg_independent);
+        // A strip is dependent (runs after the halo exchange) as soon as one member reads a received row.  The strips stay
+        // whole: cutting the dependent elements out (round 1) left 176 one-element strips per rank at 8 ranks -- the
+        // elements at both ends of every row whose face-edge neighbour lives on another rank -- each costing as much as
+        // a full strip, and shortened their rows' last strips.
+        for (size_t i = 0; i < pl.strips_all.size(); ++i) {
+            const int f = strip_first(pl.strips_all[i]), n = strip_count(pl.strips_all[i]);
+            bool dep = false;
+            for (int e = f; e < f + n; ++e) dep = dep || is_dependent[(size_t)e];
+            (dep ? pl.strips_dependent : pl.strips_independent).push_back(pl.strips_all[i]);
+            (dep ? pl.reg_dependent : pl.reg_independent).push_back(pl.reg_all[i]);
+        }
     }
 
     // ---- node groups of the local points (rspheremp, tests)
