@@ -439,7 +439,7 @@ def main():
         if os.path.exists(tr):
             try:
                 tj = json.load(open(tr))
-                want = "sweep2_strip_kernel" if dom.startswith("sweep2") else "sweep_kernel<1"
+                want = "sweep2 (default form" if dom.startswith("sweep2") else "sweep_kernel<1"
                 for kname, rec in tj["kernels"].items():
                     if want in kname:
                         roofline["traffic"] = rec["dram_bytes_per_slab"] * kq * count

@@ -1457,23 +1457,25 @@ struct WsEnd {
     int32_t pad[2];
 };
 static_assert(sizeof(WsEnd) == 48, "WsEnd layout");
-template <int STAGES>
+// ROWSETS = 2: S/N rows requested two tiles ahead (double buffered); 1: one set, requested right after the previous tile's rows
+// have been consumed -- with a 2-stage tile ring that is the 50 KB / 128-register shape that puts FOUR CTAs on an SM
+template <int STAGES, int ROWSETS>
 constexpr int wstrip_smem_bytes()
 {
-    return 1024 + 4 * STAGES * TILE_BYTES + WS_ROWBUF_BYTES + WS_ENDBUF_BYTES + 4 * (STAGES + 1) * 8 + 4 * WS_METRIC_STRIDE * 8 + 2 * 48 + 4 * 34 * 8 + 64;
+    return 1024 + 4 * STAGES * TILE_BYTES + ROWSETS * (WS_ROWBUF_BYTES / 2) + WS_ENDBUF_BYTES + 4 * (STAGES + 1) * 8 + 4 * WS_METRIC_STRIDE * 8 + 2 * 48 + 4 * 34 * 8 + 64;
 }
 __device__ __forceinline__ double shfl_up8(double x) { return __shfl_up_sync(0xffffffffu, x, 8); }
 __device__ __forceinline__ double shfl_down8(double x) { return __shfl_down_sync(0xffffffffu, x, 8); }
 
-template <int STAGES, int KIND>
-__global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_constant__ SweepParams p)
+template <int STAGES, int KIND, int MINB>
+__global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_constant__ SweepParams p)
 {
-    constexpr int SB = TILE_BYTES, WARPS = 4;
+    constexpr int SB = TILE_BYTES, WARPS = 4, ROWSETS = MINB >= 4 ? 1 : 2;
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     unsigned char *stages = smem;                                               // [warp][stage][4 members x 8 slabs x 128 B], SWIZZLE_128B
     unsigned char *rowbuf = stages + WARPS * STAGES * SB;                       // [set][warp][S,N][32 x 32 B], SWIZZLE_32B
-    unsigned char *endbuf = rowbuf + WS_ROWBUF_BYTES;                           // [warp][set][end lane][48 B]: cp.async slots of the end members
+    unsigned char *endbuf = rowbuf + ROWSETS * (WS_ROWBUF_BYTES / 2);                           // [warp][set][end lane][48 B]: cp.async slots of the end members
     uint64_t *bars = reinterpret_cast<uint64_t *>(endbuf + WS_ENDBUF_BYTES);    // full [warp][stage], qdp_full [warp]
     double *metric_s = reinterpret_cast<double *>(bars + WARPS * (STAGES + 1)); // [member][WS_METRIC_STRIDE]
     WsEnd *wsend = reinterpret_cast<WsEnd *>(metric_s + 4 * WS_METRIC_STRIDE);  // [W end, E end]
@@ -1583,7 +1585,7 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
     };
     auto issue_nbr = [&](int n) {
         const uint32_t nbar = bar0 + (n % STAGES) * 8;
-        const uint32_t rb = smem_u32(rowbuf) + (uint32_t)((((n & 1) * WARPS) + warp) * 2048);
+        const uint32_t rb = smem_u32(rowbuf) + (uint32_t)(((ROWSETS == 2 ? (n & 1) * WARPS : 0) + warp) * 2048);
         mbar_expect_tx(nbar, 2048u);
         tma_load_3d(rb, mapS, c0S, kq_of(n), elemS, nbar);
         tma_load_3d(rb + 1024, mapN, c0N, kq_of(n), elemN, nbar);
@@ -1607,7 +1609,7 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
 
     if (lane == 0) {
         issue_nbr(0);
-        if (my_n > 1) issue_nbr(1);
+        if (ROWSETS == 2 && my_n > 1) issue_nbr(1);
     }
     fetch_end(0);
     const SmemMetric M{metric_s + member * WS_METRIC_STRIDE};
@@ -1617,7 +1619,7 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
         const int kq0 = kq_of(n);
         const uint32_t parity = (uint32_t)((n / STAGES) & 1);
         unsigned char *row = stages + ((size_t)warp * STAGES + s) * SB + lane * 128;
-        const unsigned char *rb = rowbuf + (size_t)((q * WARPS + warp) * 2048) + lane * 32;
+        const unsigned char *rb = rowbuf + (size_t)(((ROWSETS == 2 ? q * WARPS : 0) + warp) * 2048) + lane * 32;
         double v[16], nbS[4], nbN[4], nbW[4], nbE[4], dg[4];
 
         mbar_wait(bar0 + s * 8, parity);
@@ -1632,6 +1634,17 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
             nbS[0] = a.x; nbS[1] = a.y; nbS[2] = b.x; nbS[3] = b.y;
             const double2 c = *reinterpret_cast<const double2 *>(rb + 1024 + (swz << 4)), d = *reinterpret_cast<const double2 *>(rb + 1024 + ((1 ^ swz) << 4));
             nbN[0] = c.x; nbN[1] = c.y; nbN[2] = d.x; nbN[3] = d.y;
+        }
+        if (ROWSETS == 1) { // the single row set has been read by every lane: it can take the next tile's rows
+            asm volatile("" ::"d"(nbS[0]), "d"(nbS[2]), "d"(nbN[0]), "d"(nbN[2]) : "memory");
+            __syncwarp();
+            if (lane == 0 && n + 1 < my_n) {
+                issue_nbr(n + 1);
+                if (STAGES == 2 && n >= 1) { // 2-stage ring: tile n+1 goes where tile n-1 was, once that tile's store has read it
+                    bulk_wait_read<0>();
+                    issue_tile(n + 1, (n + 1) % STAGES);
+                }
+            }
         }
         // ---- W/E mates are 8 lanes away: their facing columns and the facing ends of their S/N neighbour rows by shuffle
 #pragma unroll
@@ -1713,11 +1726,11 @@ __global__ void __launch_bounds__(128, 3) sweep2_wstrip_kernel(const __grid_cons
         if (lane == 0) {
             tma_store_3d_hint(&p.map4_out, 0, kq0, first, stage0 + s * SB, pol_out);
             bulk_commit();
-            if (n >= 1 && n - 1 + STAGES < my_n) { // refill the stage tile n-1 used, once its store has read it
+            if (STAGES > 2 && n >= 1 && n - 1 + STAGES < my_n) { // refill the stage tile n-1 used, once its store has read it
                 bulk_wait_read<1>();
                 issue_tile(n - 1 + STAGES, (n - 1) % STAGES);
             }
-            if (n + 2 < my_n) issue_nbr(n + 2); // rowbuf set q is free: every lane consumed it before the __syncwarp above
+            if (ROWSETS == 2 && n + 2 < my_n) issue_nbr(n + 2); // rowbuf set q is free: every lane consumed it before the __syncwarp above
         }
     }
     if (lane == 0) bulk_wait_read<0>();
@@ -1827,29 +1840,37 @@ cudaError_t launch_sweep2_persist(int mode, const SweepParams &p, cudaStream_t s
     return cudaErrorInvalidValue;
 }
 
-template <int STAGES, int KIND>
+template <int STAGES, int KIND, int MINB>
 static cudaError_t launch_wstrip_t(const SweepParams &p, cudaStream_t st)
 {
-    constexpr int smem = wstrip_smem_bytes<STAGES>();
-    static_assert(3 * (smem + 1024) <= 228 * 1024, "three CTAs per SM");
+    constexpr int smem = wstrip_smem_bytes<STAGES, (MINB >= 4 ? 1 : 2)>();
+    static_assert(MINB * (smem + 1024) <= 228 * 1024, "MINB CTAs per SM");
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(sweep2_wstrip_kernel<STAGES, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(sweep2_wstrip_kernel<STAGES, KIND, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
     if (p.strip_count <= 0 || p.units <= 0) return cudaSuccess;
     dim3 grid((unsigned)p.strip_count, (unsigned)p.units);
-    sweep2_wstrip_kernel<STAGES, KIND><<<grid, 128, smem, st>>>(p);
+    sweep2_wstrip_kernel<STAGES, KIND, MINB><<<grid, 128, smem, st>>>(p);
     return cudaGetLastError();
 }
 
 // warp-strip sweep over full regular strips whose members' S/N neighbours are consecutive elements (p.strip_reg / p.strip_count)
 cudaError_t launch_sweep2_wstrip(int mode, const SweepParams &p, cudaStream_t st)
 {
-    if (mode == MODE_SWEEP2) return launch_wstrip_t<3, SK_LAP>(p, st);
-    if (mode == MODE_DSS) return launch_wstrip_t<3, SK_DSS>(p, st);
-    if (mode == MODE_SWEEP2_POST) return launch_wstrip_t<3, SK_POST>(p, st);
+    // shape A/B (BWK_WSTRIP_SHAPE): 4 = 2-stage ring, one row set, 128 registers: four CTAs (16 warps) per SM; 3 = 3-stage ring,
+    // two row sets, 168 registers: three CTAs per SM
+    static const int shape = std::getenv("BWK_WSTRIP_SHAPE") ? std::atoi(std::getenv("BWK_WSTRIP_SHAPE")) : 3;
+    if (shape == 4) {
+        if (mode == MODE_SWEEP2) return launch_wstrip_t<2, SK_LAP, 4>(p, st);
+        if (mode == MODE_DSS) return launch_wstrip_t<2, SK_DSS, 4>(p, st);
+        if (mode == MODE_SWEEP2_POST) return launch_wstrip_t<2, SK_POST, 4>(p, st);
+    }
+    if (mode == MODE_SWEEP2) return launch_wstrip_t<3, SK_LAP, 3>(p, st);
+    if (mode == MODE_DSS) return launch_wstrip_t<3, SK_DSS, 3>(p, st);
+    if (mode == MODE_SWEEP2_POST) return launch_wstrip_t<3, SK_POST, 3>(p, st);
     return cudaErrorInvalidValue;
 }
 
