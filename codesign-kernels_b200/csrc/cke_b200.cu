@@ -144,7 +144,7 @@ bool launch_iteration(int impl) {
             ++g.launches;
         }
     }
-    const bool range = impl == 2;
+    const bool range = impl >= 2; // 3: the original loop form (level ranges, no cellMask factor), set by the yakl_* entry points
 #define CKE_CASE(V_, R_, U_)                                 \
     if (vec2 == (V_ == 2) && range == R_ && g.unroll == U_) \
         flux_kernel<V_, R_, U_><<<grid, kThreads, g.smem, g.stream>>>(p, g.edges_per_cta);
@@ -307,6 +307,64 @@ void cke_get_results(const Int, const Int, Real *highOrderFlx) {
 void cke_cleanup(void) {
     if (g.live) release();
 }
+
+/* ---- the YAKL-side entry points of the reference (nested_yakl_c.cpp:130-306) -------------------
+ * The Fortran driver publishes its arrays through bind(C) pointer globals (nested_vars.F90:7,75-86,138-151) and calls
+ * yakl_init / yakl_init_arrays once, then a loop form per iteration with the host tracerCur and normalThicknessFlux.
+ * Same names, same arguments, same transfers inside each call (yakl_update_device at entry, yakl_update_host at exit). */
+int *c_maxLevelCell = nullptr, *c_minLevelCell = nullptr, *c_nAdvCellsForEdge = nullptr, *c_advCellsForEdge = nullptr;
+double *c_advCoefs = nullptr, *c_advCoefs3rd = nullptr, *c_cellMask = nullptr, *c_advMaskHighOrder = nullptr;
+double *c_tracerCur = nullptr, *c_normalThicknessFlux = nullptr, *c_highOrderFlx = nullptr;
+
+void yakl_init(void) { kokkos_init(); }
+
+void yakl_init_arrays(int fnvldim, int fnEdges, int fnCells, int fnVertLevels, int fnAdv, double fcoef3rdOrder) {
+    if (!c_maxLevelCell || !c_minLevelCell || !c_nAdvCellsForEdge || !c_advCellsForEdge || !c_advCoefs || !c_advCoefs3rd || !c_cellMask ||
+        !c_advMaskHighOrder) {
+        g_failed = false;
+        fail("yakl_init_arrays: the c_* array pointers have not been published (nested_vars.F90:138-151)");
+        return;
+    }
+    // tracerCur and normalThicknessFlux arrive with every loop call (nested_yakl_c.cpp:187-188); start from zeros
+    const size_t ncl = (size_t)(fnCells > 0 ? fnCells : 0) * (size_t)(fnvldim > 0 ? fnvldim : 0);
+    const size_t ned = (size_t)(fnEdges > 0 ? fnEdges : 0) * (size_t)(fnvldim > 0 ? fnvldim : 0);
+    double *z = (double *)calloc(ncl > ned ? ncl + 1 : ned + 1, sizeof(double));
+    if (!z) {
+        fail("yakl_init_arrays: out of host memory");
+        return;
+    }
+    cke_init(1, fnEdges, fnCells, fnVertLevels, fnvldim, fnAdv, c_nAdvCellsForEdge, c_minLevelCell, c_maxLevelCell, c_advCellsForEdge, z, z,
+             c_advMaskHighOrder, c_cellMask, c_advCoefs, c_advCoefs3rd, fcoef3rdOrder, nullptr);
+    free(z);
+}
+
+static void yakl_loop(int impl, double *h_highOrderFlx, double *h_tracerCur, double *h_normalThicknessFlux, const char *who) {
+    if (!g.live) {
+        fail("%s called before a successful yakl_init_arrays", who);
+        return;
+    }
+    const Problem &p = g.p;
+    const size_t ncl = (size_t)p.nCells * p.nvldim * sizeof(double), ned = (size_t)p.nEdges * p.nvldim * sizeof(double);
+    if (ncl) CK(cudaMemcpyAsync(p.tracerCur, h_tracerCur, ncl, cudaMemcpyHostToDevice, g.stream));              // yakl_update_device
+    if (ned) CK(cudaMemcpyAsync(p.normalThicknessFlux, h_normalThicknessFlux, ned, cudaMemcpyHostToDevice, g.stream));
+    g.p.range_no_mask = impl == 3 ? 1 : 0;
+    const bool ok = launch_iteration(impl);
+    g.p.range_no_mask = 0;
+    if (!ok) return;
+    if (ned) CK(cudaMemcpyAsync(h_highOrderFlx, p.highOrderFlx, ned, cudaMemcpyDeviceToHost, g.stream));       // yakl_update_host
+    CK(cudaStreamSynchronize(g.stream));
+}
+
+/* nested_yakl_c.cpp:184-243 (= nested.F90:119-157): per edge, every contributing cell adds on its own level range */
+void yakl_original_loop(double *h_highOrderFlx, double *h_tracerCur, double *h_normalThicknessFlux) {
+    yakl_loop(3, h_highOrderFlx, h_tracerCur, h_normalThicknessFlux, "yakl_original_loop");
+}
+/* nested_yakl_c.cpp:260-306 (= nested.F90:606-630): collapsed (edge, level) loop, tracer * cellMask.  The device copy of the
+ * tracer is masked by the first kernel and re-uploaded by the next call, so the host array is never changed. */
+void yakl_gpu_optimized(double *h_highOrderFlx, double *h_tracerCur, double *h_normalThicknessFlux) {
+    yakl_loop(1, h_highOrderFlx, h_tracerCur, h_normalThicknessFlux, "yakl_gpu_optimized");
+}
+
 
 int cke_b200_time_ms(int impl, int iters, double *ms_per_iter) {
     if (!g.live) {

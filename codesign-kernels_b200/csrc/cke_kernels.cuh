@@ -14,6 +14,7 @@ struct Problem {
     int *nAdvCellsForEdge, *minLevelCell, *maxLevelCell, *advCellsForEdge;
     double *tracerCur, *cellMask, *normalThicknessFlux, *advMaskHighOrder, *advCoefs, *advCoefs3rd;
     double *highOrderFlx;
+    int range_no_mask = 0;  // RANGE form without the cellMask factor: the reference's yakl_original_loop (nested_yakl_c.cpp:184-243)
 };
 
 constexpr int kThreads = 256;
@@ -56,7 +57,8 @@ __global__ void __launch_bounds__(kThreads) mask_tracer_kernel(double *__restric
 }
 
 // RANGE = false: pass 2 of cke_impl1.cpp:18-36 (collapsed (edge, level) loop, nested.F90:332-349)
-// RANGE = true : cke_impl2.cpp:27-68 at pack size 1 (per-cell level range, tracer*cellMask)
+// RANGE = true : cke_impl2.cpp:27-68 at pack size 1 (per-cell level range, tracer*cellMask); with p.range_no_mask the
+//                original loop form nested.F90:119-157 / nested_yakl_c.cpp:184-243 (per-cell level range, no mask factor)
 template <int VEC, bool RANGE, int U>
 __global__ void __launch_bounds__(kThreads) flux_kernel(const Problem p, const int edges_per_cta) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -120,9 +122,11 @@ __global__ void __launch_bounds__(kThreads) flux_kernel(const Problem p, const i
                         const int k0 = (int)kg * VEC;
                         if (k0 + VEC - 1 >= ru->kmin && k0 <= ru->kmax) {
                             tr[u] = V::ldg(p.tracerCur + trow);
-                            const typename V::T cm = V::ldg(p.cellMask + trow);
+                            if (!p.range_no_mask) {
+                                const typename V::T cm = V::ldg(p.cellMask + trow);
 #pragma unroll
-                            for (int s = 0; s < VEC; ++s) V::set(tr[u], s, __dmul_rn(V::get(tr[u], s), V::get(cm, s)));
+                                for (int s = 0; s < VEC; ++s) V::set(tr[u], s, __dmul_rn(V::get(tr[u], s), V::get(cm, s)));
+                            }
                         } else {
 #pragma unroll
                             for (int s = 0; s < VEC; ++s) V::set(tr[u], s, 0.0);

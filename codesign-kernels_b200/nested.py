@@ -31,7 +31,7 @@ def lib_path():
 def declared_symbols():
     """Every function name declared in include/cke_b200.h."""
     text = re.sub(r"/\*.*?\*/", "", open(_HEADER).read(), flags=re.S)
-    return sorted(set(re.findall(r"\b((?:cke|kokkos)_[A-Za-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b((?:cke|kokkos|yakl)_[A-Za-z0-9_]+)\s*\(", text)))
 
 
 _lib = None
@@ -55,6 +55,10 @@ def lib():
     L.cke_cleanup.argtypes, L.cke_cleanup.restype = [], None
     L.cke_impl1_run.argtypes, L.cke_impl1_run.restype = [], None
     L.cke_impl2_run.argtypes, L.cke_impl2_run.restype = [], None
+    L.yakl_init.argtypes, L.yakl_init.restype = [], None
+    L.yakl_init_arrays.argtypes, L.yakl_init_arrays.restype = [i32] * 5 + [f64], None
+    for f in (L.yakl_original_loop, L.yakl_gpu_optimized):
+        f.argtypes, f.restype = [p] * 3, None
     L.cke_b200_set_abort_on_error.argtypes, L.cke_b200_set_abort_on_error.restype = [i32], None
     L.cke_b200_last_error.argtypes, L.cke_b200_last_error.restype = [], C.c_char_p
     L.cke_b200_launch_count.argtypes, L.cke_b200_launch_count.restype = [], C.c_longlong
@@ -199,3 +203,46 @@ class NestedLoops:
     def cke_cleanup(self):
         self.L.cke_cleanup()
         self._prob = None
+
+
+class YaklLoops:
+    """The YAKL leg of `program nested` as the Fortran side drives it (nested_vars.F90:75-86,138-151 publishes the arrays
+    through the bind(C) pointer globals c_*, nested.F90 then calls yakl_init, yakl_init_arrays and a loop form per iteration):
+    same symbol names as the reference's nested_yakl_c.cpp:130-306, served by libcke_b200.so."""
+
+    GLOBALS = (("c_maxLevelCell", "maxLevelCell", np.int32), ("c_minLevelCell", "minLevelCell", np.int32),
+               ("c_nAdvCellsForEdge", "nAdvCellsForEdge", np.int32), ("c_advCellsForEdge", "advCellsForEdge", np.int32),
+               ("c_advCoefs", "advCoefs", np.float64), ("c_advCoefs3rd", "advCoefs3rd", np.float64),
+               ("c_cellMask", "cellMask", np.float64), ("c_advMaskHighOrder", "advMaskHighOrder", np.float64))
+
+    def __init__(self, prob):
+        self.L = lib()
+        self.prob = prob
+        self.L.yakl_init()
+        _check(self.L, "yakl_init")
+        self._keep = {}
+        for sym, attr, dt in self.GLOBALS:
+            arr = np.asfortranarray(getattr(prob, attr), dtype=dt)
+            self._keep[sym] = arr
+            C.c_void_p.in_dll(self.L, sym).value = arr.ctypes.data
+        self.L.yakl_init_arrays(prob.nvldim, prob.nEdges, prob.nCells, prob.nVertLevels, prob.nAdv, prob.coef3rdOrder)
+        _check(self.L, "yakl_init_arrays")
+
+    def _run(self, fn, name, tracer):
+        p = self.prob
+        tr = np.array(p.tracerCur if tracer is None else tracer, dtype=np.float64, order="F", copy=True)
+        ntf = np.array(p.normalThicknessFlux, dtype=np.float64, order="F", copy=True)
+        out = np.full((p.nvldim, p.nEdges), np.nan, order="F")
+        fn(out.ctypes.data, tr.ctypes.data, ntf.ctypes.data)
+        _check(self.L, name)
+        assert np.array_equal(tr, p.tracerCur if tracer is None else tracer)  # the host tracer is input only
+        return out
+
+    def yakl_original_loop(self, tracer=None):
+        return self._run(self.L.yakl_original_loop, "yakl_original_loop", tracer)
+
+    def yakl_gpu_optimized(self, tracer=None):
+        return self._run(self.L.yakl_gpu_optimized, "yakl_gpu_optimized", tracer)
+
+    def cleanup(self):
+        self.L.cke_cleanup()

@@ -59,6 +59,22 @@ void cke_impl1_run(void);
  * contributing cell adds tracer*cellMask*wgt*(coef1+coef3*sgn) on its own level range only. */
 void cke_impl2_run(void);
 
+/* ---- the reference's YAKL-side interface, nested_loops/nested_yakl_c.cpp:130-306 ----------- */
+
+/* nested_yakl_c.cpp:130-140: the input arrays, published by the Fortran driver as type(c_ptr), bind(C) globals
+ * (nested_vars.F90:7, 75-86, 138-151).  Set them before yakl_init_arrays. */
+extern int *c_maxLevelCell, *c_minLevelCell, *c_nAdvCellsForEdge, *c_advCellsForEdge;
+extern double *c_advCoefs, *c_advCoefs3rd, *c_cellMask, *c_advMaskHighOrder, *c_tracerCur, *c_normalThicknessFlux, *c_highOrderFlx;
+/* nested_yakl_c.cpp:142-146 */
+void yakl_init(void);
+/* nested_yakl_c.cpp:148-181: copies the connectivity, coefficients and masks behind the c_* pointers to the device */
+void yakl_init_arrays(int fnvldim, int fnEdges, int fnCells, int fnVertLevels, int fnAdv, double fcoef3rdOrder);
+/* nested_yakl_c.cpp:184-243: the original loop form (per-cell level ranges); uploads the host tracerCur(nvldim,nCells) and
+ * normalThicknessFlux(nvldim,nEdges), computes, downloads highOrderFlx(nvldim,nEdges) -- all inside the call, as the reference */
+void yakl_original_loop(double *h_highOrderFlx, double *h_tracerCur, double *h_normalThicknessFlux);
+/* nested_yakl_c.cpp:260-306: the collapsed (edge, level) form with the cellMask factor */
+void yakl_gpu_optimized(double *h_highOrderFlx, double *h_tracerCur, double *h_normalThicknessFlux);
+
 /* ---- additions of this library (not in cke.hpp) -------------------------------------------- */
 
 /* 1 (default): failures abort like the reference's asserts; 0: they return and set the message. */

@@ -68,7 +68,7 @@ extern "C" int cke_emul_iteration(int unroll, int impl, int grid, int block, int
                                   double *tracerCur, const double *normalThicknessFlux, const double *advMaskHighOrder,
                                   const double *cellMask, const double *advCoefs, const double *advCoefs3rd,
                                   double coef3rdOrder, double *highOrderFlx) {
-    if ((unroll != 1 && unroll != 5 && unroll != 10) || (impl != 1 && impl != 2) || grid < 1 || block < edges_per_cta || edges_per_cta < 1) return 1;
+    if ((unroll != 1 && unroll != 5 && unroll != 10) || (impl < 1 || impl > 3) || grid < 1 || block < edges_per_cta || edges_per_cta < 1) return 1;
     if ((size_t)edges_per_cta * nAdv * sizeof(Rec) + edges_per_cta * sizeof(int) > sizeof smem_raw) return 1;
     Problem p;
     p.nIters = 1; p.nEdges = nEdges; p.nCells = nCells; p.nVertLevels = nVertLevels; p.nvldim = nvldim; p.nAdv = nAdv;
@@ -84,13 +84,14 @@ extern "C" int cke_emul_iteration(int unroll, int impl, int grid, int block, int
     p.advCoefs = const_cast<double *>(advCoefs);
     p.advCoefs3rd = const_cast<double *>(advCoefs3rd);
     p.highOrderFlx = highOrderFlx;
+    p.range_no_mask = impl == 3 ? 1 : 0;  // impl 3: the original loop form (yakl_original_loop): level ranges, no cellMask factor
     const bool vec2 = nvldim % 2 == 0;
     if (impl == 1) {
         const size_t n = (size_t)nCells * nvldim;
         launch((unsigned)grid, (unsigned)block, [=] { mask_tracer_kernel(p.tracerCur, p.cellMask, n); });
     }
 #define EMUL_CASE(V_, R_, U_)                                                                              \
-    if (vec2 == (V_ == 2) && (impl == 2) == R_ && unroll == U_)                                            \
+    if (vec2 == (V_ == 2) && (impl >= 2) == R_ && unroll == U_)                                            \
         launch((unsigned)grid, (unsigned)block, [=] { flux_kernel<V_, R_, U_>(p, edges_per_cta); });
     EMUL_CASE(1, false, 1) EMUL_CASE(1, false, 5) EMUL_CASE(1, false, 10)
     EMUL_CASE(2, false, 1) EMUL_CASE(2, false, 5) EMUL_CASE(2, false, 10)

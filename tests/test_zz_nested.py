@@ -276,6 +276,21 @@ def emul():
 
 @pytest.mark.parametrize("name", list(CASES))
 @pytest.mark.parametrize("ragged", [False, True])
+def test_emulated_original_loop_form_against_the_reference_compiled_here(nested, yref, emul, name, ragged):
+    """The device source's level-range form WITHOUT the cellMask factor (what libcke_b200's yakl_original_loop launches)
+    against the reference's own yakl_original_loop, with general masks and tracers that do not vanish outside the ranges."""
+    prob = make(nested, name, ragged)
+    rng = np.random.default_rng(9)
+    prob.cellMask = np.asfortranarray(rng.random(prob.cellMask.shape))
+    prob.tracerCur = np.asfortranarray(15.0 * rng.random(prob.tracerCur.shape))
+    nv = prob.nVertLevels
+    got, tr = emul(prob, 3, 3, 64, 4)
+    assert np.array_equal(tr, prob.tracerCur)
+    assert np.array_equal(got[:nv], yref.RefProblem(prob).original_loop()[:nv])
+
+
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("ragged", [False, True])
 @pytest.mark.parametrize("geom", [(3, 32, 8, 5), (5, 64, 4, 1), (1, 16, 1, 10), (2, 256, 14, 5)])
 def test_device_source_emulated_on_host_is_bit_identical_to_the_oracle(nested, cko, emul, name, ragged, geom):
     """The kernel source of libcke_b200.so (cke_kernels.cuh), compiled for the host with threads and
@@ -416,6 +431,30 @@ def test_gpu_namelist_problem_against_the_reference_compiled_here(nested, yref):
         rel = np.abs(out[:nv] - ref_orig[:nv]) / np.maximum(np.abs(ref_orig[:nv]), 1e-300)
         assert (rel <= nested.ERR_TOL).all()
         assert np.array_equal(out[:nv], ref_orig[:nv])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["namelist_shape_small", "gpu_target_pack8", "odd_levels_scalar_path", "single_edge_single_cell"])
+def test_gpu_yakl_entry_points_against_the_reference_compiled_here(nested, yref, name):
+    """libcke_b200's yakl_init / yakl_init_arrays / yakl_original_loop / yakl_gpu_optimized (the reference's YAKL-side
+    interface, nested_yakl_c.cpp:130-306, arrays published through the c_* globals) against the SAME entry points of the
+    reference compiled here, on general masks: bit for bit on the rows the reference writes; the host tracer is input only;
+    two calls in a row give the same result (the device tracer is re-uploaded by every call)."""
+    prob = make(nested, name, ragged=True)
+    rng = np.random.default_rng(7)
+    prob.cellMask = np.asfortranarray(rng.random(prob.cellMask.shape))
+    prob.tracerCur = np.asfortranarray(15.0 * rng.random(prob.tracerCur.shape))
+    nv = prob.nVertLevels
+    ref = yref.RefProblem(prob)
+    yk = nested.YaklLoops(prob)
+    try:
+        for _ in range(2):
+            assert np.array_equal(yk.yakl_gpu_optimized()[:nv], ref.gpu_optimized()[:nv])
+            assert np.array_equal(yk.yakl_original_loop()[:nv], ref.original_loop()[:nv])
+        tr2 = np.asfortranarray(3.0 * rng.random(prob.tracerCur.shape))
+        assert np.array_equal(yk.yakl_original_loop(tr2)[:nv], ref.original_loop(tr2)[:nv])
+    finally:
+        yk.cleanup()
 
 
 @pytest.mark.gpu
