@@ -405,9 +405,61 @@ int compute_rspheremp()
     if (!g.have_topology) return fail("no topology set");
     if ((int64_t)g.h_spheremp.size() != (int64_t)16 * g.nelem) return fail("no element metric uploaded/generated before the topology was used");
     const Plan &pl = g.plan;
+    if (pl.nranks > 1 && g.gen_nelem_global < 0) {
+        // Caller-supplied element records on several ranks (a real mesh): the sharers' spheremp on other ranks is not known
+        // here, so DSS it through the halo plan -- the spheremp values of exactly the rows the plan sends travel once with
+        // ncclSend/Recv (4 doubles per row), and the plan's own gather, evaluated on the host, gives DSS(spheremp) in the
+        // kernels' summation order.  Collective: every rank of the communicator must get here (same data source everywhere).
+        if (!g.comm) return fail("topology spans %d ranks but bwk_comm_init was not called", pl.nranks);
+        CK(cudaDeviceSynchronize());
+        const int64_t ns = g.send_offset.empty() ? 0 : g.send_offset.back(), nr = pl.recv_offset.back();
+        std::vector<double> hs((size_t)4 * std::max<int64_t>(ns, 1)), hr((size_t)4 * std::max<int64_t>(nr, 1));
+        auto row_points = [](int row, int t) { return row < 4 ? t + 4 * row : (row == ROW_W ? 0 : 3) + 4 * t; };
+        {
+            size_t k = 0;
+            for (int p = 0; p < pl.nranks; ++p)
+                for (const RowRef &r : pl.send[(size_t)p]) {
+                    const double *sp = &g.h_spheremp[(size_t)16 * (r.elem - pl.first)];
+                    for (int t = 0; t < 4; ++t) hs[4 * k + t] = sp[row_points(r.row, t)];
+                    ++k;
+                }
+        }
+        if (ns > 0) CK(cudaMemcpyAsync(g.d_send, hs.data(), sizeof(double) * 4 * ns, cudaMemcpyHostToDevice, g.s_comm));
+        NK(g_nccl.GroupStart());
+        for (int p = 0; p < pl.nranks; ++p) {
+            if (p == pl.rank) continue;
+            const int64_t a = g.send_offset[(size_t)p + 1] - g.send_offset[(size_t)p], b = pl.recv_offset[(size_t)p + 1] - pl.recv_offset[(size_t)p];
+            if (a > 0) NK(g_nccl.Send(g.d_send + 4 * g.send_offset[(size_t)p], (size_t)4 * a, ncclDouble, p, g.comm, g.s_comm));
+            if (b > 0) NK(g_nccl.Recv(g.d_halo + 4 * pl.recv_offset[(size_t)p], (size_t)4 * b, ncclDouble, p, g.comm, g.s_comm));
+        }
+        NK(g_nccl.GroupEnd());
+        if (nr > 0) CK(cudaMemcpyAsync(hr.data(), g.d_halo, sizeof(double) * 4 * nr, cudaMemcpyDeviceToHost, g.s_comm));
+        CK(cudaStreamSynchronize(g.s_comm));
+        std::vector<double> sp_g((size_t)16 * pl.nelem_global, std::nan(""));
+        std::memcpy(&sp_g[(size_t)16 * pl.first], g.h_spheremp.data(), sizeof(double) * 16 * g.nelem);
+        for (int p = 0; p < pl.nranks; ++p)
+            for (size_t i = 0; i < pl.recv[(size_t)p].size(); ++i) {
+                const RowRef &r = pl.recv[(size_t)p][i];
+                const double *v = &hr[(size_t)4 * (pl.recv_offset[(size_t)p] + (int64_t)i)];
+                for (int t = 0; t < 4; ++t) sp_g[(size_t)16 * r.elem + row_points(r.row, t)] = v[t];
+            }
+        std::vector<double> rsx((size_t)16 * g.nelem);
+        for (int64_t le = 0; le < g.nelem; ++le) {
+            double sum16[16];
+            gather_elem_host(pl, le, sp_g.data(), sum16);
+            for (int t = 0; t < 16; ++t) {
+                if (!(sum16[t] == sum16[t])) return fail("rspheremp: the halo plan did not deliver a sharer's spheremp (element %lld point %d)", (long long)le, t);
+                rsx[(size_t)16 * le + t] = 1.0 / sum16[t];
+            }
+        }
+        CK(cudaMemcpyAsync(g.d_rsph, rsx.data(), sizeof(double) * rsx.size(), cudaMemcpyHostToDevice, g.s_main));
+        CK(cudaStreamSynchronize(g.s_main));
+        g.have_rsph = true;
+        return 0;
+    }
     std::vector<double> table;
     if (g.gen_nelem_global >= 0 && g.gen_seed_mode == 0) table = lcg_table();
-    auto remote_sp = [&](int64_t gp, double *out) -> bool {
+    auto remote_sp = [&](int64_t gp, double *out) -> bool { // generator data: a sharer's spheremp by closed form
         if (g.gen_nelem_global < 0) return false;
         const int64_t d = 16 + (int64_t)ELEM_DOUBLES * (gp / 16) + 64 + (gp % 16);
         if (g.gen_seed_mode == 0) { *out = table[(size_t)(d & 131071)]; return true; }

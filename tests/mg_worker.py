@@ -23,6 +23,11 @@ def hypervis_inputs(n, nlev):
     return dp, dpd, 1.0e24  # with the LCG metric the weak biharmonic is O(1e-25): the two terms of the update are comparable
 
 
+def user_elements(n):
+    """element records (n, 144) that are NOT the generator's: the same on every rank and in the test"""
+    return 0.25 + np.random.default_rng(79).random((n, 144))
+
+
 def dp3d_v2c(n):
     """vec_sphere2cart stand-in (n, 96), the same on every rank and in the single-rank run of the test"""
     return np.random.default_rng(78).random((n, 96))
@@ -105,6 +110,15 @@ def main():
         ku.run_advance_hypervis_device(2.0, coef, 2, True)
         ku.sync()
         np.save(os.path.join(outdir, f"hv_{rank}.npy"), ku.download_elements(0, count))
+        # caller-supplied element records on several ranks (a real mesh, not the generator): rspheremp = 1/DSS(spheremp) must
+        # come out of the halo plan (the sharers' spheremp travels once with ncclSend/Recv), and the full biharmonic with it
+        ku.elem = np.zeros(count, dtype=bwk.ELEMENT_DTYPE)
+        ku.elem.view(np.float64).reshape(count, 144)[...] = user_elements(n)[first : first + count]
+        ku.update_device(elem=True, qtens=False, deriv=False)
+        np.save(os.path.join(outdir, f"rsph_user_{rank}.npy"), ku.get_rspheremp())
+        ku.run_biharmonic_device()
+        ku.sync()
+        np.save(os.path.join(outdir, f"user_{rank}.npy"), ku.download_elements(0, count))
         dist.barrier()
         ku.finalize()
     else:

@@ -70,6 +70,26 @@ def test_multi_gpu_matches_single_gpu_bitwise(bwk, oracle, tmp_path, ne, nlev, q
     dss = oracle.Dss(n, oracle.cubed_sphere_gdof(ne))
     ref = dss.biharmonic_full(elem, dss.rspheremp(elem), q, dvv)
     assert oracle.max_rel(np.asfortranarray(multi), ref) <= 1e-12
+    # caller-supplied element records: rspheremp through the halo plan == the oracle's 1/DSS(spheremp) bit for bit,
+    # and the full biharmonic with those elements matches the oracle (q after the hypervis call above is what the device held:
+    # the worker did not re-initialise it, so compare through the 1-rank device run instead)
+    from mg_worker import user_elements
+
+    uel = user_elements(n)
+    rs_multi = np.concatenate([np.load(tmp_path / f"rsph_user_{r}.npy") for r in range(world)], axis=-1)
+    assert np.array_equal(rs_multi, dss.rspheremp(uel))
+    multi_user = np.concatenate([np.load(tmp_path / f"user_{r}.npy") for r in range(world)], axis=-1)
+    with bwk.KernelUtils(n, nlev, qsize).allocate_data(host_arrays=False) as ku:
+        ku.initialize_data_device()
+        ku.set_topology_cubed_sphere(ne)
+        ku.upload_hypervis_fields(dp, dpd)
+        ku.run_advance_hypervis_device(2.0, coef, 2, True)  # the field the ranks held when the user elements arrived
+        ku.elem = np.zeros(n, dtype=bwk.ELEMENT_DTYPE)
+        ku.elem.view(np.float64).reshape(n, 144)[...] = uel
+        ku.update_device(elem=True, qtens=False, deriv=False)
+        ku.run_biharmonic_device()
+        single_user = ku.download_elements(0, n)
+    assert np.array_equal(multi_user, single_user)
 
 
 @pytest.mark.gpu
