@@ -90,10 +90,11 @@ struct NcclApi {
 constexpr int NPARTIAL_BLOCKS = 148 * 8;
 constexpr int NEVENTS = 64;
 
-// the warp-strip sweep's views of a field laid out like qtens (8-slab boxes, see bwk_kernels.h)
-struct Field4Maps {
-    CUtensorMap slab4, rows4, rows1, col, pt8;
+// the warp-strip sweep's views of a field laid out like qtens: boxes of 32/NM slabs x NM elements, NM = 4 << i
+struct FieldMaps {
+    CUtensorMap slab[3], rows[3];
 };
+constexpr int WS_NM[3] = {4, 8, 16};
 
 struct Ctx {
     bool inited = false;
@@ -103,7 +104,10 @@ struct Ctx {
     double *d_q = nullptr, *d_tmp = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
     double *d_w = nullptr, *d_ratio = nullptr; // advance_hypervis_scalar: biharmonic work buffer, dpdiss/dp [nelem][nlev][16]
     CUtensorMap map_w, map_w_rows, map_w_pt; // the work buffer seen as slabs / edge rows / i-pairs (strip sweeps reading it)
-    Field4Maps f4_tmp, f4_w, f4_q;           // warp-strip sweep: 8-slab views of tmp, the work buffer and qtens
+    FieldMaps fm_tmp, fm_w, fm_q;            // warp-strip sweep: views of tmp, the work buffer and qtens
+    CUtensorMap map_halo_nm[3];              // ... and of the received rows
+    StripReg *d_grp[3][3] = {};              // [list][i]: groups of WS_NM[i]/4 consecutive fast strips, records back to back
+    int64_t ngrp[3][3] = {};
     bool src_is_w = false;                  // strip sweeps and the halo pack read the work buffer instead of tmp
     double *d_v2c = nullptr, *d_metric_plain = nullptr; // biharmonic_wk_dp3d: vec_sphere2cart [nelem][96]; folded metric without tensorVisc
     bool have_v2c = false, have_metric_plain = false;
@@ -182,19 +186,16 @@ int make_slab_map(CUtensorMap *m, double *base, int kq, int64_t nelem)
     return make_map(m, base, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
-int make_field4_maps(Field4Maps *m, double *base, int kq, int64_t nelem)
+int make_field_maps(FieldMaps *m, double *base, int kq, int64_t nelem)
 {
     const uint64_t n = (uint64_t)std::max<int64_t>(nelem, 1);
-    const uint32_t e4 = (uint32_t)std::min<uint64_t>(4, n);
     const uint64_t dims[3] = {16, (uint64_t)kq, n}, str[2] = {128, (uint64_t)kq * 128};
-    const uint32_t b_slab4[3] = {16, 8, e4}, b_rows4[3] = {4, 8, e4}, b_rows1[3] = {4, 8, 1};
-    if (make_map(&m->slab4, base, 3, dims, str, b_slab4, CU_TENSOR_MAP_SWIZZLE_128B)) return 1;
-    if (make_map(&m->rows4, base, 3, dims, str, b_rows4, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
-    if (make_map(&m->rows1, base, 3, dims, str, b_rows1, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
-    const uint64_t cdims[4] = {4, 4, (uint64_t)kq, n}, cstr[3] = {32, 128, (uint64_t)kq * 128};
-    const uint32_t b_col[4] = {2, 4, 8, 1}, b_pt[4] = {2, 1, 8, 1};
-    if (make_map(&m->col, base, 4, cdims, cstr, b_col, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
-    if (make_map(&m->pt8, base, 4, cdims, cstr, b_pt, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+    for (int i = 0; i < 3; ++i) {
+        const uint32_t nm = (uint32_t)std::min<uint64_t>((uint64_t)WS_NM[i], n), sl = 32u / (uint32_t)WS_NM[i];
+        const uint32_t b_slab[3] = {16, sl, nm}, b_rows[3] = {4, sl, nm};
+        if (make_map(&m->slab[i], base, 3, dims, str, b_slab, CU_TENSOR_MAP_SWIZZLE_128B)) return 1;
+        if (make_map(&m->rows[i], base, 3, dims, str, b_rows, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+    }
     return 0;
 }
 
@@ -242,7 +243,7 @@ std::map<uint64_t, StripTune> g_tune;
 
 // launch sweep 2 (or the DSS-only sweep) over `count` strips of a device strip list
 int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaStream_t st, int mode = MODE_SWEEP2, const CUtensorMap *out = nullptr,
-           bool wstrip = false)
+           int members = 0 /* > 0: warp-strip sweep over `count` groups of members/4 strips */)
 {
     if (count <= 0) return 0;
     SweepParams p = g.sp;
@@ -253,22 +254,21 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
         p.map_rows = g.map_w_rows;
         p.map_pt = g.map_w_pt;
     }
-    if (wstrip) { // the same choices for the warp-strip sweep's 8-slab views
+    if (members) { // the same choices for the warp-strip sweep's views (boxes of 32/members slabs x members elements)
         static const int dbg = std::getenv("BWK_DEBUG_FLAGS") ? std::atoi(std::getenv("BWK_DEBUG_FLAGS")) : 0;
         p.debug_flags = dbg;
-        const Field4Maps &src = g.src_is_w ? g.f4_w : g.f4_tmp;
-        p.map4_tmp = src.slab4;
-        p.map4_rows = src.rows4;
-        p.map1_rows = src.rows1;
-        p.map_col = src.col;
-        p.map_pt8 = src.pt8;
-        p.map4_out = out == &g.map_w ? g.f4_w.slab4 : g.f4_q.slab4;
-        p.map4_q = g.f4_q.slab4;
+        const int i = members == 16 ? 2 : members == 8 ? 1 : 0;
+        const FieldMaps &src = g.src_is_w ? g.fm_w : g.fm_tmp;
+        p.map4_tmp = src.slab[i];
+        p.map4_rows = src.rows[i];
+        p.map4_halo = g.map_halo_nm[i];
+        p.map4_out = out == &g.map_w ? g.fm_w.slab[i] : g.fm_q.slab[i];
+        p.map4_q = g.fm_q.slab[i];
     }
     int hint = 0, timed = -1;
     StripTune *t = nullptr;
     if (sweep2_tiles_per_unit_forced() == 0 && count * ((g.kq + TILE_SLABS - 1) / TILE_SLABS) >= 148 * 64 && g_tune.size() < 4096) {
-        t = &g_tune[((uint64_t)mode << 56) ^ ((uint64_t)wstrip << 55) ^ ((uint64_t)count << 20) ^ (uint64_t)g.kq];
+        t = &g_tune[((uint64_t)mode << 56) ^ ((uint64_t)members << 50) ^ ((uint64_t)count << 20) ^ (uint64_t)g.kq];
         if (t->best >= 0) hint = TUNE_CAND[t->best];
         else if (t->calls <= 1) { hint = TUNE_CAND[0]; timed = t->calls == 1 ? 0 : -1; }
         else if (t->calls == 2) { hint = TUNE_CAND[1]; timed = 1; }
@@ -297,7 +297,7 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
         CK(cudaEventCreate(&t->ev[timed][1]));
         CK(cudaEventRecord(t->ev[timed][0], st));
     }
-    CK(wstrip ? launch_sweep2_wstrip(mode, p, st) : launch_sweep(mode, p, st));
+    CK(members ? launch_sweep2_wstrip(mode, p, st, members) : launch_sweep(mode, p, st));
     if (timed >= 0) CK(cudaEventRecord(t->ev[timed][1], st));
     g.launches++;
     return 0;
@@ -318,7 +318,13 @@ int sweep2_list(int which, cudaStream_t st, int mode = MODE_SWEEP2, const CUtens
     static const int tpu = std::getenv("BWK_PERSIST_T") ? std::max(3, std::atoi(std::getenv("BWK_PERSIST_T"))) : 4;
     const int ntiles = (g.kq + TILE_SLABS - 1) / TILE_SLABS;
     if (form == 2 && nf > 0) {
-        if (sweep2(ds[which], dr[which], nf, st, mode, out, true)) return 1;
+        for (int gi = 2; gi >= 0; --gi) {
+            // (SK_POST keeps two more arrays per member in shared memory: 16 members do not fit, their groups were not built
+            //  unless BWK_WSTRIP_MEMBERS >= 16, in which case the hyperviscosity pass falls back to the one-warp-per-member form)
+            if (g.ngrp[which][gi] == 0) continue;
+            if (mode == MODE_SWEEP2_POST && WS_NM[gi] == 16) return sweep2(ds[which], dr[which], n, st, mode, out);
+            if (sweep2(nullptr, g.d_grp[which][gi], g.ngrp[which][gi], st, mode, out, WS_NM[gi])) return 1;
+        }
         return sweep2(ds[which] + nf, dr[which] + nf, n - nf, st, mode, out);
     }
     if (form != 1 || ntiles < 3 || (mode != MODE_SWEEP2 && mode != MODE_DSS)) nf = 0;
@@ -556,6 +562,38 @@ int install_plan(Plan &&pl)
                 }
             g.nfast[w] = nf;
             if (upload_list(hs, ds[w]) || upload_regs(hr, dr[w])) return 1;
+            // groups of 4 / 2 / 1 consecutive fast strips for the warp-strip sweep with 16 / 8 / 4 members per warp: the next
+            // strip continues the previous one (its first element follows, and so do its members' S and N neighbours)
+            static const int max_members = std::getenv("BWK_WSTRIP_MEMBERS") ? std::atoi(std::getenv("BWK_WSTRIP_MEMBERS")) : 8; // tuning knob
+            // b continues a: same row of elements (a's E neighbour is b's first member and vice versa, plain W-E link), the
+            // members' S and N neighbours continue too, and the diagonal contributors at the joint are the facing ends of the
+            // other strip's S/N rows -- exactly the relations that hold between the members of one strip
+            auto chains = [](const StripReg &a, const StripReg &b) {
+                if (b.first != a.first + STRIP_MAX) return false;
+                if (b.s_src[0] != a.s_src[0] + STRIP_MAX || b.s_c0[0] != a.s_c0[0] || b.n_src[0] != a.n_src[0] + STRIP_MAX || b.n_c0[0] != a.n_c0[0]) return false;
+                if (a.end_kind[1] != SRC_TMPCOL || a.end_src[1] != b.first || a.end_row[1] != 0 || a.end_rev[1]) return false;
+                if (b.end_kind[0] != SRC_TMPCOL || b.end_src[0] != a.first + STRIP_MAX - 1 || b.end_row[0] != 1 || b.end_rev[0]) return false;
+                auto diag_is = [](const StripReg &r, int d, int32_t src, int c0, int pos) { // diagonal d of r == value `pos` of the row (src, c0)
+                    if (r.diag_src[d] != src) return false;
+                    if (c0 == ROW_IN_HALO) return r.diag_kind[d] == SRC_HALO && r.diag_pt[d] == pos;
+                    return r.diag_kind[d] == SRC_TMPCOL && r.diag_pt[d] == c0 + pos;
+                };
+                return diag_is(a, 2, b.s_src[0], b.s_c0[0], 0) && diag_is(a, 3, b.n_src[0], b.n_c0[0], 0) &&
+                       diag_is(b, 0, a.s_src[STRIP_MAX - 1], a.s_c0[STRIP_MAX - 1], 3) && diag_is(b, 1, a.n_src[STRIP_MAX - 1], a.n_c0[STRIP_MAX - 1], 3);
+            };
+            std::vector<StripReg> grp[3];
+            for (int64_t i = 0; i < nf;) {
+                int64_t run = 1;
+                while (run < 4 && i + run < nf && chains(hr[(size_t)(i + run - 1)], hr[(size_t)(i + run)])) ++run;
+                const int take = (run >= 4 && max_members >= 16) ? 4 : (run >= 2 && max_members >= 8) ? 2 : 1;
+                const int gi = take == 4 ? 2 : take == 2 ? 1 : 0;
+                for (int k = 0; k < take; ++k) grp[gi].push_back(hr[(size_t)(i + k)]);
+                i += take;
+            }
+            for (int gi = 0; gi < 3; ++gi) {
+                g.ngrp[w][gi] = (int64_t)grp[gi].size() / (WS_NM[gi] / 4);
+                if (upload_regs(grp[gi], &g.d_grp[w][gi])) return 1;
+            }
         }
     }
     // halo (receive) buffer and send buffer, rows of [KQ][4] doubles
@@ -598,17 +636,15 @@ int install_plan(Plan &&pl)
             if (make_map(&g.sp.map_halo_pt, g.d_halo, 3, hdims, hstr, hpbox, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
         }
     }
-    // warp-strip sweep: 8-slab views of tmp and qtens, and of the received rows
-    if (make_field4_maps(&g.f4_tmp, g.d_tmp, g.kq, g.nelem) || make_field4_maps(&g.f4_q, g.d_q, g.kq, g.nelem)) return 1;
-    g.sp.map4_halo = g.f4_tmp.rows4; // (never dereferenced without a halo)
-    g.sp.map1_halo = g.f4_tmp.rows1;
-    g.sp.map_halo_pt8 = g.f4_tmp.rows1;
-    if (nrecv > 0) {
-        const uint64_t hdims[3] = {4, (uint64_t)g.kq, (uint64_t)nrecv}, hstr[2] = {32, (uint64_t)g.kq * 32};
-        const uint32_t b4[3] = {4, 8, (uint32_t)std::min<int64_t>(4, nrecv)}, b1[3] = {4, 8, 1}, bp[3] = {2, 8, 1};
-        if (make_map(&g.sp.map4_halo, g.d_halo, 3, hdims, hstr, b4, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
-        if (make_map(&g.sp.map1_halo, g.d_halo, 3, hdims, hstr, b1, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
-        if (make_map(&g.sp.map_halo_pt8, g.d_halo, 3, hdims, hstr, bp, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
+    // warp-strip sweep: views of tmp and qtens, and of the received rows
+    if (make_field_maps(&g.fm_tmp, g.d_tmp, g.kq, g.nelem) || make_field_maps(&g.fm_q, g.d_q, g.kq, g.nelem)) return 1;
+    for (int i = 0; i < 3; ++i) {
+        g.map_halo_nm[i] = g.fm_tmp.rows[i]; // (never dereferenced without a halo)
+        if (nrecv > 0) {
+            const uint64_t hdims[3] = {4, (uint64_t)g.kq, (uint64_t)nrecv}, hstr[2] = {32, (uint64_t)g.kq * 32};
+            const uint32_t bh[3] = {4, 32u / (uint32_t)WS_NM[i], (uint32_t)std::min<int64_t>(WS_NM[i], nrecv)};
+            if (make_map(&g.map_halo_nm[i], g.d_halo, 3, hdims, hstr, bh, CU_TENSOR_MAP_SWIZZLE_32B)) return 1;
+        }
     }
     g.sp.tmp = g.d_tmp;
     g.sp.halo = g.d_halo;
@@ -741,7 +777,7 @@ int hypervis_device(double dt2, double nu_q, int subcycles, int limiter)
         const uint64_t cdims[4] = {4, 4, (uint64_t)g.kq, (uint64_t)g.nelem}, cstr[3] = {32, 128, (uint64_t)g.kq * 128};
         const uint32_t pbox[4] = {2, 1, TILE_SLABS, 1};
         if (make_map(&g.map_w_pt, g.d_w, 4, cdims, cstr, pbox, CU_TENSOR_MAP_SWIZZLE_NONE)) return 1;
-        if (make_field4_maps(&g.f4_w, g.d_w, g.kq, g.nelem)) return 1;
+        if (make_field_maps(&g.fm_w, g.d_w, g.kq, g.nelem)) return 1;
     }
     g.sp.prescale = g.d_ratio;
     g.sp.nlev = g.nlev;
@@ -972,6 +1008,7 @@ int bwk_finalize(void)
                 if (kv.second.ev[c][e]) cudaEventDestroy(kv.second.ev[c][e]);
     g_tune.clear();
     free_dev(g.d_work);
+    for (auto &row : g.d_grp) for (StripReg *&q : row) { free_dev(q); q = nullptr; }
     free_dev(g.d_w); free_dev(g.d_ratio); free_dev(g.d_v2c); free_dev(g.d_metric_plain);
     free_dev(g.d_save); free_dev(g.d_table); free_dev(g.d_partials); free_dev(g.d_halo); free_dev(g.d_send); free_dev(g.d_dummy);
     free_dev(g.d_dss); free_dev(g.d_boundary); free_dev(g.d_interior); free_dev(g.d_dependent); free_dev(g.d_independent);

@@ -1444,9 +1444,10 @@ __global__ void __launch_bounds__(WARPS * 32, 3) sweep2_persist_kernel(const __g
 //   * a CTA = 4 warps on the same strip, warp w takes slabs [8w, 8w+8) of every 32-slab tile of the unit, so the
 //     CTA still streams 4 KB contiguous per element and tile.
 // ------------------------------------------------------------------------------------------
-constexpr int WS_SLABS = 8;                                   // slabs of one member in a warp tile
-constexpr int WS_ROWBUF_BYTES = 2 * 4 * 2 * 1024;             // [set][warp][S,N][4 members x 8 slabs x 32 B]
-constexpr int WS_ENDBUF_BYTES = 4 * 2 * 16 * 48;              // [warp][set][end lane 16][4 edge values, 2 diagonals]
+// NM members per warp (4, 8 or 16 = 1, 2 or 4 consecutive strips), 32 / NM slabs of each per warp tile: the strip ends'
+// share of the work falls with NM (16, 8 or 4 end lanes per warp)
+constexpr int WS_ROWBUF_BYTES = 2 * 4 * 2 * 1024;             // [set][warp][S,N][32 rows x 32 B]
+template <int NM> constexpr int ws_endbuf_bytes() { return 4 * 2 * 2 * (32 / NM) * 48; } // [warp][set][end lane][4 edge values, 2 diagonals]
 constexpr int WS_METRIC_STRIDE = METRIC_DOUBLES + 2;          // doubles; +16 B per member: the four members' reads hit different banks
 // Source of one strip end, decoded once per CTA: the outside neighbour's four values along the facing edge in THIS
 // element's orientation are at col + slab * slab_bytes + t * step (a column or a row of a local slab, or a received halo
@@ -1459,37 +1460,42 @@ struct WsEnd {
 static_assert(sizeof(WsEnd) == 48, "WsEnd layout");
 // ROWSETS = 2: S/N rows requested two tiles ahead (double buffered); 1: one set, requested right after the previous tile's rows
 // have been consumed -- with a 2-stage tile ring that is the 50 KB / 128-register shape that puts FOUR CTAs on an SM
-template <int STAGES, int ROWSETS>
+template <int STAGES, int ROWSETS, int NM, bool POST>
 constexpr int wstrip_smem_bytes()
 {
-    return 1024 + 4 * STAGES * TILE_BYTES + ROWSETS * (WS_ROWBUF_BYTES / 2) + WS_ENDBUF_BYTES + 4 * (STAGES + 1) * 8 + 4 * WS_METRIC_STRIDE * 8 + 2 * 48 + 4 * 34 * 8 + 64;
+    return 1024 + 4 * STAGES * TILE_BYTES + ROWSETS * (WS_ROWBUF_BYTES / 2) + ws_endbuf_bytes<NM>() + 4 * (STAGES + 1) * 8 + NM * WS_METRIC_STRIDE * 8 + 2 * 48 +
+           (POST ? NM * 34 * 8 : 0);
 }
-__device__ __forceinline__ double shfl_up8(double x) { return __shfl_up_sync(0xffffffffu, x, 8); }
-__device__ __forceinline__ double shfl_down8(double x) { return __shfl_down_sync(0xffffffffu, x, 8); }
+template <int D> __device__ __forceinline__ double shfl_up_d(double x) { return __shfl_up_sync(0xffffffffu, x, D); }
+template <int D> __device__ __forceinline__ double shfl_down_d(double x) { return __shfl_down_sync(0xffffffffu, x, D); }
 
-template <int STAGES, int KIND, int MINB>
+template <int STAGES, int KIND, int MINB, int NM>
 __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_constant__ SweepParams p)
 {
     constexpr int SB = TILE_BYTES, WARPS = 4, ROWSETS = MINB >= 4 ? 1 : 2;
+    constexpr int SL = 32 / NM, NG = NM / 4;   // slabs of a member per warp tile; strips (StripReg records) per warp
+    constexpr int ENDSET = 2 * SL * 48, ENDWARP = 2 * ENDSET;
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     unsigned char *stages = smem;                                               // [warp][stage][4 members x 8 slabs x 128 B], SWIZZLE_128B
     unsigned char *rowbuf = stages + WARPS * STAGES * SB;                       // [set][warp][S,N][32 x 32 B], SWIZZLE_32B
     unsigned char *endbuf = rowbuf + ROWSETS * (WS_ROWBUF_BYTES / 2);                           // [warp][set][end lane][48 B]: cp.async slots of the end members
-    uint64_t *bars = reinterpret_cast<uint64_t *>(endbuf + WS_ENDBUF_BYTES);    // full [warp][stage], qdp_full [warp]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(endbuf + WARPS * ENDWARP);    // full [warp][stage], qdp_full [warp]
     double *metric_s = reinterpret_cast<double *>(bars + WARPS * (STAGES + 1)); // [member][WS_METRIC_STRIDE]
-    WsEnd *wsend = reinterpret_cast<WsEnd *>(metric_s + 4 * WS_METRIC_STRIDE);  // [W end, E end]
+    WsEnd *wsend = reinterpret_cast<WsEnd *>(metric_s + NM * WS_METRIC_STRIDE); // [W end, E end]
     double *hv_s = reinterpret_cast<double *>(wsend + 2);                       // SK_POST: [member][spheremp 16 | rspheremp 16 | pad 2]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int member = lane >> 3, j = lane & 7;
-    const StripReg &rg = p.strip_reg[blockIdx.x];
+    const int member = lane / SL, j = lane % SL;
+    const StripReg *regs = p.strip_reg + (size_t)blockIdx.x * NG; // NG consecutive strips: members 4g .. 4g+3 are strip g's
+    const StripReg &rg = regs[0], &rgl = regs[NG - 1], &rgm = regs[member >> 2];
     const int first = rg.first;
     const int ntiles = (p.kq + TILE_SLABS - 1) / TILE_SLABS;
     const int t0 = blockIdx.y * p.tiles_per_unit;
     const int t1 = min(t0 + p.tiles_per_unit, ntiles);
-    int my_n = t1 - t0; // this warp's tiles: slabs [(t0 + n) * 32 + 8 warp, + 8) of the four members
-    if (my_n > 0 && (t1 - 1) * TILE_SLABS + warp * WS_SLABS >= p.kq) --my_n;
+    // this warp's tiles: slabs [t0 * 32 + n * 4 SL + SL warp, + SL) of the NM members (a CTA step covers 4 SL consecutive slabs)
+    int my_n = (t1 - t0) * (8 / SL);
+    while (my_n > 0 && t0 * TILE_SLABS + (my_n - 1) * 4 * SL + warp * SL >= p.kq) --my_n;
     const uint32_t stage0 = smem_u32(stages + (size_t)warp * STAGES * SB);
     const uint32_t bar0 = smem_u32(&bars[warp * STAGES]);
     const uint32_t qbar = smem_u32(&bars[WARPS * STAGES + warp]);
@@ -1502,14 +1508,14 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
         const int pre = my_n < STAGES ? my_n : STAGES;
         for (int n = 0; n < pre; ++n) {
             mbar_expect_tx(bar0 + n * 8, (uint32_t)TILE_BYTES);
-            tma_load_3d(stage0 + n * SB, &p.map4_tmp, 0, (t0 + n) * TILE_SLABS + warp * WS_SLABS, first, bar0 + n * 8);
+            tma_load_3d(stage0 + n * SB, &p.map4_tmp, 0, t0 * TILE_SLABS + n * 4 * SL + warp * SL, first, bar0 + n * 8);
         }
     }
-    { // the four members' folded metric (thread t: 16 bytes), shared by the four warps
-        const int m = threadIdx.x >> 5, c = (threadIdx.x & 31) * 2;
+    for (int t = threadIdx.x; t < NM * 32; t += WARPS * 32) { // the members' folded metric (16 bytes per item), shared by the four warps
+        const int m = t >> 5, c = (t & 31) * 2;
         *reinterpret_cast<double2 *>(metric_s + m * WS_METRIC_STRIDE + c) = __ldg(reinterpret_cast<const double2 *>(p.metric + (size_t)(first + m) * METRIC_DOUBLES + c));
         if (KIND == SK_POST) {
-            const int l = threadIdx.x & 31;
+            const int l = t & 31;
             hv_s[m * 34 + l] = l < 16 ? p.elem[(size_t)(first + m) * ELEM_DOUBLES + 64 + l] : p.rsph[(size_t)(first + m) * 16 + l - 16];
         }
     }
@@ -1518,8 +1524,9 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
         const size_t kq = (size_t)p.kq;
         const unsigned char *tmp = reinterpret_cast<const unsigned char *>(p.tmp), *halo = reinterpret_cast<const unsigned char *>(p.halo);
         WsEnd e{nullptr, nullptr, nullptr, 0, 0, 0, 0, {0, 0}};
-        const int kind = rg.end_kind[side], row = rg.end_row[side], rev = rg.end_rev[side];
-        const size_t src = (size_t)rg.end_src[side];
+        const StripReg &re = side ? rgl : rg; // W end: the first strip's record; E end: the last strip's
+        const int kind = re.end_kind[side], row = re.end_row[side], rev = re.end_rev[side];
+        const size_t src = (size_t)re.end_src[side];
         if (kind == SRC_TMPCOL) { // the neighbour's i = 1 (row 0) or i = np (row 1) column: points i + 4 t
             e.col = tmp + src * kq * 128 + ((row ? 3 : 0) + (rev ? 12 : 0)) * 8;
             e.step = rev ? -32 : 32;
@@ -1538,10 +1545,10 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
             const int d = side * 2 + which;
             const unsigned char *ptr = nullptr;
             int sb = 0;
-            if (rg.diag_src[d] >= 0) {
-                const size_t ds = (size_t)rg.diag_src[d];
-                if (rg.diag_kind[d] == SRC_HALO) { ptr = halo + ds * kq * 32 + rg.diag_pt[d] * 8; sb = 32; }
-                else { ptr = tmp + ds * kq * 128 + rg.diag_pt[d] * 8; sb = 128; }
+            if (re.diag_src[d] >= 0) {
+                const size_t ds = (size_t)re.diag_src[d];
+                if (re.diag_kind[d] == SRC_HALO) { ptr = halo + ds * kq * 32 + re.diag_pt[d] * 8; sb = 32; }
+                else { ptr = tmp + ds * kq * 128 + re.diag_pt[d] * 8; sb = 128; }
             }
             if (which == 0) { e.d0 = ptr; e.d0_slab_bytes = sb; }
             else { e.d1 = ptr; e.d1_slab_bytes = sb; }
@@ -1565,20 +1572,22 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
     const int rawS = (p.debug_flags & 1) ? 0 : rg.s_c0[0], rawN = (p.debug_flags & 1) ? 12 : rg.n_c0[0];
     const CUtensorMap *mapS = rawS == ROW_IN_HALO ? &p.map4_halo : &p.map4_rows, *mapN = rawN == ROW_IN_HALO ? &p.map4_halo : &p.map4_rows;
     const int c0S = rawS == ROW_IN_HALO ? 0 : rawS, c0N = rawN == ROW_IN_HALO ? 0 : rawN;
-    const bool std_corners = rg.all_std != 0;
+    bool std_corners = true;
+#pragma unroll
+    for (int g = 0; g < NG; ++g) std_corners = std_corners && regs[g].all_std != 0;
     uint32_t cn_pack = 0, cperm_pack = 0; // this lane's member: four corner counts / summation orders
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-        cn_pack |= (uint32_t)rg.corner_n[member][c] << (8 * c);
-        cperm_pack |= (uint32_t)rg.corner_perm[member][c] << (8 * c);
+        cn_pack |= (uint32_t)rgm.corner_n[member & 3][c] << (8 * c);
+        cperm_pack |= (uint32_t)rgm.corner_perm[member & 3][c] << (8 * c);
     }
     const uint64_t pol_out = l2_policy_evict_first();
     // end-member lanes: slot of this lane in the warp's two cp.async sets, and the strip end it serves
-    const bool end_lane = member == 0 || member == 3;
-    const int eside = member == 3 ? 1 : 0;
-    const uint32_t eslot0 = smem_u32(endbuf) + (uint32_t)(warp * 1536 + (eside * 8 + j) * 48);
-    const unsigned char *eslot0_p = endbuf + warp * 1536 + (eside * 8 + j) * 48;
-    auto kq_of = [&](int n) { return (t0 + n) * TILE_SLABS + warp * WS_SLABS; };
+    const bool end_lane = member == 0 || member == NM - 1;
+    const int eside = member == NM - 1 ? 1 : 0;
+    const uint32_t eslot0 = smem_u32(endbuf) + (uint32_t)(warp * ENDWARP + (eside * SL + j) * 48);
+    const unsigned char *eslot0_p = endbuf + warp * ENDWARP + (eside * SL + j) * 48;
+    auto kq_of = [&](int n) { return t0 * TILE_SLABS + n * 4 * SL + warp * SL; };
     auto issue_tile = [&](int n, int s) {
         mbar_expect_tx(bar0 + s * 8, (uint32_t)TILE_BYTES);
         tma_load_3d(stage0 + s * SB, &p.map4_tmp, 0, kq_of(n), first, bar0 + s * 8);
@@ -1597,7 +1606,7 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
             const int slab = kq_of(n) + j;
             const uint32_t ok = slab < p.kq ? 8u : 0u; // slabs past a ragged end: zero fill, nothing is read
             const size_t sl = ok ? (size_t)slab : 0;
-            const uint32_t dst = eslot0 + (uint32_t)((n & 1) * 768);
+            const uint32_t dst = eslot0 + (uint32_t)((n & 1) * ENDSET);
             const unsigned char *c = e.col + sl * (size_t)e.slab_bytes;
 #pragma unroll
             for (int t = 0; t < 4; ++t) cp_async8(dst + t * 8, c + t * e.step, ok);
@@ -1646,20 +1655,20 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
                 }
             }
         }
-        // ---- W/E mates are 8 lanes away: their facing columns and the facing ends of their S/N neighbour rows by shuffle
+        // ---- W/E mates are SL lanes away: their facing columns and the facing ends of their S/N neighbour rows by shuffle
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
-            nbW[t] = shfl_up8(v[3 + 4 * t]);   // west mate's E column (points 3,7,11,15)
-            nbE[t] = shfl_down8(v[4 * t]);     // east mate's W column (points 0,4,8,12)
+            nbW[t] = shfl_up_d<SL>(v[3 + 4 * t]);   // west mate's E column (points 3,7,11,15)
+            nbE[t] = shfl_down_d<SL>(v[4 * t]);     // east mate's W column (points 0,4,8,12)
         }
-        dg[0] = shfl_up8(nbS[3]);   // SW: east end of the west mate's S row
-        dg[2] = shfl_up8(nbN[3]);   // NW
-        dg[1] = shfl_down8(nbS[0]); // SE: west end of the east mate's S row
-        dg[3] = shfl_down8(nbN[0]); // NE
+        dg[0] = shfl_up_d<SL>(nbS[3]);   // SW: east end of the west mate's S row
+        dg[2] = shfl_up_d<SL>(nbN[3]);   // NW
+        dg[1] = shfl_down_d<SL>(nbS[0]); // SE: west end of the east mate's S row
+        dg[3] = shfl_down_d<SL>(nbN[0]); // NE
         // strip ends: the outside neighbour's values, fetched by this lane's own cp.async one tile ago
         asm volatile("cp.async.wait_all;" ::: "memory");
         if (end_lane) {
-            const double2 *es = reinterpret_cast<const double2 *>(eslot0_p + q * 768);
+            const double2 *es = reinterpret_cast<const double2 *>(eslot0_p + q * ENDSET);
             const double2 c01 = es[0], c23 = es[1], dd = es[2];
             if (member == 0) { nbW[0] = c01.x; nbW[1] = c01.y; nbW[2] = c23.x; nbW[3] = c23.y; dg[0] = dd.x; dg[2] = dd.y; }
             else { nbE[0] = c01.x; nbE[1] = c01.y; nbE[2] = c23.x; nbE[3] = c23.y; dg[1] = dd.x; dg[3] = dd.y; }
@@ -1840,37 +1849,47 @@ cudaError_t launch_sweep2_persist(int mode, const SweepParams &p, cudaStream_t s
     return cudaErrorInvalidValue;
 }
 
-template <int STAGES, int KIND, int MINB>
+template <int STAGES, int KIND, int MINB, int NM>
 static cudaError_t launch_wstrip_t(const SweepParams &p, cudaStream_t st)
 {
-    constexpr int smem = wstrip_smem_bytes<STAGES, (MINB >= 4 ? 1 : 2)>();
+    constexpr int smem = wstrip_smem_bytes<STAGES, (MINB >= 4 ? 1 : 2), NM, KIND == SK_POST>();
     static_assert(MINB * (smem + 1024) <= 228 * 1024, "MINB CTAs per SM");
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(sweep2_wstrip_kernel<STAGES, KIND, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(sweep2_wstrip_kernel<STAGES, KIND, MINB, NM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
     if (p.strip_count <= 0 || p.units <= 0) return cudaSuccess;
     dim3 grid((unsigned)p.strip_count, (unsigned)p.units);
-    sweep2_wstrip_kernel<STAGES, KIND, MINB><<<grid, 128, smem, st>>>(p);
+    sweep2_wstrip_kernel<STAGES, KIND, MINB, NM><<<grid, 128, smem, st>>>(p);
     return cudaGetLastError();
 }
 
-// warp-strip sweep over full regular strips whose members' S/N neighbours are consecutive elements (p.strip_reg / p.strip_count)
-cudaError_t launch_sweep2_wstrip(int mode, const SweepParams &p, cudaStream_t st)
+// warp-strip sweep over groups of `members`/4 consecutive full regular strips whose members' S/N neighbours are consecutive elements:
+// p.strip_reg holds the groups' StripReg records back to back, p.strip_count = number of groups; the map4_* tensor maps must
+// have boxes of 32/members slabs x members elements
+cudaError_t launch_sweep2_wstrip(int mode, const SweepParams &p, cudaStream_t st, int members)
 {
-    // shape A/B (BWK_WSTRIP_SHAPE): 4 = 2-stage ring, one row set, 128 registers: four CTAs (16 warps) per SM; 3 = 3-stage ring,
-    // two row sets, 168 registers: three CTAs per SM
+    // shape A/B (BWK_WSTRIP_SHAPE): 4 = 2-stage ring, one row set, 128 registers: four CTAs (16 warps) per SM (4 members only);
+    // 3 = 3-stage ring, two row sets, 168 registers: three CTAs per SM
     static const int shape = std::getenv("BWK_WSTRIP_SHAPE") ? std::atoi(std::getenv("BWK_WSTRIP_SHAPE")) : 3;
-    if (shape == 4) {
-        if (mode == MODE_SWEEP2) return launch_wstrip_t<2, SK_LAP, 4>(p, st);
-        if (mode == MODE_DSS) return launch_wstrip_t<2, SK_DSS, 4>(p, st);
-        if (mode == MODE_SWEEP2_POST) return launch_wstrip_t<2, SK_POST, 4>(p, st);
+    if (shape == 4 && members == 4) {
+        if (mode == MODE_SWEEP2) return launch_wstrip_t<2, SK_LAP, 4, 4>(p, st);
+        if (mode == MODE_DSS) return launch_wstrip_t<2, SK_DSS, 4, 4>(p, st);
+        if (mode == MODE_SWEEP2_POST) return launch_wstrip_t<2, SK_POST, 4, 4>(p, st);
     }
-    if (mode == MODE_SWEEP2) return launch_wstrip_t<3, SK_LAP, 3>(p, st);
-    if (mode == MODE_DSS) return launch_wstrip_t<3, SK_DSS, 3>(p, st);
-    if (mode == MODE_SWEEP2_POST) return launch_wstrip_t<3, SK_POST, 3>(p, st);
+#define BWK_WS_CASE(NM_)                                                                   \
+    if (members == NM_) {                                                                  \
+        if (mode == MODE_SWEEP2) return launch_wstrip_t<3, SK_LAP, 3, NM_>(p, st);         \
+        if (mode == MODE_DSS) return launch_wstrip_t<3, SK_DSS, 3, NM_>(p, st);            \
+    }
+    BWK_WS_CASE(4)
+    BWK_WS_CASE(8)
+    BWK_WS_CASE(16)
+#undef BWK_WS_CASE
+    if (mode == MODE_SWEEP2_POST && members == 4) return launch_wstrip_t<3, SK_POST, 3, 4>(p, st);
+    if (mode == MODE_SWEEP2_POST && members == 8) return launch_wstrip_t<3, SK_POST, 3, 8>(p, st);
     return cudaErrorInvalidValue;
 }
 

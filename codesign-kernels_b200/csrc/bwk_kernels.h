@@ -30,17 +30,12 @@ struct SweepParams {
     CUtensorMap map_pt;     // tmp as {4 (i), 4 (j), KQ, nelem}, box {2,1,32,1}: the 16-byte i-pair holding one point of 32 consecutive slabs
     CUtensorMap map_halo_pt;// received edge rows as {4, KQ, nrows}, box {2,32,1}: half a halo row (aliases a 3-D view of tmp when there is no halo)
     CUtensorMap map_out;    // where sweep 2 / the DSS-only sweep store their result (qtens, or the hyperviscosity work buffer)
-    // warp-strip sweep: boxes of 8 slabs x 4 consecutive elements (one strip per warp)
-    CUtensorMap map4_tmp;   // source field as {16, KQ, nelem}, box {16,8,4}, SWIZZLE_128B
-    CUtensorMap map4_rows;  // source field, box {4,8,4}, SWIZZLE_32B: one edge row of 8 slabs of 4 consecutive elements
-    CUtensorMap map1_rows;  // source field, box {4,8,1}, SWIZZLE_32B (a strip end facing with a row)
-    CUtensorMap map_col;    // source field as {4 (i), 4 (j), KQ, nelem}, box {2,4,8,1}: an i-pair column of 8 slabs
-    CUtensorMap map_pt8;    // same view, box {2,1,8,1}: one point of 8 slabs
-    CUtensorMap map4_halo;  // received edge rows {4, KQ, nrows}, box {4,8,4}, SWIZZLE_32B
-    CUtensorMap map1_halo;  // box {4,8,1}
-    CUtensorMap map_halo_pt8; // box {2,8,1}
-    CUtensorMap map4_out;   // destination, box {16,8,4}, SWIZZLE_128B
-    CUtensorMap map4_q;     // qtens, box {16,8,4} (SK_POST reads Qdp)
+    // warp-strip sweep: boxes of 32/NM slabs x NM consecutive elements (NM = 4, 8 or 16 members per warp; set per launch)
+    CUtensorMap map4_tmp;   // source field as {16, KQ, nelem}, box {16, 32/NM, NM}, SWIZZLE_128B
+    CUtensorMap map4_rows;  // source field, box {4, 32/NM, NM}, SWIZZLE_32B: one edge row of the warp tile's slabs
+    CUtensorMap map4_halo;  // received edge rows {4, KQ, nrows}, box {4, 32/NM, NM}, SWIZZLE_32B
+    CUtensorMap map4_out;   // destination, box {16, 32/NM, NM}, SWIZZLE_128B
+    CUtensorMap map4_q;     // qtens, same box (SK_POST reads Qdp)
     const double *prescale; // MODE_SWEEP1_PRE: [nelem][nlev][16] factors applied to the input slab of level k
     int nlev;               // MODE_SWEEP1_PRE: slab kq belongs to level kq % nlev
     const double *elem;     // MODE_SWEEP2_POST: element records [nelem][144] (spheremp at +64); Qdp is read through map_q
@@ -76,7 +71,7 @@ int sweep2_tiles_per_unit_forced();
 
 cudaError_t launch_sweep(int mode, const SweepParams &p, cudaStream_t st);
 // warp-strip sweep (MODE_SWEEP2 / MODE_DSS / MODE_SWEEP2_POST): grid (p.strip_count, p.units), p.tiles_per_unit tiles of 32 slabs per CTA
-cudaError_t launch_sweep2_wstrip(int mode, const SweepParams &p, cudaStream_t st);
+cudaError_t launch_sweep2_wstrip(int mode, const SweepParams &p, cudaStream_t st, int members = 4);
 // persistent strip sweep (MODE_SWEEP2 / MODE_DSS) over full regular strips only: p.strip_reg / p.strip_count, p.units units of >= 3 tiles
 cudaError_t launch_sweep2_persist(int mode, const SweepParams &p, cudaStream_t st);
 // MODE_SWEEP1_PRE needs nlev*128 more bytes of shared memory per CTA than the other element-local sweeps; false if that does not fit

@@ -1,0 +1,12 @@
+#!/bin/bash
+tag=$1
+mkdir -p gpurun_out
+( time timeout 600 python -m pytest tests -m gpu -x -q ) > gpurun_out/${tag}_pytest.log 2>&1; echo "rc $?" >> gpurun_out/${tag}_pytest.log
+tail -6 gpurun_out/${tag}_pytest.log
+for cfg in BWK_WSTRIP_MEMBERS=4 BWK_WSTRIP_MEMBERS=8 BWK_WSTRIP_MEMBERS=4 BWK_WSTRIP_MEMBERS=8; do
+  env $(echo $cfg | tr ',' ' ') timeout 300 python profiles/prof_run.py 120 72 40 2>&1 | grep -E "rep [234] sweep2|rror" | sed "s/^/[$cfg] /"
+done
+for cfg in BWK_WSTRIP_MEMBERS=4 BWK_WSTRIP_MEMBERS=8; do
+  echo "== fake rank 0 of 8, $cfg"
+  env BWK_FAKE_RANKS=0,8 BWK_TRACE=1 $cfg timeout 300 python profiles/prof_fake_rank.py 120 72 40 4 2>&1 | grep -A7 "rep 3" | grep -E "produce|consume|strips"
+done
