@@ -317,6 +317,14 @@ int sweep2_list(int which, cudaStream_t st, int mode = MODE_SWEEP2, const CUtens
     static const int form = std::getenv("BWK_STRIP_FORM") ? std::atoi(std::getenv("BWK_STRIP_FORM")) : 2;
     static const int tpu = std::getenv("BWK_PERSIST_T") ? std::max(3, std::atoi(std::getenv("BWK_PERSIST_T"))) : 4;
     const int ntiles = (g.kq + TILE_SLABS - 1) / TILE_SLABS;
+    // groups of chained strips pay on long lists only (measured: -4..6 % on the full ne120 sphere, +2 % on a rank's block of an
+    // 8-rank run, where the halved CTA count costs more than the halved strip ends give): below BWK_WSTRIP_GROUP_MIN fast
+    // strips every strip runs alone (4 members per warp)
+    static const int64_t group_min = std::getenv("BWK_WSTRIP_GROUP_MIN") ? std::atoll(std::getenv("BWK_WSTRIP_GROUP_MIN")) : 4096;
+    if (form == 2 && nf > 0 && nf < group_min) {
+        if (sweep2(nullptr, dr[which], nf, st, mode, out, 4)) return 1;
+        return sweep2(ds[which] + nf, dr[which] + nf, n - nf, st, mode, out);
+    }
     if (form == 2 && nf > 0) {
         for (int gi = 2; gi >= 0; --gi) {
             // (SK_POST keeps two more arrays per member in shared memory: 16 members do not fit, their groups were not built
