@@ -1473,6 +1473,11 @@ template <int STAGES, int KIND, int MINB, int NM>
 __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_constant__ SweepParams p)
 {
     constexpr int SB = TILE_BYTES, WARPS = 4, ROWSETS = MINB >= 4 ? 1 : 2;
+    // S/N rows: two {4, SL, NM} TMA boxes per tile issued by lane 0.  The alternative kept below (ROWS_BY_TMA = false: every lane
+    // fetches the 64 bytes of its own slab's S and N rows with four 16-byte cp.async in the group of the strip-end values, no
+    // lane-0 code, one mbarrier arrival per tile) is correct but SLOWER: 13.6-14.0 ms against 11.4-11.8 ms at ne120 with 8
+    // members (profiles/r2w_*): a warp-wide 16-byte gather touches 32 different lines, and the L1/LSU path pays for each.
+    constexpr bool ROWS_BY_TMA = true;
     constexpr int SL = 32 / NM, NG = NM / 4;   // slabs of a member per warp tile; strips (StripReg records) per warp
     constexpr int ENDSET = 2 * SL * 48, ENDWARP = 2 * ENDSET;
     extern __shared__ unsigned char smem_raw[];
@@ -1501,7 +1506,7 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
     const uint32_t qbar = smem_u32(&bars[WARPS * STAGES + warp]);
     if (lane == 0) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + s * 8, 2u); // tile + S/N rows
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + s * 8, ROWS_BY_TMA ? 2u : 1u); // tile (+ S/N rows when TMA stages them)
         mbar_init(qbar, 1u);
         fence_barrier_init();
         fence_proxy_async();
@@ -1600,7 +1605,23 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
         tma_load_3d(rb + 1024, mapN, c0N, kq_of(n), elemN, nbar);
     };
     // end-member lanes: fetch the strip-end values of tile n into set n & 1 (six 8-byte cp.async, one group)
+    const unsigned char *rowS_src = rawS == ROW_IN_HALO ? reinterpret_cast<const unsigned char *>(p.halo) + (size_t)(elemS + member) * p.kq * 32
+                                                        : reinterpret_cast<const unsigned char *>(p.tmp) + (size_t)(elemS + member) * p.kq * 128 + c0S * 8;
+    const unsigned char *rowN_src = rawN == ROW_IN_HALO ? reinterpret_cast<const unsigned char *>(p.halo) + (size_t)(elemN + member) * p.kq * 32
+                                                        : reinterpret_cast<const unsigned char *>(p.tmp) + (size_t)(elemN + member) * p.kq * 128 + c0N * 8;
+    const int rowS_stride = rawS == ROW_IN_HALO ? 32 : 128, rowN_stride = rawN == ROW_IN_HALO ? 32 : 128;
     auto fetch_end = [&](int n) {
+        if (!ROWS_BY_TMA) { // this lane's S and N rows of tile n, into the SWIZZLE_32B positions the TMA form uses
+            const int slab = kq_of(n) + j;
+            const uint32_t ok = slab < p.kq ? 16u : 0u;
+            const size_t sl = ok ? (size_t)slab : 0;
+            const uint32_t rb = smem_u32(rowbuf) + (uint32_t)(((n & 1) * WARPS + warp) * 2048) + lane * 32;
+            const unsigned char *a = rowS_src + sl * rowS_stride, *b = rowN_src + sl * rowN_stride;
+            cp_async16(rb + (swz << 4), a, ok);
+            cp_async16(rb + ((1 ^ swz) << 4), a + 16, ok);
+            cp_async16(rb + 1024 + (swz << 4), b, ok);
+            cp_async16(rb + 1024 + ((1 ^ swz) << 4), b + 16, ok);
+        }
         if (end_lane) {
             const WsEnd e = wsend[eside];
             const int slab = kq_of(n) + j;
@@ -1616,7 +1637,7 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
-    if (lane == 0) {
+    if (ROWS_BY_TMA && lane == 0) {
         issue_nbr(0);
         if (ROWSETS == 2 && my_n > 1) issue_nbr(1);
     }
@@ -1638,6 +1659,7 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
             v[2 * c] = t.x;
             v[2 * c + 1] = t.y;
         }
+        asm volatile("cp.async.wait_all;" ::: "memory"); // this lane's S/N rows and strip-end values of this tile (fetched one tile ago)
         {
             const double2 a = *reinterpret_cast<const double2 *>(rb + (swz << 4)), b = *reinterpret_cast<const double2 *>(rb + ((1 ^ swz) << 4));
             nbS[0] = a.x; nbS[1] = a.y; nbS[2] = b.x; nbS[3] = b.y;
@@ -1666,7 +1688,6 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
         dg[1] = shfl_down_d<SL>(nbS[0]); // SE: west end of the east mate's S row
         dg[3] = shfl_down_d<SL>(nbN[0]); // NE
         // strip ends: the outside neighbour's values, fetched by this lane's own cp.async one tile ago
-        asm volatile("cp.async.wait_all;" ::: "memory");
         if (end_lane) {
             const double2 *es = reinterpret_cast<const double2 *>(eslot0_p + q * ENDSET);
             const double2 c01 = es[0], c23 = es[1], dd = es[2];
@@ -1739,7 +1760,7 @@ __global__ void __launch_bounds__(128, MINB) sweep2_wstrip_kernel(const __grid_c
                 bulk_wait_read<1>();
                 issue_tile(n - 1 + STAGES, (n - 1) % STAGES);
             }
-            if (ROWSETS == 2 && n + 2 < my_n) issue_nbr(n + 2); // rowbuf set q is free: every lane consumed it before the __syncwarp above
+            if (ROWS_BY_TMA && ROWSETS == 2 && n + 2 < my_n) issue_nbr(n + 2); // rowbuf set q is free: every lane consumed it before the __syncwarp above
         }
     }
     if (lane == 0) bulk_wait_read<0>();
