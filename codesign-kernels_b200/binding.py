@@ -72,6 +72,7 @@ def lib():
         "bwk_compute_l2norm": [dp],
         "bwk_checksum": [dp, dp],
         "bwk_checksum_bits": [i64, C.POINTER(C.c_uint64)],
+        "bwk_set_phase_event": [i32],
         "bwk_periodicity_defect": [i64, dp],
         "bwk_download_elements": [i64, i64, p],
         "bwk_upload_elements": [i64, i64, p],
@@ -408,6 +409,10 @@ class KernelUtils:
 
     def event_record(self, slot):
         _ck(lib().bwk_event_record(slot))
+
+    def set_phase_event(self, slot):
+        """record event `slot` between sweep 1 and the strip sweep of the following full-biharmonic calls (1 rank; -1 = off)"""
+        _ck(lib().bwk_set_phase_event(slot))
 
     def event_elapsed_ms(self, a, b):
         v = C.c_float()

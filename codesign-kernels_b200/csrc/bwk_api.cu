@@ -100,7 +100,7 @@ struct Ctx {
     bool inited = false;
     int nelem = 0, nlev = 0, qsize = 0, kq = 0;
     size_t q_doubles = 0;
-    cudaStream_t s_main = nullptr, s_comm = nullptr, s_dep = nullptr, s_h2d = nullptr, s_d2h = nullptr;
+    cudaStream_t s_main = nullptr, s_comm = nullptr, s_dep = nullptr, s_aux = nullptr, s_h2d = nullptr, s_d2h = nullptr;
     double *d_q = nullptr, *d_tmp = nullptr, *d_elem = nullptr, *d_metric = nullptr, *d_rsph = nullptr;
     double *d_w = nullptr, *d_ratio = nullptr; // advance_hypervis_scalar: biharmonic work buffer, dpdiss/dp [nelem][nlev][16]
     CUtensorMap map_w, map_w_rows, map_w_pt; // the work buffer seen as slabs / edge rows / i-pairs (strip sweeps reading it)
@@ -129,11 +129,12 @@ struct Ctx {
     int gen_seed_mode = 0;
     int64_t gen_elem_first = -1;
     int variant = 0;
+    int phase_event = -1;             // bwk_set_phase_event: event slot recorded between sweep 1 and the strip sweep (1 rank)
     int64_t launches = 0;
     // comm
     ncclComm_t comm = nullptr;
     int rank = 0, nranks = 1;
-    cudaEvent_t ev_b = nullptr, ev_halo = nullptr, ev_misc = nullptr, ev_start = nullptr, ev_int = nullptr;
+    cudaEvent_t ev_b = nullptr, ev_halo = nullptr, ev_misc = nullptr, ev_start = nullptr, ev_int = nullptr, ev_aux0 = nullptr, ev_aux1 = nullptr;
     cudaEvent_t events[NEVENTS] = {};
     std::vector<cudaEvent_t> chunk_up, chunk_done;
     // host-buffer pipeline of the full biharmonic (bwk_biharmonic_wk_scalar_full): strips_all re-ordered
@@ -239,6 +240,10 @@ struct StripTune {
     cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
 };
 constexpr int TUNE_CAND[2] = {15, 9};
+// warp-strip sweep with NM members per warp: a CTA walks NM/4 times as many (smaller) steps per tile and lives as much longer,
+// and DRAM reads grow with the CTA lifetime (neighbouring CTAs drift apart): 8 members at ne120: 5 tiles 11.3 ms / 1.06x reads,
+// 7: 11.2 ms / 1.13x, 9: 11.4 ms / 1.19x, 15: 12.9 ms / 1.43x (profiles/r2y_*)
+inline int tune_cand(int members, int c) { return members >= 16 ? (c ? 3 : 4) : members >= 8 ? (c ? 5 : 7) : TUNE_CAND[c]; }
 std::map<uint64_t, StripTune> g_tune;
 
 // launch sweep 2 (or the DSS-only sweep) over `count` strips of a device strip list
@@ -269,9 +274,9 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
     StripTune *t = nullptr;
     if (sweep2_tiles_per_unit_forced() == 0 && count * ((g.kq + TILE_SLABS - 1) / TILE_SLABS) >= 148 * 64 && g_tune.size() < 4096) {
         t = &g_tune[((uint64_t)mode << 56) ^ ((uint64_t)members << 50) ^ ((uint64_t)count << 20) ^ (uint64_t)g.kq];
-        if (t->best >= 0) hint = TUNE_CAND[t->best];
-        else if (t->calls <= 1) { hint = TUNE_CAND[0]; timed = t->calls == 1 ? 0 : -1; }
-        else if (t->calls == 2) { hint = TUNE_CAND[1]; timed = 1; }
+        if (t->best >= 0) hint = tune_cand(members, t->best);
+        else if (t->calls <= 1) { hint = tune_cand(members, 0); timed = t->calls == 1 ? 0 : -1; }
+        else if (t->calls == 2) { hint = tune_cand(members, 1); timed = 1; }
         else {
             float ms[2] = {0.f, 0.f};
             for (int c = 0; c < 2; ++c) {
@@ -282,10 +287,11 @@ int sweep2(const int32_t *d_strips, const StripReg *d_reg, int64_t count, cudaSt
                 t->ev[c][0] = t->ev[c][1] = nullptr;
             }
             t->best = ms[1] < 0.975f * ms[0] ? 1 : 0; // single samples: the default keeps the shape unless the alternative wins clearly
-            hint = TUNE_CAND[t->best];
+            hint = tune_cand(members, t->best);
         }
         t->calls++;
     }
+    if (hint == 0 && members) hint = tune_cand(members, 0);
     const SweepGeometry geo = choose_geometry(g.kq, count, mode, hint);
     p.tiles_per_unit = geo.tiles_per_unit;
     p.units = geo.units;
@@ -321,19 +327,29 @@ int sweep2_list(int which, cudaStream_t st, int mode = MODE_SWEEP2, const CUtens
     // 8-rank run, where the halved CTA count costs more than the halved strip ends give): below BWK_WSTRIP_GROUP_MIN fast
     // strips every strip runs alone (4 members per warp)
     static const int64_t group_min = std::getenv("BWK_WSTRIP_GROUP_MIN") ? std::atoll(std::getenv("BWK_WSTRIP_GROUP_MIN")) : 4096;
-    if (form == 2 && nf > 0 && nf < group_min) {
-        if (sweep2(nullptr, dr[which], nf, st, mode, out, 4)) return 1;
-        return sweep2(ds[which] + nf, dr[which] + nf, n - nf, st, mode, out);
-    }
     if (form == 2 && nf > 0) {
-        for (int gi = 2; gi >= 0; --gi) {
-            // (SK_POST keeps two more arrays per member in shared memory: 16 members do not fit, their groups were not built
-            //  unless BWK_WSTRIP_MEMBERS >= 16, in which case the hyperviscosity pass falls back to the one-warp-per-member form)
-            if (g.ngrp[which][gi] == 0) continue;
-            if (mode == MODE_SWEEP2_POST && WS_NM[gi] == 16) return sweep2(ds[which], dr[which], n, st, mode, out);
-            if (sweep2(nullptr, g.d_grp[which][gi], g.ngrp[which][gi], st, mode, out, WS_NM[gi])) return 1;
+        // The strips the warp-strip sweep does not take (1.1 % of them on the ne120 sphere: face-edge strips with reversed rows,
+        // short strips) go through sweep2_strip_kernel on a side stream, launched FIRST: their few CTAs run at full occupancy
+        // while the main grid fills in behind them, instead of as a 3-wave tail of their own (0.43 ms = 3.8 % of the sweep).
+        const bool side = n > nf;
+        if (side) {
+            CK(cudaEventRecord(g.ev_aux0, st));
+            CK(cudaStreamWaitEvent(g.s_aux, g.ev_aux0, 0));
+            if (sweep2(ds[which] + nf, dr[which] + nf, n - nf, g.s_aux, mode, out)) return 1;
+            CK(cudaEventRecord(g.ev_aux1, g.s_aux));
         }
-        return sweep2(ds[which] + nf, dr[which] + nf, n - nf, st, mode, out);
+        if (nf < group_min) {
+            if (sweep2(nullptr, dr[which], nf, st, mode, out, 4)) return 1;
+        } else {
+            for (int gi = 2; gi >= 0; --gi) {
+                if (g.ngrp[which][gi] == 0) continue;
+                // (SK_POST keeps two more arrays per member in shared memory: 16 members do not fit)
+                if (mode == MODE_SWEEP2_POST && WS_NM[gi] == 16) return fail("advance_hypervis_scalar with BWK_WSTRIP_MEMBERS=16 is not supported");
+                if (sweep2(nullptr, g.d_grp[which][gi], g.ngrp[which][gi], st, mode, out, WS_NM[gi])) return 1;
+            }
+        }
+        if (side) CK(cudaStreamWaitEvent(st, g.ev_aux1, 0));
+        return 0;
     }
     if (form != 1 || ntiles < 3 || (mode != MODE_SWEEP2 && mode != MODE_DSS)) nf = 0;
     if (nf > 0) {
@@ -699,6 +715,7 @@ int dss_pass(Produce produce, int consume_mode, const CUtensorMap *out)
     const Plan &P = g.plan;
     if (P.nranks == 1) {
         if (produce(0, g.nelem, (const int32_t *)nullptr, g.s_main)) return 1;
+        if (g.phase_event >= 0) CK(cudaEventRecord(g.events[g.phase_event], g.s_main));
         return sweep2_list(0, g.s_main, consume_mode, out);
     }
     static const bool trace = std::getenv("BWK_TRACE") != nullptr; // debugging aid: serialised phases with their durations on stderr
@@ -980,6 +997,9 @@ int bwk_init(int nelemd, int nlev, int qsize)
         CK(cudaStreamCreateWithPriority(&g.s_comm, cudaStreamNonBlocking, prio_hi));
     }
     CK(cudaStreamCreateWithFlags(&g.s_dep, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&g.s_aux, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&g.ev_aux0, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&g.ev_aux1, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&g.ev_b, cudaEventDisableTiming));
@@ -1031,6 +1051,9 @@ int bwk_finalize(void)
     if (g.ev_start) cudaEventDestroy(g.ev_start);
     if (g.ev_int) cudaEventDestroy(g.ev_int);
     if (g.s_dep) cudaStreamDestroy(g.s_dep);
+    if (g.s_aux) cudaStreamDestroy(g.s_aux);
+    if (g.ev_aux0) cudaEventDestroy(g.ev_aux0);
+    if (g.ev_aux1) cudaEventDestroy(g.ev_aux1);
     if (g.s_main) cudaStreamDestroy(g.s_main);
     if (g.s_comm) cudaStreamDestroy(g.s_comm);
     if (g.s_h2d) cudaStreamDestroy(g.s_h2d);
@@ -1068,6 +1091,7 @@ int bwk_sync(void)
     CK(cudaStreamSynchronize(g.s_main));
     CK(cudaStreamSynchronize(g.s_comm));
     CK(cudaStreamSynchronize(g.s_dep));
+    CK(cudaStreamSynchronize(g.s_aux));
     CK(cudaStreamSynchronize(g.s_h2d));
     CK(cudaStreamSynchronize(g.s_d2h));
     return 0;
@@ -1566,6 +1590,13 @@ int bwk_event_record(int slot)
     if (need_init()) return 1;
     if (slot < 0 || slot >= NEVENTS) return fail("event slot out of range");
     CK(cudaEventRecord(g.events[slot], g.s_main));
+    return 0;
+}
+int bwk_set_phase_event(int slot)
+{
+    if (need_init()) return 1;
+    if (slot >= NEVENTS) return fail("event slot out of range");
+    g.phase_event = slot < 0 ? -1 : slot;
     return 0;
 }
 int bwk_event_elapsed_ms(int a, int b, float *ms)

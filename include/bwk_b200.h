@@ -93,6 +93,10 @@ int bwk_get_device_qtens(uint64_t *ptr);
  * 572-576, but on the device): 64 slots; elapsed blocks until event `b` has happened. */
 int bwk_event_record(int slot);
 int bwk_event_elapsed_ms(int a, int b, float *ms);
+/* Single rank: record event `slot` on the library stream between the element-local sweep and the strip sweep of every
+ * DSS-containing call that follows (slot < 0 switches it off), so that a harness can time the two sweeps INSIDE its timed
+ * steps: bwk_event_elapsed_ms(start, slot) and (slot, end). */
+int bwk_set_phase_event(int slot);
 
 /* ------------------------------------------------------------------------------------
  * Harness helpers, mirroring module kernel_utils (F90:7-93) on the device so that the
