@@ -22,6 +22,7 @@ struct State {
     size_t flush_bytes = 0;
     cudaStream_t stream = nullptr;
     int block = 0, chunks = 0;  // 0 = chosen by the library (see plan_launch)
+    int force_generic = 0;      // MPDATA_B200_GENERIC=1: the run-time-size kernel even at the reference sizes (A/B, tests)
     int use_block = 1024, use_chunks = 1, nlmax = 0, grid = 0, sms = 0, smem_optin = 0, smem_sm = 0;
     size_t smem = 0;
 } g;
@@ -67,6 +68,9 @@ int plan_launch() {
     if (chunks <= 0) {
         chunks = g.sms / g.ns;
         if (chunks > nzm / 8) chunks = nzm / 8;
+        // at least as many slices as SMs: two half-slice CTAs per SM overlap each other's barriers and load phases
+        // (measured: 1,184 slices 0.160 against 0.171 ms, 9,472 slices 1.23 against 1.29 ms; profiles/r2a_mpdata_prof.json)
+        if (chunks < 2 && g.ns >= g.sms && nzm >= 16) chunks = 2;
     }
     if (chunks > nzm) chunks = nzm;
     if (chunks < 1) chunks = 1;
@@ -91,14 +95,18 @@ int plan_launch() {
     if (per_sm < 1) per_sm = 1;
     const long long items = (long long)g.ns * chunks, resident = (long long)per_sm * g.sms;
     g.grid = (int)(items < resident ? items : resident);
-    CU(cudaFuncSetAttribute(mpd_dev::advect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaFuncSetAttribute(mpd_dev::advect_kernel<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaFuncSetAttribute(mpd_dev::advect_kernel<32, 58>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     return 0;
 }
 
 int launch_step() {
     // f -> f1, then the two swap roles: a level chunk's halo must read the other chunks' input
     mpd_dev::Problem p{g.ns, g.nx, g.nz, g.f, g.f1, g.u, g.w, g.rho, g.rhow, g.adz, g.flux};
-    mpd_dev::advect_kernel<<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax);
+    if (g.nx == 32 && g.nz == 58 && !g.force_generic)  // the reference sizes (A:6-8): plane sizes as compile-time constants
+        mpd_dev::advect_kernel<32, 58><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax);
+    else
+        mpd_dev::advect_kernel<0, 0><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax);
     ++g_launches;
     CU(cudaGetLastError());
     double *t = g.f; g.f = g.f1; g.f1 = t;
@@ -155,6 +163,7 @@ int mpdata_init(int nslices, int nx, int nz) {
         return fail(3, "mpdata_init: even one level of a slice with its halo does not fit shared memory (nx=%d): %zu B, the SM has %zu",
                     nx, mpd_dev::item_doubles(nx, 2 * mpd_dev::kHalo + 1) * sizeof(double), (size_t)prop.sharedMemPerBlockOptin);
     release();
+    g.force_generic = getenv("MPDATA_B200_GENERIC") && atoi(getenv("MPDATA_B200_GENERIC")) != 0;
     g.ns = nslices; g.nx = nx; g.nz = nz;
     const size_t nzm = nz - 1;
     g.nf = (size_t)nslices * (nx + 6) * nzm;

@@ -76,9 +76,12 @@ __device__ __forceinline__ void split(int q, int W, float invW, int &k, int &i) 
     i = q - k * W;
 }
 
+// NXC, NZC > 0: the plane sizes as compile-time constants (the library instantiates the reference sizes, A:6-8: every plane
+// stride, loop bound and index split below becomes an immediate); 0: taken from the problem at run time.
+template <int NXC, int NZC>
 __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p, int chunks, int nlmax) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int nx = p.nx, nz = p.nz, nzm = nz - 1, ns = p.ns;
+    const int nx = NXC > 0 ? NXC : p.nx, nz = NZC > 0 ? NZC : p.nz, nzm = nz - 1, ns = p.ns;
     const int FX = nx + 6, UX = nx + 5, WX = nx + 4, MW = nx + 2;
     const int nxp1 = nx + 1, nxp2 = nx + 2;
     const int tid = threadIdx.x, nth = blockDim.x;

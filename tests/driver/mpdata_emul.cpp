@@ -31,6 +31,10 @@ alignas(16) unsigned char smem_raw[227 * 1024];  // the block-scope `extern ... 
 }
 #include "../../codesign-kernels_b200/csrc/mpdata_kernels.cuh"
 
+// 1: use the run-time-size kernel even at the reference sizes (the library's MPDATA_B200_GENERIC=1)
+static int mpdata_emul_generic = 0;
+extern "C" void mpdata_emul_set_generic(int on) { mpdata_emul_generic = on; }
+
 // One step exactly as mpdata_b200.cu's launch_step issues it (grid CTAs of `block` threads, `chunks`
 // level ranges per slice), on
 // host pointers.  Returns 0, 1 on bad arguments, 3 if a slice does not fit the shared memory.
@@ -52,7 +56,9 @@ extern "C" int mpdata_emul_step(int grid, int block, int chunks, int ns, int nx,
             threadIdx.x = (unsigned)t;
             for (int b = 0; b < grid; ++b) {
                 blockIdx.x = (unsigned)b;
-                mpd_dev::advect_kernel(p, chunks, nlmax);
+                // the library's dispatch: the reference sizes run the instantiation with compile-time plane sizes
+                if (nx == 32 && nz == 58 && !mpdata_emul_generic) mpd_dev::advect_kernel<32, 58>(p, chunks, nlmax);
+                else mpd_dev::advect_kernel<0, 0>(p, chunks, nlmax);
                 bar.arrive_and_wait();  // CTAs share the one shared-memory buffer: run them in turn
             }
         });

@@ -223,6 +223,21 @@ def test_device_source_on_host_bit_identical_to_oracle(mpdata, mpo, emul, ns, nx
         assert np.array_equal(fle, fl), chunks
 
 
+def test_device_source_generic_instantiation_at_the_reference_sizes(mpdata, mpo, emul):
+    """At nx = 32, nz = 58 the library launches advect_kernel<32, 58> (plane sizes as compile-time constants; the cases above);
+    MPDATA_B200_GENERIC=1 / mpdata_emul_set_generic(1) selects the run-time-size instantiation there too: same bits."""
+    P = mpdata.TestAdvect(5, 32, 58).init(seed=12, signed_velocity=True)
+    f, fl = _run_oracle(mpo, P)
+    emul.mpdata_emul_set_generic(1)
+    try:
+        for chunks in (1, 2, 3):
+            fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
+            assert emul.mpdata_emul_step(7, 96, chunks, 5, 32, 58, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)]) == 0
+            assert np.array_equal(fe, f) and np.array_equal(fle, fl), chunks
+    finally:
+        emul.mpdata_emul_set_generic(0)
+
+
 def test_device_source_on_host_full_block(mpdata, mpo, emul):
     """1024 threads per CTA (the launch default) at the reference sizes, CTAs walking several slices."""
     P = mpdata.TestAdvect().init(seed=100)
@@ -321,8 +336,9 @@ def test_gpu_automatic_launch_shape(mpdata):
     assert L.mpdata_init(48, 32, 58) == 0
     grid, block, chunks, smem = mpdata.launch_shape()
     assert chunks == max(1, min(sms // 48, 7)) and grid == 48 * chunks and block in (512, 1024)
+    # at least as many slices as SMs: two half-slice CTAs per SM (they overlap each other's barriers and load phases)
     assert L.mpdata_init(4 * sms, 32, 58) == 0
-    assert mpdata.launch_shape()[2] == 1 and mpdata.launch_shape()[3] == 117936
+    assert mpdata.launch_shape()[2] == 2 and mpdata.launch_shape()[3] <= 113 * 1024
     # a slice too tall for shared memory is split further instead of being refused
     assert L.mpdata_init(4 * sms, 32, 400) == 0
     assert mpdata.launch_shape()[2] > 1 and mpdata.launch_shape()[3] <= 227 * 1024
