@@ -1228,9 +1228,12 @@ int bwk_initialize_data_device(int64_t nelemd_global, int64_t elem_first, int se
     if (need_init()) return 1;
     if (elem_first < 0 || elem_first + g.nelem > nelemd_global) return fail("elements [%lld,%lld) outside global 0..%lld", (long long)elem_first,
                                                                             (long long)(elem_first + g.nelem), (long long)nelemd_global);
-    const std::vector<double> table = lcg_table();
-    if (!g.d_table) CK(cudaMalloc(&g.d_table, sizeof(double) * 131072));
-    CK(cudaMemcpyAsync(g.d_table, table.data(), sizeof(double) * 131072, cudaMemcpyHostToDevice, g.s_main));
+    static const std::vector<double> table = lcg_table();
+    if (!g.d_table) { // once per context: a 1 MB copy from pageable memory would put a host-side wait into every call
+        CK(cudaMalloc(&g.d_table, sizeof(double) * 131072));
+        CK(cudaMemcpyAsync(g.d_table, table.data(), sizeof(double) * 131072, cudaMemcpyHostToDevice, g.s_main));
+        CK(cudaStreamSynchronize(g.s_main));
+    }
     double dvv[16];
     for (int t = 0; t < 16; ++t) {
         if (seed_mode == 0) dvv[t] = table[(size_t)t];
