@@ -22,6 +22,7 @@ struct State {
     size_t flush_bytes = 0;
     cudaStream_t stream = nullptr;
     int block = 0, chunks = 0;  // 0 = chosen by the library (see plan_launch)
+    int prefetch = 0;           // the launch uses the prefetching form (see plan_launch)
     int force_generic = 0;      // MPDATA_B200_GENERIC=1: the run-time-size kernel even at the reference sizes (A/B, tests)
     int use_block = 1024, use_chunks = 1, nlmax = 0, grid = 0, sms = 0, smem_optin = 0, smem_sm = 0;
     size_t smem = 0;
@@ -95,6 +96,24 @@ int plan_launch() {
     if (per_sm < 1) per_sm = 1;
     const long long items = (long long)g.ns * chunks, resident = (long long)per_sm * g.sms;
     g.grid = (int)(items < resident ? items : resident);
+    // Prefetching form (MPDATA_B200_PREFETCH=1, off by default): when a CTA walks several items and a second set of the input
+    // planes fits without costing a resident CTA, the next item's f, u, w and level columns travel (cp.async) while the
+    // current item is computed.  Measured (profiles/r3h_*): bit-identical, but no gain at the default shape (9,472 slices: 1.27
+    // against 1.22 ms with two half-slice CTAs per SM; it only helps one CTA per SM, 1.24 against 1.30 ms) -- the global-load
+    // phase is not what bounds this kernel.
+    g.prefetch = 0;
+    {
+        const size_t smem2 = smem + mpd_dev::prefetch_doubles(g.nx, nlmax) * sizeof(double);
+        int per_sm2 = (int)((size_t)g.smem_sm / (smem2 + 1024));
+        if (per_sm2 > 1024 / block) per_sm2 = 1024 / block;
+        const char *env = getenv("MPDATA_B200_PREFETCH");
+        const bool want = env ? atoi(env) != 0 : false;
+        if (want && items > g.grid && smem2 <= (size_t)g.smem_optin && per_sm2 >= per_sm) {
+            g.prefetch = 1;
+            smem = smem2;
+            g.smem = smem2;
+        }
+    }
     CU(cudaFuncSetAttribute(mpd_dev::advect_kernel<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CU(cudaFuncSetAttribute(mpd_dev::advect_kernel<32, 58>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     return 0;
@@ -104,9 +123,9 @@ int launch_step() {
     // f -> f1, then the two swap roles: a level chunk's halo must read the other chunks' input
     mpd_dev::Problem p{g.ns, g.nx, g.nz, g.f, g.f1, g.u, g.w, g.rho, g.rhow, g.adz, g.flux};
     if (g.nx == 32 && g.nz == 58 && !g.force_generic)  // the reference sizes (A:6-8): plane sizes as compile-time constants
-        mpd_dev::advect_kernel<32, 58><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax);
+        mpd_dev::advect_kernel<32, 58><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax, g.prefetch);
     else
-        mpd_dev::advect_kernel<0, 0><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax);
+        mpd_dev::advect_kernel<0, 0><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax, g.prefetch);
     ++g_launches;
     CU(cudaGetLastError());
     double *t = g.f; g.f = g.f1; g.f1 = t;

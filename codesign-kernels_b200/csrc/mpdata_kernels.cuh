@@ -57,6 +57,25 @@ __host__ __device__ inline size_t item_doubles(int nx, int nl) {
            6 * (size_t)nl;
 }
 
+// extra doubles of shared memory the prefetching form needs: a second set of the three input planes and two sets of the raw
+// rho / adz / rhow columns
+__host__ __device__ inline size_t prefetch_doubles(int nx, int nl) {
+    return (size_t)(nx + 6) * nl + (size_t)(nx + 5) * nl + (size_t)(nx + 4) * nl + 6 * (size_t)nl;
+}
+// 8-byte asynchronous global -> shared copy (cp.async); the host emulation copies at once
+__device__ __forceinline__ void async_copy8(double *dst, const double *src) {
+#ifdef __CUDA_ARCH__
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+#else
+    *dst = *src;
+#endif
+}
+__device__ __forceinline__ void async_wait_all() {
+#ifdef __CUDA_ARCH__
+    asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
+}
+
 // Fortran MAX/MIN as compare-select, in the oracle's argument order (so even the sign of a zero
 // agrees).  CUDA's fmax/fmin cost ~8 instructions each on sm_100a (DSETP pair, two selects, the
 // NaN-quieting LOP3s and register moves); these are DSETP + two selects.
@@ -79,7 +98,7 @@ __device__ __forceinline__ void split(int q, int W, float invW, int &k, int &i) 
 // NXC, NZC > 0: the plane sizes as compile-time constants (the library instantiates the reference sizes, A:6-8: every plane
 // stride, loop bound and index split below becomes an immediate); 0: taken from the problem at run time.
 template <int NXC, int NZC>
-__global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p, int chunks, int nlmax) {
+__global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p, int chunks, int nlmax, int prefetch) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int nx = NXC > 0 ? NXC : p.nx, nz = NZC > 0 ? NZC : p.nz, nzm = nz - 1, ns = p.ns;
     const int FX = nx + 6, UX = nx + 5, WX = nx + 4, MW = nx + 2;
@@ -90,15 +109,36 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p, int chunks, 
     const float invP3 = 1.0f / (float)(nx + 3), invP5 = 1.0f / (float)nxp1;
 
     // planes of nlmax local levels (www: one more, the level above the last), row = k - klo
-    double *sf = reinterpret_cast<double *>(smem_raw);  // f   [row][i+2]
-    double *su = sf + FX * nlmax;                       // u   [row][i+1]
-    double *sw = su + UX * nlmax;                       // w   [row][i+1]
-    double *suuu = sw + WX * nlmax;                     // uuu [row][i+1]
+    double *sfA = reinterpret_cast<double *>(smem_raw); // f   [row][i+2]
+    double *suA = sfA + FX * nlmax;                     // u   [row][i+1]
+    double *swA = suA + UX * nlmax;                     // w   [row][i+1]
+    double *suuu = swA + WX * nlmax;                    // uuu [row][i+1]
     double *swww = suuu + UX * nlmax;                   // www [row][i+1], nlmax + 1 rows
     double *smx = swww + WX * (nlmax + 1);              // mx  [row][i]
     double *smn = smx + MW * nlmax;                     // mn  [row][i]
     double *srho = smn + MW * nlmax;                    // per-level columns, nlmax each
     double *sdd = srho + nlmax, *sirho = sdd + nlmax, *siadz = sirho + nlmax, *sirhow = siadz + nlmax, *sflux = sirhow + nlmax;
+    // prefetching form (prefetch != 0, a CTA walks several items): a second set of the input planes and two sets of the raw
+    // rho / adz / rhow columns; the loads of item n+1 travel (cp.async) while item n is computed
+    double *sfB = sflux + nlmax, *suB = sfB + FX * nlmax, *swB = suB + UX * nlmax, *sraw = swB + WX * nlmax;  // sraw [set][rho,adz,rhow][nlmax]
+    const int nitems = ns * chunks;
+    auto fetch_item = [&](int item, int set) { // every thread: its share of the item's f, u, w planes and level columns
+        const int c = item / ns, sl = item - c * ns;
+        int ka, kz, klo, khi;
+        chunk_range(nzm, chunks, c, ka, kz, klo, khi);
+        const int nl = khi - klo + 1;
+        double *df = set ? sfB : sfA, *du = set ? suB : suA, *dw = set ? swB : swA, *dr = sraw + set * 3 * nlmax;
+        for (int q = tid; q < FX * nl; q += nth) async_copy8(df + q, p.f + sl + (size_t)ns * (q + FX * (klo - 1)));
+        for (int q = tid; q < UX * nl; q += nth) async_copy8(du + q, p.u + sl + (size_t)ns * (q + UX * (klo - 1)));
+        for (int q = tid; q < WX * nl; q += nth) async_copy8(dw + q, p.w + sl + (size_t)ns * (q + WX * (klo - 1)));
+        for (int k = klo + tid; k <= khi; k += nth) {
+            async_copy8(dr + (k - klo), p.rho + sl + (size_t)ns * (k - 1));
+            async_copy8(dr + nlmax + (k - klo), p.adz + sl + (size_t)ns * (k - 1));
+            async_copy8(dr + 2 * nlmax + (k - klo), p.rhow + sl + (size_t)ns * (k - 1));
+        }
+    };
+    if (prefetch && (int)blockIdx.x < nitems) fetch_item(blockIdx.x, 0);
+    int it = 0;
 
 #define SF(i, k) sf[((i) + 2) + FX * ((k)-klo)]
 #define SU(i, k) su[((i) + 1) + UX * ((k)-klo)]
@@ -113,24 +153,44 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p, int chunks, 
 #define KB(k) ((k) > klo ? (k)-1 : klo)
 #define KC(k) ((k) < khi ? (k) + 1 : khi)
 
-    for (int item = blockIdx.x; item < ns * chunks; item += gridDim.x) {
+    for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
         const int c = item / ns, sl = item - c * ns;  // neighbouring CTAs: neighbouring slices, same levels
         int ka, kz, klo, khi;
         chunk_range(nzm, chunks, c, ka, kz, klo, khi);
         const int nl = khi - klo + 1;
+        const int set = prefetch ? (it & 1) : 0;
+        double *sf = set ? sfB : sfA, *su = set ? suB : suA, *sw = set ? swB : swA;
 
-        // ---- P0: the item's planes; slice stride in global memory
-        for (int q = tid; q < FX * nl; q += nth) sf[q] = p.f[sl + (size_t)ns * (q + FX * (klo - 1))];
-        for (int q = tid; q < UX * nl; q += nth) su[q] = p.u[sl + (size_t)ns * (q + UX * (klo - 1))];
-        for (int q = tid; q < WX * nl; q += nth) sw[q] = p.w[sl + (size_t)ns * (q + WX * (klo - 1))];
-        for (int k = klo + tid; k <= khi; k += nth) {
-            const double r = p.rho[sl + (size_t)ns * (k - 1)], a = p.adz[sl + (size_t)ns * (k - 1)];
-            const int kbg = k > 1 ? k - 1 : 1, kcg = k < nzm ? k + 1 : nzm;
-            COL(srho, k) = r;
-            COL(sdd, k) = 2.0 / (double)(kcg - kbg) / a;                          // A:569, the same for every x
-            COL(sirho, k) = 1.0 / r;                                              // A:552
-            COL(siadz, k) = 1.0 / a;                                              // A:553
-            COL(sirhow, k) = 1.0 / (p.rhow[sl + (size_t)ns * (k - 1)] * a);       // A:565
+        if (prefetch) {
+            // ---- P0 (prefetching form): this item's planes were requested one item ago; every thread's copies have landed
+            //      after its wait, everybody's after the barrier -- which is also the barrier that ends the previous item
+            async_wait_all();
+            __syncthreads();
+            if (item + (int)gridDim.x < nitems) fetch_item(item + gridDim.x, set ^ 1); // travels while this item is computed
+            const double *raw = sraw + set * 3 * nlmax;
+            for (int k = klo + tid; k <= khi; k += nth) {
+                const double r = raw[k - klo], a = raw[nlmax + (k - klo)];
+                const int kbg = k > 1 ? k - 1 : 1, kcg = k < nzm ? k + 1 : nzm;
+                COL(srho, k) = r;
+                COL(sdd, k) = 2.0 / (double)(kcg - kbg) / a;
+                COL(sirho, k) = 1.0 / r;
+                COL(siadz, k) = 1.0 / a;
+                COL(sirhow, k) = 1.0 / (raw[2 * nlmax + (k - klo)] * a);
+            }
+        } else {
+            // ---- P0: the item's planes; slice stride in global memory
+            for (int q = tid; q < FX * nl; q += nth) sf[q] = p.f[sl + (size_t)ns * (q + FX * (klo - 1))];
+            for (int q = tid; q < UX * nl; q += nth) su[q] = p.u[sl + (size_t)ns * (q + UX * (klo - 1))];
+            for (int q = tid; q < WX * nl; q += nth) sw[q] = p.w[sl + (size_t)ns * (q + WX * (klo - 1))];
+            for (int k = klo + tid; k <= khi; k += nth) {
+                const double r = p.rho[sl + (size_t)ns * (k - 1)], a = p.adz[sl + (size_t)ns * (k - 1)];
+                const int kbg = k > 1 ? k - 1 : 1, kcg = k < nzm ? k + 1 : nzm;
+                COL(srho, k) = r;
+                COL(sdd, k) = 2.0 / (double)(kcg - kbg) / a;                          // A:569, the same for every x
+                COL(sirho, k) = 1.0 / r;                                              // A:552
+                COL(siadz, k) = 1.0 / a;                                              // A:553
+                COL(sirhow, k) = 1.0 / (p.rhow[sl + (size_t)ns * (k - 1)] * a);       // A:565
+            }
         }
         __syncthreads();
 
@@ -243,7 +303,7 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p, int chunks, 
                 v = dmax(0.0, v - (SUUU(i + 1, k) - SUUU(i, k) + (SWWW(i, k + 1) - SWWW(i, k)) * COL(siadz, k)) * COL(sirho, k));
             p.fout[sl + (size_t)ns * ((i + 2) + FX * (k - 1))] = v;
         }
-        __syncthreads();  // the next item of this CTA reuses the planes
+        if (!prefetch) __syncthreads();  // the next item of this CTA reuses the planes (prefetching form: the barrier at the top of the next item)
     }
 #undef SF
 #undef SU

@@ -38,11 +38,16 @@ extern "C" void mpdata_emul_set_generic(int on) { mpdata_emul_generic = on; }
 // One step exactly as mpdata_b200.cu's launch_step issues it (grid CTAs of `block` threads, `chunks`
 // level ranges per slice), on
 // host pointers.  Returns 0, 1 on bad arguments, 3 if a slice does not fit the shared memory.
+// 1: the prefetching form (second set of input planes, the next item's loads issued one item ahead)
+static int mpdata_emul_prefetch = 0;
+extern "C" void mpdata_emul_set_prefetch(int on) { mpdata_emul_prefetch = on; }
+
 extern "C" int mpdata_emul_step(int grid, int block, int chunks, int ns, int nx, int nz, double *f, const double *u, const double *w,
                                 const double *rho, const double *rhow, const double *adz, double *flux) {
     if (grid < 1 || block < 1 || block > 1024 || ns < 1 || nx < 1 || nz < 3 || chunks < 1 || chunks > nz - 1) return 1;
     const int nlmax = mpd_dev::max_local_levels(nz - 1, chunks);
-    if (mpd_dev::item_doubles(nx, nlmax) * sizeof(double) > sizeof mpd_dev::smem_raw) return 3;
+    if ((mpd_dev::item_doubles(nx, nlmax) + (mpdata_emul_prefetch ? mpd_dev::prefetch_doubles(nx, nlmax) : 0)) * sizeof(double) > sizeof mpd_dev::smem_raw) return 3;
+    const int prefetch = mpdata_emul_prefetch;
     for (size_t j = 0; j < sizeof mpd_dev::smem_raw; ++j) mpd_dev::smem_raw[j] = 0xff;  // shared memory starts uninitialised: all-ones bytes = NaN, which would poison any output it reached
     const std::vector<double> fin(f, f + (size_t)ns * (nx + 6) * (nz - 1));  // the library ping-pongs two device buffers
     mpd_dev::Problem p{ns, nx, nz, fin.data(), f, u, w, rho, rhow, adz, flux};
@@ -57,8 +62,8 @@ extern "C" int mpdata_emul_step(int grid, int block, int chunks, int ns, int nx,
             for (int b = 0; b < grid; ++b) {
                 blockIdx.x = (unsigned)b;
                 // the library's dispatch: the reference sizes run the instantiation with compile-time plane sizes
-                if (nx == 32 && nz == 58 && !mpdata_emul_generic) mpd_dev::advect_kernel<32, 58>(p, chunks, nlmax);
-                else mpd_dev::advect_kernel<0, 0>(p, chunks, nlmax);
+                if (nx == 32 && nz == 58 && !mpdata_emul_generic) mpd_dev::advect_kernel<32, 58>(p, chunks, nlmax, prefetch);
+                else mpd_dev::advect_kernel<0, 0>(p, chunks, nlmax, prefetch);
                 bar.arrive_and_wait();  // CTAs share the one shared-memory buffer: run them in turn
             }
         });

@@ -223,6 +223,31 @@ def test_device_source_on_host_bit_identical_to_oracle(mpdata, mpo, emul, ns, nx
         assert np.array_equal(fle, fl), chunks
 
 
+@pytest.mark.parametrize("ns,nx,nz,signed", EMUL_CASES)
+@pytest.mark.parametrize("block,grid", [(96, 2), (32, 1), (64, 5)])
+def test_device_source_prefetching_form_on_host(mpdata, mpo, emul, ns, nx, nz, signed, block, grid):
+    """The prefetching form (a CTA walks several items; the next item's planes are requested one item ahead into a second
+    set of input planes; the barrier at the top of an item ends the previous one) gives the oracle's bits for every chunk
+    count -- shared memory pre-filled with NaN, so a read of a plane that was not (yet) loaded would poison the output.
+    (cp.async is an immediate copy on the host: the ORDER of waits and barriers is what the GPU tests add.)"""
+    P = mpdata.TestAdvect(ns, nx, nz).init(seed=13, signed_velocity=signed)
+    f, fl = _run_oracle(mpo, P)
+    emul.mpdata_emul_set_prefetch(1)
+    try:
+        for chunks in sorted({1, 2, 3, 7, nz - 1}):
+            if chunks > nz - 1:
+                continue
+            fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
+            rc = emul.mpdata_emul_step(min(grid, ns * chunks), block, chunks, ns, nx, nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)])
+            if rc == 3:  # two sets of input planes of a whole slice do not fit the emulation's 227 KB at this shape
+                continue
+            assert rc == 0
+            assert np.array_equal(fe, f), chunks
+            assert np.array_equal(fle, fl), chunks
+    finally:
+        emul.mpdata_emul_set_prefetch(0)
+
+
 def test_device_source_generic_instantiation_at_the_reference_sizes(mpdata, mpo, emul):
     """At nx = 32, nz = 58 the library launches advect_kernel<32, 58> (plane sizes as compile-time constants; the cases above);
     MPDATA_B200_GENERIC=1 / mpdata_emul_set_generic(1) selects the run-time-size instantiation there too: same bits."""
