@@ -120,6 +120,8 @@ def lib():
         getattr(L, name).argtypes = [p, i32]
     L.bwk_plan_strip_count.restype = i64
     L.bwk_plan_strip_count.argtypes = [p, i32]
+    L.bwk_plan_strip_groups.restype = i64
+    L.bwk_plan_strip_groups.argtypes = [p, i32, i32, p, p]
     _lib = L
     return L
 
@@ -192,6 +194,16 @@ class Plan:
             _ck(lib().bwk_plan_strip_list(self._h, which, _ptr(f), _ptr(c), _ptr(r)))
         self.strip_regular = r
         return f, c
+
+    def strip_groups(self, which=0, max_members=8):
+        """(first local element, chained full strips) per warp-strip work unit; 0 strips = left to the round-1 strip kernel."""
+        cap = lib().bwk_plan_strip_count(self._h, which)
+        f = np.empty(cap, dtype=np.int32)
+        k = np.empty(cap, dtype=np.int32)
+        n = lib().bwk_plan_strip_groups(self._h, which, max_members, _ptr(f), _ptr(k))
+        if n < 0:
+            raise ValueError("which must be 0, 1 or 2")
+        return f[:n].copy(), k[:n].copy()
 
     def apply_host(self, field_global):
         f = np.ascontiguousarray(field_global, dtype=np.float64)

@@ -565,55 +565,14 @@ int install_plan(Plan &&pl)
         const std::vector<StripReg> *R[3] = {&P.reg_all, &P.reg_dependent, &P.reg_independent};
         int32_t **ds[3] = {&g.d_strips_all, &g.d_strips_dep, &g.d_strips_indep};
         StripReg **dr[3] = {&g.d_reg_all, &g.d_reg_dep, &g.d_reg_indep};
+        static const int max_members = std::getenv("BWK_WSTRIP_MEMBERS") ? std::atoi(std::getenv("BWK_WSTRIP_MEMBERS")) : 8; // tuning knob
         for (int w = 0; w < 3; ++w) {
-            std::vector<int32_t> hs;
-            std::vector<StripReg> hr;
-            hs.reserve(S[w]->size());
-            hr.reserve(S[w]->size());
-            // fast = full regular strip whose members' S (and N) neighbours are consecutive elements (or consecutive halo
-            // slots) facing with the same row: one {4, 8 slabs, 4 elements} TMA box fetches the four members' rows
-            auto is_fast = [](const StripReg &r, int32_t strip) {
-                if (!r.regular || strip_count(strip) != STRIP_MAX) return false;
-                for (int m = 1; m < STRIP_MAX; ++m)
-                    if (r.s_src[m] != r.s_src[0] + m || r.s_c0[m] != r.s_c0[0] || r.n_src[m] != r.n_src[0] + m || r.n_c0[m] != r.n_c0[0]) return false;
-                return true;
-            };
-            int64_t nf = 0;
-            for (int pass = 0; pass < 2; ++pass) // pass 0 collects the fast strips, pass 1 the rest
-                for (size_t i = 0; i < S[w]->size(); ++i) {
-                    const bool fast = is_fast((*R[w])[i], (*S[w])[i]);
-                    if (fast == (pass == 0)) { hs.push_back((*S[w])[i]); hr.push_back((*R[w])[i]); nf += pass == 0; }
-                }
-            g.nfast[w] = nf;
-            if (upload_list(hs, ds[w]) || upload_regs(hr, dr[w])) return 1;
-            // groups of 4 / 2 / 1 consecutive fast strips for the warp-strip sweep with 16 / 8 / 4 members per warp: the next
-            // strip continues the previous one (its first element follows, and so do its members' S and N neighbours)
-            static const int max_members = std::getenv("BWK_WSTRIP_MEMBERS") ? std::atoi(std::getenv("BWK_WSTRIP_MEMBERS")) : 8; // tuning knob
-            // b continues a: same row of elements (a's E neighbour is b's first member and vice versa, plain W-E link), the
-            // members' S and N neighbours continue too, and the diagonal contributors at the joint are the facing ends of the
-            // other strip's S/N rows -- exactly the relations that hold between the members of one strip
-            auto chains = [](const StripReg &a, const StripReg &b) {
-                if (b.first != a.first + STRIP_MAX) return false;
-                if (b.s_src[0] != a.s_src[0] + STRIP_MAX || b.s_c0[0] != a.s_c0[0] || b.n_src[0] != a.n_src[0] + STRIP_MAX || b.n_c0[0] != a.n_c0[0]) return false;
-                if (a.end_kind[1] != SRC_TMPCOL || a.end_src[1] != b.first || a.end_row[1] != 0 || a.end_rev[1]) return false;
-                if (b.end_kind[0] != SRC_TMPCOL || b.end_src[0] != a.first + STRIP_MAX - 1 || b.end_row[0] != 1 || b.end_rev[0]) return false;
-                auto diag_is = [](const StripReg &r, int d, int32_t src, int c0, int pos) { // diagonal d of r == value `pos` of the row (src, c0)
-                    if (r.diag_src[d] != src) return false;
-                    if (c0 == ROW_IN_HALO) return r.diag_kind[d] == SRC_HALO && r.diag_pt[d] == pos;
-                    return r.diag_kind[d] == SRC_TMPCOL && r.diag_pt[d] == c0 + pos;
-                };
-                return diag_is(a, 2, b.s_src[0], b.s_c0[0], 0) && diag_is(a, 3, b.n_src[0], b.n_c0[0], 0) &&
-                       diag_is(b, 0, a.s_src[STRIP_MAX - 1], a.s_c0[STRIP_MAX - 1], 3) && diag_is(b, 1, a.n_src[STRIP_MAX - 1], a.n_c0[STRIP_MAX - 1], 3);
-            };
-            std::vector<StripReg> grp[3];
-            for (int64_t i = 0; i < nf;) {
-                int64_t run = 1;
-                while (run < 4 && i + run < nf && chains(hr[(size_t)(i + run - 1)], hr[(size_t)(i + run)])) ++run;
-                const int take = (run >= 4 && max_members >= 16) ? 4 : (run >= 2 && max_members >= 8) ? 2 : 1;
-                const int gi = take == 4 ? 2 : take == 2 ? 1 : 0;
-                for (int k = 0; k < take; ++k) grp[gi].push_back(hr[(size_t)(i + k)]);
-                i += take;
-            }
+            // fast strips first, then groups of 4 / 2 / 1 chained fast strips for the warp-strip sweep with 16 / 8 / 4 members per
+            // warp (bwk_plan.cpp: strip_is_fast, strips_chain, group_strips)
+            const StripGroups G = group_strips(*S[w], *R[w], max_members);
+            const std::vector<StripReg> *grp = G.grp;
+            g.nfast[w] = G.nfast;
+            if (upload_list(G.strips, ds[w]) || upload_regs(G.regs, dr[w])) return 1;
             for (int gi = 0; gi < 3; ++gi) {
                 g.ngrp[w][gi] = (int64_t)grp[gi].size() / (WS_NM[gi] / 4);
                 if (upload_regs(grp[gi], &g.d_grp[w][gi])) return 1;
@@ -1663,6 +1622,22 @@ int bwk_plan_strip_list(const bwk_plan_t *h, int which, int32_t *first, int32_t 
         if (regular) regular[i] = r[i].regular;
     }
     return 0;
+}
+int64_t bwk_plan_strip_groups(const bwk_plan_t *h, int which, int max_members, int32_t *first, int32_t *nstrips)
+{
+    const std::vector<int32_t> *v = strip_vec(h, which);
+    if (!v) return -1;
+    const std::vector<StripReg> &r = which == 0 ? h->p.reg_all : which == 1 ? h->p.reg_dependent : h->p.reg_independent;
+    const StripGroups G = group_strips(*v, r, max_members);
+    int64_t n = 0;
+    for (int gi = 2; gi >= 0; --gi) { // the order the sweep launches them in does not matter; report the widest groups first
+        const int per = 1 << gi;
+        for (size_t i = 0; i + per <= G.grp[gi].size(); i += (size_t)per, ++n)
+            if (first) { first[n] = G.grp[gi][i].first; nstrips[n] = per; }
+    }
+    for (size_t i = (size_t)G.nfast; i < G.strips.size(); ++i, ++n)
+        if (first) { first[n] = strip_first(G.strips[i]); nstrips[n] = 0; }
+    return n;
 }
 int bwk_plan_apply_host(const bwk_plan_t *h, const double *field, double *out)
 {

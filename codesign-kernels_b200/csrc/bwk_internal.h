@@ -99,6 +99,21 @@ constexpr int STRIP_MAX = 4;
 inline int strip_first(int32_t s) { return s >> 3; }
 inline int strip_count(int32_t s) { return (s & 7) + 1; }
 
+// ---- grouping of the strip lists for the warp-strip sweep (bwk_plan.cpp; used by bwk_api.cu and by the CPU tests)
+// fast = full regular strip whose members' S (and N) neighbours are consecutive elements (or consecutive halo slots) facing with
+// the same row: one {4, SL slabs, NM elements} TMA box fetches the members' rows
+bool strip_is_fast(const StripReg &r, int32_t strip);
+// b continues a: same row of elements (plain W-E link between a's last and b's first member), the members' S and N neighbours
+// continue too, and the diagonal contributors at the joint are the facing ends of the other strip's S/N rows
+bool strips_chain(const StripReg &a, const StripReg &b);
+struct StripGroups {
+    std::vector<int32_t> strips;  // the list re-ordered: fast strips first (element order kept in both parts)
+    std::vector<StripReg> regs;   // same order
+    int64_t nfast = 0;
+    std::vector<StripReg> grp[3]; // groups of 1 / 2 / 4 chained fast strips (4 / 8 / 16 members per warp), records back to back
+};
+StripGroups group_strips(const std::vector<int32_t> &strips, const std::vector<StripReg> &regs, int max_members);
+
 // partition: rank r owns [first, first+count)
 void partition(int64_t nelem_global, int rank, int nranks, int64_t *first, int64_t *count);
 int owner_of(int64_t nelem_global, int nranks, int64_t e);

@@ -437,6 +437,50 @@ Plan build_plan(int64_t nelem_global, const int64_t *gdof, int rank, int nranks)
 }
 
 // Host restatement of exactly what the sweep-2 kernel's gather does with an ElemDss.
+bool strip_is_fast(const StripReg &r, int32_t strip)
+{
+    if (!r.regular || strip_count(strip) != STRIP_MAX) return false;
+    for (int m = 1; m < STRIP_MAX; ++m)
+        if (r.s_src[m] != r.s_src[0] + m || r.s_c0[m] != r.s_c0[0] || r.n_src[m] != r.n_src[0] + m || r.n_c0[m] != r.n_c0[0]) return false;
+    return true;
+}
+
+bool strips_chain(const StripReg &a, const StripReg &b)
+{
+    if (b.first != a.first + STRIP_MAX) return false;
+    if (b.s_src[0] != a.s_src[0] + STRIP_MAX || b.s_c0[0] != a.s_c0[0] || b.n_src[0] != a.n_src[0] + STRIP_MAX || b.n_c0[0] != a.n_c0[0]) return false;
+    if (a.end_kind[1] != SRC_TMPCOL || a.end_src[1] != b.first || a.end_row[1] != 0 || a.end_rev[1]) return false;
+    if (b.end_kind[0] != SRC_TMPCOL || b.end_src[0] != a.first + STRIP_MAX - 1 || b.end_row[0] != 1 || b.end_rev[0]) return false;
+    auto diag_is = [](const StripReg &r, int d, int32_t src, int c0, int pos) { // diagonal d of r == value `pos` of the row (src, c0)
+        if (r.diag_src[d] != src) return false;
+        if (c0 == ROW_IN_HALO) return r.diag_kind[d] == SRC_HALO && r.diag_pt[d] == pos;
+        return r.diag_kind[d] == SRC_TMPCOL && r.diag_pt[d] == c0 + pos;
+    };
+    return diag_is(a, 2, b.s_src[0], b.s_c0[0], 0) && diag_is(a, 3, b.n_src[0], b.n_c0[0], 0) &&
+           diag_is(b, 0, a.s_src[STRIP_MAX - 1], a.s_c0[STRIP_MAX - 1], 3) && diag_is(b, 1, a.n_src[STRIP_MAX - 1], a.n_c0[STRIP_MAX - 1], 3);
+}
+
+StripGroups group_strips(const std::vector<int32_t> &S, const std::vector<StripReg> &R, int max_members)
+{
+    StripGroups G;
+    G.strips.reserve(S.size());
+    G.regs.reserve(S.size());
+    for (int pass = 0; pass < 2; ++pass) // pass 0 collects the fast strips, pass 1 the rest
+        for (size_t i = 0; i < S.size(); ++i) {
+            const bool fast = strip_is_fast(R[i], S[i]);
+            if (fast == (pass == 0)) { G.strips.push_back(S[i]); G.regs.push_back(R[i]); G.nfast += pass == 0; }
+        }
+    for (int64_t i = 0; i < G.nfast;) {
+        int64_t run = 1;
+        while (run < 4 && i + run < G.nfast && strips_chain(G.regs[(size_t)(i + run - 1)], G.regs[(size_t)(i + run)])) ++run;
+        const int take = (run >= 4 && max_members >= 16) ? 4 : (run >= 2 && max_members >= 8) ? 2 : 1;
+        const int gi = take == 4 ? 2 : take == 2 ? 1 : 0;
+        for (int k = 0; k < take; ++k) G.grp[gi].push_back(G.regs[(size_t)(i + k)]);
+        i += take;
+    }
+    return G;
+}
+
 void gather_elem_host(const Plan &pl, int64_t le, const double *field, double *out)
 {
     const ElemDss &d = pl.dss[(size_t)le];

@@ -231,6 +231,11 @@ int64_t bwk_plan_dependent_elems(const bwk_plan_t *); /* local elements that nee
 int64_t bwk_plan_strip_count(const bwk_plan_t *, int which);
 /* regular[i] = 1 if strip i takes the fully asynchronous structured-patch path (may be NULL) */
 int bwk_plan_strip_list(const bwk_plan_t *, int which, int32_t *first_local_elem, int32_t *count, int32_t *regular);
+/* How install_plan groups list `which` for the warp-strip sweep when a warp may carry up to max_members
+ * elements (4, 8 or 16): returns the number of work units and, when first != NULL, writes for each the first local element and
+ * the number of chained full strips in it (4, 2 or 1; 0 = a strip the warp-strip sweep does not take, which runs in the
+ * round-1 strip kernel).  Both arrays need bwk_plan_strip_count(plan, which) entries.  Host only; used by the CPU tests. */
+int64_t bwk_plan_strip_groups(const bwk_plan_t *, int which, int max_members, int32_t *first_local_elem, int32_t *nstrips);
 /* CPU evaluation of the plan's gather for one slab field (16 doubles per GLOBAL element in
  * `field`): writes the DSS sums of the local elements to out (16*local_count).  Test hook
  * proving the plan equals a node-wise sum; not used by the GPU path. */

@@ -150,3 +150,63 @@ def test_patch_oracle_equals_full_oracle(oracle, ne, nlev, qsize):
     for e in sorted({0, ne - 1, ne * ne - 1, ne * ne, n - 1, n // 2, 2 * ne * ne + ne + 1}):
         got = patch_oracle_full(oracle, ne, nlev, qsize, gd, e)
         assert np.array_equal(got[..., 0], ref[..., e]), e
+
+
+@pytest.mark.parametrize("ne,nranks", [(4, 1), (8, 1), (30, 1), (16, 2), (12, 5), (120, 1), (120, 8)])
+def test_warp_strip_groups_are_whole_face_rows_chained_west_to_east(bwk, ne, nranks):
+    """The grouping install_plan feeds the warp-strip sweep (bwk_plan.cpp: group_strips), checked against the
+    gdof ids alone: the work units partition the strips of the list; a unit of k chained strips holds 4k consecutive
+    elements of ONE row of one face, every consecutive pair linked E column -> W column in the natural orientation, and the
+    members' S (and N) neighbours are consecutive elements too, all facing with the same one of their rows.  (The NM = 8
+    form once chained strips across the end of a face row: wrong values at ne = 4.)"""
+    n = 6 * ne * ne
+    g = bwk.cubed_sphere_gdof(ne).reshape(n, 4, 4)  # [e][j][i]
+    owner = {}
+    for e in range(n):
+        for j in (0, 3):
+            owner.setdefault(tuple(g[e][j, :]), []).append((e, j))  # natural rows
+            owner.setdefault(tuple(g[e][j, ::-1]), []).append((e, 10 + j))  # anything else: reversed rows, columns
+            owner.setdefault(tuple(g[e][:, j]), []).append((e, 20 + j))
+            owner.setdefault(tuple(g[e][::-1, j]), []).append((e, 30 + j))
+
+    def facing(e, j):  # the other element holding row j of e on one of its edges, and how
+        o = [x for x in owner[tuple(g[e][j, :])] if x[0] != e]
+        assert len(o) == 1
+        return o[0]
+
+    ranks = range(nranks) if ne < 100 else (0, nranks - 1)
+    for r in ranks:
+        pl = bwk.Plan(n, g.reshape(-1), r, nranks)
+        lo, cnt = pl.local_first, pl.local_count
+        for which in (0, 1, 2):
+            sf, sc = pl.strips(which)
+            strips = dict(zip(sf.tolist(), sc.tolist()))
+            for members in (4, 8, 16):
+                gf, gk = pl.strip_groups(which, members)
+                assert np.all(gk <= members // 4)
+                seen = []
+                for a, k in zip(gf.tolist(), gk.tolist()):
+                    if k == 0:  # left to the round-1 strip kernel: one strip of the list, untouched
+                        seen.append(a)
+                        continue
+                    for s in range(k):
+                        assert strips[a + 4 * s] == 4
+                        seen.append(a + 4 * s)
+                    el = np.arange(lo + a, lo + a + 4 * k)
+                    assert len(set((el // ne).tolist())) == 1  # one face, one row of elements
+                    for e in el[:-1]:
+                        assert np.array_equal(g[e][:, 3], g[e + 1][:, 0])
+                    for j in (0, 3):
+                        nb = [facing(int(e), j) for e in el]
+                        ids = np.array([x[0] for x in nb])
+                        local = (ids >= lo) & (ids < lo + cnt)
+                        assert local.all() or not local.any()  # a unit's rows come from tmp or from the halo, never both
+                        if local.all():  # rows read from tmp in place: one natural row of consecutive elements
+                            assert len({x[1] for x in nb}) == 1 and nb[0][1] in (0, 3)
+                            assert np.array_equal(ids, ids[0] + np.arange(4 * k))
+                assert sorted(seen) == sorted(strips)
+            if which == 0 and nranks == 1 and ne == 120:
+                gf, gk = pl.strip_groups(0, 8)
+                assert (gk == 2).sum() == 10680 and (gk == 1).sum() == 0 and (gk == 0).sum() == 240  # headline config
+            if which == 0 and ne == 4:
+                assert np.all(pl.strip_groups(0, 16)[1] <= 1)  # a face row is one strip: nothing to chain
