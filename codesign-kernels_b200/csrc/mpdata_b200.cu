@@ -10,6 +10,7 @@
 
 #include "../../include/mpdata_b200.h"
 #include "mpdata_kernels.cuh"
+#include "mpdata_march.cuh"
 
 namespace {
 
@@ -24,6 +25,8 @@ struct State {
     int block = 0, chunks = 0;  // 0 = chosen by the library (see plan_launch)
     int prefetch = 0;           // the launch uses the prefetching form (see plan_launch)
     int force_generic = 0;      // MPDATA_B200_GENERIC=1: the run-time-size kernel even at the reference sizes (A/B, tests)
+    int form = 0, march_warps = 0;  // mpdata_set_form: 0 = chosen by the library, 1 = barrier-phased CTA per slice, 2 / 3 = marching warp per slice / per two slices
+    int use_form = 1;
     int use_block = 1024, use_chunks = 1, nlmax = 0, grid = 0, sms = 0, smem_optin = 0, smem_sm = 0;
     size_t smem = 0;
 } g;
@@ -63,8 +66,40 @@ int release() {
 // recomputed levels, mpdata_kernels.cuh) only while there are fewer slices than SMs, so that
 // slices x chunks fills the SMs once (48 slices -> 3 chunks -> 144 CTAs on 148 SMs); block: about two
 // points of the widest plane per thread.  Results do not depend on either.
+// The marching forms (mpdata_march.cuh): a warp per slice (form 2) or per pair of slices (form 3), `warps` of them per CTA,
+// as many CTAs per SM as their rings allow.
+template <int NS2>
+int plan_march() {
+    auto kernel = mpd_dev::advect_march_kernel<32, 58, NS2>;
+    const size_t per_warp = NS2 * mpd_dev::march_warp_doubles(g.nx) * sizeof(double);
+    const int cap = 12 / NS2;  // the kernel's __launch_bounds__: 12 warps of 162 registers / 6 warps of up to 255
+    int warps = g.march_warps > 0 ? g.march_warps : cap;
+    if (warps > cap) warps = cap;
+    if ((size_t)warps * per_warp > (size_t)g.smem_optin) warps = (int)((size_t)g.smem_optin / per_warp);
+    if (warps < 1) return fail(3, "the rings of one warp need %zu B of shared memory (nx=%d), the SM has %d", per_warp, g.nx, g.smem_optin);
+    const size_t smem = (size_t)warps * per_warp;
+    CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, warps * 32, smem));
+    if (per_sm < 1) return fail(3, "the marching form does not fit an SM with %d warps per CTA", warps);
+    const long long per_cta = (long long)warps * NS2, ctas = ((long long)g.ns + per_cta - 1) / per_cta, resident = (long long)per_sm * g.sms;
+    g.use_form = 1 + NS2; g.use_chunks = 1; g.use_block = warps * 32; g.nlmax = g.nz - 1; g.smem = smem; g.prefetch = 0;
+    g.grid = (int)(ctas < resident ? ctas : resident);
+    return 0;
+}
+
 int plan_launch() {
     const int nzm = g.nz - 1;
+    {
+        int form = g.form;
+        if (form == 0)
+            if (const char *env = getenv("MPDATA_B200_FORM")) form = atoi(env);
+        const bool ref_sizes = g.nx == 32 && g.nz == 58;  // the sizes the marching form is instantiated for (A:6-8)
+        if (form >= 2 && !ref_sizes) return fail(2, "the marching form is compiled for nx=32, nz=58 only (got nx=%d, nz=%d)", g.nx, g.nz);
+        if (form == 2) return plan_march<1>();
+        if (form == 3) return plan_march<2>();
+        g.use_form = 1;
+    }
     int chunks = g.chunks;
     if (chunks <= 0) {
         chunks = g.sms / g.ns;
@@ -122,7 +157,11 @@ int plan_launch() {
 int launch_step() {
     // f -> f1, then the two swap roles: a level chunk's halo must read the other chunks' input
     mpd_dev::Problem p{g.ns, g.nx, g.nz, g.f, g.f1, g.u, g.w, g.rho, g.rhow, g.adz, g.flux};
-    if (g.nx == 32 && g.nz == 58 && !g.force_generic)  // the reference sizes (A:6-8): plane sizes as compile-time constants
+    if (g.use_form == 2)
+        mpd_dev::advect_march_kernel<32, 58, 1><<<g.grid, g.use_block, g.smem, g.stream>>>(p);
+    else if (g.use_form == 3)
+        mpd_dev::advect_march_kernel<32, 58, 2><<<g.grid, g.use_block, g.smem, g.stream>>>(p);
+    else if (g.nx == 32 && g.nz == 58 && !g.force_generic)  // the reference sizes (A:6-8): plane sizes as compile-time constants
         mpd_dev::advect_kernel<32, 58><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax, g.prefetch);
     else
         mpd_dev::advect_kernel<0, 0><<<g.grid, g.use_block, g.smem, g.stream>>>(p, g.use_chunks, g.nlmax, g.prefetch);
@@ -154,6 +193,22 @@ int mpdata_set_chunks(int chunks) {
     if (chunks < 0) return fail(2, "mpdata_set_chunks: %d is negative (0 = automatic)", chunks);
     g.chunks = chunks;
     return g.ready ? plan_launch() : 0;
+}
+
+int mpdata_set_form(int form, int warps_per_cta) {
+    if (form < 0 || form > 3 || warps_per_cta < 0 || warps_per_cta > 12)
+        return fail(2, "mpdata_set_form: form %d is not 0 (automatic), 1 (phases), 2 or 3 (marching, one / two slices per warp), or %d warps per CTA is not in 0..12", form, warps_per_cta);
+    const int form0 = g.form, warps0 = g.march_warps;
+    g.form = form;
+    g.march_warps = warps_per_cta;
+    if (!g.ready) return 0;
+    const int rc = plan_launch();
+    if (rc) {  // e.g. the marching form asked for while a context of other plane sizes is live: nothing changes
+        g.form = form0;
+        g.march_warps = warps0;
+        plan_launch();
+    }
+    return rc;
 }
 
 int mpdata_get_launch(int *grid, int *block, int *chunks, long long *smem_bytes) {

@@ -86,6 +86,16 @@ __device__ __forceinline__ double andiff(double x1, double x2, double a, double 
 __device__ __forceinline__ double across(double x1, double a1, double a2) { return 0.03125 * a1 * a2 * x1; }
 __device__ __forceinline__ double pp(double y) { return dmax(0.0, y); }
 __device__ __forceinline__ double pn(double y) { return -dmin(0.0, y); }
+// num / den of the limiter ratios (A:601-612), bit-identical to the IEEE quotient for every input.  den is a sum of
+// non-negative terms plus eps, and the numerator r * (mx - f) is exactly zero wherever f is a local extremum -- a zero
+// numerator sends the lane through the out-of-line slow path of CUDA's double division (ncu, profiles/r3l_*: a call per
+// division for ~6 lanes of every warp, 15 % of all executed instructions).  Those lanes divide 1 by den instead and take
+// the zero IEEE gives them: (+-0) / den = +-0 for den > 0.
+__device__ __forceinline__ double div_ratio(double num, double den) {
+    const bool zero = num == 0.0 && den > 0.0;
+    const double q = (zero ? 1.0 : num) / den;
+    return zero ? num : q;
+}
 
 // q -> (k = q / W, i = q % W) without an integer division: exact for q < 65536, W < 16384
 // (checked exhaustively in tests/test_zzz_mpdata.py); a plane never has more than 29,056 points
@@ -264,8 +274,8 @@ __global__ void __launch_bounds__(1024, 1) advect_kernel(Problem p, int chunks, 
             const int kc = KC(k), ic = i + 1;
             const double fk = SF(i, k), r = COL(srho, k), ia = COL(siadz, k);
             const double ui = SUUU(i, k), uc = SUUU(ic, k), wk = SWWW(i, k), wc = SWWW(i, kc);
-            SMX(i, k) = r * (SMX(i, k) - fk) / (pn(uc) + pp(ui) + ia * (pn(wc) + pp(wk)) + eps);
-            SMN(i, k) = r * (fk - SMN(i, k)) / (pp(uc) + pn(ui) + ia * (pp(wc) + pn(wk)) + eps);
+            SMX(i, k) = div_ratio(r * (SMX(i, k) - fk), pn(uc) + pp(ui) + ia * (pn(wc) + pp(wk)) + eps);
+            SMN(i, k) = div_ratio(r * (fk - SMN(i, k)), pp(uc) + pn(ui) + ia * (pp(wc) + pn(wk)) + eps);
         }
         __syncthreads();
 

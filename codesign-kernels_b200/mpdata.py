@@ -56,6 +56,7 @@ def lib():
     L.mpdata_time_steps.argtypes, L.mpdata_time_steps.restype = [i32, i32, C.POINTER(C.c_float)], i32
     L.mpdata_set_block.argtypes, L.mpdata_set_block.restype = [i32], i32
     L.mpdata_set_chunks.argtypes, L.mpdata_set_chunks.restype = [i32], i32
+    L.mpdata_set_form.argtypes, L.mpdata_set_form.restype = [i32, i32], i32
     L.mpdata_get_launch.argtypes, L.mpdata_get_launch.restype = [C.POINTER(i32)] * 3 + [C.POINTER(C.c_longlong)], i32
     L.mpdata_slice_smem_bytes.argtypes, L.mpdata_slice_smem_bytes.restype = [i32, i32], C.c_longlong
     L.mpdata_launch_count.argtypes, L.mpdata_launch_count.restype = [], C.c_longlong
@@ -136,10 +137,18 @@ def launch_shape():
     return g.value, b.value, c.value, s.value
 
 
-def time_steps(prob, iters=50, flush_l2=False, block=None, chunks=None):
+def set_form(form=0, warps_per_cta=0):
+    """Which kernel runs the step: 0 the library's choice, 1 barrier-phased CTA per slice, 2 / 3 marching warp per slice /
+    per two slices (reference sizes only).  Results do not depend on it."""
+    _check(lib().mpdata_set_form(form, warps_per_cta))
+
+
+def time_steps(prob, iters=50, flush_l2=False, block=None, chunks=None, form=None, warps_per_cta=0):
     """Device-resident timing of one step at prob's sizes: mean kernel time in ms (CUDA events).
-    block / chunks: None leaves the library's setting, 0 = automatic."""
+    block / chunks / form: None leaves the library's setting, 0 = automatic."""
     L = lib()
+    if form is not None:
+        _check(L.mpdata_set_form(form, warps_per_cta))
     if block is not None:
         _check(L.mpdata_set_block(block))
     if chunks is not None:

@@ -54,6 +54,12 @@ int mpdata_set_block(int threads);
  * default: floor(SMs / nslices) while there are fewer slices than SMs, 1 otherwise, more when a whole slice does not
  * fit shared memory -- results do not depend on it */
 int mpdata_set_chunks(int chunks);
+/* Which kernel runs the step (results do not depend on it): 0 = chosen by the library, 1 = a CTA per slice (or level range)
+ * with the seven phases separated by barriers, 2 = a warp per slice marching through the levels without any CTA-wide
+ * barrier, 3 = the same with two slices per warp (2 and 3 are compiled for the reference sizes nx=32, nz=58 only:
+ * mpdata_init fails for other sizes while one of them is selected).
+ * warps_per_cta: for forms 2 and 3, 0 = the library's choice, else 1..12 (form 3: at most 6 are used). */
+int mpdata_set_form(int form, int warps_per_cta);
 /* the launch shape in use after mpdata_init (any pointer may be NULL) */
 int mpdata_get_launch(int *grid, int *block, int *chunks, long long *smem_bytes);
 /* bytes of shared memory a whole slice (chunks = 1) needs at these sizes */

@@ -23,5 +23,20 @@ int main() {
         printf("chunks %d rc %d f[100]=%g\n", chunks, rc, f[100]);
         worst |= rc;
     }
+#ifndef MPDATA_EMUL_NO_MARCH
+    {   // the marching form (mpdata_march.cuh): lanes are host threads, __syncwarp a barrier of the warp's 32
+        const int ns = 4, nx = 7, nz = 12, nzm = nz - 1;
+        std::vector<double> f((size_t)ns * (nx + 6) * nzm), u((size_t)ns * (nx + 5) * nzm), w((size_t)ns * (nx + 4) * nz), rho(ns * nzm), rhow(ns * nz), adz(ns * nzm), flux(ns * nz);
+        for (auto *v : {&f, &u, &w, &rho, &rhow, &adz, &flux}) for (auto &x : *v) x = U(g);
+        for (auto &x : u) x -= 0.5;
+        for (auto &x : w) x -= 0.5;
+        for (int spw : {1, 2}) {  // slices per warp
+            std::vector<double> fc = f, fl = flux;
+            int rc = mpdata_emul_march_step(2, 64, spw, ns, nx, nz, fc.data(), u.data(), w.data(), rho.data(), rhow.data(), adz.data(), fl.data());
+            printf("march%d rc %d f[100]=%g\n", spw, rc, fc[100]);
+            worst |= rc;
+        }
+    }
+#endif
     return worst;
 }

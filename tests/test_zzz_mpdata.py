@@ -46,6 +46,8 @@ def emul():
     E = C.CDLL(os.path.join(ROOT, "tests", "driver", "libmpdata_emul.so"))
     E.mpdata_emul_step.argtypes = [C.c_int] * 6 + [C.c_void_p] * 7
     E.mpdata_emul_step.restype = C.c_int
+    E.mpdata_emul_march_step.argtypes = [C.c_int] * 6 + [C.c_void_p] * 7
+    E.mpdata_emul_march_step.restype = C.c_int
     return E
 
 
@@ -263,6 +265,46 @@ def test_device_source_generic_instantiation_at_the_reference_sizes(mpdata, mpo,
         emul.mpdata_emul_set_generic(0)
 
 
+MARCH_CASES = [  # (slices, nx, nz, signed velocities, threads per CTA, CTAs): sizes the emulation instantiates
+    (3, 5, 8, True, 32, 1), (5, 5, 8, True, 64, 2), (4, 7, 12, False, 96, 1), (9, 7, 12, True, 64, 2), (5, 1, 3, True, 64, 1),
+    (3, 40, 6, True, 32, 5), (6, 32, 58, True, 128, 1), (7, 32, 58, False, 96, 2), (14, 32, 58, True, 384, 1),
+]
+
+
+@pytest.mark.parametrize("spw", [1, 2])
+@pytest.mark.parametrize("ns,nx,nz,signed,block,grid", MARCH_CASES)
+def test_marching_form_on_host_bit_identical_to_oracle(mpdata, mpo, emul, ns, nx, nz, signed, block, grid, spw):
+    """mpdata_march.cuh (a warp per slice marching through the levels three at a time, rings of 8 rows, no CTA-wide barrier)
+    compiled for the host, lanes as threads and __syncwarp as a barrier of the warp: the oracle's bits, for the reference
+    plane, the smallest admissible one (nx 1, nz 3: two levels, fewer than one step), a level count that is not a multiple
+    of three, a plane wider than a warp round, warps that walk several slices and warps that get none; with one slice per
+    warp and with two (odd slice counts: the last warp's second slice does not exist).  Shared memory starts as NaN, so a
+    ring slot read before it is written would poison the output."""
+    P = mpdata.TestAdvect(ns, nx, nz).init(seed=11, signed_velocity=signed)
+    f, fl = _run_oracle(mpo, P)
+    fe, fle = P.f.copy(order="F"), P.flux.copy(order="F")
+    if block * spw * 8 * (7 * nx + 34) * 8 // 32 > 227 * 1024:
+        block = 192  # two sets of rings per warp: fewer warps fit the emulation's 227 KB
+    assert emul.mpdata_emul_march_step(grid, block, spw, ns, nx, nz, *[a.ctypes.data for a in (fe, P.u, P.w, P.rho, P.rhow, P.adz, fle)]) == 0
+    assert np.array_equal(fe, f) and np.array_equal(fle, fl)
+    assert np.array_equal(fle.reshape(-1, order="F")[-ns:], P.flux.reshape(-1, order="F")[-ns:])  # flux(:, nz) untouched (A:482)
+
+
+def test_div_ratio_is_the_ieee_quotient_for_every_input(emul):
+    """div_ratio (zero numerators divide 1 instead and take the zero, to stay off the slow path of CUDA's division) returns
+    the bits of num / den for ordinary values, both zeros, denormals, infinities, NaN and non-positive denominators."""
+    emul.mpdata_emul_div_ratio.argtypes = [C.c_double, C.c_double]
+    emul.mpdata_emul_div_ratio.restype = C.c_double
+    rng = np.random.default_rng(3)
+    special = [0.0, -0.0, 5e-324, -5e-324, 2.2250738585072014e-308, 1.0, -1.0, 1e-10, 1.7976931348623157e308, np.inf, -np.inf, np.nan]
+    vals = special + list(rng.standard_normal(20)) + list(rng.random(20) * 1e-300)
+    with np.errstate(all="ignore"):
+        for n in vals:
+            for d in vals:
+                got, want = np.float64(emul.mpdata_emul_div_ratio(n, d)), np.float64(n) / np.float64(d)
+                assert got.tobytes() == want.tobytes() or (np.isnan(got) and np.isnan(want)), (n, d, got, want)
+
+
 def test_device_source_on_host_full_block(mpdata, mpo, emul):
     """1024 threads per CTA (the launch default) at the reference sizes, CTAs walking several slices."""
     P = mpdata.TestAdvect().init(seed=100)
@@ -279,7 +321,7 @@ def test_device_source_on_host_full_block(mpdata, mpo, emul):
 def test_abi_exports_and_no_fallback(mpdata):
     L = mpdata.lib()
     names = mpdata.declared_symbols()
-    assert "mpdata_advect_scalar2D" in names and len(names) == 13
+    assert "mpdata_advect_scalar2D" in names and "mpdata_set_form" in names and len(names) == 14
     for n in names:
         assert hasattr(L, n), n
     # shared-memory budget at the reference sizes: one slice = 7 planes + columns
@@ -348,6 +390,38 @@ def test_gpu_result_independent_of_chunk_count(mpdata, mpo, chunks):
     finally:
         L.mpdata_set_chunks(0)
     assert np.array_equal(P.f, f) and np.array_equal(P.flux, fl)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("form", [2, 3])
+@pytest.mark.parametrize("ns,warps", [(48, 0), (5, 12), (1001, 0), (1000, 4), (2501, 7), (4736, 6)])
+def test_gpu_marching_form_bit_identical_to_oracle(mpdata, mpo, ns, warps, form):
+    """The marching kernels (mpdata_march.cuh: a warp per slice -- form 2 -- or per two slices -- form 3 --, no CTA-wide
+    barrier) give the oracle's bits whatever the number of warps per CTA (odd slice counts: form 3's last warp has one
+    slice); one launch per step; only the reference plane sizes are compiled."""
+    L = mpdata.lib()
+    P = mpdata.TestAdvect(ns, 32, 58).init(seed=100 + ns, signed_velocity=True)
+    f, fl = _run_oracle(mpo, P)
+    assert L.mpdata_finalize() == 0
+    try:
+        mpdata.set_form(form, warps)
+        n0 = L.mpdata_launch_count()
+        P.advect_scalar2D()
+        assert L.mpdata_launch_count() == n0 + 1
+        grid, block, chunks, smem = mpdata.launch_shape()
+        cap = 12 // (form - 1)
+        assert block == 32 * min(warps or cap, cap) and chunks == 1 and smem == (block // 32) * (form - 1) * 8 * (7 * 32 + 34) * 8 and grid >= 1
+        assert np.array_equal(P.f, f) and np.array_equal(P.flux, fl)
+        # a second step from the advanced field (the two device buffers have swapped roles)
+        f2, fl2 = f.copy(order="F"), fl.copy(order="F")
+        mpo.advect_scalar2D_cpu(ns, 32, 58, f2, P.u, P.w, P.rho, P.rhow, P.adz, fl2)
+        P.advect_scalar2D()
+        assert np.array_equal(P.f, f2) and np.array_equal(P.flux, fl2)
+        # other plane sizes are refused loudly while the marching form is selected
+        assert L.mpdata_init(8, 16, 12) == 2 and b"marching form" in L.mpdata_last_error()
+    finally:
+        mpdata.set_form(0, 0)
+    assert L.mpdata_init(8, 16, 12) == 0
 
 
 @pytest.mark.gpu
@@ -590,13 +664,15 @@ def test_gpu_driver_prints_the_reference_lines(mpdata, sizes):
 # ------------------------------------------------------------------- race check of the barrier-phased kernel
 
 
-def _tsan_run(tmp_path, emul_source=None, tag="real"):
+def _tsan_run(tmp_path, emul_source=None, tag="real", defines=()):
     drv = os.path.join(ROOT, "tests", "driver")
     exe = str(tmp_path / f"mpdata_tsan_{tag}")
     cmd = ["/usr/bin/g++", "-O1", "-g", "-fsanitize=thread", "-ffp-contract=off", "-std=c++20", "-pthread", "-I" + drv, "-o", exe,
            os.path.join(drv, "mpdata_tsan.cpp")]
     if emul_source:
         cmd.insert(1, f'-DMPDATA_EMUL_SOURCE="{emul_source}"')
+    for d in defines:
+        cmd.insert(1, "-D" + d)
     b = subprocess.run(cmd, capture_output=True, text=True)
     if b.returncode != 0:
         pytest.skip("ThreadSanitizer build not available here: " + b.stderr[-200:])
@@ -609,7 +685,7 @@ def test_device_source_has_no_race_between_phases_under_tsan(tmp_path):
     as shipped is clean (chunks 1 and 3), and the same kernel with ONE barrier removed is reported -- so the check
     would see a missing __syncthreads."""
     rc, out = _tsan_run(tmp_path)
-    assert rc == 0 and "chunks 1 rc 0" in out and "chunks 3 rc 0" in out
+    assert rc == 0 and "chunks 1 rc 0" in out and "chunks 3 rc 0" in out and "march1 rc 0" in out and "march2 rc 0" in out
     assert "ThreadSanitizer" not in out, out[-800:]
     # negative control
     src = open(os.path.join(ROOT, "codesign-kernels_b200", "csrc", "mpdata_kernels.cuh")).read()
@@ -620,5 +696,17 @@ def test_device_source_has_no_race_between_phases_under_tsan(tmp_path):
     inc = '#include "../../codesign-kernels_b200/csrc/mpdata_kernels.cuh"'
     assert inc in emu
     (tmp_path / "mpdata_emul_nobarrier.cpp").write_text(emu.replace(inc, f'#include "{tmp_path}/mpdata_kernels_nobarrier.cuh"'))
-    rc, out = _tsan_run(tmp_path, str(tmp_path / "mpdata_emul_nobarrier.cpp"), tag="nobarrier")
+    rc, out = _tsan_run(tmp_path, str(tmp_path / "mpdata_emul_nobarrier.cpp"), tag="nobarrier", defines=("MPDATA_EMUL_NO_MARCH",))
+    assert "ThreadSanitizer: data race" in out
+    # negative control of the marching form: the same with the __syncwarp between its stages S2 and S3 removed
+    msrc = open(os.path.join(ROOT, "codesign-kernels_b200", "csrc", "mpdata_march.cuh")).read()
+    at = msrc.index("MPD_MARCH_STAGE(march_s3,")
+    cut = msrc.rfind("__syncwarp();", 0, at)
+    minc = '#include "../../codesign-kernels_b200/csrc/mpdata_march.cuh"'
+    assert minc in emu and '#include "mpdata_kernels.cuh"' in msrc
+    kinc = f'#include "{os.path.join(ROOT, "codesign-kernels_b200", "csrc", "mpdata_kernels.cuh")}"'
+    msrc = msrc[:cut] + "/* __syncwarp removed */" + msrc[cut + len("__syncwarp();"):]
+    (tmp_path / "mpdata_march_nosync.cuh").write_text(msrc.replace('#include "mpdata_kernels.cuh"', kinc))
+    (tmp_path / "mpdata_emul_nosync.cpp").write_text(emu.replace(inc, kinc).replace(minc, f'#include "{tmp_path}/mpdata_march_nosync.cuh"'))
+    rc, out = _tsan_run(tmp_path, str(tmp_path / "mpdata_emul_nosync.cpp"), tag="nosync")
     assert "ThreadSanitizer: data race" in out
