@@ -25,4 +25,6 @@ from .binding import (  # noqa: F401
     cubed_sphere_gdof,
     partition,
     Plan,
+    NOALLOC_MAX_NELEMD,
+    biharmonic_wk_scalar_noalloc,
 )

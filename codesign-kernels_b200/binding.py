@@ -58,6 +58,7 @@ def lib():
         "bwk_biharmonic_wk_scalar": [p, p, p, p, C.POINTER(i32), C.POINTER(i32)],
         "bwk_biharmonic_wk_scalar_nets": [p, p, p, C.POINTER(i32), C.POINTER(i32)],
         "bwk_biharmonic_wk_scalar_full": [p, p, p],
+        "bwk_biharmonic_wk_scalar_noalloc": [p, p, p, i32, i32, i32, C.c_uint64],
         "bwk_host_alloc": [C.POINTER(p), C.c_uint64],
         "bwk_host_free": [p],
         "bwk_host_register": [p, C.c_uint64],
@@ -133,6 +134,17 @@ def _ck(rc):
 
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+NOALLOC_MAX_NELEMD = 8192  # BWK_NOALLOC_MAX_NELEMD, include/bwk_b200.h
+
+
+def biharmonic_wk_scalar_noalloc(d_elem, d_qtens, deriv, nelemd, nlev, qsize, stream=0):
+    """Allocation-free single Laplacian on DEVICE pointers (integers); deriv is a host DERIVATIVE_DTYPE array.
+
+    No counterpart in the reference (added for callers that cannot cudaMalloc); needs no bwk_init; asynchronous on `stream`.
+    """
+    _ck(lib().bwk_biharmonic_wk_scalar_noalloc(C.c_void_p(d_elem), C.c_void_p(d_qtens), _ptr(deriv), nelemd, nlev, qsize, stream))
 
 
 def cubed_sphere_gdof(ne):

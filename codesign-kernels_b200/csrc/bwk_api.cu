@@ -1646,3 +1646,64 @@ int bwk_plan_apply_host(const bwk_plan_t *h, const double *field, double *out)
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------ allocation-free single Laplacian
+// The sweep reads the folded metric ([nelemd][64] doubles, written by fold_metric_kernel from elem) as scratch.  Here that
+// scratch is a file-scope device array instead of a cudaMalloc'd buffer: every GPU that loads the library holds it until exit.
+// Its name below is only the host-side stand-in of the array; the address a kernel can use comes from cudaGetSymbolAddress,
+// asked once per device with that device current.
+static __device__ __align__(256) double g_noalloc_metric[(size_t)BWK_NOALLOC_MAX_NELEMD * METRIC_DOUBLES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+double *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+int noalloc_scratch(double **ptr)
+{
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail("device ordinal %d outside 0..%d", dev, NOALLOC_MAX_DEVICES - 1);
+    if (!g_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_metric));
+        if (!p) return fail("cudaGetSymbolAddress returned a null address for the scratch array");
+        g_noalloc_ptr[dev] = static_cast<double *>(p);
+    }
+    *ptr = g_noalloc_ptr[dev];
+    return 0;
+}
+} // namespace
+
+extern "C" int bwk_biharmonic_wk_scalar_noalloc(const bwk_element_t *d_elem, double *d_qtens, const bwk_derivative_t *deriv, int nelemd, int nlev,
+                                                int qsize, uint64_t stream)
+{
+    if (nelemd < 1 || nlev < 1 || qsize < 1) return fail("bad sizes nelemd=%d nlev=%d qsize=%d", nelemd, nlev, qsize);
+    if (nelemd > BWK_NOALLOC_MAX_NELEMD)
+        return fail("bwk_biharmonic_wk_scalar_noalloc: nelemd=%d exceeds BWK_NOALLOC_MAX_NELEMD=%d (the static scratch array holds the folded "
+                    "metric of that many elements); use bwk_init/bwk_upload/bwk_run for larger problems",
+                    nelemd, BWK_NOALLOC_MAX_NELEMD);
+    if ((int64_t)nlev * qsize > 0x7fffffff / 64) return fail("nlev*qsize too large");
+    if (!d_elem || !d_qtens || !deriv) return fail("bwk_biharmonic_wk_scalar_noalloc: null pointer argument");
+    if ((reinterpret_cast<uintptr_t>(d_qtens) & 127) != 0) return fail("bwk_biharmonic_wk_scalar_noalloc: d_qtens must be 128-byte aligned");
+    double *scratch = nullptr;
+    if (noalloc_scratch(&scratch)) return 1;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(static_cast<uintptr_t>(stream));
+    const int kq = nlev * qsize;
+    SweepParams p{};
+    if (make_slab_map(&p.map_q, d_qtens, kq, nelemd)) return 1;
+    p.map_tmp = p.map_q;
+    p.map_out = p.map_q;
+    p.metric = scratch;
+    p.kq = kq;
+    const SweepGeometry geo = choose_geometry(kq, nelemd, MODE_LAPLACE);
+    p.tiles_per_unit = geo.tiles_per_unit;
+    p.units = geo.units;
+    p.elem_first = 0;
+    p.elem_count = nelemd;
+    CK(set_dvv(&deriv->Dvv[0][0], st));
+    // every call rewrites the nelemd*64 doubles it reads: nothing in the array has to start at zero, and what an earlier
+    // call left beyond nelemd*64 is never read
+    CK(launch_fold_metric(reinterpret_cast<const double *>(d_elem), scratch, nelemd, st));
+    CK(launch_sweep(MODE_LAPLACE, p, st));
+    return 0;
+}

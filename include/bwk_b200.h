@@ -80,6 +80,22 @@ int bwk_host_free(void *ptr);
 int bwk_host_register(void *ptr, uint64_t bytes);
 int bwk_host_unregister(void *ptr);
 
+/* Allocation-free form of the single Laplacian above, for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * Needs no bwk_init and touches no context state.  d_elem (nelemd element_t records) and d_qtens
+ * (np,np,nlev,qsize,nelemd; 128-byte aligned; updated in place as F90:186-200) are DEVICE pointers of the current device,
+ * deriv is a HOST pointer (64 bytes, staged into the library's __constant__ Dvv as bwk_upload does), stream is a
+ * cudaStream_t as an integer (0 = the default stream); the two kernels are queued on it and the call returns without
+ * synchronising.  The folded per-point metric, which bwk_init keeps in a cudaMalloc'd buffer, lives here in a file-scope
+ * static __device__ array of BWK_NOALLOC_MAX_NELEMD * 64 doubles (4 MiB, held by every GPU that loads the library until the
+ * process exits); nelemd beyond that is rejected with an error.  The call makes no cudaMalloc / cudaFree and calls no
+ * allocating library routine.  All calls share the one array and each rewrites the part it reads, so nothing has to be
+ * cleared between calls, but two calls that overlap on the GPU (different streams, or a graph replayed concurrently) race
+ * on it, and so does a concurrent bwk_upload of another Dvv: serialise them. */
+#define BWK_NOALLOC_MAX_NELEMD 8192
+int bwk_biharmonic_wk_scalar_noalloc(const bwk_element_t *d_elem, double *d_qtens, const bwk_derivative_t *deriv,
+                                     int nelemd, int nlev, int qsize, uint64_t stream);
+
 const char *bwk_last_error(void);
 /* kernel variant for bwk_run: 0 = TMA-pipelined (default), 1 = plain loads (kept for ncu A/B) */
 int bwk_set_variant(int variant);
