@@ -68,12 +68,39 @@ int release() {
 // points of the widest plane per thread.  Results do not depend on either.
 // The marching forms (mpdata_march.cuh): a warp per slice (form 2) or per pair of slices (form 3), `warps` of them per CTA,
 // as many CTAs per SM as their rings allow.
+}  // namespace
+
+// Which form is faster at the reference plane sizes (32 x 58), from the measured behaviour of the two kernels on a B200
+// (profiles/r3n_*, r3o_*, r3p_*; times in ms):
+//   barrier-phased, two half-slice CTAs per SM: linear in the slice count, 0.1325 us per slice on 148 SMs
+//     (1,184 slices 0.159, 2,368 0.320, 4,736 0.627, 9,472 1.231);
+//   marching, 6 warps per CTA, two CTAs per SM: a warp needs ~0.197 ms per slice whatever its neighbours do, so the time goes
+//     in waves of 12 slices per SM (1,776 slices on 148 SMs): 1,776 slices 0.200, 3,552 0.393, 7,104 0.786, and a partial last
+//     wave costs 0.12 (a third full), 0.16 (0.46) to 0.19 (two thirds): 2,368 0.328, 2,600 0.359, 4,736 0.584, 9,472 1.096,
+//     1,184 alone 0.193, 1,600 alone 0.196.
+// Host only; exported so that the CPU tests can check the choice against those measurements.
+extern "C" int mpdata_march_wins(long long nslices, int sms) {
+    if (nslices < 1 || sms < 1) return 0;
+    const double wave = 12.0 * sms;                       // slices in flight: 2 CTAs x 6 warps per SM
+    const double scale = 148.0 / sms;                     // the per-slice rate of the phased kernel was measured on 148 SMs
+    const double phased = 0.1325e-3 * scale * (double)nslices;
+    const long long full = (long long)((double)nslices / wave);
+    const double r = ((double)nslices - (double)full * wave) / wave;  // fill of the last wave, 0..1
+    double last = 0.0;
+    if (r > 0.0)
+        last = r <= 1.0 / 3 ? 0.08 + 0.04 * (3 * r) : r <= 0.5 ? 0.12 + 0.05 * (6 * r - 2) : r <= 2.0 / 3 ? 0.17 + 0.02 * (6 * r - 3) : 0.19 + 0.007 * (3 * r - 2);
+    const double march = 0.197 * (double)full + last;
+    return march < 0.97 * phased ? 1 : 0;  // within the model's error (2,600 slices: 0.359 against 0.350 ms) the phased kernel stays
+}
+
+namespace {
+
 template <int NS2>
-int plan_march() {
+int plan_march(int default_warps = 0) {
     auto kernel = mpd_dev::advect_march_kernel<32, 58, NS2>;
     const size_t per_warp = NS2 * mpd_dev::march_warp_doubles(g.nx) * sizeof(double);
     const int cap = 12 / NS2;  // the kernel's __launch_bounds__: 12 warps of 162 registers / 6 warps of up to 255
-    int warps = g.march_warps > 0 ? g.march_warps : cap;
+    int warps = g.march_warps > 0 ? g.march_warps : default_warps > 0 ? default_warps : cap;
     if (warps > cap) warps = cap;
     if ((size_t)warps * per_warp > (size_t)g.smem_optin) warps = (int)((size_t)g.smem_optin / per_warp);
     if (warps < 1) return fail(3, "the rings of one warp need %zu B of shared memory (nx=%d), the SM has %d", per_warp, g.nx, g.smem_optin);
@@ -98,6 +125,13 @@ int plan_launch() {
         if (form >= 2 && !ref_sizes) return fail(2, "the marching form is compiled for nx=32, nz=58 only (got nx=%d, nz=%d)", g.nx, g.nz);
         if (form == 2) return plan_march<1>();
         if (form == 3) return plan_march<2>();
+        // Automatic choice (form 0, no launch-shape override) at the reference plane sizes: the marching kernel with 6 warps
+        // per CTA where march_wins() expects it to be the faster one.  Both forms give the oracle's bits.
+        if (form == 0 && ref_sizes && g.chunks <= 0 && g.block <= 0 && !g.force_generic) {
+            int on = 1;
+            if (const char *env = getenv("MPDATA_B200_AUTO_MARCH")) on = atoi(env);
+            if (on && mpdata_march_wins(g.ns, g.sms)) return plan_march<1>(6);
+        }
         g.use_form = 1;
     }
     int chunks = g.chunks;

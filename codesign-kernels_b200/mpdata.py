@@ -57,6 +57,7 @@ def lib():
     L.mpdata_set_block.argtypes, L.mpdata_set_block.restype = [i32], i32
     L.mpdata_set_chunks.argtypes, L.mpdata_set_chunks.restype = [i32], i32
     L.mpdata_set_form.argtypes, L.mpdata_set_form.restype = [i32, i32], i32
+    L.mpdata_march_wins.argtypes, L.mpdata_march_wins.restype = [C.c_longlong, i32], i32
     L.mpdata_get_launch.argtypes, L.mpdata_get_launch.restype = [C.POINTER(i32)] * 3 + [C.POINTER(C.c_longlong)], i32
     L.mpdata_slice_smem_bytes.argtypes, L.mpdata_slice_smem_bytes.restype = [i32, i32], C.c_longlong
     L.mpdata_launch_count.argtypes, L.mpdata_launch_count.restype = [], C.c_longlong

@@ -60,6 +60,10 @@ int mpdata_set_chunks(int chunks);
  * mpdata_init fails for other sizes while one of them is selected).
  * warps_per_cta: for forms 2 and 3, 0 = the library's choice, else 1..12 (form 3: at most 6 are used). */
 int mpdata_set_form(int form, int warps_per_cta);
+/* The automatic choice (form 0) at the reference plane sizes: 1 if the marching kernel (form 2, 6 warps per CTA) is expected
+ * to be faster than the barrier-phased one at `nslices` slices on a GPU of `sms` SMs, from the two kernels' measured
+ * behaviour on a B200 (csrc/mpdata_b200.cu).  Host only, no GPU needed; MPDATA_B200_AUTO_MARCH=0 switches the choice off. */
+int mpdata_march_wins(long long nslices, int sms);
 /* the launch shape in use after mpdata_init (any pointer may be NULL) */
 int mpdata_get_launch(int *grid, int *block, int *chunks, long long *smem_bytes);
 /* bytes of shared memory a whole slice (chunks = 1) needs at these sizes */

@@ -318,10 +318,38 @@ def test_device_source_on_host_full_block(mpdata, mpo, emul):
     assert np.array_equal(fe, f) and np.array_equal(fle, fl)
 
 
+def test_automatic_form_choice_follows_the_measurements(mpdata):
+    """mpdata_march_wins (host only) against what was measured on a B200, profiles/r3n_*, r3o_*, r3p_* (ms: barrier-phased, marching
+    with 6 warps per CTA): the automatic choice must be the faster form wherever the two differ by more than 3 %."""
+    import glob
+    import json
+
+    L = mpdata.lib()
+    seen = 0
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r3[nop]_mpdata_shapes_*.json"))):
+        d = json.load(open(path))
+        sh = d["shapes"]
+        phased = sh.get("2x512", sh.get("0x0") if path.split(os.sep)[-1].startswith("r3n") else None)
+        if not phased or "m6" not in sh:
+            continue
+        a, b = phased["ms_per_step"], sh["m6"]["ms_per_step"]
+        assert phased["bitwise_equal_to_oracle"] and sh["m6"]["bitwise_equal_to_oracle"]
+        if abs(a - b) > 0.03 * min(a, b):
+            assert L.mpdata_march_wins(d["nslices"], 148) == int(b < a), (d["nslices"], a, b)
+            seen += 1
+    assert seen >= 7
+    assert L.mpdata_march_wins(2600, 148) == 0  # measured 0.359 against 0.350 ms: inside the margin, the phased kernel stays
+    # small slice counts stay with the barrier-phased kernel (48 = the reference's own size, A:6-8), bad arguments choose nothing
+    assert [L.mpdata_march_wins(n, 148) for n in (1, 48, 148, 592, 1184)] == [0] * 5
+    assert L.mpdata_march_wins(0, 148) == 0 and L.mpdata_march_wins(1000, 0) == 0
+    # whole waves of 12 slices per SM are where the marching kernel is at its best, on any SM count
+    assert all(L.mpdata_march_wins(12 * sms * w, sms) == 1 for sms in (132, 148, 160) for w in (1, 2, 5, 40))
+
+
 def test_abi_exports_and_no_fallback(mpdata):
     L = mpdata.lib()
     names = mpdata.declared_symbols()
-    assert "mpdata_advect_scalar2D" in names and "mpdata_set_form" in names and len(names) == 14
+    assert "mpdata_advect_scalar2D" in names and "mpdata_set_form" in names and len(names) == 15
     for n in names:
         assert hasattr(L, n), n
     # shared-memory budget at the reference sizes: one slice = 7 planes + columns
