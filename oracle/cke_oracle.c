@@ -3,11 +3,13 @@
  * loop of the reference mini-app nested_loops/ (cited as nested.F90:<line>, cke_impl1.cpp:<line>).
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may link or call this.
  *
- * PARITY UNPINNED: the reference stores no outputs for this kernel (no results/ directory, its
- * inputs come from the compiler's random_number).  What it does hold is its own acceptance
- * test -- every loop form must agree with the "original CPU" form to errTol = 1e-10 relative
- * (nested_vars.F90:33, nested.F90:267-279) -- and tests/test_zz_nested.py reproduces that test
- * between the three forms below, plus an independent numpy restatement.
+ * PARITY: pinned on the reference compiled here.  The reference stores no outputs for this kernel (no
+ * results/ directory, its inputs come from the compiler's random_number), but its plain-C++ form
+ * nested_loops/nested_yakl_c.cpp:142-306 compiles in this image: `make -C oracle ref` builds it where it
+ * lies into oracle/_ref/libnested_yakl_ref.so (oracle/ref_yakl_py.py) and tests/test_zz_nested.py requires
+ * the forms below to equal it bit for bit.  The reference's own acceptance test -- every loop form must
+ * agree with the "original CPU" form to errTol = 1e-10 relative (nested_vars.F90:33, nested.F90:267-279) --
+ * is reproduced there too, plus an independent numpy restatement.
  *
  * Arrays keep the Fortran layouts: x(nvldim, n) column-major == C x[n][nvldim] (level fastest),
  * advCellsForEdge(nAdv, nEdges) == C [nEdges][nAdv]; cell and level indices are 1-based as in

@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- ctypes view of oracle/cke_oracle.c (the nested_loops loop forms).
 
 Only tests/, __graft_entry__.smoke() and bench.py's / profiles' cpu_baseline legs may import this
-module; the product package never does.  PARITY UNPINNED (see the header of cke_oracle.c).
+module; the product package never does.  Pinned on the reference's own C++ compiled here (oracle/ref_yakl_py.py).
 """
 import ctypes as C
 import os

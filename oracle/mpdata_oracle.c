@@ -7,10 +7,15 @@
  * the Fortran; build with -ffp-contract=off.  Only tests/, __graft_entry__ and bench/profile CPU
  * legs may load this; the product (libmpdata_b200.so) never does.
  *
- * PARITY UNPINNED: the reference stores no outputs for this kernel and draws its inputs from the
- * compiler's random_number (A:645-665); its own check is "relative L1 error of f and flux against
- * the CPU subroutine" (A:679-683): exactly 0 for gnu.7.1.0, up to 1e-4 for other builds under results/
- * (tests/golden/mpdata_results.json).
+ * PARITY: pinned on the reference's own source, mechanically translated.  The reference stores no outputs
+ * for this kernel and draws its inputs from the compiler's random_number (A:645-665); its own check is
+ * "relative L1 error of f and flux against the CPU subroutine" (A:679-683): exactly 0 for gnu.7.1.0, up to
+ * 1e-4 for other builds under results/ (tests/golden/mpdata_results.json).  There is no Fortran compiler in
+ * this image, so `make -C oracle ref` translates A:477-642 statement by statement to C (oracle/f90_to_c.py,
+ * a Fortran-subset translator that refuses what it does not know) and compiles it into oracle/_ref;
+ * tests/test_mpdata_ref.py requires THIS file to equal that build bit for bit (7 shapes, both velocity
+ * signs) and reproduces the reference's acceptance test on the translated OpenACC forms (exactly 0).
+ * Not the output of a Fortran compiler -- see oracle/ref_mpdata_py.py for what the claim is.
  *
  * Array shapes (Fortran, column-major; A:14-36), nzm = nz-1:
  *   f   (nslices, -2:nx+3, 1, nzm)    u (nslices, -1:nx+3, 1, nzm)    w (nslices, -1:nx+2, 1, nz)

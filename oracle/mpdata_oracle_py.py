@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- ctypes view of oracle/mpdata_oracle.c (advect_scalar2D_cpu restated).
 
 Only tests/, __graft_entry__ and bench / profiles cpu_baseline legs may import this module; the
-product package never does.  PARITY UNPINNED (see the header of mpdata_oracle.c).
+product package never does.  Pinned bit for bit on the reference's source translated to C (oracle/ref_mpdata_py.py).
 """
 import ctypes as C
 import os

@@ -52,8 +52,14 @@ def main():
         variants = {"chunks1_b1024": (1, 1024), "chunks1_b512": (1, 512), "chunks2": (2, 0), "chunks3": (3, 0), "chunks4": (4, 0)}
         by_shape = {name: mpdata.time_steps(P, iters=max(5, args.iters // 5), flush_l2=args.flush, block=b_, chunks=c_)
                     for name, (c_, b_) in variants.items()}
-        ms = mpdata.time_steps(P, iters=args.iters, flush_l2=args.flush, block=0, chunks=0)
+        try:  # the marching kernel (reference plane sizes only), 6 warps per CTA; then back to the automatic choice
+            by_shape["marching_6warps"] = mpdata.time_steps(P, iters=max(5, args.iters // 5), flush_l2=args.flush, block=0, chunks=0, form=2, warps_per_cta=6)
+        except Exception as e:
+            by_shape["marching_6warps"] = str(e)[:120]
+        ms = mpdata.time_steps(P, iters=args.iters, flush_l2=args.flush, block=0, chunks=0, form=0)
         shape = dict(zip(("grid", "block", "chunks", "smem_bytes"), mpdata.launch_shape()))
+        # which kernel the library chose: the marching form's shared memory is 8 ring rows x (7 nx + 34) doubles per warp
+        shape["form"] = "marching" if shape["chunks"] == 1 and shape["smem_bytes"] == (shape["block"] // 32) * 8 * (7 * nx + 34) * 8 else "barrier-phased"
         fo, flo = np.empty_like(P.f), P.flux.copy(order="F")
         assert mpdata.lib().mpdata_download(fo.ctypes.data, flo.ctypes.data) == 0
         pts = ns * nx * (nz - 1)
@@ -70,6 +76,18 @@ def main():
             s = time.perf_counter() - t0
             run["cpu_serial"] = {"s": s, "points_per_s": pts / s, "cores": 1, "kind": "port",
                                  "sample": "one step of advect_scalar2D_cpu (A:477-642), the reference's own timed region"}
+            try:  # the reference's own subroutine, translated from its Fortran to C and compiled (oracle/ref_mpdata_py.py)
+                import ref_mpdata_py as ref
+
+                if ref.available():
+                    f3, fl3 = P.f.copy(order="F"), P.flux.copy(order="F")
+                    t0 = time.perf_counter()
+                    ref.advect_scalar2D_cpu(ns, nx, nz, f3, P.u, P.w, P.rho, P.rhow, P.adz, fl3)
+                    s = time.perf_counter() - t0
+                    run["cpu_reference_translated"] = {"s": s, "points_per_s": pts / s, "cores": 1, "kind": "reference (Fortran translated to C by oracle/f90_to_c.py, gcc -O2)",
+                                                       "gpu_bitwise_equal": bool(np.array_equal(fo, f3) and np.array_equal(flo, fl3))}
+            except Exception as e:
+                run["cpu_reference_translated"] = {"error": str(e)[:120]}
         out["runs"].append(run)
     print(json.dumps(out))
 

@@ -9,6 +9,9 @@
 (2) A regression pin of the C oracle (NOT reference output): SHA-256 of f and flux after one step
     of oracle/mpdata_oracle.c on inputs from the integer LCG below (no numpy RNG, no libm), at the
     reference sizes.  It changes if anybody edits the oracle's arithmetic.
+(3) The same digest from the reference's own advect_scalar2D_cpu, mechanically translated to C from
+    the source under /root/reference (oracle/f90_to_c.py, `make -C oracle ref`): the two are equal,
+    which makes (2) a pin on the reference's arithmetic.
 """
 import glob
 import hashlib
@@ -62,6 +65,18 @@ def oracle_digest():
             "f_sum": float(f.sum()), "flux_sum_levels_1_nzm": float(fl[:, :-1].sum())}
 
 
+def translated_reference_digest():
+    """The same digest from the REFERENCE'S OWN advect_scalar2D_cpu (A:477-642), translated mechanically by
+    oracle/f90_to_c.py from the source under /root/reference and compiled here (oracle/ref_mpdata_py.py)."""
+    import ref_mpdata_py as ref
+
+    a = lcg_fields()
+    f, fl = a["f"].copy(order="F"), a["flux"].copy(order="F")
+    ref.advect_scalar2D_cpu(48, 32, 58, f, a["u"], a["w"], a["rho"], a["rhow"], a["adz"], fl)
+    return {"f_sha256": hashlib.sha256(f.tobytes(order="F")).hexdigest(), "flux_sha256": hashlib.sha256(fl.tobytes(order="F")).hexdigest(),
+            "f_sum": float(f.sum()), "flux_sum_levels_1_nzm": float(fl[:, :-1].sum())}
+
+
 def main():
     files = {}
     for path in sorted(glob.glob(os.path.join(REF, "advect.*"))):
@@ -87,7 +102,11 @@ def main():
                           "gpu_build": "advect.pgiacc.17.7",
                           "gpu_build_rel_l1_f": max(files["advect.pgiacc.17.7"]["rel_l1_f"]),
                           "gpu_build_rel_l1_flux": max(files["advect.pgiacc.17.7"]["rel_l1_flux"])},
-           "oracle_regression_pin": dict(oracle_digest(), note="NOT reference output: builder's C restatement on LCG inputs")}
+           "oracle_regression_pin": dict(oracle_digest(), note="NOT reference output: builder's C restatement on LCG inputs"),
+           "translated_reference_pin": dict(translated_reference_digest(),
+                                            note="output of the reference's own advect_scalar2D_cpu (A:477-642) on the same LCG inputs, the "
+                                                 "Fortran translated statement by statement by oracle/f90_to_c.py and compiled with gcc -O2 "
+                                                 "-ffp-contract=off (no Fortran compiler in the image); equal to the oracle's pin")}
     with open(os.path.join(ROOT, "tests", "golden", "mpdata_results.json"), "w") as fh:
         json.dump(out, fh, indent=1)
     print(json.dumps(out["acceptance"]), json.dumps(out["oracle_regression_pin"]))

@@ -2,8 +2,11 @@
 
 Reference: mmf-mpdata-tracer/advect_scalar2D_pushncols_openacc.F90 (cited as A:<line>).
 
-PARITY UNPINNED: the reference holds no outputs for this kernel (its inputs come from the compiler's
-random_number, A:645-665).  What it holds is its acceptance test -- relative L1 error of f and flux
+PARITY: the reference holds no outputs for this kernel (its inputs come from the compiler's random_number, A:645-665)
+and is Fortran, which this image cannot compile; the oracle is pinned bit for bit on the reference's own source
+translated statement by statement to C (oracle/f90_to_c.py -> oracle/_ref, tests/test_mpdata_ref.py), and
+test_gpu_bit_identical_to_the_translated_reference below compares the CUDA result with that build directly.
+What the reference does hold is its acceptance test -- relative L1 error of f and flux
 against advect_scalar2D_cpu (A:679-683): exactly 0 for gnu.7.1.0, up to 1e-4 for other CPU builds of the
 OpenACC-annotated forms (intel, pgi, gnu.4.9.3), 2.2e-16 / 8.2e-17 for the one GPU build (results/advect.pgiacc.17.7;
 all extracted into tests/golden/mpdata_results.json).  Here the CUDA path is required to
@@ -11,7 +14,7 @@ be BIT-IDENTICAL to the C restatement of advect_scalar2D_cpu, which is itself ch
 an independent numpy restatement written from the Fortran, and the device source is run on the host
 (tests/driver/mpdata_emul.cpp) to check indexing and phase ordering without a GPU.
 
-This file sorts last on purpose: its -m gpu tests are the newest in the suite and have not yet run on a B200.
+This file sorts late on purpose (it was the newest of the suite when written); tests/test_zzzz_no_alloc.py comes after it.
 """
 import ctypes as C
 import os
@@ -687,6 +690,28 @@ def test_gpu_driver_prints_the_reference_lines(mpdata, sizes):
     vals = {k.strip(): float(v) for k, v in vals.items()}
     assert vals["Relative L1 Error - f"] == 0.0 and vals["Relative L1 Error - flux"] == 0.0
     assert vals["CPU Timing"] > 0.0 and 0.0 < vals["B200 Timing"] < 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ns,form", [(48, 0), (1001, 0), (4736, 0), (300, 2)])
+def test_gpu_bit_identical_to_the_translated_reference(mpdata, ns, form):
+    """The CUDA step against the REFERENCE'S OWN advect_scalar2D_cpu (A:477-642) -- its Fortran translated statement by
+    statement to C (oracle/f90_to_c.py) and compiled, oracle/ref_mpdata_py.py -- with no hand-written oracle in between:
+    the barrier-phased kernel (48 and 1,001 slices), the automatic choice at 4,736 slices (the marching kernel) and the
+    marching kernel forced at 300."""
+    import ref_mpdata_py as ref
+
+    if not ref.available():
+        pytest.skip("oracle/_ref/libmpdata_f90ref.so did not travel and /root/reference is not here to build it")
+    P = mpdata.TestAdvect(ns, 32, 58).init(seed=300 + ns, signed_velocity=True)
+    want = [a.copy(order="F") for a in P.arrays()]
+    ref.advect_scalar2D_cpu(ns, 32, 58, *want)
+    try:
+        mpdata.set_form(form, 0)
+        P.advect_scalar2D()
+    finally:
+        mpdata.set_form(0, 0)
+    assert np.array_equal(P.f, want[0]) and np.array_equal(P.flux, want[6])
 
 
 # ------------------------------------------------------------------- race check of the barrier-phased kernel
