@@ -183,6 +183,19 @@ def cpu_baseline(ne_small, nlev, qsize, reps, want_serial=False, ne_full=None, f
         pr.reinit()
         out["laplace_only_serial_value"] = pr.updates / pr.step_laplace(omp=False)
         out["serial_note"] = "1 core, no OpenMP: the reference's own CPU path is serial (no !$omp in atmosphere/)"
+        try:  # the reference's own CPU module (F90:100-202), its Fortran translated statement by statement to C and compiled here
+            import ref_atm_py
+
+            if ref_atm_py.available():
+                pr.reinit()
+                t = time.perf_counter()
+                ref_atm_py.biharmonic_wk_scalar_cpu(pr.elem, pr.q, pr.dvv)
+                dt = time.perf_counter() - t
+                out["laplace_only_reference_translated"] = {
+                    "value": pr.updates / dt, "unit": UNIT, "cores": 1, "sample": pr.label(),
+                    "kind": "reference (module biharmonic_wk_scalar_cpu translated to C by oracle/f90_to_c.py, gcc -O2 -ffp-contract=off; reproduces the published L2 norms)"}
+        except Exception as ex:
+            out["laplace_only_reference_translated"] = {"error": str(ex)[:160]}
     small_rate = out["value"]
     del pr
     if ne_full and ne_full != ne_small:

@@ -3,16 +3,19 @@
  *
  * Plain-C CPU restatement of the hot path in the reference file
  *   atmosphere/biharmonic_wk_kernel.F90            (cited below as F90:<line>)
- * The reference is Fortran and no Fortran compiler exists in this image, so the
- * reference itself cannot be compiled (oracle/_ref is therefore never built);
- * this restatement is pinned instead against the two known-answer scalars the
- * reference publishes in atmosphere/results/ (see tests/golden/kat.json).
+ * The reference is Fortran and no Fortran compiler exists in this image.  This
+ * restatement is pinned twice: against the two known-answer scalars the reference
+ * publishes in atmosphere/results/ (tests/golden/kat.json, tests/test_oracle_kat.py),
+ * and BIT FOR BIT against the reference's own three modules translated mechanically
+ * from the Fortran to C and compiled here (oracle/f90_to_c.py -> oracle/_ref/libatm_f90ref.so,
+ * oracle/ref_atm_py.py, tests/test_zzy_atm_ref.py) -- a translation that itself
+ * reproduces those published scalars to all 17 digits.
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
  * reference legs may load this library.  The product (libbwk_b200.so) never does.
  *
  * Parity status:
- *   - single weak Laplacian (F90:100-202 and the GPU1/GPU2 orders):  PINNED by KAT-1/KAT-2.
+ *   - single weak Laplacian (F90:100-202 and the GPU1/GPU2 orders):  PINNED by KAT-1/KAT-2 and by the translated reference.
  *   - DSS + rspheremp + second Laplacian (upstream HOMME viscosity_base/edge_mod_base,
  *     not vendored under /root/reference, only the comment F90:518-519):  PARITY UNPINNED.
  *

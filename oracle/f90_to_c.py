@@ -25,6 +25,22 @@ Subset (enough for mmf-mpdata-tracer/advect_scalar2D_pushncols_openacc.F90, subr
   * --check-bounds (what gfortran -fcheck=bounds would abort on): a statement one of whose subscripts leaves the declared
     bounds is skipped and counted, <subroutine>_violations() reports the count and the first one (line, array, dimension)
 
+Unit mode (--module M --uses U1,U2 ENTRY): every routine of module M becomes a static C function and ENTRY is exported;
+enough for the three modules of atmosphere/biharmonic_wk_kernel.F90 (CPU lines 100-202, GPU1 209-362, GPU2 369-536):
+
+    python oracle/f90_to_c.py F.F90 biharmonic_wk_scalar --module biharmonic_wk_scalar_cpu --uses kernel_utils \
+           --runtime nlev,qsize --export atm_cpu_biharmonic_wk_scalar --out oracle/_ref/atm_f90_cpu.c
+
+  * the specification parts of the used modules: integer and real parameters (a real parameter keeps the precision of its
+    literal: `rrearth = 0.00000016666666666666` is float32-rounded, as in Fortran), initialised integer module variables,
+    derived types (-> C structs whose array components keep the column-major order; components by `%`)
+  * subroutines and functions with a `result(..)` that is an array (-> a trailing output pointer); `x = f(..)` evaluates into a
+    temporary and then copies, as Fortran does, so `q(:,:,k) = f(q(:,:,k))` is safe; `call` of the module's own subroutines
+  * actual arguments: whole arrays, whole components (`elem%Dinv`), contiguous leading sections (`qtens(:,:,k,q,ie)`), elements
+    and whole sections of derived-type arrays (`elem(ie)`, `elem(:)`), scalars by value; assumed-shape dummies `elem(:)`
+  * whole-array copies `a = b`, rank-1 section copies `a = b(i,j,:,k)`, `sum(<elementwise expression over rank-1 sections>)`
+    (first to last from zero), declarations without `::`, parameters repeated inside routines (same value only)
+
 Mixed-mode arithmetic follows from C's own usual conversions, which coincide with Fortran's for integer / real(4) / real(8):
 a default-real literal such as 1.e-10 or 0.5 is emitted as a C float literal (1.e-10f), so `eps = 1.e-10` assigns
 float32(1e-10) to the double exactly as the Fortran does, and 2./(kc-kb) is a single-precision quotient in both languages.
@@ -81,7 +97,7 @@ def logical_lines(text):
 # ------------------------------------------------------------------------------------------------ expressions
 TOKEN = re.compile(
     r"\s*(?:(?P<lop>\.(?:and|or|not|lt|le|gt|ge|eq|ne)\.)|(?P<num>(?:\d+\.(?![A-Za-z]{2,}\.)\d*|\.\d+|\d+)(?:[eEdD][-+]?\d+)?(?:_[A-Za-z]\w*)?)|(?P<log>\.(?:true|false)\.)"
-    r"|(?P<id>[A-Za-z]\w*)|(?P<op>\*\*|>=|<=|==|/=|[-+*/(),:=<>]))",
+    r"|(?P<id>[A-Za-z]\w*)|(?P<op>\*\*|>=|<=|==|/=|[-+*/(),:=<>%]))",
     re.I,
 )
 
@@ -201,9 +217,36 @@ class Parser:
                             continue
                         break
                 self.take(")")
-                return Node("call", name=name, args=args)
-            return Node("var", name=name)
+                return self.components(Node("call", name=name, args=args))
+            return self.components(Node("var", name=name))
         raise Unsupported(f"unexpected token {v!r}")
+
+    def arglist(self):
+        self.take("(")
+        args = []
+        if self.peek()[1] != ")":
+            while True:
+                if self.peek()[1] == ":":
+                    self.take()
+                    args.append(Node("colon"))
+                else:
+                    args.append(self.expr())
+                if self.peek()[1] == ",":
+                    self.take()
+                    continue
+                break
+        self.take(")")
+        return args
+
+    def components(self, node):
+        while self.peek()[1] == "%":
+            self.take()
+            k, v = self.take()
+            if k != "id":
+                raise Unsupported("component name expected after %")
+            args = self.arglist() if self.peek()[1] == "(" else None
+            node = Node("comp", base=node, name=v.lower(), args=args)
+        return node
 
 
 def parse_expr(s):
@@ -374,7 +417,6 @@ class Translator:
         raise Unsupported(k)
 
     def linear(self, name, idx):
-        s = self.lookup(name)
         e = ""
         for d in reversed(range(len(idx))):
             term = f"(({idx[d]}) - {name}_lo{d})"
@@ -426,6 +468,10 @@ class Translator:
             if not self.parse_decl(st, "host", self.host_arrays):
                 raise Unsupported(f"line {no}: host-scope statement outside the subset: {st}")
         # pass 2: the subroutine
+        self.body = self.run_body(sub_lines)
+        return self.emit()
+
+    def run_body(self, sub_lines):
         executable = False
         out = []
         depth = 1
@@ -439,6 +485,10 @@ class Translator:
                     continue
                 if re.match(r"call\s+system_clock\b", low) or re.match(r"write\s*\(", low):
                     continue  # timing and printing only
+                if re.match(r"call\s+\w+\s*\(", low):
+                    executable = True
+                    out.append("  " * depth + self.call_statement(st[4:].strip()) + f"  /* line {no} */")
+                    continue
                 m = re.match(r"do\s+(\w+)\s*=\s*(.*)$", st, re.I)
                 if m:
                     executable = True
@@ -494,6 +544,10 @@ class Translator:
                     self.stmt_funcs[ln.name] = (args, parse_expr(rhs), locs)
                     continue
                 executable = True
+                special = self.special_assignment(ln, parse_expr(rhs), guard)
+                if special is not None:
+                    out.append("  " * depth + special + f"  /* line {no} */")
+                    continue
                 rc, rt = self.cx(parse_expr(rhs))
                 if ln.kind == "var":
                     s = self.lookup(ln.name)
@@ -531,8 +585,7 @@ class Translator:
                 raise Unsupported(f"line {no}: {e}: {st}") from None
         if depth != 1:
             raise Unsupported("unbalanced do / if nesting")
-        self.body = out
-        return self.emit()
+        return out
 
     def emit(self):
         sub = self.sub
@@ -613,8 +666,480 @@ class Translator:
         c.append("  return 0;\n}")
         return "\n".join(c) + "\n"
 
+    # hooks of the unit (module) mode; the single-subroutine mode has neither calls nor array-valued assignments
+    def call_statement(self, text):
+        raise Unsupported("call statement")
+
+    def special_assignment(self, lhs, rhs, guard):
+        return None
+
     def used_as_variable(self, name):
         return any(re.search(rf"\b{name}\b", ln) for ln in self.body)
+
+
+# ================================================================================================ unit (module) mode
+class Routine:
+    def __init__(self, name, kind, args, result, first):
+        self.name, self.kind, self.args, self.result, self.first, self.last = name, kind, args, result, first, first
+        self.lines, self.syms, self.body = [], {}, []
+
+
+class UnitTranslator(Translator):
+    """All routines of one module (which may `use` others) -> one C file: the routines become static functions, `entry`
+    is exported.  On top of the single-subroutine subset: derived types (-> C structs, components by `%`), functions whose
+    result is an array (-> a trailing output pointer; `x = f(..)` evaluates into a temporary and copies, as Fortran does),
+    `call` of the module's own subroutines, actual arguments that are whole arrays, components, contiguous leading sections
+    `a(:,:,k)` or elements of a derived-type array, whole-array copies `a = b`, real parameters, declarations without `::`."""
+
+    def __init__(self, text, module, uses, entry, runtime, export=None):
+        super().__init__(text, entry, runtime, False)
+        self.module, self.uses, self.entry = module.lower(), [u.lower() for u in uses], entry.lower()
+        self.export = export or f"{self.module}_{self.entry}"
+        self.types = {}       # type name -> {component name -> Sym}
+        self.routines = {}    # name -> Routine
+        self.param_types = {}
+        self.host_scalars = {}
+        self.host_vars = []      # initialised integer module variables
+        self.section_var = None  # inside sum(..) / an array assignment: the loop variable a `:` subscript stands for
+        self.section_extents = []
+
+    # ---- declarations of the unit mode
+    def parse_decl(self, stmt, role_default, table):
+        st = stmt
+        m = re.match(r"type\s*\(\s*(\w+)\s*\)\s*((?:,\s*[^:]+?)*)\s*::\s*(.*)$", st, re.I)
+        if m:
+            tname, attrs = m.group(1).lower(), m.group(2).lower()
+            if tname not in self.types:
+                raise Unsupported(f"unknown derived type {tname}")
+            role = "arg" if "intent" in attrs else role_default
+            for name, dims in split_top(m.group(3), with_init=False):
+                table[name.lower()] = Sym(name.lower(), ("type", tname), dims, role)
+            return True
+        # `integer i,j` (no double colon), `real(kind=k)`, `integer :: n = 16` (initialised module variable)
+        m = re.match(r"(real|integer|logical)\s*(\([^)]*\))?\s+([A-Za-z]\w*(?:\s*,\s*[A-Za-z]\w*)*)$", st, re.I)
+        if m and "::" not in st:
+            st = f"{m.group(1)}{m.group(2) or ''} :: {m.group(3)}"
+        st = re.sub(r"\(\s*kind\s*=\s*(\w+)\s*\)", r"(\1)", st, count=1, flags=re.I)
+        m = re.match(r"(real|integer|logical)\s*(\(([^)]*)\))?\s*((?:,\s*[^:]+?)*)\s*::\s*(.*)$", st, re.I)
+        if not m:
+            return False
+        base, kind, attrs, rest = m.group(1).lower(), (m.group(3) or "").strip().lower(), m.group(4).lower(), m.group(5)
+        if "parameter" in attrs and base == "real":
+            typ = self.real_kind.get(kind, FLT if kind == "" else None)
+            if typ is None:
+                raise Unsupported(f"real kind {kind!r}")
+            for name, val in split_top(rest, with_init=True):
+                self.host_params.append((name.lower(), val))
+                self.param_types[name.lower()] = typ
+            return True
+        if "parameter" not in attrs and "=" in rest and role_default == "host":
+            for ent in split_commas(rest):  # initialised module variables (`integer :: nelemd = 16`): file-scope statics
+                name, val = (x.strip() for x in ent.split("=", 1))
+                if base != "integer":
+                    raise Unsupported("initialised module variable that is not an integer")
+                self.host_vars.append((name.lower(), val))
+                self.param_types[name.lower()] = INT
+            return True
+        if "allocatable" in attrs or re.search(r"\(\s*:", rest):
+            if role_default == "host":
+                for name, dims in split_top(re.sub(r"\(([\s:,]*)\)", "", rest), with_init=False):
+                    self.host_scalars[name.lower()] = True  # deferred-shape module arrays: shadowed by dummies in the routines
+                return True
+        before = len(self.host_params)
+        ok = super().parse_decl(st, role_default, table)
+        new, seen = self.host_params[before:], dict(self.host_params[:before])
+        del self.host_params[before:]
+        for name, val in new:  # a routine may repeat a parameter of the module (kchunk): once, and only with the same value
+            if name in seen:
+                if seen[name].replace(" ", "") != val.replace(" ", ""):
+                    raise Unsupported(f"parameter {name} redefined with another value")
+                continue
+            self.host_params.append((name, val))
+            self.param_types[name] = INT
+        return ok
+
+    def lookup(self, name):
+        if name in self.syms:
+            return self.syms[name]
+        if name in self.param_types:
+            return Sym(name, self.param_types[name])
+        if name in self.host_scalars:
+            raise Unsupported(f"module variable {name} used inside a routine")
+        raise Unsupported(f"undeclared name {name!r}")
+
+    # ---- expressions: components and whole-array operands
+    def struct_base(self, node):
+        """C lvalue of the derived-type object a component is selected from, and its type name."""
+        if node.kind == "var":
+            s = self.lookup(node.name)
+            if not isinstance(s.typ, tuple):
+                raise Unsupported(f"{node.name} is not of derived type")
+            if s.dims:
+                raise Unsupported("component of a whole derived-type array")
+            return f"{node.name}[0]", s.typ[1]
+        if node.kind == "call":
+            s = self.lookup(node.name)
+            if not isinstance(s.typ, tuple) or not s.dims or len(node.args) != 1 or node.args[0].kind == "colon":
+                raise Unsupported(f"{node.name}(..) is not an element of a derived-type array")
+            c, t = self.cx(node.args[0])
+            return f"{node.name}[({c}) - {node.name}_lo0]", s.typ[1]
+        raise Unsupported("nested derived types")
+
+    def cx(self, n, locals_=None):
+        if n.kind == "comp":
+            base, tname = self.struct_base(n.base)
+            comp = self.types[tname].get(n.name)
+            if comp is None:
+                raise Unsupported(f"type {tname} has no component {n.name}")
+            if n.args is None:
+                if comp.dims:
+                    raise Unsupported(f"whole component array {n.name} inside an expression")
+                return f"{base}.{n.name}", comp.typ
+            if not comp.dims or len(n.args) != len(comp.dims):
+                raise Unsupported(f"rank mismatch in component {n.name}")
+            idx = self.subscripts(tname + "_" + n.name, n.args, locals_)
+            return f"{base}.{n.name}[{self.linear(tname + '_' + n.name, idx)}]", comp.typ
+        if n.kind == "call" and n.name in self.routines:
+            raise Unsupported(f"call of {n.name} inside an expression (only `x = {n.name}(..)` is in the subset)")
+        if n.kind == "call" and n.name == "sum":
+            if len(n.args) != 1 or self.section_var:
+                raise Unsupported("sum with more than one argument, or nested")
+            self.section_var, self.section_extents = "t_", []
+            try:
+                c, t = self.cx(n.args[0], locals_)
+                ext = self.section_extents
+            finally:
+                self.section_var, self.section_extents = None, []
+            if t != DBL or not ext:
+                raise Unsupported("sum of something that is not a double array section")
+            # first to last from zero, as gfortran expands it (for the two-element sums of the reference the order is immaterial)
+            return f"({{ double s_ = 0.0; for (int t_ = 0; t_ < {ext[0]}; ++t_) s_ = s_ + ({c}); s_; }})", DBL
+        if n.kind == "call" and n.name in self.syms and self.syms[n.name].dims and not isinstance(self.syms[n.name].typ, tuple) \
+                and any(a.kind == "colon" for a in n.args):
+            sy = self.syms[n.name]
+            if len(n.args) != len(sy.dims):
+                raise Unsupported(f"rank mismatch in reference to {n.name}")
+            return f"{n.name}[{self.linear(n.name, self.subscripts(n.name, n.args, locals_))}]", sy.typ
+        return super().cx(n, locals_)
+
+    def subscripts(self, prefix, args, locals_=None):
+        idx, colons = [], 0
+        for d, a in enumerate(args):
+            if a.kind == "colon":
+                colons += 1
+                if not self.section_var or colons > 1:
+                    raise Unsupported("array section inside an expression")
+                idx.append(f"{prefix}_lo{d} + {self.section_var}")
+                self.section_extents.append(f"{prefix}_n{d}")
+            else:
+                c, t = self.cx(a, locals_)
+                if t != INT:
+                    raise Unsupported("non-integer subscript")
+                idx.append(c)
+        return idx
+
+    def pointer_to(self, node):
+        """C pointer to the first element of an array-valued operand (whole array, whole component, leading section)."""
+        if node.kind == "var":
+            s = self.lookup(node.name)
+            if not s.dims:
+                raise Unsupported(f"{node.name} is not an array")
+            return node.name, s
+        if node.kind == "comp" and node.args is None:
+            base, tname = self.struct_base(node.base)
+            comp = self.types[tname][node.name]
+            if not comp.dims:
+                raise Unsupported(f"component {node.name} is not an array")
+            return f"{base}.{node.name}", comp
+        if node.kind == "call":
+            s = self.lookup(node.name)
+            if not s.dims or len(node.args) != len(s.dims):
+                raise Unsupported(f"{node.name}(..) is not an array section")
+            idx, colons = [], 0
+            for d, a in enumerate(node.args):
+                if a.kind == "colon":
+                    if d != colons:
+                        raise Unsupported("a section whose colons are not the leading subscripts is not contiguous")
+                    colons += 1
+                    idx.append(f"{node.name}_lo{d}")
+                else:
+                    c, t = self.cx(a)
+                    if t != INT:
+                        raise Unsupported("non-integer subscript")
+                    idx.append(c)
+            if isinstance(s.typ, tuple):
+                if colons == 1 and len(node.args) == 1:
+                    return node.name, s  # elem(:)
+                if colons:
+                    raise Unsupported("section of a derived-type array")
+                return f"&{node.name}[({idx[0]}) - {node.name}_lo0]", Sym(node.name, s.typ)
+            if not colons:
+                raise Unsupported("an array element passed where an array is expected")
+            return f"&{node.name}[{self.linear(node.name, idx)}]", Sym(node.name, s.typ, s.dims[:colons])
+        raise Unsupported("operand that is not an array")
+
+    def actual(self, node, dummy):
+        if dummy.dims or isinstance(dummy.typ, tuple):
+            c, s = self.pointer_to(node) if (dummy.dims or node.kind == "call") else (None, None)
+            if c is None:  # scalar of derived type passed on
+                s = self.lookup(node.name) if node.kind == "var" else None
+                if s is None or s.typ != dummy.typ or s.dims:
+                    raise Unsupported("actual argument for a derived-type dummy")
+                return node.name
+            if s.typ != dummy.typ:
+                raise Unsupported("type mismatch between actual and dummy argument")
+            return c
+        c, t = self.cx(node)
+        if (dummy.typ == INT) != (t == INT):
+            raise Unsupported("integer / real mismatch between actual and dummy argument")
+        return c
+
+    def actuals(self, r, args):
+        if len(args) != len(r.args):
+            raise Unsupported(f"{r.name} takes {len(r.args)} arguments")
+        return [self.actual(a, r.syms[d]) for a, d in zip(args, r.args)]
+
+    def call_statement(self, text):
+        n = parse_expr(text)
+        if n.kind != "call" or n.name not in self.routines or self.routines[n.name].kind != "subroutine":
+            raise Unsupported("call of something that is not a subroutine of this module")
+        return f"r_{n.name}({', '.join(self.actuals(self.routines[n.name], n.args))});"
+
+    def total(self, prefix, ndims):
+        return " * ".join(f"(long){prefix}_n{d}" for d in range(ndims))
+
+    def special_assignment(self, lhs, rhs, guard):
+        if rhs.kind == "call" and rhs.name in self.routines and self.routines[rhs.name].kind == "function":
+            r = self.routines[rhs.name]
+            res = r.syms[r.result]
+            dst, _ = self.pointer_to(lhs)
+            saved, self.syms = self.syms, {}
+            try:  # the result's extents are module constants
+                size = " * ".join("((" + self.cx(parse_expr(hi))[0] + ") - (" + (self.cx(parse_expr(lo))[0] if lo else "1") + ") + 1)" for lo, hi in res.dims)
+            finally:
+                self.syms = saved
+            args = ", ".join(self.actuals(r, rhs.args) + ["t_"])
+            return (f"{guard}{{ double t_[{size}]; r_{r.name}({args}); double *d_ = {dst}; "
+                    f"for (long q_ = 0; q_ < {size}; ++q_) d_[q_] = t_[q_]; }}")
+        def has_colon(n):
+            if n is None or not isinstance(n, Node):
+                return False
+            if n.kind in ("call", "comp") and n.args and any(a.kind == "colon" for a in n.args):
+                return True
+            return any(has_colon(getattr(n, f, None)) for f in ("a", "b", "base")) or \
+                (n.kind == "call" and n.name != "sum" and any(has_colon(a) for a in n.args))
+        if lhs.kind == "var" and rhs.kind != "var" and has_colon(rhs) and not (rhs.kind == "call" and rhs.name in self.routines):
+            a = self.lookup(lhs.name)
+            if not a.dims or len(a.dims) != 1 or isinstance(a.typ, tuple):
+                raise Unsupported("section assigned to something that is not a rank-1 array")
+            def mentions(n, name):
+                if not isinstance(n, Node):
+                    return False
+                if getattr(n, "name", None) == name:
+                    return True
+                return any(mentions(getattr(n, f, None), name) for f in ("a", "b", "base")) or any(mentions(x, name) for x in (getattr(n, "args", None) or []))
+            if mentions(rhs, lhs.name):
+                raise Unsupported("array assignment whose right side reads the left side")
+            self.section_var, self.section_extents = "t_", []
+            try:
+                c, t = self.cx(rhs)
+                ext = self.section_extents
+            finally:
+                self.section_var, self.section_extents = None, []
+            return f"{guard}for (int t_ = 0; t_ < {ext[0]}; ++t_) {lhs.name}[t_] = {c};"
+        if lhs.kind == "var" and rhs.kind == "var":
+            a, b = self.lookup(lhs.name), self.lookup(rhs.name)
+            if a.dims and b.dims:
+                if len(a.dims) != len(b.dims) or a.typ != b.typ:
+                    raise Unsupported("whole-array copy between different shapes")
+                return f"{guard}for (long q_ = 0; q_ < {self.total(lhs.name, len(a.dims))}; ++q_) {lhs.name}[q_] = {rhs.name}[q_];"
+        return None
+
+    # ---- the unit
+    def run(self):
+        # split the file into units; keep the specification parts of the used modules and of the target, and its routines
+        unit, in_contains, spec, cur = None, False, [], None
+        for no, st in self.lines:
+            low = st.lower()
+            m = re.match(r"(module|program)\s+(\w+)$", low)
+            if m and unit is None:
+                unit, in_contains = m.group(2), False
+                continue
+            if re.match(r"end\s*(module|program)\b", low):
+                unit, cur = None, None
+                continue
+            if unit is None:
+                continue
+            wanted = unit in self.uses or unit == self.module
+            if low == "contains":
+                in_contains = True
+                continue
+            if not in_contains:
+                if wanted:
+                    spec.append((no, st))
+                continue
+            if unit != self.module:
+                continue
+            m = re.match(r"(subroutine|function)\s+(\w+)\s*\(([^)]*)\)\s*(?:result\s*\(\s*(\w+)\s*\))?$", low)
+            if m and cur is None:
+                cur = Routine(m.group(2), m.group(1), [a.strip() for a in m.group(3).split(",") if a.strip()], m.group(4), no)
+                if cur.kind == "function" and not cur.result:
+                    raise Unsupported(f"line {no}: function without a result clause")
+                self.routines[cur.name] = cur
+                continue
+            if re.match(r"end\s*(subroutine|function)\b", low):
+                cur.last = no
+                cur = None
+                continue
+            if cur is None:
+                raise Unsupported(f"line {no}: statement between routines: {st}")
+            cur.lines.append((no, st))
+        if self.entry not in self.routines:
+            raise Unsupported(f"{self.entry} is not a routine of module {self.module}")
+        # specification parts
+        in_type = None
+        for no, st in spec:
+            low = st.lower()
+            try:
+                if re.match(r"(implicit|use|private|public)\b", low):
+                    continue
+                m = re.match(r"type\s*(?:::)?\s*(\w+)$", low)
+                if m and not low.startswith("type("):
+                    in_type = m.group(1)
+                    self.types[in_type] = {}
+                    continue
+                if re.match(r"end\s*type\b", low):
+                    in_type = None
+                    continue
+                if in_type:
+                    if not self.parse_decl(st, "component", self.types[in_type]):
+                        raise Unsupported("component declaration")
+                    continue
+                if not self.parse_decl(st, "host", self.host_arrays):
+                    raise Unsupported("specification statement outside the subset")
+            except Unsupported as e:
+                raise Unsupported(f"line {no}: {e}: {st}") from None
+        # declarations of every routine first (calls need the callee's dummies), then the bodies
+        for r in self.routines.values():
+            decl_end = 0
+            for i, (no, st) in enumerate(r.lines):
+                if st.lower().startswith("implicit"):
+                    decl_end = i + 1
+                    continue
+                try:
+                    if self.parse_decl(st, "local", r.syms):
+                        decl_end = i + 1
+                        continue
+                except Unsupported as e:
+                    raise Unsupported(f"line {no}: {e}: {st}") from None
+                break
+            r.exec_lines = r.lines[decl_end:]
+            for a in r.args + ([r.result] if r.result else []):
+                if a not in r.syms:
+                    raise Unsupported(f"{r.name}: dummy argument {a} is not declared")
+                r.syms[a].role = "arg"
+        for r in self.routines.values():
+            self.syms, self.stmt_funcs = r.syms, {}
+            r.body = self.translate_body(r.exec_lines)
+        return self.emit_unit()
+
+    def translate_body(self, lines):
+        """The statement loop of the base class on a routine's executable part."""
+        keep_lines, keep_run = self.lines, None
+        out = Translator.run_body(self, lines)
+        self.lines = keep_lines
+        return out
+
+    def dims_consts(self, prefix, s, c, indent="  ", const="const int"):
+        for d, (lo, hi) in enumerate(s.dims):
+            loc = self.cx(parse_expr(lo))[0] if lo else "1"
+            if hi in (None, ""):
+                c.append(f"{indent}{const} {prefix}_lo{d} = {loc};")
+            else:
+                c.append(f"{indent}{const} {prefix}_lo{d} = {loc}, {prefix}_n{d} = ({self.cx(parse_expr(hi))[0]}) - ({loc}) + 1;")
+
+    def ctype_of(self, s):
+        return s.typ[1] if isinstance(s.typ, tuple) else CTYPE[s.typ]
+
+    def signature(self, r):
+        ps = []
+        for a in r.args + ([r.result] if r.result else []):
+            s = r.syms[a]
+            ps.append(f"{self.ctype_of(s)} *{a}" if (s.dims or isinstance(s.typ, tuple)) else f"{CTYPE[s.typ]} {a}")
+        return f"void r_{r.name}({', '.join(ps)})"
+
+    def emit_unit(self):
+        c = [f"/* GENERATED by oracle/f90_to_c.py from the reference's module {self.module} (routines "
+             + ", ".join(f"{r.name} {r.first}-{r.last}" for r in self.routines.values()) + ").",
+             "   Test infrastructure; lives under oracle/_ref/ (git-ignored), never committed.  Do not edit. */",
+             "#include <math.h>\n#include <stdlib.h>\n",
+             "static inline int f90_imax(int a, int b) { return b > a ? b : a; }",
+             "static inline int f90_imin(int a, int b) { return b < a ? b : a; }",
+             "static inline double f90_dmax(double a, double b) { return b > a ? b : a; }",
+             "static inline double f90_dmin(double a, double b) { return b < a ? b : a; }",
+             "static inline double f90_dabs(double a) { return fabs(a); }\n"]
+        self.syms = {}
+        for name, val in self.host_params:
+            typ = self.param_types[name]
+            if name in self.runtime:
+                if typ != INT:
+                    raise Unsupported(f"--runtime {name} is not an integer parameter")
+                c.append(f"static int {name};  /* compile-time parameter of the reference, a run-time argument here */")
+            elif typ == INT:
+                c.append(f"enum {{ {name} = {self.cx(parse_expr(val))[0]} }};")
+            else:
+                c.append(f"static const {CTYPE[typ]} {name} = {self.cx(parse_expr(val))[0]};")
+        for name, val in self.host_vars:
+            c.append(f"static int {name} = {self.cx(parse_expr(val))[0]};  /* module variable of the reference" + (", set from an argument here */" if name in self.runtime else " */"))
+        for r in self.runtime:
+            if r not in self.param_types:
+                raise Unsupported(f"--runtime {r} is not a parameter of the used modules")
+        for tname, comps in self.types.items():
+            fields = []
+            for cname, s in comps.items():
+                if s.dims:
+                    self.dims_consts(f"{tname}_{cname}", s, c, indent="", const="static const int")
+                    fields.append(f"{CTYPE[s.typ]} {cname}[{' * '.join('((' + self.cx(parse_expr(hi))[0] + ') - (' + (self.cx(parse_expr(lo))[0] if lo else '1') + ') + 1)' for lo, hi in s.dims)}];")
+                else:
+                    fields.append(f"{CTYPE[s.typ]} {cname};")
+            c.append(f"typedef struct {{ {' '.join(fields)} }} {tname};")
+        c.append("")
+        for r in self.routines.values():
+            c.append(f"static {self.signature(r)};")
+        for r in self.routines.values():
+            self.syms = r.syms
+            c.append(f"\n/* {r.kind} {r.name}, source lines {r.first}-{r.last} */\nstatic {self.signature(r)}\n{{")
+            for s in r.syms.values():
+                if s.dims:
+                    self.dims_consts(s.name, s, c)
+            for s in r.syms.values():
+                if s.role == "arg":
+                    continue
+                if s.dims:
+                    c.append(f"  {self.ctype_of(s)} {s.name}[{self.total(s.name, len(s.dims))}];")
+                    if s.typ in (DBL, FLT):
+                        c.append(f"  for (long t_ = 0; t_ < {self.total(s.name, len(s.dims))}; ++t_) {s.name}[t_] = NAN;  /* undefined in Fortran */")
+                else:
+                    c.append(f"  {self.ctype_of(s)} {s.name};")
+            c.append("")
+            c.extend(r.body)
+            unused = [s.name for s in r.syms.values() if not (s.role == "arg" and (s.dims or isinstance(s.typ, tuple)))]
+            c.append("  " + " ".join(f"(void){u};" for u in unused))
+            dimvars = [f"(void){s.name}_lo{d};" + (f" (void){s.name}_n{d};" if hi not in (None, "") else "") for s in r.syms.values() if s.dims for d, (lo, hi) in enumerate(s.dims)]
+            c.append("  " + " ".join(dimvars))
+            c.append("}")
+        e = self.routines[self.entry]
+        ps = [f"int {r}_" for r in self.runtime]
+        call = []
+        for a in e.args:
+            s = e.syms[a]
+            ps.append(f"{self.ctype_of(s)} *{a}" if (s.dims or isinstance(s.typ, tuple)) else f"{CTYPE[s.typ]} {a}")
+            call.append(a)
+        c.append(f"\nint {self.export}({', '.join(ps)})\n{{")
+        for r in self.runtime:
+            c.append(f"  {r} = {r}_;")
+        c.append(f"  r_{e.name}({', '.join(call)});\n  return 0;\n}}")
+        return "\n".join(c) + "\n"
 
 
 def matching_paren(s, start):
@@ -685,14 +1210,21 @@ def split_assignment(st):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("source")
-    ap.add_argument("subroutine")
+    ap.add_argument("subroutine", help="the subroutine to translate (single-subroutine mode) or the entry routine (--module)")
+    ap.add_argument("--module", help="unit mode: translate every routine of this module, export the entry")
+    ap.add_argument("--uses", default="", help="unit mode: modules whose specification part the module uses")
+    ap.add_argument("--export", help="unit mode: name of the exported C function")
     ap.add_argument("--runtime", default="", help="integer parameters of the program that become C arguments")
     ap.add_argument("--check-bounds", action="store_true", help="skip and count statements whose subscripts leave the declared bounds")
     ap.add_argument("--out", required=True)
     a = ap.parse_args()
     text = open(a.source, errors="replace").read()
     try:
-        c = Translator(text, a.subroutine, [r for r in a.runtime.split(",") if r], a.check_bounds).run()
+        runtime = [r for r in a.runtime.split(",") if r]
+        if a.module:
+            c = UnitTranslator(text, a.module, [u for u in a.uses.split(",") if u], a.subroutine, runtime, a.export).run()
+        else:
+            c = Translator(text, a.subroutine, runtime, a.check_bounds).run()
     except Unsupported as e:
         sys.exit(f"f90_to_c: {e}")
     open(a.out, "w").write(c)
