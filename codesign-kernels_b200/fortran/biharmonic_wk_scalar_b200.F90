@@ -20,6 +20,7 @@ module biharmonic_wk_scalar_b200
 
   public :: biharmonic_wk_scalar
   public :: biharmonic_wk_scalar_cpusig
+  public :: biharmonic_wk_scalar_present
   public :: advance_hypervis_scalar
   public :: biharmonic_wk_dp3d
   public :: b200_set_topology_gdof
@@ -71,6 +72,18 @@ module biharmonic_wk_scalar_b200
       integer(c_int), value :: var_coef1_c, undamprrcart_c
       integer(c_int) :: rc
     end function bwk_biharmonic_wk_dp3d
+    function bwk_biharmonic_wk_scalar_noalloc(d_elem_c, d_qtens_c, deriv_c, nelemd_c, nlev_c, qsize_c, stream_c) &
+        bind(c, name="bwk_biharmonic_wk_scalar_noalloc") result(rc)
+      use iso_c_binding
+      type(c_ptr), value :: d_elem_c, d_qtens_c, deriv_c
+      integer(c_int), value :: nelemd_c, nlev_c, qsize_c
+      integer(c_int64_t), value :: stream_c
+      integer(c_int) :: rc
+    end function bwk_biharmonic_wk_scalar_noalloc
+    function cudaDeviceSynchronize() bind(c, name="cudaDeviceSynchronize") result(rc)
+      use iso_c_binding
+      integer(c_int) :: rc
+    end function cudaDeviceSynchronize
   end interface
 
 contains
@@ -174,5 +187,25 @@ contains
                                        int(nets,c_int), int(nete,c_int))
     if (rc /= 0) error stop "bwk_biharmonic_wk_scalar_nets failed"
   end subroutine biharmonic_wk_scalar_cpusig
+
+  !! For an OpenACC build of the driver (pgiacc=1): elem and qtens are already present on the device (`enter data pcreate`,
+  !! F90:553, and `update device`, F90:573), so the B200 kernel can run on those device copies in place -- no transfer, no
+  !! allocation, no bwk_init (bwk_biharmonic_wk_scalar_noalloc, include/bwk_b200.h; nelemd <= 8192).  The two kernels are queued
+  !! on the default stream and waited for here, so the `update host(qtens)` that follows (F90:575) sees the result.
+  subroutine biharmonic_wk_scalar_present(elem,qtens,deriv)
+    implicit none
+    type (element_t)     , intent(in   ), target :: elem(:)
+    real (kind=real_kind), intent(inout), target :: qtens(np,np,nlev,qsize,nelemd)
+    type (derivative_t)  , intent(in   ), target :: deriv
+    integer(c_int) :: rc
+    integer(c_int64_t) :: default_stream
+    default_stream = 0
+    !$acc host_data use_device(elem, qtens)
+    rc = bwk_biharmonic_wk_scalar_noalloc(c_loc(elem(1)), c_loc(qtens), c_loc(deriv), &
+                                          int(nelemd,c_int), int(nlev,c_int), int(qsize,c_int), default_stream)
+    !$acc end host_data
+    if (rc /= 0) error stop "bwk_biharmonic_wk_scalar_noalloc failed"
+    if (cudaDeviceSynchronize() /= 0) error stop "cudaDeviceSynchronize failed"
+  end subroutine biharmonic_wk_scalar_present
 
 end module biharmonic_wk_scalar_b200

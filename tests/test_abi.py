@@ -72,6 +72,7 @@ def test_fortran_wrapper_matches_reference_signature():
     subs = {b["name"]: b for b in mods["biharmonic_wk_scalar_b200"]["body"] if b["block"] == "subroutine"}
     assert subs["biharmonic_wk_scalar"]["args"] == ["elem", "qtens", "grads", "deriv", "nets", "nete"]
     assert subs["biharmonic_wk_scalar_cpusig"]["args"] == ["elem", "qtens", "deriv", "nets", "nete"]
+    assert subs["biharmonic_wk_scalar_present"]["args"] == ["elem", "qtens", "deriv"]  # the allocation-free form on OpenACC-present data
     assert subs["advance_hypervis_scalar"]["args"] == ["elem", "qdp", "dp", "dpdiss", "deriv", "dt2", "nu_q", "hypervis_subcycle_q", "limiter"]
     assert subs["biharmonic_wk_dp3d"]["args"] == ["elem", "vec_sphere2cart", "dptens", "ttens", "vtens", "deriv", "var_coef1", "undamprrcart"]
     # the dp3d entry needs a context with qsize = 4 while kernel_utils' qsize is a compile-time 40: b200_init takes the
