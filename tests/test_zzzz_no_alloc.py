@@ -115,3 +115,10 @@ def _check_rejections(bwk):
 def test_noalloc_rejects_sizes_beyond_the_static_scratch(bwk):
     # the argument checks come before any CUDA call, so this one also runs on a box without a GPU
     _check_rejections(bwk)
+    # the limit the binding advertises is the header's, and the header says what the entry point is
+    import os
+    import re
+
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "bwk_b200.h")).read()
+    assert int(re.search(r"#define\s+BWK_NOALLOC_MAX_NELEMD\s+(\d+)", hdr).group(1)) == bwk.NOALLOC_MAX_NELEMD
+    assert "NO COUNTERPART IN THE REFERENCE" in hdr and "bwk_biharmonic_wk_scalar_noalloc" in bwk.declared_symbols()
