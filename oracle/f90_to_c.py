@@ -1045,10 +1045,7 @@ class UnitTranslator(Translator):
 
     def translate_body(self, lines):
         """The statement loop of the base class on a routine's executable part."""
-        keep_lines, keep_run = self.lines, None
-        out = Translator.run_body(self, lines)
-        self.lines = keep_lines
-        return out
+        return self.run_body(lines)
 
     def dims_consts(self, prefix, s, c, indent="  ", const="const int"):
         for d, (lo, hi) in enumerate(s.dims):
