@@ -202,3 +202,16 @@ def test_translator_unit_mode_semantics_on_synthetic_modules(tmp_path):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "f90_to_c.py"), str(src), "driver", "--module", "work", "--uses", "consts",
                         "--out", str(out)], capture_output=True, text=True)
     assert r.returncode != 0 and "f90_to_c:" in r.stderr
+
+
+def test_baseline_config_3_whole_array_oracle_equals_the_translated_reference(oracle, ref):
+    """BASELINE.json config 3 verbatim -- ne30np4 (5,400 elements) nlev = 72 qsize = 40, 15.5 M slabs, 2 GB -- and config 2
+    (qsize = 10): the oracle (OpenMP build, the one bench.py and the large GPU tests use) against the translated CPU module on
+    the WHOLE array, bit for bit.  The GPU test test_ne30_q40_whole_array_against_the_oracle compares the CUDA result with this
+    oracle at the same size."""
+    for qsize in (10, 40):
+        dvv, elem, q = oracle.initialize_data_parallel(5400, 72, qsize)
+        a = oracle.biharmonic_wk_scalar_cpu(elem, q.copy(order="F"), dvv, omp=True)
+        b = ref.biharmonic_wk_scalar_cpu(elem, q, dvv)  # in place on q: 2 GB are enough once
+        assert np.array_equal(_bits(a), _bits(b))
+        del a, b, q
