@@ -703,6 +703,10 @@ def test_gpu_bit_identical_to_the_translated_reference(mpdata, ns, form):
 
     if not ref.available():
         pytest.skip("oracle/_ref/libmpdata_f90ref.so did not travel and /root/reference is not here to build it")
+    try:
+        ref.lib()
+    except OSError as e:  # the checker itself could not be loaded on this box: nothing was compared
+        pytest.skip(f"oracle/_ref library did not load: {e}")
     P = mpdata.TestAdvect(ns, 32, 58).init(seed=300 + ns, signed_velocity=True)
     want = [a.copy(order="F") for a in P.arrays()]
     ref.advect_scalar2D_cpu(ns, 32, 58, *want)
