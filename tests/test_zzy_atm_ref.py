@@ -219,3 +219,25 @@ def test_baseline_config_3_whole_array_oracle_equals_the_translated_reference(or
         b = ref.biharmonic_wk_scalar_cpu(elem, q, dvv)  # in place on q: 2 GB are enough once
         assert np.array_equal(_bits(a), _bits(b))
         del a, b, q
+
+
+def test_oracle_hashes_to_the_committed_digests_of_the_translated_reference(oracle):
+    """tests/golden/atm_translated.json (made by tests/golden/make_atm_golden.py from the translated reference) against the
+    hand-written oracle: runs anywhere, with or without oracle/_ref.  The default case also carries the two published norms."""
+    import hashlib
+
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "atm_translated.json")))
+    sha = lambda a: hashlib.sha256(np.asfortranarray(a).tobytes(order="F")).hexdigest()  # noqa: E731
+    for c in gold["cases"]:
+        dvv, elem, q = oracle.initialize_data(c["nelemd"], c["nlev"], c["qsize"])
+        assert sha(q) == c["input_sha256"]
+        cpu = oracle.biharmonic_wk_scalar_cpu(elem, q.copy(order="F"), dvv)
+        g1 = oracle.biharmonic_wk_scalar_gpu1(elem, q.copy(order="F"), dvv)
+        g2 = oracle.biharmonic_wk_scalar_gpu2(elem, q.copy(order="F"), dvv)
+        assert (sha(cpu), sha(g1), sha(g2)) == (c["cpu_sha256"], c["gpu1_sha256"], c["gpu2_sha256"])
+    d = gold["cases"][0]
+    assert (d["nelemd"], d["nlev"], d["qsize"]) == (16, 72, 40)
+    assert d["gpu2_vs_cpu_rel_l2"] == "%.16E" % KAT["KAT1_gpu2_vs_cpu_rel_l2"] and d["gpu1_vs_cpu_rel_l2"] == "%.16E" % KAT["KAT2_gpu1_vs_cpu_rel_l2"]
+    n = gold["nets_nete_case"]
+    dvv, elem, q = oracle.initialize_data(n["nelemd"], n["nlev"], n["qsize"])
+    assert sha(oracle.biharmonic_wk_scalar_cpu(elem, q.copy(order="F"), dvv, n["nets"], n["nete"])) == n["cpu_sha256"]
