@@ -41,6 +41,21 @@ enough for the three modules of atmosphere/biharmonic_wk_kernel.F90 (CPU lines 1
   * whole-array copies `a = b`, rank-1 section copies `a = b(i,j,:,k)`, `sum(<elementwise expression over rank-1 sections>)`
     (first to last from zero), declarations without `::`, parameters repeated inside routines (same value only)
 
+State mode (--module M --uses U --state R1,R2 [--also OTHER.F90]): for routines that take no arguments and work on module
+state -- nested_loops/nested.F90, internal subroutines run_original_cpu_directive (lines 495-564) and
+run_gpu_optimized_directive (593-630) of `program nested`, on the allocatable arrays of `module nested_vars`:
+
+    python oracle/f90_to_c.py nested.F90 run_original_cpu_directive,run_gpu_optimized_directive --also nested_vars.F90 \
+           --module nested --uses nested_vars --state --export nested_f90 --out oracle/_ref/nested_f90.c
+
+  * #ifdef / #ifndef / #else / #endif are evaluated with nothing defined (the plain CPU build); line numbers are kept
+  * module scalars and allocatable arrays become file-scope C variables; array shapes come from the module's own
+    `allocate(..)` statements; <export>_set_int / <export>_bind set the integers and hand over the arrays
+  * `dimension(..)` attributes, routines without an argument list, the `sign` intrinsic; specification statements no routine
+    needs (namelists, c_ptr globals, timers, the main program's executable part) are skipped in this mode only
+This is where the translator itself is checked against COMPILED reference code: the reference has C++ forms of the same two
+loops, g++ builds them, and tests/test_zz_nested.py requires the translated Fortran to equal them bit for bit.
+
 Mixed-mode arithmetic follows from C's own usual conversions, which coincide with Fortran's for integer / real(4) / real(8):
 a default-real literal such as 1.e-10 or 0.5 is emitted as a C float literal (1.e-10f), so `eps = 1.e-10` assigns
 float32(1e-10) to the double exactly as the Fortran does, and 2./(kc-kb) is a single-precision quotient in both languages.
@@ -61,6 +76,39 @@ class Unsupported(Exception):
 
 
 # ------------------------------------------------------------------------------------------------ source lines
+def preprocess(text, defines=()):
+    """#ifdef / #ifndef / #else / #endif / #define with the given set of defined names (none by default: the plain CPU build);
+    dropped lines become empty so that line numbers stay the reference's."""
+    defines, out, stack = set(defines), [], []  # stack of (taking this branch, some parent is off)
+    for raw in text.splitlines():
+        st = raw.strip()
+        m = re.match(r"#\s*(ifdef|ifndef|else|endif|define|undef|include|if|elif)\b\s*(\w+)?", st)
+        if not m:
+            out.append(raw if all(t for t, _ in stack) else "")
+            continue
+        d, name = m.group(1), m.group(2)
+        if d in ("ifdef", "ifndef"):
+            on = (name in defines) == (d == "ifdef")
+            stack.append((on, False))
+        elif d == "else":
+            if not stack:
+                raise Unsupported("#else without #ifdef")
+            on, _ = stack.pop()
+            stack.append((not on, False))
+        elif d == "endif":
+            if not stack:
+                raise Unsupported("#endif without #ifdef")
+            stack.pop()
+        elif d == "define":
+            pass  # macros of the reference (C_WRAP) are used only inside blocks this build drops
+        else:
+            raise Unsupported(f"preprocessor directive #{d}")
+        out.append("")
+    if stack:
+        raise Unsupported("unterminated #ifdef")
+    return "\n".join(out)
+
+
 def logical_lines(text):
     """Comment-free statements with continuation lines joined; yields (first line number, statement)."""
     out, cur, start = [], "", None
@@ -267,7 +315,10 @@ class Translator:
     def __init__(self, text, sub, runtime, check_bounds=False):
         self.check = check_bounds
         self.cur_line = 0
-        self.lines = logical_lines(text)
+        # `text` may be a list of sources: the used modules' files first, the unit's own file last (its line numbers are the
+        # ones the generated comments quote)
+        texts = text if isinstance(text, (list, tuple)) else [text]
+        self.lines = [ln for t in texts for ln in logical_lines(preprocess(t))]
         self.sub = sub.lower()
         self.runtime = [r.lower() for r in runtime]
         self.host_params = []   # (name, expr string) in source order
@@ -392,6 +443,11 @@ class Translator:
                 for c, _ in parts[1:]:
                     acc = f"{fn}({acc}, {c})"
                 return acc, rt
+            if name == "sign" and len(n.args) == 2:
+                (a, ta), (b, tb) = self.cx(n.args[0], locals_), self.cx(n.args[1], locals_)
+                if (ta, tb) != (DBL, DBL):
+                    raise Unsupported("sign of non-doubles")
+                return f"copysign({a}, {b})", DBL  # |a| with the sign of b (the sign bit, as Fortran 95 and later)
             if name == "abs":
                 c, t = self.cx(n.args[0], locals_)
                 if t == DBL:
@@ -980,9 +1036,9 @@ class UnitTranslator(Translator):
                 continue
             if unit != self.module:
                 continue
-            m = re.match(r"(subroutine|function)\s+(\w+)\s*\(([^)]*)\)\s*(?:result\s*\(\s*(\w+)\s*\))?$", low)
+            m = re.match(r"(subroutine|function)\s+(\w+)\s*(?:\(([^)]*)\))?\s*(?:result\s*\(\s*(\w+)\s*\))?$", low)
             if m and cur is None:
-                cur = Routine(m.group(2), m.group(1), [a.strip() for a in m.group(3).split(",") if a.strip()], m.group(4), no)
+                cur = Routine(m.group(2), m.group(1), [a.strip() for a in (m.group(3) or "").split(",") if a.strip()], m.group(4), no)
                 if cur.kind == "function" and not cur.result:
                     raise Unsupported(f"line {no}: function without a result clause")
                 self.routines[cur.name] = cur
@@ -1018,7 +1074,9 @@ class UnitTranslator(Translator):
                 if not self.parse_decl(st, "host", self.host_arrays):
                     raise Unsupported("specification statement outside the subset")
             except Unsupported as e:
-                raise Unsupported(f"line {no}: {e}: {st}") from None
+                if not self.spec_unknown(no, st, e):
+                    raise Unsupported(f"line {no}: {e}: {st}") from None
+        self.after_spec()
         # declarations of every routine first (calls need the callee's dummies), then the bodies
         for r in self.routines.values():
             decl_end = 0
@@ -1042,6 +1100,13 @@ class UnitTranslator(Translator):
             self.syms, self.stmt_funcs = r.syms, {}
             r.body = self.translate_body(r.exec_lines)
         return self.emit_unit()
+
+    def spec_unknown(self, no, st, err):
+        """A specification statement outside the subset: an error (the state mode skips what no routine needs)."""
+        return False
+
+    def after_spec(self):
+        pass
 
     def translate_body(self, lines):
         """The statement loop of the base class on a routine's executable part."""
@@ -1101,6 +1166,7 @@ class UnitTranslator(Translator):
                     fields.append(f"{CTYPE[s.typ]} {cname};")
             c.append(f"typedef struct {{ {' '.join(fields)} }} {tname};")
         c.append("")
+        self.emit_state(c)
         for r in self.routines.values():
             c.append(f"static {self.signature(r)};")
         for r in self.routines.values():
@@ -1125,6 +1191,13 @@ class UnitTranslator(Translator):
             dimvars = [f"(void){s.name}_lo{d};" + (f" (void){s.name}_n{d};" if hi not in (None, "") else "") for s in r.syms.values() if s.dims for d, (lo, hi) in enumerate(s.dims)]
             c.append("  " + " ".join(dimvars))
             c.append("}")
+        self.emit_entry(c)
+        return "\n".join(c) + "\n"
+
+    def emit_state(self, c):
+        pass
+
+    def emit_entry(self, c):
         e = self.routines[self.entry]
         ps = [f"int {r}_" for r in self.runtime]
         call = []
@@ -1136,7 +1209,123 @@ class UnitTranslator(Translator):
         for r in self.runtime:
             c.append(f"  {r} = {r}_;")
         c.append(f"  r_{e.name}({', '.join(call)});\n  return 0;\n}}")
-        return "\n".join(c) + "\n"
+
+
+class StateUnitTranslator(UnitTranslator):
+    """Unit mode for routines that work on MODULE STATE instead of dummy arguments (nested_loops/nested.F90: the internal
+    subroutines of `program nested` take no arguments and use the allocatable arrays and scalars of `module nested_vars`).
+    The module variables become file-scope C variables, as they are file-scope Fortran variables; the shapes of the allocatable
+    arrays are read from the module's own `allocate(..)` statements; the caller sets the integers with <export>_set_int and
+    hands over the arrays with <export>_bind, then calls <export>_<routine>().  Specification statements no routine needs
+    (namelists, c_ptr globals, timers, the main program's executable part) are skipped."""
+
+    def __init__(self, text, module, uses, entries, export):
+        super().__init__(text, module, uses, entries[0], [], export)
+        self.entries = [e.lower() for e in entries]
+        self.state_scalars = {}  # name -> type
+        self.state_arrays = {}   # name -> Sym (dims None until an allocate statement gives them)
+
+    def parse_decl(self, stmt, role_default, table):
+        if role_default != "host":
+            return super().parse_decl(stmt, role_default, table)
+        st = re.sub(r"\(\s*kind\s*=\s*(\w+)\s*\)", r"(\1)", stmt, count=1, flags=re.I)
+        m = re.match(r"(real|integer|logical)\s*(\(([^)]*)\))?\s*((?:,\s*(?:dimension\s*\([^)]*\)|[^:,]+))*)\s*::\s*(.*)$", st, re.I)
+        if not m:
+            return False
+        base, kind, attrs, rest = m.group(1).lower(), (m.group(3) or "").strip().lower(), m.group(4).lower(), m.group(5)
+        if "parameter" in attrs:
+            return super().parse_decl(stmt, role_default, table)
+        if base == "real":
+            typ = self.real_kind.get(kind, FLT if kind == "" else None)
+            if typ is None:
+                raise Unsupported(f"real kind {kind!r}")
+        else:
+            typ = INT if base == "integer" else LOG
+        dm = re.search(r"dimension\s*\(([^)]*)\)", attrs)
+        for ent in split_commas(rest):
+            em = re.match(r"(\w+)\s*(?:\((.*)\))?\s*(?:=\s*(.*))?$", ent.strip())
+            if not em:
+                raise Unsupported(f"declaration entity {ent!r}")
+            name, edims, init = em.group(1).lower(), em.group(2), em.group(3)
+            if init is not None:
+                raise Unsupported("initialised module variable in state mode")
+            dims = edims if edims is not None else (dm.group(1) if dm else None)
+            if dims is None:
+                self.state_scalars[name] = typ
+            elif ":" in dims:
+                self.state_arrays[name] = Sym(name, typ, None, "state")
+                self.state_arrays[name].rank = len(split_commas(dims))
+            else:
+                self.state_arrays[name] = Sym(name, typ, [(None, d.strip()) for d in split_commas(dims)], "state")
+        return True
+
+    def spec_unknown(self, no, st, err):
+        return True  # namelist, type(c_ptr) globals, timers, the main program's executable statements
+
+    def after_spec(self):
+        for no, st in self.lines:  # the shapes: every allocate(..) of the used modules and of the unit
+            m = re.match(r"allocate\s*\((.*)\)$", st, re.I)
+            if not m:
+                continue
+            for ent in split_commas(m.group(1)):
+                em = re.match(r"(\w+)\s*\((.*)\)$", ent.strip())
+                if not em or em.group(1).lower() not in self.state_arrays:
+                    continue
+                a = self.state_arrays[em.group(1).lower()]
+                dims = [(None, d.strip()) for d in split_commas(em.group(2))]
+                if getattr(a, "rank", len(dims)) != len(dims):
+                    raise Unsupported(f"line {no}: allocate({a.name}) with a rank other than declared")
+                a.dims = dims
+
+    def lookup(self, name):
+        if name in self.syms:
+            return self.syms[name]
+        if name in self.param_types:
+            return Sym(name, self.param_types[name])
+        if name in self.state_scalars:
+            return Sym(name, self.state_scalars[name])
+        if name in self.state_arrays:
+            a = self.state_arrays[name]
+            if a.dims is None:
+                raise Unsupported(f"no allocate statement gives the shape of {name}")
+            return a
+        raise Unsupported(f"undeclared name {name!r}")
+
+    def run(self):
+        for e in self.entries:
+            self.entry = e
+        return super().run()
+
+    def emit_state(self, c):
+        c.append("/* module state of the reference: scalars and allocatable arrays, file scope there and here */")
+        for name, typ in self.state_scalars.items():
+            c.append(f"static {CTYPE[typ]} {name};")
+        used = [a for a in self.state_arrays.values() if a.dims is not None]
+        for a in used:
+            c.append(f"static {CTYPE[a.typ]} *{a.name};")
+            c.append("static int " + ", ".join(f"{a.name}_lo{d} = 1, {a.name}_n{d}" for d in range(len(a.dims))) + ";")
+        self.syms = {}
+        c.append("static void f90_shapes(void)\n{  /* the extents the module's allocate statements give */")
+        for a in used:
+            for d, (_, hi) in enumerate(a.dims):
+                c.append(f"  {a.name}_n{d} = {self.cx(parse_expr(hi))[0]};")
+        c.append("}\n")
+        c.append("#include <string.h>")
+        c.append(f"int {self.export}_set_int(const char *name, int v)\n{{")
+        for name, typ in self.state_scalars.items():
+            if typ == INT:
+                c.append(f'  if (!strcmp(name, "{name}")) {{ {name} = v; return 0; }}')
+        c.append("  return 1;\n}")
+        c.append(f"int {self.export}_bind(const char *name, void *p)\n{{")
+        for a in used:
+            c.append(f'  if (!strcmp(name, "{a.name}")) {{ {a.name} = ({CTYPE[a.typ]} *)p; return 0; }}')
+        c.append("  return 1;\n}\n")
+
+    def emit_entry(self, c):
+        for e in self.entries:
+            if e not in self.routines or self.routines[e].args:
+                raise Unsupported(f"{e} is not an argument-less routine of {self.module}")
+            c.append(f"\nint {self.export}_{e}(void)\n{{\n  f90_shapes();\n  r_{e}();\n  return 0;\n}}")
 
 
 def matching_paren(s, start):
@@ -1211,14 +1400,20 @@ def main():
     ap.add_argument("--module", help="unit mode: translate every routine of this module, export the entry")
     ap.add_argument("--uses", default="", help="unit mode: modules whose specification part the module uses")
     ap.add_argument("--export", help="unit mode: name of the exported C function")
+    ap.add_argument("--also", default="", help="unit mode: further source files (comma list) holding the used modules")
+    ap.add_argument("--state", action="store_true", help="unit mode on module state: SUBROUTINE is a comma list of argument-less routines")
     ap.add_argument("--runtime", default="", help="integer parameters of the program that become C arguments")
     ap.add_argument("--check-bounds", action="store_true", help="skip and count statements whose subscripts leave the declared bounds")
     ap.add_argument("--out", required=True)
     a = ap.parse_args()
     text = open(a.source, errors="replace").read()
+    if a.also:
+        text = [open(f, errors="replace").read() for f in a.also.split(",") if f] + [text]
     try:
         runtime = [r for r in a.runtime.split(",") if r]
-        if a.module:
+        if a.module and a.state:
+            c = StateUnitTranslator(text, a.module, [u for u in a.uses.split(",") if u], a.subroutine.split(","), a.export or a.module).run()
+        elif a.module:
             c = UnitTranslator(text, a.module, [u for u in a.uses.split(",") if u], a.subroutine, runtime, a.export).run()
         else:
             c = Translator(text, a.subroutine, runtime, a.check_bounds).run()

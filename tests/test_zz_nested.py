@@ -134,6 +134,33 @@ def test_oracle_is_pinned_on_the_reference_compiled_here(nested, cko, yref, name
     assert bad == 0, worst
 
 
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("ragged", [False, True])
+def test_translated_fortran_forms_equal_the_compiled_cpp_reference(nested, cko, yref, name, ragged):
+    """The Fortran loop forms of `program nested` (run_original_cpu_directive nested.F90:495-564, run_gpu_optimized_directive
+    nested.F90:593-630), translated mechanically by oracle/f90_to_c.py, against the reference's own C++ forms of the same loops
+    compiled by g++ (nested_yakl_c.cpp:184-306): bit for bit.  Both sides are reference code; what this checks is the
+    TRANSLATOR -- the tool that also produces oracle/_ref for the two Fortran-only paths (atmosphere, MPDATA) -- against
+    compiled reference code.  It also reproduces, on the translation, that coef3rdOrder = 2.14 is a default-real literal."""
+    import ref_nested_f90_py as f90
+
+    if not f90.available():
+        pytest.skip("oracle/_ref/libnested_f90ref.so is absent and /root/reference is not here to build it")
+    prob = make(nested, name, ragged)
+    nv = prob.nVertLevels
+    r = yref.RefProblem(prob)
+    t_orig, t_opt = f90.run(prob, "original"), f90.run(prob, "gpu_optimized")
+    assert np.array_equal(t_orig[:nv].view(np.uint64), r.original_loop()[:nv].view(np.uint64))
+    assert np.array_equal(t_opt[:nv].view(np.uint64), r.gpu_optimized()[:nv].view(np.uint64))
+    assert np.array_equal(t_orig[:nv], cko.original_cpu(prob)[:nv]) and np.array_equal(t_opt[:nv], cko.gpu_optimized(prob)[:nv])
+    # the reference's own acceptance test between its two Fortran forms (errTol, nested.F90:267-279)
+    bad, worst = cko.check(t_opt, t_orig, prob, nested.ERR_TOL)
+    assert bad == 0, worst
+    if prob.nAdv:  # a double-precision 2.14 would differ from the translated module parameter in the 8th digit
+        wrong = nested.NestedProblem(nEdges=prob.nEdges, nCells=prob.nCells, nVertLevels=nv, nAdv=prob.nAdv, nIters=1, packn=1, seed=3)
+        assert wrong.coef3rdOrder == float(np.float32(2.14)) != 2.14
+
+
 def test_oracle_vs_reference_with_general_masks(nested, cko, yref):
     """Non-0/1 cellMask and tracers that do not vanish outside the level range: the two reference forms differ from
     each other, and each oracle form still follows its own reference form bit for bit."""
