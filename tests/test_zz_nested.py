@@ -156,9 +156,9 @@ def test_translated_fortran_forms_equal_the_compiled_cpp_reference(nested, cko, 
     # the reference's own acceptance test between its two Fortran forms (errTol, nested.F90:267-279)
     bad, worst = cko.check(t_opt, t_orig, prob, nested.ERR_TOL)
     assert bad == 0, worst
-    if prob.nAdv:  # a double-precision 2.14 would differ from the translated module parameter in the 8th digit
-        wrong = nested.NestedProblem(nEdges=prob.nEdges, nCells=prob.nCells, nVertLevels=nv, nAdv=prob.nAdv, nIters=1, packn=1, seed=3)
-        assert wrong.coef3rdOrder == float(np.float32(2.14)) != 2.14
+    # the translation takes coef3rdOrder from the module's own `parameter :: coef3rdOrder = 2.14` (nested_vars.F90:32), the C++
+    # side gets the value the problem carries: equal bits above mean the problem's float32(2.14) is what the Fortran uses
+    assert prob.coef3rdOrder == float(np.float32(2.14)) != 2.14
 
 
 def test_oracle_vs_reference_with_general_masks(nested, cko, yref):
