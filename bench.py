@@ -161,6 +161,24 @@ def _host_mem_available_gb():
         return 0.0
 
 
+def port_equals_translated_reference(orc, nlev, qsize):
+    """The CPU legs time the C port (OpenMP build).  Where oracle/_ref travelled, say in the line itself whether that port's
+    Laplacian equals the reference's own CPU module (F90:100-202, translated from the Fortran to C, oracle/ref_atm_py.py) bit
+    for bit on the reference's default problem (F90:11-17).  None = the checker is not on this box."""
+    try:
+        import numpy as np
+        import ref_atm_py
+
+        if not ref_atm_py.available():
+            return None
+        dvv, elem, q = orc.initialize_data(16, nlev, qsize)
+        a = orc.biharmonic_wk_scalar_cpu(elem, q.copy(order="F"), dvv, omp=True)
+        b = ref_atm_py.biharmonic_wk_scalar_cpu(elem, q.copy(order="F"), dvv)
+        return bool(np.array_equal(a, b))
+    except Exception:
+        return None
+
+
 def cpu_baseline(ne_small, nlev, qsize, reps, want_serial=False, ne_full=None, full_budget_s=25.0):
     """The oracle with OpenMP over elements on all host cores: a small sphere (ne_small) timed `reps` times and, when
     host memory and the time budget allow, ONE step of the headline sphere itself (ne_full)."""
@@ -178,6 +196,7 @@ def cpu_baseline(ne_small, nlev, qsize, reps, want_serial=False, ne_full=None, f
         "sample": f"{pr.label()}, full biharmonic, OpenMP over elements, best of {reps}",
         "times_s": [round(t, 4) for t in times],
         "laplace_only_value": pr.updates / min(lap_times),
+        "port_laplacian_bit_identical_to_translated_reference": port_equals_translated_reference(orc, nlev, qsize),
     }
     if want_serial:
         pr.reinit()
@@ -263,6 +282,7 @@ def run_reference(args, rank, world):
         "data": "synthetic (reference LCG, F90:77-91)",
         "config": workload_config(args.ne, args.nlev, args.qsize, nglob, world, args.variant),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "same_config": same,
+                         "port_laplacian_bit_identical_to_translated_reference": port_equals_translated_reference(orc, args.nlev, args.qsize),
                          "probe_rate_small_sphere": rate, "probe_sample": f"ne{args.cpu_ne}np4 L{args.nlev} q{args.qsize}"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
