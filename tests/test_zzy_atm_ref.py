@@ -241,3 +241,93 @@ def test_oracle_hashes_to_the_committed_digests_of_the_translated_reference(orac
     n = gold["nets_nete_case"]
     dvv, elem, q = oracle.initialize_data(n["nelemd"], n["nlev"], n["qsize"])
     assert sha(oracle.biharmonic_wk_scalar_cpu(elem, q.copy(order="F"), dvv, n["nets"], n["nete"])) == n["cpu_sha256"]
+
+
+STATE_DEMO_VARS = """
+! synthetic module for the translator's state mode (not reference code)
+#define UNUSED_MACRO(x) x
+module shelf
+  implicit none
+  public
+  integer, parameter :: RK = selected_real_kind(12)
+  integer :: n, m, &! sizes, set by the caller
+     j, i        ! loop indices are module variables too
+  namelist /sizes/ n, m
+  real (kind=RK), parameter :: gain = 0.1
+#ifdef WIDE
+  real (kind=RK), dimension(:,:), allocatable :: acc
+#else
+  real (kind=RK), dimension(:), allocatable :: acc
+#endif
+  real (kind=RK), dimension(:,:), allocatable :: &
+     field, &! (n, m)
+     weight
+  integer, dimension(:), allocatable :: first
+contains
+  subroutine alloc_all
+    allocate(field(n,m), weight(n,m), &
+             first(m))
+#ifdef WIDE
+    allocate(acc(n,m))
+#else
+    allocate(acc(n))
+#endif
+  end subroutine alloc_all
+end module shelf
+"""
+STATE_DEMO_MAIN = """
+program main
+  use shelf
+  implicit none
+  call alloc_all
+  call fold
+contains
+  subroutine fold
+    do j = 1, m
+      do i = 1, n
+        acc(i) = 0.0_RK
+      end do
+      do i = first(j), n
+        acc(i) = acc(i) + field(i,j)*weight(i,j) * gain + sign(1.0_RK, field(i,j))
+      end do
+      do i = 1, n
+        field(i,j) = acc(i)
+      end do
+    end do
+  end subroutine fold
+end program main
+"""
+
+
+def test_translator_state_mode_on_synthetic_sources(tmp_path):
+    """Module state as file-scope variables, #ifdef with nothing defined, shapes from the module's allocate statements, several
+    source files, routines without an argument list, dimension(..) attributes, sign -- the constructs of nested_loops."""
+    import ctypes as C
+    import subprocess
+
+    (tmp_path / "shelf.F90").write_text(STATE_DEMO_VARS)
+    (tmp_path / "main.F90").write_text(STATE_DEMO_MAIN)
+    out, so = tmp_path / "s.c", tmp_path / "libs.so"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "f90_to_c.py"), str(tmp_path / "main.F90"), "fold", "--also", str(tmp_path / "shelf.F90"),
+                        "--module", "main", "--uses", "shelf", "--state", "--export", "demo", "--out", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    src = out.read_text()
+    assert "0.1f" in src and "static double *acc;" in src and "acc_n1" not in src  # the #else branch: acc is rank 1
+    subprocess.run(["/usr/bin/gcc", "-O2", "-ffp-contract=off", "-fPIC", "-std=gnu11", "-shared", "-o", str(so), str(out), "-lm"], check=True)
+    L = C.CDLL(str(so))
+    L.demo_set_int.argtypes, L.demo_bind.argtypes = [C.c_char_p, C.c_int], [C.c_char_p, C.c_void_p]
+    n, m = 5, 3
+    rng = np.random.default_rng(2)
+    field, weight = np.asfortranarray(rng.random((n, m)) - 0.5), np.asfortranarray(rng.random((n, m)))
+    first, acc = np.array([1, 3, 6], dtype=np.int32), np.full(n, np.nan)
+    f0 = field.copy(order="F")
+    assert L.demo_set_int(b"n", n) == 0 and L.demo_set_int(b"m", m) == 0 and L.demo_set_int(b"nope", 1) == 1
+    for name, a in (("field", field), ("weight", weight), ("first", first), ("acc", acc)):
+        assert L.demo_bind(name.encode(), a.ctypes.data) == 0
+    assert L.demo_fold() == 0
+    gain = np.float64(np.float32(0.1))
+    for j in range(m):
+        want = np.zeros(n)
+        for i in range(first[j] - 1, n):
+            want[i] = 0.0 + f0[i, j] * weight[i, j] * gain + np.copysign(1.0, f0[i, j])
+        assert np.array_equal(field[:, j].view(np.uint64), want.view(np.uint64))
