@@ -53,6 +53,10 @@ run_gpu_optimized_directive (593-630) of `program nested`, on the allocatable ar
     `allocate(..)` statements; <export>_set_int / <export>_bind set the integers and hand over the arrays
   * `dimension(..)` attributes, routines without an argument list, the `sign` intrinsic; specification statements no routine
     needs (namelists, c_ptr globals, timers, the main program's executable part) are skipped in this mode only
+  * also in the unit / state modes: `optional` dummies with present(), keyword and omitted optional arguments, `save`d
+    initialised locals, functions with a scalar result, x**2, sqrt, mod, dble, product(shape(x)), whole arrays inside sum(..)
+    -- what module kernel_utils of the atmosphere file needs (initialize_data + myrandom, save_qtens, compute_l2norm), so
+    that the reference PROGRAM's whole sequence runs translated
 This is where the translator itself is checked against COMPILED reference code: the reference has C++ forms of the same two
 loops, g++ builds them, and tests/test_zz_nested.py requires the translated Fortran to equal them bit for bit.
 
@@ -237,9 +241,14 @@ class Parser:
         return node
 
     def factor(self):
+        node = self.primary()
+        if self.peek()[1] == "**":  # binds tighter than * and unary minus, groups right to left
+            self.take()
+            return Node("pow", a=node, b=self.factor())
+        return node
+
+    def primary(self):
         k, v = self.take()
-        if self.peek()[1] == "**" or v == "**":
-            raise Unsupported("the ** operator is outside the subset")
         if k == "num":
             return Node("num", text=v)
         if k == "log":
@@ -251,21 +260,7 @@ class Parser:
         if k == "id":
             name = v.lower()
             if self.peek()[1] == "(":
-                self.take("(")
-                args = []
-                if self.peek()[1] != ")":
-                    while True:
-                        if self.peek()[1] == ":":
-                            self.take()
-                            args.append(Node("colon"))
-                        else:
-                            args.append(self.expr())
-                        if self.peek()[1] == ",":
-                            self.take()
-                            continue
-                        break
-                self.take(")")
-                return self.components(Node("call", name=name, args=args))
+                return self.components(Node("call", name=name, args=self.arglist()))
             return self.components(Node("var", name=name))
         raise Unsupported(f"unexpected token {v!r}")
 
@@ -277,6 +272,10 @@ class Parser:
                 if self.peek()[1] == ":":
                     self.take()
                     args.append(Node("colon"))
+                elif self.peek()[0] == "id" and self.i + 1 < len(self.t) and self.t[self.i + 1][1] == "=":
+                    name = self.take()[1].lower()  # keyword argument  name = value
+                    self.take("=")
+                    args.append(Node("kwarg", name=name, a=self.lexpr()))
                 else:
                     args.append(self.expr())
                 if self.peek()[1] == ",":
@@ -309,6 +308,8 @@ def parse_expr(s):
 class Sym:
     def __init__(self, name, typ, dims=None, role="local"):
         self.name, self.typ, self.dims, self.role = name, typ, dims, role  # dims: list of (lo expr str | None, hi expr str)
+        self.optional = False   # `optional` dummy: passed by address, absent = NULL
+        self.save_init = None   # `integer, save :: old = 11`: a static local with that initial value
 
 
 class Translator:
@@ -413,6 +414,11 @@ class Translator:
             if LOG in (ta, tb):
                 raise Unsupported("relational operator on logicals")
             return f"({a}) {n.op} ({b})", LOG
+        if k == "pow":
+            a, ta = self.cx(n.a, locals_)
+            if n.b.kind != "num" or n.b.text != "2" or ta != DBL:
+                raise Unsupported("the ** operator with anything but a double base and the literal exponent 2")
+            return f"({{ const double p_ = {a}; p_ * p_; }})", DBL  # x**2 is x*x
         if k == "bin":
             a, ta = self.cx(n.a, locals_)
             b, tb = self.cx(n.b, locals_)
@@ -448,6 +454,19 @@ class Translator:
                 if (ta, tb) != (DBL, DBL):
                     raise Unsupported("sign of non-doubles")
                 return f"copysign({a}, {b})", DBL  # |a| with the sign of b (the sign bit, as Fortran 95 and later)
+            if name == "sqrt" and len(n.args) == 1:
+                c, t = self.cx(n.args[0], locals_)
+                if t != DBL:
+                    raise Unsupported("sqrt of a non-double")
+                return f"sqrt({c})", DBL  # correctly rounded in both languages
+            if name == "mod" and len(n.args) == 2:
+                (a, ta), (b, tb) = self.cx(n.args[0], locals_), self.cx(n.args[1], locals_)
+                if (ta, tb) != (INT, INT):
+                    raise Unsupported("mod of non-integers")
+                return f"(({a}) % ({b}))", INT  # the sign follows the dividend in both languages
+            if name == "dble" and len(n.args) == 1:
+                c, t = self.cx(n.args[0], locals_)
+                return f"((double)({c}))", DBL
             if name == "abs":
                 c, t = self.cx(n.args[0], locals_)
                 if t == DBL:
@@ -788,6 +807,24 @@ class UnitTranslator(Translator):
                 self.host_params.append((name.lower(), val))
                 self.param_types[name.lower()] = typ
             return True
+        if role_default == "local" and "save" in attrs and "=" in rest:
+            for ent in split_commas(rest):
+                name, val = (x.strip() for x in ent.split("=", 1))
+                if base != "integer":
+                    raise Unsupported("saved local that is not an integer")
+                table[name.lower()] = Sym(name.lower(), INT, None, "local")
+                table[name.lower()].save_init = val
+            return True
+        if "optional" in attrs:
+            typ = INT if base == "integer" else LOG if base == "logical" else self.real_kind.get(kind)
+            if typ is None:
+                raise Unsupported("optional dummy of this type")
+            for name, dims in split_top(rest, with_init=False):
+                if dims:
+                    raise Unsupported("optional array dummy")
+                table[name.lower()] = Sym(name.lower(), typ, None, "arg")
+                table[name.lower()].optional = True
+            return True
         if "parameter" not in attrs and "=" in rest and role_default == "host":
             for ent in split_commas(rest):  # initialised module variables (`integer :: nelemd = 16`): file-scope statics
                 name, val = (x.strip() for x in ent.split("=", 1))
@@ -857,6 +894,22 @@ class UnitTranslator(Translator):
             return f"{base}.{n.name}[{self.linear(tname + '_' + n.name, idx)}]", comp.typ
         if n.kind == "call" and n.name in self.routines:
             raise Unsupported(f"call of {n.name} inside an expression (only `x = {n.name}(..)` is in the subset)")
+        if n.kind == "call" and n.name == "present" and len(n.args) == 1 and n.args[0].kind == "var":
+            sy = self.lookup(n.args[0].name)
+            if not sy.optional:
+                raise Unsupported("present() of a dummy that is not optional")
+            return f"({sy.name} != 0)", LOG
+        if n.kind == "call" and n.name == "product" and len(n.args) == 1 and n.args[0].kind == "call" and n.args[0].name == "shape":
+            _, sy = self.pointer_to(n.args[0].args[0])  # product(shape(x)): the number of elements of x
+            prefix = sy.name if not getattr(sy, "comp_of", None) else sy.comp_of + "_" + sy.name
+            return "(" + " * ".join(f"{prefix}_n{d}" for d in range(len(sy.dims))) + ")", INT
+        if n.kind == "var" and n.name in self.syms and self.syms[n.name].optional:
+            return f"(*{n.name})", self.syms[n.name].typ
+        if n.kind == "var" and self.section_var and (locals_ is None or n.name not in locals_):
+            sy = self.lookup(n.name)
+            if sy.dims and not isinstance(sy.typ, tuple):  # a whole array inside sum(..): element t_ in array-element order
+                self.section_extents.append(self.total(n.name, len(sy.dims)))
+                return f"{n.name}[{self.section_var}]", sy.typ
         if n.kind == "call" and n.name == "sum":
             if len(n.args) != 1 or self.section_var:
                 raise Unsupported("sum with more than one argument, or nested")
@@ -869,7 +922,7 @@ class UnitTranslator(Translator):
             if t != DBL or not ext:
                 raise Unsupported("sum of something that is not a double array section")
             # first to last from zero, as gfortran expands it (for the two-element sums of the reference the order is immaterial)
-            return f"({{ double s_ = 0.0; for (int t_ = 0; t_ < {ext[0]}; ++t_) s_ = s_ + ({c}); s_; }})", DBL
+            return f"({{ double s_ = 0.0; for (long t_ = 0; t_ < {ext[0]}; ++t_) s_ = s_ + ({c}); s_; }})", DBL
         if n.kind == "call" and n.name in self.syms and self.syms[n.name].dims and not isinstance(self.syms[n.name].typ, tuple) \
                 and any(a.kind == "colon" for a in n.args):
             sy = self.syms[n.name]
@@ -906,6 +959,7 @@ class UnitTranslator(Translator):
             comp = self.types[tname][node.name]
             if not comp.dims:
                 raise Unsupported(f"component {node.name} is not an array")
+            comp.comp_of = tname
             return f"{base}.{node.name}", comp
         if node.kind == "call":
             s = self.lookup(node.name)
@@ -951,9 +1005,32 @@ class UnitTranslator(Translator):
         return c
 
     def actuals(self, r, args):
-        if len(args) != len(r.args):
-            raise Unsupported(f"{r.name} takes {len(r.args)} arguments")
-        return [self.actual(a, r.syms[d]) for a, d in zip(args, r.args)]
+        given, pos = {}, 0
+        for a in args:
+            if a.kind == "kwarg":
+                if a.name not in r.args:
+                    raise Unsupported(f"{r.name} has no dummy {a.name}")
+                given[a.name] = a.a
+            else:
+                if pos >= len(r.args):
+                    raise Unsupported(f"{r.name} takes {len(r.args)} arguments")
+                given[r.args[pos]] = a
+                pos += 1
+        out = []
+        for d in r.args:
+            sy = r.syms[d]
+            if d not in given:
+                if not sy.optional:
+                    raise Unsupported(f"{r.name}: argument {d} is missing")
+                out.append("0")  # absent optional argument
+            elif sy.optional:
+                c, t = self.cx(given[d])
+                if (t == LOG) != (sy.typ == LOG):
+                    raise Unsupported("type mismatch for an optional argument")
+                out.append(f"&({CTYPE[sy.typ]}){{{c}}}")  # by address, as Fortran passes it
+            else:
+                out.append(self.actual(given[d], sy))
+        return out
 
     def call_statement(self, text):
         n = parse_expr(text)
@@ -1050,8 +1127,20 @@ class UnitTranslator(Translator):
             if cur is None:
                 raise Unsupported(f"line {no}: statement between routines: {st}")
             cur.lines.append((no, st))
-        if self.entry not in self.routines:
-            raise Unsupported(f"{self.entry} is not a routine of module {self.module}")
+        roots = getattr(self, "entries", [self.entry])
+        for e in roots:
+            if e not in self.routines:
+                raise Unsupported(f"{e} is not a routine of module {self.module}")
+        # only what the entries reach is translated (the module may hold routines outside the subset that nothing here calls)
+        reach, todo = set(), list(roots)
+        while todo:
+            name = todo.pop()
+            if name in reach:
+                continue
+            reach.add(name)
+            words = set(re.findall(r"[a-z]\w*", " ".join(st.lower() for _, st in self.routines[name].lines)))
+            todo.extend(w for w in words if w in self.routines and w not in reach)
+        self.routines = {k: v for k, v in self.routines.items() if k in reach}
         # specification parts
         in_type = None
         for no, st in spec:
@@ -1125,10 +1214,12 @@ class UnitTranslator(Translator):
 
     def signature(self, r):
         ps = []
-        for a in r.args + ([r.result] if r.result else []):
+        scalar_result = bool(r.result) and not r.syms[r.result].dims
+        for a in r.args + ([r.result] if r.result and not scalar_result else []):
             s = r.syms[a]
-            ps.append(f"{self.ctype_of(s)} *{a}" if (s.dims or isinstance(s.typ, tuple)) else f"{CTYPE[s.typ]} {a}")
-        return f"void r_{r.name}({', '.join(ps)})"
+            ps.append(f"{self.ctype_of(s)} *{a}" if (s.dims or isinstance(s.typ, tuple) or s.optional) else f"{CTYPE[s.typ]} {a}")
+        ret = CTYPE[r.syms[r.result].typ] if scalar_result else "void"
+        return f"{ret} r_{r.name}({', '.join(ps) or 'void'})"
 
     def emit_unit(self):
         c = [f"/* GENERATED by oracle/f90_to_c.py from the reference's module {self.module} (routines "
@@ -1176,7 +1267,10 @@ class UnitTranslator(Translator):
                 if s.dims:
                     self.dims_consts(s.name, s, c)
             for s in r.syms.values():
-                if s.role == "arg":
+                if s.role == "arg" and not (r.result == s.name and not s.dims):
+                    continue
+                if s.save_init is not None:
+                    c.append(f"  static {CTYPE[s.typ]} {s.name} = {self.cx(parse_expr(s.save_init))[0]};  /* save */")
                     continue
                 if s.dims:
                     c.append(f"  {self.ctype_of(s)} {s.name}[{self.total(s.name, len(s.dims))}];")
@@ -1190,6 +1284,8 @@ class UnitTranslator(Translator):
             c.append("  " + " ".join(f"(void){u};" for u in unused))
             dimvars = [f"(void){s.name}_lo{d};" + (f" (void){s.name}_n{d};" if hi not in (None, "") else "") for s in r.syms.values() if s.dims for d, (lo, hi) in enumerate(s.dims)]
             c.append("  " + " ".join(dimvars))
+            if r.result and not r.syms[r.result].dims:
+                c.append(f"  return {r.result};")
             c.append("}")
         self.emit_entry(c)
         return "\n".join(c) + "\n"
@@ -1223,11 +1319,23 @@ class StateUnitTranslator(UnitTranslator):
         super().__init__(text, module, uses, entries[0], [], export)
         self.entries = [e.lower() for e in entries]
         self.state_scalars = {}  # name -> type
+        self.state_init = {}     # name -> initial value of `integer :: nelemd = 16`
         self.state_arrays = {}   # name -> Sym (dims None until an allocate statement gives them)
 
     def parse_decl(self, stmt, role_default, table):
         if role_default != "host":
             return super().parse_decl(stmt, role_default, table)
+        m = re.match(r"type\s*\(\s*(\w+)\s*\)\s*((?:,\s*[^:]+?)*)\s*::\s*(.*)$", stmt, re.I)
+        if m and m.group(1).lower() in self.types:  # a module variable of derived type: bound by the caller, like the arrays
+            for name, dims in split_top(re.sub(r"\(([\s:,]*)\)", lambda g: "(" + g.group(1) + ")", m.group(3)), with_init=False):
+                sy = Sym(name.lower(), ("type", m.group(1).lower()), None, "state")
+                if dims:
+                    sy.rank = len(dims)
+                else:
+                    sy.dims = []  # a scalar: nothing to allocate
+                    sy.scalar_struct = True
+                self.state_arrays[name.lower()] = sy
+            return True
         st = re.sub(r"\(\s*kind\s*=\s*(\w+)\s*\)", r"(\1)", stmt, count=1, flags=re.I)
         m = re.match(r"(real|integer|logical)\s*(\(([^)]*)\))?\s*((?:,\s*(?:dimension\s*\([^)]*\)|[^:,]+))*)\s*::\s*(.*)$", st, re.I)
         if not m:
@@ -1247,9 +1355,11 @@ class StateUnitTranslator(UnitTranslator):
             if not em:
                 raise Unsupported(f"declaration entity {ent!r}")
             name, edims, init = em.group(1).lower(), em.group(2), em.group(3)
-            if init is not None:
-                raise Unsupported("initialised module variable in state mode")
             dims = edims if edims is not None else (dm.group(1) if dm else None)
+            if init is not None:
+                if dims is not None or typ != INT:
+                    raise Unsupported("initialised module variable that is not an integer scalar")
+                self.state_init[name] = init
             if dims is None:
                 self.state_scalars[name] = typ
             elif ":" in dims:
@@ -1288,6 +1398,8 @@ class StateUnitTranslator(UnitTranslator):
             a = self.state_arrays[name]
             if a.dims is None:
                 raise Unsupported(f"no allocate statement gives the shape of {name}")
+            if getattr(a, "scalar_struct", False):
+                return Sym(name, a.typ)
             return a
         raise Unsupported(f"undeclared name {name!r}")
 
@@ -1298,12 +1410,15 @@ class StateUnitTranslator(UnitTranslator):
 
     def emit_state(self, c):
         c.append("/* module state of the reference: scalars and allocatable arrays, file scope there and here */")
+        self.syms = {}
         for name, typ in self.state_scalars.items():
-            c.append(f"static {CTYPE[typ]} {name};")
+            init = f" = {self.cx(parse_expr(self.state_init[name]))[0]}" if name in self.state_init else ""
+            c.append(f"static {CTYPE[typ]} {name}{init};")
         used = [a for a in self.state_arrays.values() if a.dims is not None]
         for a in used:
-            c.append(f"static {CTYPE[a.typ]} *{a.name};")
-            c.append("static int " + ", ".join(f"{a.name}_lo{d} = 1, {a.name}_n{d}" for d in range(len(a.dims))) + ";")
+            c.append(f"static {self.ctype_of(a)} *{a.name};")
+            if a.dims:
+                c.append("static int " + ", ".join(f"{a.name}_lo{d} = 1, {a.name}_n{d}" for d in range(len(a.dims))) + ";")
         self.syms = {}
         c.append("static void f90_shapes(void)\n{  /* the extents the module's allocate statements give */")
         for a in used:
@@ -1318,14 +1433,20 @@ class StateUnitTranslator(UnitTranslator):
         c.append("  return 1;\n}")
         c.append(f"int {self.export}_bind(const char *name, void *p)\n{{")
         for a in used:
-            c.append(f'  if (!strcmp(name, "{a.name}")) {{ {a.name} = ({CTYPE[a.typ]} *)p; return 0; }}')
+            c.append(f'  if (!strcmp(name, "{a.name}")) {{ {a.name} = ({self.ctype_of(a)} *)p; return 0; }}')
         c.append("  return 1;\n}\n")
 
     def emit_entry(self, c):
         for e in self.entries:
             if e not in self.routines or self.routines[e].args:
                 raise Unsupported(f"{e} is not an argument-less routine of {self.module}")
-            c.append(f"\nint {self.export}_{e}(void)\n{{\n  f90_shapes();\n  r_{e}();\n  return 0;\n}}")
+            r = self.routines[e]
+            if r.result:  # a scalar function: its value is the entry's value
+                if r.syms[r.result].dims or r.syms[r.result].typ != DBL:
+                    raise Unsupported("an entry function whose result is not a double scalar")
+                c.append(f"\ndouble {self.export}_{e}(void)\n{{\n  f90_shapes();\n  return r_{e}();\n}}")
+            else:
+                c.append(f"\nint {self.export}_{e}(void)\n{{\n  f90_shapes();\n  r_{e}();\n  return 0;\n}}")
 
 
 def matching_paren(s, start):

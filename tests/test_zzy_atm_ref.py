@@ -331,3 +331,25 @@ def test_translator_state_mode_on_synthetic_sources(tmp_path):
         for i in range(first[j] - 1, n):
             want[i] = 0.0 + f0[i, j] * weight[i, j] * gain + np.copysign(1.0, f0[i, j])
         assert np.array_equal(field[:, j].view(np.uint64), want.view(np.uint64))
+
+
+def test_the_reference_program_runs_translated_and_prints_the_published_lines(oracle, ref):
+    """program biharmonic_wk_scalar_kernel (F90:545-580, GPU1 block restored) with NOTHING but translated reference code between
+    the memory and the printed numbers: initialize_data + myrandom, the CPU / GPU1 / GPU2 modules, save_qtens, compute_l2norm.
+    The two L2-norm lines are those of atmosphere/results/atm.gnu.4.9.3, atm.gnu.7.1.0 and atm.pgi.17.7, digit for digit.  The
+    oracle's own restatements of the harness (LCG fill order, norm) are pinned on the translated ones on the way."""
+    prog = ref.Program()
+    lines = dict(prog.run())
+    assert "%.16E" % lines["GPU1 L2 norm"] == "1.4477731365593603E-16" == "%.16E" % KAT["KAT2_gpu1_vs_cpu_rel_l2"]
+    assert "%.16E" % lines["GPU2 L2 norm"] == "1.3341964743086566E-16" == "%.16E" % KAT["KAT1_gpu2_vs_cpu_rel_l2"]
+    # initialize_data / compute_l2norm: oracle == translated, bit for bit
+    prog.initialize_data()
+    dvv, elem, q = oracle.initialize_data(prog.NELEMD, prog.NLEV, prog.QSIZE)
+    assert np.array_equal(_bits(dvv), _bits(prog.deriv)) and np.array_equal(_bits(elem), _bits(prog.elem)) and np.array_equal(_bits(q), _bits(prog.qtens))
+    prog.save_qtens()
+    assert np.array_equal(prog.qtens_save, prog.qtens)
+    ref.biharmonic_wk_scalar_gpu2(prog.elem, prog.qtens, prog.deriv)
+    assert prog.compute_l2norm() == oracle.compute_l2norm(prog.qtens, prog.qtens_save)
+    # a second initialize_data restarts the generator (reset = .true., F90:51 / F90:84-85): same values again
+    prog.initialize_data()
+    assert np.array_equal(_bits(q), _bits(prog.qtens))
