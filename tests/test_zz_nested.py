@@ -161,6 +161,23 @@ def test_translated_fortran_forms_equal_the_compiled_cpp_reference(nested, cko, 
     assert prob.coef3rdOrder == float(np.float32(2.14)) != 2.14
 
 
+def test_oracle_hashes_to_the_committed_digests_of_the_reference(nested, cko):
+    """tests/golden/nested_reference.json (made by tests/golden/make_nested_golden.py from the reference's C++ compiled here; the
+    translated Fortran forms gave the same bytes) against the hand-written oracle: runs anywhere, with or without oracle/_ref."""
+    import hashlib
+    import json
+
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "nested_reference.json")))
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()  # noqa: E731
+    for name, c in gold["cases"].items():
+        prob = nested.NestedProblem(nEdges=c["nEdges"], nCells=c["nCells"], nVertLevels=c["nVertLevels"], nAdv=c["nAdv"], nIters=1,
+                                    packn=c["packn"], seed=c["seed"])
+        assert sha(prob.tracerCur) == c["tracer_sha256"], name  # the seeded problem is the one the digests were made on
+        nv = prob.nVertLevels
+        assert sha(cko.original_cpu(prob)[:nv]) == c["original_sha256"], name
+        assert sha(cko.gpu_optimized(prob)[:nv]) == c["gpu_optimized_sha256"], name
+
+
 def test_oracle_vs_reference_with_general_masks(nested, cko, yref):
     """Non-0/1 cellMask and tracers that do not vanish outside the level range: the two reference forms differ from
     each other, and each oracle form still follows its own reference form bit for bit."""
